@@ -1,0 +1,295 @@
+/*
+ * lgk.h -- C ABI of the B200-native legged_gym step kernels (liblgk.so).
+ *
+ * Drop-in boundary for the per-env data-parallel path of the reference's
+ * LeggedRobot.step() / post_physics_step()
+ * (/root/reference/legged_gym/envs/base/legged_robot.py:79-231,337-474,818-966,
+ *  envs/go1/go1.py:68-107, envs/cassie/cassie.py:43-46).
+ *
+ * Conventions
+ *  - plain C, no torch / C++ types; every pointer is a raw CUDA device pointer unless
+ *    the field name ends in _host.
+ *  - the library never allocates, frees or retains caller memory; LgkConsts is read
+ *    during the call only (copied by value into kernel parameters).
+ *  - every entry point is asynchronous on the given stream (a cudaStream_t passed as
+ *    void*), performs no host synchronisation and may be captured in a CUDA graph.
+ *  - return value: 0 = success; negative = LgkStatus argument error; positive =
+ *    cudaError_t raised by the launch.
+ *  - all floating point data is fp32; index / counter types are called out per field.
+ */
+#ifndef LGK_H_
+#define LGK_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LGK_ABI_VERSION 3
+
+#define LGK_MAX_DOF     16   /* num_dof = num_actions (12 for every shipped robot)        */
+#define LGK_MAX_FEET     8
+#define LGK_MAX_PEN     16   /* penalised-contact bodies                                  */
+#define LGK_MAX_TERM     8   /* termination-contact bodies                                */
+#define LGK_MAX_REWARDS 32   /* active reward terms incl. termination                     */
+#define LGK_MAX_HIP      4
+
+typedef enum LgkStatus {
+  LGK_OK = 0,
+  LGK_ERR_NULL = -1,          /* required pointer is NULL                                  */
+  LGK_ERR_DIM = -2,           /* dimension outside the supported range                     */
+  LGK_ERR_CONTROL_TYPE = -3,  /* unknown control type (reference: NameError, :391)         */
+  LGK_ERR_REWARD = -4,        /* unknown reward term id (reference: AttributeError, :593)  */
+  LGK_ERR_ALIGN = -5,         /* pointer not aligned as required                           */
+  LGK_ERR_VERSION = -6,       /* struct_size / abi_version mismatch                        */
+  LGK_ERR_TERRAIN = -7        /* heights requested but no height field given (:833-834)    */
+} LgkStatus;
+
+/* control_type of LeggedRobotCfg.control (legged_robot.py:383-391) */
+typedef enum LgkControlType { LGK_CTRL_P = 0, LGK_CTRL_V = 1, LGK_CTRL_T = 2 } LgkControlType;
+
+/* reward term ids: one per _reward_<name> of the reference (legged_robot.py:857-966,
+ * cassie.py:43-46).  The host passes the ACTIVE terms in evaluation order (alphabetical,
+ * the order class_to_dict yields -- utils/helpers.py:41-56). */
+typedef enum LgkRewardTerm {
+  LGK_REW_ACTION_RATE = 0,
+  LGK_REW_ANG_VEL_XY,
+  LGK_REW_BASE_HEIGHT,
+  LGK_REW_COLLISION,
+  LGK_REW_DOF_ACC,
+  LGK_REW_DOF_POS_LIMITS,
+  LGK_REW_DOF_VEL,
+  LGK_REW_DOF_VEL_LIMITS,
+  LGK_REW_ENERGY,
+  LGK_REW_FEET_AIR_TIME,
+  LGK_REW_FEET_CONTACT_FORCES,
+  LGK_REW_HIP_MOTION,
+  LGK_REW_LIN_VEL_Z,
+  LGK_REW_NO_FLY,
+  LGK_REW_ORIENTATION,
+  LGK_REW_STAND_STILL,
+  LGK_REW_STUMBLE,
+  LGK_REW_TORQUE_LIMITS,
+  LGK_REW_TORQUES,
+  LGK_REW_TRACKING_ANG_VEL,
+  LGK_REW_TRACKING_LIN_VEL,
+  LGK_REW_EXTERNAL,          /* value supplied per env by the host in ext_rewards        */
+  LGK_REW_COUNT
+} LgkRewardTerm;
+
+/* LgkConsts.index_math -- the two device-dependent roundings on the height-index path
+ * (legged_robot.py:839-842, utils/math.py:38-42).  torch evaluates them differently on CPU and
+ * on CUDA, and a last-bit difference moves ~2e-5 of the truncated indices, so the caller names
+ * the torch device it must agree with bit-for-bit.
+ *  bit 0    (p / horizontal_scale): 0 = IEEE division (torch CPU), 1 = multiply by the fp32
+ *           reciprocal (torch CUDA div-by-scalar).
+ *  bits 1-2 norm([0,0,qz,qw]): 0 = sqrtf(fma(w,w,z*z)), 1 = sqrtf(z*z + w*w) with separately
+ *           rounded squares, 2 = sqrtf(fma(z,z,w*w)), 3 = (float)sqrt((double)(z*z + w*w)) with
+ *           separately rounded squares (what torch 2.11 CPU computes; measured). */
+typedef enum LgkIndexMath {
+  LGK_INDEX_DIV = 0,
+  LGK_INDEX_MUL_RCP = 1,
+  LGK_NORM_FMA_W = 0 << 1,
+  LGK_NORM_SEPARATE = 1 << 1,
+  LGK_NORM_FMA_Z = 2 << 1,
+  LGK_NORM_SEPARATE_F64SQRT = 3 << 1
+} LgkIndexMath;
+#define LGK_INDEX_MATH_TORCH_CPU (LGK_INDEX_DIV | LGK_NORM_SEPARATE_F64SQRT)
+
+/* random-number source */
+typedef enum LgkRngMode {
+  LGK_RNG_PHILOX = 0,  /* in-kernel Philox4x32-10 keyed by (seed, step, env, site)         */
+  LGK_RNG_TAPS = 1     /* caller-provided uniforms, one row per env (parity mode)          */
+} LgkRngMode;
+
+enum {                                   /* LgkConsts.flags                                */
+  LGK_F_HEADING_COMMAND   = 1u << 0,     /* cfg.commands.heading_command                   */
+  LGK_F_MEASURE_HEIGHTS   = 1u << 1,     /* cfg.terrain.measure_heights                    */
+  LGK_F_TERRAIN_PLANE     = 1u << 2,     /* mesh_type == 'plane' -> heights are zeros      */
+  LGK_F_ADD_NOISE         = 1u << 3,     /* cfg.noise.add_noise                            */
+  LGK_F_PUSH_ROBOTS       = 1u << 4,     /* cfg.domain_rand.push_robots                    */
+  LGK_F_TERRAIN_CURRICULUM= 1u << 5,     /* cfg.terrain.curriculum (rough terrain only)    */
+  LGK_F_CUSTOM_ORIGINS    = 1u << 6,     /* rough terrain: xy jitter on reset (:422-425)   */
+  LGK_F_ONLY_POSITIVE     = 1u << 7,     /* cfg.rewards.only_positive_rewards              */
+  LGK_F_HAS_TERMINATION   = 1u << 8,     /* 'termination' scale is non-zero (:209-212)     */
+  LGK_F_INIT_DONE         = 1u << 9      /* self.init_done (curriculum skipped before)     */
+};
+
+typedef struct LgkRewardEntry {
+  int32_t term;    /* LgkRewardTerm                                                        */
+  float   scale;   /* cfg scale * dt, fp32 (legged_robot.py:584)                           */
+} LgkRewardEntry;
+
+/* Constant block: everything _parse_cfg/_init_buffers/_prepare_reward_function derive from
+ * LeggedRobotCfg (legged_robot.py:503-598,769-779).  Host memory, passed by pointer. */
+typedef struct LgkConsts {
+  uint32_t struct_size;       /* sizeof(LgkConsts), checked                                */
+  uint32_t abi_version;       /* LGK_ABI_VERSION                                           */
+  /* dimensions */
+  int32_t  num_envs;          /* N (this rank)                                             */
+  int32_t  num_dof;           /* D                                                         */
+  int32_t  num_bodies;        /* B                                                         */
+  int32_t  num_feet;          /* F                                                         */
+  int32_t  num_pen;           /* P                                                         */
+  int32_t  num_term;          /* T                                                         */
+  int32_t  num_height_points; /* H (0 when measure_heights is off)                         */
+  int32_t  num_obs;           /* O                                                         */
+  int32_t  num_rewards;       /* R: entries of rewards[] (termination excluded)            */
+  int32_t  num_commands;      /* 4                                                         */
+  int32_t  env_id_offset;     /* global id of local env 0 (multi-GPU sharding)             */
+  uint32_t flags;             /* LGK_F_*                                                   */
+  int32_t  control_type;      /* LgkControlType                                            */
+  int32_t  index_math;        /* LgkIndexMath                                              */
+  int32_t  rng_mode;          /* LgkRngMode                                                */
+  int32_t  envs_per_warp;     /* 0 = library picks                                         */
+  /* timing */
+  float    dt;                /* decimation * sim.dt                                       */
+  float    sim_dt;
+  int64_t  max_episode_length;/* ceil(episode_length_s / dt)                               */
+  int64_t  resample_interval; /* int(resampling_time / dt)                                 */
+  int64_t  push_interval;     /* ceil(push_interval_s / dt)                                */
+  float    max_episode_length_s;
+  float    max_push_vel_xy;
+  /* normalisation */
+  float    clip_actions, clip_obs;
+  float    obs_scale_lin_vel, obs_scale_ang_vel, obs_scale_dof_pos, obs_scale_dof_vel, obs_scale_height;
+  float    commands_scale[3];
+  /* control */
+  float    action_scale;
+  float    p_gains[LGK_MAX_DOF], d_gains[LGK_MAX_DOF], torque_limits[LGK_MAX_DOF];
+  float    default_dof_pos[LGK_MAX_DOF];
+  float    dof_pos_lo[LGK_MAX_DOF], dof_pos_hi[LGK_MAX_DOF];   /* soft limits (:305-309)   */
+  float    dof_vel_limits[LGK_MAX_DOF];
+  /* rewards */
+  float    soft_dof_vel_limit, soft_torque_limit, base_height_target, tracking_sigma, max_contact_force;
+  float    termination_scale;                                   /* scale * dt              */
+  LgkRewardEntry rewards[LGK_MAX_REWARDS];
+  int32_t  feet_idx[LGK_MAX_FEET], pen_idx[LGK_MAX_PEN], term_idx[LGK_MAX_TERM];
+  int32_t  hip_idx[LGK_MAX_HIP];                                /* [0,3,6,9] (:966)        */
+  int32_t  num_hip;
+  /* reset */
+  float    base_init_state[13];
+  /* terrain */
+  float    border_size, horizontal_scale, vertical_scale;
+  float    half_env_length;                                     /* terrain.env_length / 2  */
+  int32_t  terrain_rows, terrain_cols;                          /* height_samples.shape    */
+  int32_t  terrain_pitch;                                       /* elements per row of height_min3 */
+  int32_t  max_terrain_level;                                   /* cfg.terrain.num_rows    */
+  int32_t  num_terrain_types;                                   /* cfg.terrain.num_cols    */
+  /* rng */
+  uint64_t seed;
+} LgkConsts;
+
+/* Device buffers of one env shard.  Names follow the reference's attributes
+ * (legged_robot.py:503-598, base_task.py:70-78). */
+typedef struct LgkBuffers {
+  /* simulator-owned (gymtorch views): read every step, written on reset / push */
+  float*       root_states;        /* [N,13] pos3 quat4(xyzw) linvel3 angvel3              */
+  float*       dof_state;          /* [N,D,2] (pos, vel) interleaved                       */
+  const float* contact_forces;     /* [N,B,3]                                              */
+  const float* torques;            /* [N,D] simulator-reported dof forces                  */
+  /* env state */
+  const float* actions;            /* [N,D] already clipped (lgk_clip_actions)             */
+  float*       last_actions;       /* [N,D]                                                */
+  float*       last_dof_vel;       /* [N,D]                                                */
+  float*       last_root_vel;      /* [N,6]                                                */
+  float*       commands;           /* [N,4]                                                */
+  float*       feet_air_time;      /* [N,F]                                                */
+  float*       episode_sums;       /* [R(+1 if termination), N] term-major                 */
+  int64_t*     episode_length_buf; /* [N]                                                  */
+  int64_t*     terrain_levels;     /* [N]  (NULL without custom origins)                   */
+  const int64_t* terrain_types;    /* [N]                                                  */
+  float*       env_origins;        /* [N,3]                                                */
+  /* outputs */
+  float*       obs_buf;            /* [N,O]                                                */
+  float*       rew_buf;            /* [N]                                                  */
+  uint8_t*     reset_buf;          /* [N] torch.bool                                       */
+  uint8_t*     time_out_buf;       /* [N] torch.bool                                       */
+  float*       base_lin_vel;       /* [N,3]                                                */
+  float*       base_ang_vel;       /* [N,3]                                                */
+  float*       projected_gravity;  /* [N,3]                                                */
+  float*       measured_heights;   /* [N,H] or NULL (not materialised)                     */
+  int32_t*     reset_ids;          /* [N] ascending env ids reset this step                */
+  int32_t*     resample_ids;       /* [N] ascending env ids whose command was resampled    */
+  int32_t*     counts;             /* [2] {n_reset, n_resample}; counts_host mirrors it    */
+  float*       episode_stats;      /* [R(+1)+3]: sum over reset ids of episode_sums[k],
+                                      then n_reset, sum(terrain_levels), spare             */
+  float*       extras;             /* [R(+1)+2]: rew_<k> means / max_episode_length_s,
+                                      terrain_level mean; only rewritten when n_reset > 0  */
+  const float* ext_rewards;        /* [n_ext, N] values of LGK_REW_EXTERNAL terms or NULL  */
+  /* constant tables */
+  const int16_t* height_min3;      /* [rows, pitch] min(h[x,y],h[x+1,y],h[x,y+1])          */
+  const float* height_points_xy;   /* [H,2] body-frame scan offsets (:802-816)             */
+  const float* noise_scale_vec;    /* [O]                                                  */
+  const float* terrain_origins;    /* [num_rows, num_cols, 3]                              */
+  float*       command_ranges;     /* [8] lin_vel_x lo/hi, lin_vel_y, ang_vel_yaw, heading */
+  /* random taps (rng_mode == LGK_RNG_TAPS), uniform [0,1), one row per env */
+  const float* tap_cmd_callback;   /* [N,3]                                                */
+  const float* tap_cmd_reset;      /* [N,3]                                                */
+  const float* tap_push;           /* [N,2]                                                */
+  const float* tap_dof;            /* [N,D]                                                */
+  const float* tap_root_xy;        /* [N,2]                                                */
+  const float* tap_root_vel;       /* [N,6]                                                */
+  const float* tap_noise;          /* [N,O]                                                */
+  const int64_t* tap_level;        /* [N] ints in [0, max_terrain_level)                   */
+  /* scratch owned by the caller, sized by lgk_workspace_bytes(), zero-initialised once */
+  void*        workspace;
+} LgkBuffers;
+
+/* bytes of LgkBuffers.workspace for N envs and R episode_sums rows */
+int64_t lgk_workspace_bytes(int32_t num_envs, int32_t num_sum_rows);
+
+/* ABI version the library was built with */
+int32_t lgk_abi_version(void);
+
+/* Derived terrain table: out[x*pitch+y] = min(h[x,y], h[x+1,y], h[x,y+1]) for x<=rows-2,
+ * y<=cols-2 (legged_robot.py:845-852); pitch >= cols, multiple of 8.  Run once per terrain. */
+int lgk_build_height_min3(const int16_t* height_samples, int32_t rows, int32_t cols,
+                          int16_t* out, int32_t pitch, void* stream);
+
+/* actions = clip(actions_in, +-clip_actions)            (legged_robot.py:85-86) */
+int lgk_clip_actions(const float* actions_in, float* actions_out, int64_t count,
+                     float clip_actions, void* stream);
+
+/* target_poses = clip(a*action_scale + default_dof_pos, lo, hi)  (legged_robot.py:394-397) */
+int lgk_compute_poses(const LgkConsts* c, const float* actions, float* target_poses, void* stream);
+
+/* torques = clip(PD(...), +-torque_limits) for control_type P / V / T (legged_robot.py:370-392) */
+int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* dof_state,
+                        const float* last_dof_vel, float* torques_out, void* stream);
+
+/* Go1 / Aliengo actuator net (go1.py:79-107): shifts the 5-deep joint-error / velocity
+ * histories, packs model_ins [N,120] and evaluates the 30-128-128-128-3 tanh MLP per leg.
+ * weights: fp32 blob W0[128,30] b0[128] W1[128,128] b1 W2[128,128] b2 W3[3,128] b3[3].
+ * norm: pos_err_mean[12] pos_err_std[12] vel_mean[12] vel_std[12]. */
+int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state,
+                         float* pos_err_hist, float* vel_hist, float* model_ins,
+                         const float* weights, const float* norm, float* dvel_out, void* stream);
+
+/* Everything post_physics_step() does for every env (legged_robot.py:109-141) in one launch. */
+int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream);
+
+/* reset_idx(env_ids) (legged_robot.py:150-193) for an ascending int64 id list on the device
+ * (env_ids == NULL means arange(n)); n == 0 returns at once like the reference (:160).
+ * Writes reset_ids[0..n), counts[0] = n and the episode statistics / extras. */
+int lgk_reset_idx(const LgkConsts* c, const LgkBuffers* b, const int64_t* env_ids, int32_t n, void* stream);
+
+/* reset_idx(arange(N)) as issued by BaseTask.reset() (base_task.py:111-115). */
+int lgk_reset_all(const LgkConsts* c, const LgkBuffers* b, void* stream);
+
+/* Sets the device copy of common_step_counter (legged_robot.py:119,527) held in the workspace;
+ * the step kernel increments it itself.  Not capturable in a CUDA graph. */
+int lgk_set_step_counter(void* workspace, int64_t value, void* stream);
+
+/* sizeof(LgkConsts) / sizeof(LgkBuffers) as compiled, for binding self-checks */
+int64_t lgk_sizeof_consts(void);
+int64_t lgk_sizeof_buffers(void);
+
+/* Number of kernel launches issued by this library since load (bench bookkeeping). */
+int64_t lgk_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* LGK_H_ */

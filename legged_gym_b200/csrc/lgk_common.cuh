@@ -1,0 +1,117 @@
+// Device helpers shared by the legged_gym step kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/lgk.h"
+
+#define LGK_WARPS_PER_CTA 4
+#define LGK_CTA_THREADS (LGK_WARPS_PER_CTA * 32)
+#define LGK_FULL_MASK 0xffffffffu
+
+// ---- workspace (device memory owned by the caller, zeroed once) ---------------------
+struct LgkWorkspace {
+  unsigned long long step_counter;   // == reference common_step_counter (legged_robot.py:119)
+  unsigned int done_ticket;          // CTAs finished in the current launch
+  unsigned int pad0;
+  int level_sum[2];                  // sum(terrain_levels) accumulators, indexed by step parity
+  unsigned int pad1[2];
+  float stats[2][LGK_MAX_REWARDS + 4];   // per-parity: sum over reset ids of episode_sums[k]
+  // followed by: uint32 reset_mask[max_warps]; uint32 resample_mask[max_warps];
+};
+#define LGK_WS_HEADER_BYTES 512
+static_assert(sizeof(LgkWorkspace) <= LGK_WS_HEADER_BYTES, "workspace header too large");
+
+__host__ __device__ inline int lgk_max_warps(int num_envs) { return (num_envs + 3) / 4 + LGK_WARPS_PER_CTA; }
+
+// ---- Philox4x32-10 (counter-based; same generator family torch/curand use) ----------
+struct Philox {
+  static __device__ __forceinline__ uint4 round(uint4 ctr, uint2 key) {
+    const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+    unsigned int hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    unsigned int hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    return make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+  }
+  template <int ROUNDS = 10>
+  static __device__ __forceinline__ uint4 gen(uint4 ctr, uint2 key) {
+#pragma unroll
+    for (int i = 0; i < ROUNDS; ++i) {
+      ctr = round(ctr, key);
+      key.x += 0x9E3779B9u;
+      key.y += 0xBB67AE85u;
+    }
+    return ctr;
+  }
+};
+// uniform in [0,1) with 24 random bits (torch's float convention)
+__device__ __forceinline__ float u01(unsigned int x) { return (float)(x >> 8) * 5.9604644775390625e-08f; }
+
+// RNG "sites" of one env-step; each owns a range of Philox blocks
+enum : unsigned int {
+  LGK_SITE_NOISE = 0,        // blocks 0..63: lane + 32*k
+  LGK_SITE_CMD_CB = 64,
+  LGK_SITE_CMD_RESET = 65,
+  LGK_SITE_PUSH = 66,
+  LGK_SITE_LEVEL = 67,
+  LGK_SITE_ROOT = 68,        // 2 blocks: xy(2) + vel(6)
+  LGK_SITE_DOF = 70          // ceil(D/4) blocks
+};
+__device__ __forceinline__ uint4 lgk_philox(const uint64_t seed, unsigned long long step, unsigned int env_global,
+                                            unsigned int block) {
+  return Philox::gen<10>(make_uint4(env_global, block, (unsigned int)step, (unsigned int)(step >> 32)),
+                         make_uint2((unsigned int)seed, (unsigned int)(seed >> 32)));
+}
+
+// ---- exact-order fp32 helpers (no contraction) ----------------------------------------
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+// lower + (upper-lower)*u exactly as torch_rand_float evaluates it (two roundings)
+__device__ __forceinline__ float rand_affine(float range, float lo, float u) { return add_rn(mul_rn(range, u), lo); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(LGK_FULL_MASK, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_sum_int(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(LGK_FULL_MASK, v, o);
+  return v;
+}
+
+// quat_rotate_inverse(q, v), q = xyzw  (isaacgym.torch_utils; SURVEY A-1)
+__device__ __forceinline__ void quat_rotate_inverse(const float q[4], float vx, float vy, float vz, float out[3]) {
+  const float w = q[3];
+  const float s = 2.0f * w * w - 1.0f;
+  const float cx = q[1] * vz - q[2] * vy, cy = q[2] * vx - q[0] * vz, cz = q[0] * vy - q[1] * vx;
+  const float d = q[0] * vx + q[1] * vy + q[2] * vz;
+  const float w2 = w * 2.0f, d2 = d * 2.0f;
+  out[0] = vx * s - cx * w2 + q[0] * d2;
+  out[1] = vy * s - cy * w2 + q[1] * d2;
+  out[2] = vz * s - cz * w2 + q[2] * d2;
+}
+// quat_apply(q, v)
+__device__ __forceinline__ void quat_apply(const float q[4], float vx, float vy, float vz, float out[3]) {
+  const float tx = 2.0f * (q[1] * vz - q[2] * vy), ty = 2.0f * (q[2] * vx - q[0] * vz),
+              tz = 2.0f * (q[0] * vy - q[1] * vx);
+  out[0] = vx + q[3] * tx + (q[1] * tz - q[2] * ty);
+  out[1] = vy + q[3] * ty + (q[2] * tx - q[0] * tz);
+  out[2] = vz + q[3] * tz + (q[0] * ty - q[1] * tx);
+}
+
+// wrap_to_pi (utils/math.py:45-48): python-style modulo by fp32(2*pi), then fold (pi, 2pi) down
+__device__ __forceinline__ float wrap_to_pi(float a) {
+  const float TWO_PI = 6.283185307179586f, PI_F = 3.141592653589793f;
+  float m = fmodf(a, TWO_PI);
+  if (m != 0.0f && m < 0.0f) m += TWO_PI;
+  if (m > PI_F) m -= TWO_PI;
+  return m;
+}
+
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+
+#define LGK_CUDA_RETURN_IF(err)            \
+  do {                                     \
+    cudaError_t e__ = (err);               \
+    if (e__ != cudaSuccess) return (int)e__; \
+  } while (0)

@@ -1,0 +1,280 @@
+// Control-side kernels: action clip, position targets, PD torques, terrain min-of-3 table,
+// Go1 actuator-net history + MLP (sm_100a).
+#include "lgk_common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// height_min3[x,y] = min(h[x,y], h[x+1,y], h[x,y+1])   (legged_robot.py:848-852)
+__global__ void lgk_min3_kernel(const int16_t* __restrict__ hs, int rows, int cols, int16_t* __restrict__ out, int pitch) {
+  const int y = blockIdx.x * blockDim.x + threadIdx.x;
+  const int x = blockIdx.y;
+  if (y >= pitch) return;
+  int16_t v = 0;
+  if (y < cols) {
+    v = hs[(size_t)x * cols + y];
+    if (x + 1 < rows) v = min(v, hs[(size_t)(x + 1) * cols + y]);
+    if (y + 1 < cols) v = min(v, hs[(size_t)x * cols + y + 1]);
+  }
+  out[(size_t)x * pitch + y] = v;
+}
+
+extern "C" int lgk_build_height_min3_impl(const int16_t* hs, int rows, int cols, int16_t* out, int pitch, cudaStream_t st) {
+  dim3 grid((pitch + 255) / 256, rows);
+  lgk_min3_kernel<<<grid, 256, 0, st>>>(hs, rows, cols, out, pitch);
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void lgk_clip_kernel(const float* __restrict__ in, float* __restrict__ out, long long n, float lim) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long n4 = n >> 2;
+  if (i < n4) {
+    float4 v = __ldg(reinterpret_cast<const float4*>(in) + i);
+    v.x = clampf(v.x, -lim, lim); v.y = clampf(v.y, -lim, lim);
+    v.z = clampf(v.z, -lim, lim); v.w = clampf(v.w, -lim, lim);
+    reinterpret_cast<float4*>(out)[i] = v;
+  }
+  if (i < (n & 3)) out[n4 * 4 + i] = clampf(in[n4 * 4 + i], -lim, lim);
+}
+__global__ void lgk_clip_kernel_scalar(const float* __restrict__ in, float* __restrict__ out, long long n, float lim) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = clampf(in[i], -lim, lim);
+}
+
+extern "C" int lgk_clip_actions_impl(const float* in, float* out, long long n, float lim, cudaStream_t st) {
+  if (n <= 0) return 0;
+  const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 15) == 0;
+  if (aligned) {
+    const long long work = (n >> 2) > 3 ? (n >> 2) : 4;
+    lgk_clip_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(in, out, n, lim);
+  } else {
+    lgk_clip_kernel_scalar<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, out, n, lim);
+  }
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+struct CtrlArgs {
+  float action_scale, sim_dt;
+  int D, control_type;
+  float def[LGK_MAX_DOF], lo[LGK_MAX_DOF], hi[LGK_MAX_DOF];
+  float kp[LGK_MAX_DOF], kd[LGK_MAX_DOF], tl[LGK_MAX_DOF];
+};
+
+// _compute_poses (:394-397): clip(a * action_scale + default, lo, hi)
+__global__ void lgk_poses_kernel(const __grid_constant__ CtrlArgs a, const float* __restrict__ actions,
+                                 float* __restrict__ out, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int d = (int)(i % a.D);
+  const float t = add_rn(mul_rn(__ldg(actions + i), a.action_scale), a.def[d]);
+  out[i] = clampf(t, a.lo[d], a.hi[d]);
+}
+
+// _compute_torques (:370-392)
+__global__ void lgk_torques_kernel(const __grid_constant__ CtrlArgs a, const float* __restrict__ actions,
+                                   const float* __restrict__ dof_state, const float* __restrict__ last_dof_vel,
+                                   float* __restrict__ out, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int d = (int)(i % a.D);
+  const float as = mul_rn(__ldg(actions + i), a.action_scale);
+  const float2 s = __ldg(reinterpret_cast<const float2*>(dof_state) + i);   // (pos, vel)
+  float t;
+  if (a.control_type == LGK_CTRL_P) {
+    t = sub_rn(mul_rn(a.kp[d], sub_rn(add_rn(as, a.def[d]), s.x)), mul_rn(a.kd[d], s.y));
+  } else if (a.control_type == LGK_CTRL_V) {
+    const float dv = sub_rn(s.y, __ldg(last_dof_vel + i));
+    t = sub_rn(mul_rn(a.kp[d], sub_rn(as, s.y)), __fdiv_rn(mul_rn(a.kd[d], dv), a.sim_dt));
+  } else {
+    t = as;
+  }
+  out[i] = clampf(t, -a.tl[d], a.tl[d]);
+}
+
+static void fill_ctrl(const LgkConsts* c, CtrlArgs& a) {
+  a.action_scale = c->action_scale;
+  a.sim_dt = c->sim_dt;
+  a.D = c->num_dof;
+  a.control_type = c->control_type;
+  for (int d = 0; d < LGK_MAX_DOF; ++d) {
+    a.def[d] = c->default_dof_pos[d]; a.lo[d] = c->dof_pos_lo[d]; a.hi[d] = c->dof_pos_hi[d];
+    a.kp[d] = c->p_gains[d]; a.kd[d] = c->d_gains[d]; a.tl[d] = c->torque_limits[d];
+  }
+}
+
+extern "C" int lgk_compute_poses_impl(const LgkConsts* c, const float* actions, float* out, cudaStream_t st) {
+  CtrlArgs a;
+  fill_ctrl(c, a);
+  const long long n = (long long)c->num_envs * c->num_dof;
+  lgk_poses_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a, actions, out, n);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int lgk_compute_torques_impl(const LgkConsts* c, const float* actions, const float* dof_state,
+                                        const float* last_dof_vel, float* out, cudaStream_t st) {
+  CtrlArgs a;
+  fill_ctrl(c, a);
+  const long long n = (long long)c->num_envs * c->num_dof;
+  lgk_torques_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a, actions, dof_state, last_dof_vel, out, n);
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Go1 / Aliengo actuator net (go1.py:79-107)
+#define ACT_LEGS 4
+#define ACT_LEG_DOF 3
+#define ACT_HIST 5
+#define ACT_DOF (ACT_LEGS * ACT_LEG_DOF)
+#define ACT_IN (2 * ACT_LEG_DOF * ACT_HIST)   // 30
+#define ACT_HID 128
+
+// history shift + pack: one thread per (env, joint)
+__global__ void lgk_act_hist_kernel(int N, const float* __restrict__ actions, const float* __restrict__ dof_state,
+                                    float* __restrict__ pe_hist, float* __restrict__ v_hist,
+                                    float* __restrict__ model_ins, const float* __restrict__ norm) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * ACT_DOF) return;
+  const int j = i % ACT_DOF;
+  const float2 s = __ldg(reinterpret_cast<const float2*>(dof_state) + i);
+  // pos_err uses the RAW action, not the scaled one (go1.py:81)
+  const float pe = __fdiv_rn(sub_rn(sub_rn(__ldg(actions + i), s.x), norm[j]), norm[ACT_DOF + j]);
+  const float vs = __fdiv_rn(sub_rn(s.y, norm[2 * ACT_DOF + j]), norm[3 * ACT_DOF + j]);
+  float* ph = pe_hist + (size_t)i * ACT_HIST;
+  float* vh = v_hist + (size_t)i * ACT_HIST;
+  float* mi = model_ins + (size_t)(i / ACT_DOF) * (ACT_DOF * 2 * ACT_HIST) + j * 2 * ACT_HIST;
+#pragma unroll
+  for (int k = 0; k < ACT_HIST; ++k) {
+    const float a = (k < ACT_HIST - 1) ? ph[k + 1] : pe;   // drop the oldest, append the newest
+    const float b = (k < ACT_HIST - 1) ? vh[k + 1] : vs;
+    ph[k] = a;
+    vh[k] = b;
+    mi[k] = a;
+    mi[ACT_HIST + k] = b;
+  }
+}
+
+// MLP 30 -> 128 -> 128 -> 128 -> 3 (tanh), fp32 SIMT; weights resident in shared memory,
+// persistent CTAs over tiles of 64 leg-rows.
+#define MLP_ROWS 64
+#define MLP_THREADS 256
+struct MlpSmem {
+  float w0[32][ACT_HID];        // [k][n], k padded 30 -> 32
+  float w1[ACT_HID][ACT_HID];   // [k][n]
+  float w2[ACT_HID][ACT_HID];
+  float w3[ACT_LEG_DOF][ACT_HID];
+  float b0[ACT_HID], b1[ACT_HID], b2[ACT_HID], b3[4];
+  float act[2][ACT_HID][MLP_ROWS];   // [k][row]
+};
+
+template <int K>
+__device__ __forceinline__ void mlp_layer(const float (*__restrict__ wt)[ACT_HID], const float* __restrict__ bias,
+                                          const float (*__restrict__ in)[MLP_ROWS], float (*__restrict__ out)[MLP_ROWS],
+                                          int tr, int tn) {
+  float acc[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < K; ++k) {
+    const float4 a4 = *reinterpret_cast<const float4*>(&in[k][tr * 4]);
+    const float4 wa = *reinterpret_cast<const float4*>(&wt[k][tn * 4]);
+    const float4 wb = *reinterpret_cast<const float4*>(&wt[k][64 + tn * 4]);
+    const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+    const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int n = (j < 4) ? tn * 4 + j : 64 + tn * 4 + (j - 4);
+    const float bb = bias[n];
+    float4 o;
+    o.x = tanhf(acc[0][j] + bb); o.y = tanhf(acc[1][j] + bb);
+    o.z = tanhf(acc[2][j] + bb); o.w = tanhf(acc[3][j] + bb);
+    *reinterpret_cast<float4*>(&out[n][tr * 4]) = o;
+  }
+}
+
+__global__ void __launch_bounds__(MLP_THREADS, 1)
+lgk_act_mlp_kernel(int rows_total, const float* __restrict__ model_ins, const float* __restrict__ weights,
+                   const float* __restrict__ norm, float* __restrict__ dvel) {
+  extern __shared__ __align__(16) unsigned char raw[];
+  MlpSmem& s = *reinterpret_cast<MlpSmem*>(raw);
+  const int tid = threadIdx.x;
+  // weights blob: W0[128,30] b0 W1[128,128] b1 W2[128,128] b2 W3[3,128] b3   (torch Linear: [out,in])
+  const float* W0 = weights;
+  const float* B0 = W0 + ACT_HID * ACT_IN;
+  const float* W1 = B0 + ACT_HID;
+  const float* B1 = W1 + ACT_HID * ACT_HID;
+  const float* W2 = B1 + ACT_HID;
+  const float* B2 = W2 + ACT_HID * ACT_HID;
+  const float* W3 = B2 + ACT_HID;
+  const float* B3 = W3 + ACT_LEG_DOF * ACT_HID;
+  for (int i = tid; i < 32 * ACT_HID; i += MLP_THREADS) {
+    const int k = i / ACT_HID, n = i % ACT_HID;
+    s.w0[k][n] = (k < ACT_IN) ? W0[n * ACT_IN + k] : 0.f;
+  }
+  for (int i = tid; i < ACT_HID * ACT_HID; i += MLP_THREADS) {
+    const int n = i / ACT_HID, k = i % ACT_HID;   // coalesced global read, transposed store
+    s.w1[k][n] = W1[i];
+    s.w2[k][n] = W2[i];
+  }
+  for (int i = tid; i < ACT_LEG_DOF * ACT_HID; i += MLP_THREADS) s.w3[i / ACT_HID][i % ACT_HID] = W3[i];
+  if (tid < ACT_HID) { s.b0[tid] = B0[tid]; s.b1[tid] = B1[tid]; s.b2[tid] = B2[tid]; }
+  if (tid < ACT_LEG_DOF) s.b3[tid] = B3[tid];
+  __syncthreads();
+
+  const int tr = tid % 16, tn = tid / 16;
+  const int num_tiles = (rows_total + MLP_ROWS - 1) / MLP_ROWS;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int row0 = tile * MLP_ROWS;
+    // stage inputs: act[0][k][row] = model_ins[row0+row][k]
+    for (int i = tid; i < MLP_ROWS * 32; i += MLP_THREADS) {
+      const int r = i / 32, k = i % 32;
+      float v = 0.f;
+      if (k < ACT_IN && row0 + r < rows_total) v = __ldg(model_ins + (size_t)(row0 + r) * ACT_IN + k);
+      s.act[0][k][r] = v;
+    }
+    __syncthreads();
+    mlp_layer<32>(s.w0, s.b0, s.act[0], s.act[1], tr, tn);
+    __syncthreads();
+    mlp_layer<ACT_HID>(s.w1, s.b1, s.act[1], s.act[0], tr, tn);
+    __syncthreads();
+    mlp_layer<ACT_HID>(s.w2, s.b2, s.act[0], s.act[1], tr, tn);
+    __syncthreads();
+    if (tid < MLP_ROWS * ACT_LEG_DOF) {
+      const int r = tid % MLP_ROWS, o = tid / MLP_ROWS;
+      float acc = 0.f;
+#pragma unroll 8
+      for (int k = 0; k < ACT_HID; ++k) acc = fmaf(s.act[1][k][r], s.w3[o][k], acc);
+      const int g = row0 + r;
+      if (g < rows_total) {
+        const int leg = g % ACT_LEGS;
+        // dVel = net(x) * vel_std   (go1.py:102-105)
+        dvel[(size_t)g * ACT_LEG_DOF + o] = (acc + s.b3[o]) * norm[3 * ACT_DOF + leg * ACT_LEG_DOF + o];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
+                                         float* v_hist, float* model_ins, const float* weights, const float* norm,
+                                         float* dvel, cudaStream_t st) {
+  const int n = N * ACT_DOF;
+  lgk_act_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
+  LGK_CUDA_RETURN_IF(cudaGetLastError());
+  const int rows = N * ACT_LEGS;
+  const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = tiles < sms ? tiles : sms;
+  const int smem = (int)sizeof(MlpSmem);
+  LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  lgk_act_mlp_kernel<<<grid, MLP_THREADS, smem, st>>>(rows, model_ins, weights, norm, dvel);
+  return (int)cudaGetLastError();
+}
