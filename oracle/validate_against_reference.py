@@ -1,0 +1,97 @@
+"""Runs the reference's own code (through the shim) and the restated oracle side by side on the same
+synthetic frames and taps, and requires BIT-IDENTICAL buffers on the same torch device.
+TEST INFRASTRUCTURE; only runs where /root/reference exists.
+
+    python -m oracle.validate_against_reference [--envs 256] [--steps 12]
+"""
+from __future__ import annotations
+
+import argparse
+import sys
+
+import torch
+
+from legged_gym_b200.utils import scenarios, synthetic
+from oracle import legged_oracle as lo
+from oracle.reference_loader import TapHarness, make_reference_env
+
+CHECK = ("obs_buf", "rew_buf", "reset_buf", "time_out_buf", "episode_length_buf", "commands", "root_states",
+         "dof_state", "last_actions", "last_dof_vel", "last_root_vel", "feet_air_time", "base_lin_vel",
+         "base_ang_vel", "projected_gravity", "env_origins")
+
+
+def compare_step(env, s, p, tag):
+    bad = []
+    for name in CHECK:
+        a = getattr(env, name)
+        b = getattr(s, name)
+        if not torch.equal(a.reshape(-1), b.reshape(-1).to(a.dtype)):
+            bad.append(name)
+    if hasattr(env, "terrain_levels") and not torch.equal(env.terrain_levels, s.terrain_levels):
+        bad.append("terrain_levels")
+    for k in env.episode_sums:
+        if not torch.equal(env.episode_sums[k], s.episode_sums[k]):
+            bad.append("episode_sums." + k)
+    if torch.is_tensor(env.measured_heights) and not torch.equal(env.measured_heights, s.measured_heights):
+        bad.append("measured_heights")
+    ea, eb = env.extras.get("episode", {}), s.extras.get("episode", {})
+    for k in ea:
+        va, vb = torch.as_tensor(ea[k]), torch.as_tensor(eb[k])
+        if not torch.equal(va.float(), vb.float()):
+            bad.append("extras." + k)
+    if bad:
+        raise AssertionError(f"{tag}: oracle != reference in {bad}")
+
+
+def run_scenario(name, num_envs=256, steps=12, seed=0, verbose=True):
+    task, mutate = scenarios.SCENARIOS[name]
+    env = make_reference_env(task, mutate, num_envs=num_envs, seed=seed)
+    p = lo.OracleParams.from_env(env)
+    frames = synthetic.make_frames(env, 4, seed=1234 + seed)
+    # start from a mid-episode state so resampling / time-outs / pushes fire within a few steps
+    g = torch.Generator().manual_seed(seed)
+    env.episode_length_buf[:] = torch.randint(0, int(env.max_episode_length) + 2, (num_envs,), generator=g)
+    env.episode_length_buf[: num_envs // 8] = 499          # callback resample on the first step
+    env.common_step_counter = int(env.cfg.domain_rand.push_interval) - 3   # a push on the third step
+    env.commands[:] = torch.rand(num_envs, 4, generator=g) * 2 - 1
+    env.feet_air_time[:] = torch.rand(num_envs, env.feet_air_time.shape[1], generator=g) * 0.6
+    env.last_actions[:] = torch.randn(num_envs, env.num_actions, generator=g)
+    env.last_dof_vel[:] = torch.randn(num_envs, env.num_dof, generator=g)
+    for k in env.episode_sums:
+        env.episode_sums[k][:] = torch.randn(num_envs, generator=g)
+    synthetic.load_frame(env, frames[0])
+    s = lo.OracleState.from_env(env, p)
+    harness = TapHarness(env)
+    n_resets = 0
+    for it in range(steps):
+        fr = frames[it % len(frames)]
+        taps = synthetic.make_taps(env, seed=100 * seed + it)
+        # reference: step() with the frame written in place of simulate()
+        synthetic.load_frame(env, fr)
+        with harness.active(taps):
+            env.step(fr["actions"].clone())
+        # oracle
+        s.root_states.copy_(fr["root_states"]); s.dof_state.copy_(fr["dof_state"])
+        s.contact_forces.copy_(fr["contact_forces"].view_as(s.contact_forces)); s.torques.copy_(fr["torques"])
+        target = lo.step(p, s, fr["actions"].clone(), taps)
+        compare_step(env, s, p, f"{name} step {it}")
+        assert torch.equal(env.target_poses, target)
+        n_resets += int(env.reset_buf.sum())
+    if verbose:
+        print(f"  {name}: {steps} steps x {num_envs} envs bit-identical ({n_resets} resets, "
+              f"rewards {list(env.reward_names)} + {'termination' if 'termination' in env.reward_scales else '-'})")
+    return n_resets
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--envs", type=int, default=256)
+    ap.add_argument("--steps", type=int, default=12)
+    a = ap.parse_args(argv)
+    for name in scenarios.SCENARIOS:
+        run_scenario(name, a.envs, a.steps)
+    print("oracle == reference on every scenario")
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,131 @@
+"""Shared test helpers: env construction and the kernel-vs-oracle comparison."""
+from __future__ import annotations
+
+import copy
+
+import numpy as np
+import torch
+
+import legged_gym_b200.envs  # noqa: F401  (registers tasks)
+from legged_gym_b200.sim import gymapi, gymutil
+from legged_gym_b200.utils import scenarios, synthetic
+from legged_gym_b200.utils.helpers import class_to_dict
+from legged_gym_b200.utils.task_registry import task_registry
+
+# north-star tolerance for floating point outputs: |a-b| <= 1e-5 * max(|a|,|b|) + 1e-6
+RTOL, ATOL = 1e-5, 1e-6
+
+
+def make_env(scenario: str, num_envs: int, device: str = "cpu", seed: int = 0, extra=None):
+    task, mutate = scenarios.SCENARIOS[scenario]
+    cfg = copy.deepcopy(task_registry.env_cfgs[task])
+    cfg.env.num_envs = num_envs
+    cfg.seed = seed
+    if task in ("go1", "aliengo"):
+        cfg.control.actuator_net_random_seed = 0
+    mutate(cfg)
+    if extra is not None:
+        extra(cfg)
+    sp = gymapi.SimParams()
+    gymutil.parse_sim_config(class_to_dict(cfg.sim), sp)
+    sp.use_gpu_pipeline = device.startswith("cuda")
+    np.random.seed(seed)
+    torch.manual_seed(seed)
+    return task_registry.get_task_class(task)(cfg=cfg, sim_params=sp, physics_engine=gymapi.SIM_PHYSX,
+                                              sim_device=device, headless=True)
+
+
+def randomise_env_state(env, seed: int):
+    """Mid-episode state so that command resampling, time-outs and a push fire within a few steps."""
+    g = torch.Generator().manual_seed(seed)
+    N = env.num_envs
+    dev = env.device
+    ep = torch.randint(0, int(env.max_episode_length) + 2, (N,), generator=g)
+    ep[: max(N // 8, 1)] = int(env.cfg.commands.resampling_time / env.dt) - 1
+    env.episode_length_buf = ep.to(dev)
+    env.common_step_counter = int(env.cfg.domain_rand.push_interval) - 3
+    env.commands[:] = (torch.rand(N, 4, generator=g) * 2 - 1).to(dev)
+    env.feet_air_time[:] = (torch.rand(N, env.feet_air_time.shape[1], generator=g) * 0.6).to(dev)
+    env.last_actions[:] = torch.randn(N, env.num_actions, generator=g).to(dev)
+    env.last_dof_vel[:] = torch.randn(N, env.num_dof, generator=g).to(dev)
+    for k in env.episode_sums:
+        env.episode_sums[k][:] = torch.randn(N, generator=g).to(dev)
+
+
+def assert_close(name, got, want, exact=False):
+    got = got.detach().cpu()
+    want = want.detach().cpu()
+    assert got.shape == want.shape, f"{name}: shape {tuple(got.shape)} != {tuple(want.shape)}"
+    if exact or not got.dtype.is_floating_point:
+        bad = (got != want.to(got.dtype))
+        assert not bad.any(), f"{name}: {int(bad.sum())} of {bad.numel()} elements differ (bit-exact required)"
+        return
+    a, b = got.double(), want.double()
+    tol = RTOL * torch.maximum(a.abs(), b.abs()) + ATOL
+    bad = (a - b).abs() > tol
+    if bad.any():
+        idx = bad.nonzero()[0].tolist()
+        raise AssertionError(f"{name}: {int(bad.sum())} of {bad.numel()} outside 1e-5 rel; first at {idx}: "
+                             f"got {got[tuple(idx)].item()!r} want {want[tuple(idx)].item()!r}")
+
+
+FLOAT_BUFFERS = ("obs_buf", "rew_buf", "commands", "root_states", "dof_state", "last_actions", "last_dof_vel",
+                 "last_root_vel", "feet_air_time", "base_lin_vel", "base_ang_vel", "projected_gravity", "env_origins")
+EXACT_BUFFERS = ("reset_buf", "time_out_buf", "episode_length_buf")
+
+
+def compare_env_to_oracle(env, s, tag=""):
+    """`env`: this repo's LeggedRobot after a step; `s`: OracleState after the same step."""
+    for name in EXACT_BUFFERS:
+        assert_close(f"{tag}{name}", getattr(env, name), getattr(s, name), exact=True)
+    if hasattr(env, "terrain_levels"):
+        assert_close(f"{tag}terrain_levels", env.terrain_levels, s.terrain_levels, exact=True)
+    n = int(env.step_counts[0])
+    want_ids = s.reset_env_ids.cpu().to(torch.int32)
+    assert n == len(want_ids), f"{tag}n_reset {n} != {len(want_ids)}"
+    assert_close(f"{tag}reset_ids", env.reset_ids[:n], want_ids, exact=True)
+    m = int(env.step_counts[1])
+    want_rs = s.resample_env_ids.cpu().to(torch.int32)
+    assert m == len(want_rs), f"{tag}n_resample {m} != {len(want_rs)}"
+    assert_close(f"{tag}resample_ids", env.resample_ids[:m], want_rs, exact=True)
+    if torch.is_tensor(env.measured_heights) and torch.is_tensor(s.measured_heights):
+        # int16 * 0.005f: exact iff the height-field indices are exact
+        assert_close(f"{tag}measured_heights", env.measured_heights, s.measured_heights, exact=True)
+    for name in FLOAT_BUFFERS:
+        assert_close(f"{tag}{name}", getattr(env, name).reshape(-1), getattr(s, name).reshape(-1))
+    for k in env.episode_sums:
+        assert_close(f"{tag}episode_sums[{k}]", env.episode_sums[k], s.episode_sums[k])
+    if n > 0:
+        for k, v in s.extras.get("episode", {}).items():
+            if k in env.extras["episode"] and torch.is_tensor(env.extras["episode"][k]):
+                assert_close(f"{tag}extras[{k}]", env.extras["episode"][k].reshape(1), torch.as_tensor(v).reshape(1).float())
+
+
+def run_parity(scenario, num_envs, steps, oracle_device="cpu", index_math=None, seed=0, materialize=True):
+    """Steps this repo's env (CUDA kernels, taps) and the oracle on the same frames; compares every step."""
+    from legged_gym_b200 import _lgk
+    from oracle import legged_oracle as lo
+    env = make_env(scenario, num_envs, device="cuda:0", seed=seed)
+    randomise_env_state(env, seed)
+    frames = synthetic.make_frames(env, 4, seed=1234 + seed)
+    synthetic.load_frame(env, frames[0])
+    p = lo.OracleParams.from_env(env, device=oracle_device)
+    s = lo.OracleState.from_env(env, p, device=oracle_device)
+    if index_math is None:
+        index_math = _lgk.INDEX_MATH_TORCH_CPU if oracle_device == "cpu" else _lgk.INDEX_MATH_TORCH_CUDA
+    total_resets = 0
+    for it in range(steps):
+        fr = frames[it % len(frames)]
+        taps = synthetic.make_taps(env, seed=100 * seed + it)
+        synthetic.load_frame(env, fr)
+        env.use_rng_taps(taps, index_math=index_math)
+        env.step(fr["actions"].clone())
+        torch.cuda.synchronize()
+        od = {k: v.to(oracle_device) for k, v in fr.items()}
+        s.root_states.copy_(od["root_states"]); s.dof_state.copy_(od["dof_state"])
+        s.contact_forces.copy_(od["contact_forces"].view_as(s.contact_forces)); s.torques.copy_(od["torques"])
+        target = lo.step(p, s, od["actions"].clone(), {k: v.to(oracle_device) for k, v in taps.items()})
+        compare_env_to_oracle(env, s, tag=f"[{scenario} step {it}] ")
+        assert_close("target_poses", env.target_poses, target)
+        total_resets += int(env.step_counts[0])
+    return total_resets
