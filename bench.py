@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""Benchmark of the per-env step path (BASELINE.json metric: env-steps/s, Go1 rough terrain, 187-point
+height scan, full reward set) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--envs E] [--impl ours|reference]
+
+One "step" = one LeggedRobot.step() without physics: action clip, position-target control for the
+`decimation` substeps, and the fused post_physics_step kernel, over E envs per GPU of synthetic
+simulator state (legged_gym_b200/utils/synthetic.py).  Prints ONE JSON line (rank 0).
+
+  value     device-resident: the step is replayed from CUDA graphs over 8 pre-generated state frames
+            that live in HBM (8 x 29 MB of inputs at 65536 envs, larger than L2).
+  e2e       the same step through the public API with HOST buffers: every step copies that step's
+            simulator state + actions from pinned host memory and reads obs / rewards / resets back.
+  roofline  dominant kernel (lgk_step_kernel): algorithmic bytes per launch / CUDA-event time.
+  cpu_baseline  the oracle (CPU torch restatement of the reference, validated bit-identical to it)
+            timed on this box's host cores on a bounded sample of the same workload.
+
+`--impl reference` times that CPU implementation alone on the same config (the reference is pure
+Python/torch and cannot travel to the GPU box; its restatement in oracle/ is what runs).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+
+SCENARIO = "go1_rough_full"
+NUM_FRAMES = 8
+METRIC = "env_steps_per_sec"
+UNIT = "env-steps/s"
+
+
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:   # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index=0):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:   # noqa: BLE001
+            self.nv = None
+
+    def _one(self):
+        nv = self.nv
+        self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:   # noqa: BLE001
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake", 0x2: "app_clocks_setting"}
+        for bit, n in names.items():
+            if r & bit:
+                self.reasons.add(n)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self._one()
+            except Exception:   # noqa: BLE001
+                break
+            time.sleep(0.002)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def _dist_setup(n_gpus):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(0)
+        local = 0
+    return world, rank, local
+
+
+def _build_env(envs, device, rank, world):
+    import helpers
+
+    def extra(cfg):
+        cfg.env.shard_rank, cfg.env.shard_world = rank, world
+        cfg.terrain.materialize_heights = False     # measured_heights stays in registers (algorithmic bytes)
+    env = helpers.make_env(SCENARIO, envs, device=device, seed=1 + rank, extra=extra)
+    g = torch.Generator().manual_seed(99 + rank)
+    env.episode_length_buf = torch.randint(0, int(env.max_episode_length), (envs,), generator=g).to(device)
+    return env
+
+
+def _bytes_per_env(env):
+    from legged_gym_b200.utils.scenarios import algorithmic_bytes_per_env_step
+    return algorithmic_bytes_per_env_step(env.num_dof, env.num_bodies, len(env.feet_indices), env._num_sum_rows,
+                                          env.num_obs)
+
+
+def run_ours(args):
+    world, rank, local = _dist_setup(args.gpus)
+    device = f"cuda:{local}"
+    from legged_gym_b200 import _lgk
+    from legged_gym_b200.utils import synthetic
+    from legged_gym_b200.utils.distributed import ShardedStats
+    lib = _lgk.load()
+    env = _build_env(args.envs, device, rank, world)
+    N = env.num_envs
+    frames = synthetic.make_frames(env, NUM_FRAMES, seed=1234 + 1000 * 2 + rank, device=device)
+    stats = ShardedStats(env, interval=24) if world > 1 else None
+    stream = torch.cuda.Stream(device)
+    torch.cuda.synchronize()
+
+    # ---- device-resident path: one CUDA graph per frame ------------------------------------------
+    graphs, launches_per_step = [], 0
+    with torch.cuda.stream(stream):
+        env.bind_sim_tensors(**{k: frames[0][k] for k in ("root_states", "dof_state", "contact_forces", "torques")})
+        for _ in range(3):      # eager warm-up (loads kernels, seeds the device step counter)
+            env.step(frames[0]["actions"])
+        stream.synchronize()
+        for k in range(NUM_FRAMES):
+            fr = frames[k]
+            env.bind_sim_tensors(**{n: fr[n] for n in ("root_states", "dof_state", "contact_forces", "torques")})
+            g = torch.cuda.CUDAGraph()
+            l0 = lib.lgk_launch_count()
+            with torch.cuda.graph(g, stream=stream):
+                env.step(fr["actions"])
+            launches_per_step = lib.lgk_launch_count() - l0
+            graphs.append(g)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def replay(i):
+        graphs[i % NUM_FRAMES].replay()
+        if stats is not None:
+            stats.after_step(i)
+
+    with torch.cuda.stream(stream):
+        for i in range(max(args.warmup, 3)):
+            replay(i)
+        t_end = time.time() + 0.3          # settle clocks under load before timing
+        i = 0
+        while time.time() < t_end:
+            replay(i)
+            i += 1
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as clocks:
+            e0.record(stream)
+            for i in range(args.steps):
+                replay(i)
+            e1.record(stream)
+            barrier()
+        ms_total = e0.elapsed_time(e1)
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms_total], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    value = N * world * args.steps / (ms_total * 1e-3)
+
+    # ---- dominant kernel alone: events around the fused post-physics launch ---------------------
+    import ctypes as C
+    with torch.cuda.stream(stream):
+        st = C.c_void_p(stream.cuda_stream)
+        reps = max(20, min(args.steps, 200))
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+        kt = []
+        for i in range(reps + 3):
+            fr = frames[i % NUM_FRAMES]
+            env.bind_sim_tensors(**{n: fr[n] for n in ("root_states", "dof_state", "contact_forces", "torques")})
+            flush.zero_()                       # evict L2 between timed launches
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(stream)
+            _lgk.check("step", lib.lgk_post_physics_step(C.byref(env._consts), C.byref(env._bufs), st))
+            a1.record(stream)
+            stream.synchronize()
+            if i >= 3:
+                kt.append(a0.elapsed_time(a1))
+        del flush
+    k_ms = sum(kt) / len(kt)
+    bpe = _bytes_per_env(env)
+    peak, peak_src = _peaks()
+    achieved = bpe * N / (k_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "step_kernel_traffic.json")
+    if os.path.isfile(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(str(N))
+        except Exception:   # noqa: BLE001
+            traffic = None
+    roofline = {"kernel": "lgk_step_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
+                "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
+                "algorithmic_bytes_per_env_step": bpe, "kernel_ms": round(k_ms, 5), "peak_source": peak_src,
+                "timing": "CUDA events around single launches, L2 flushed (256 MB memset) before each"}
+
+    # ---- end to end through the public API with host buffers --------------------------------------
+    e2e = run_e2e(env, frames, args, world, device, stream)
+
+    # ---- CPU baseline (rank 0, single-GPU runs only) ------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_reference(args.envs, budget_s=args.cpu_budget)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 6), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"Go1 rough terrain, 187-point height scan, full reward set (20 terms + "
+                                   f"termination), terrain curriculum, {N} envs/GPU, position control x"
+                                   f"{env.cfg.control.decimation} substeps + fused post_physics_step",
+                       "envs_per_gpu": N, "envs_total": N * world, "num_obs": env.num_obs,
+                       "reward_terms": env._num_sum_rows, "rng": "in-kernel Philox4x32-10",
+                       "l2": f"inputs cycle through {NUM_FRAMES} state frames resident in HBM "
+                             f"({NUM_FRAMES * N * 448 / 1e6:.0f} MB) -- larger than L2 at the default size",
+                       "parallelism": f"env-sharded x{world}, terrain replica per GPU, "
+                                      f"NCCL all-reduce of episode statistics every 24 steps"},
+            "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "launches_per_step": int(launches_per_step),
+            "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(env, frames, args, world, device, stream):
+    """Public-API path with host buffers: pinned host -> device copies of that step's simulator state and
+    actions, env.step(), device -> pinned host read-back of observations, rewards and resets."""
+    N = env.num_envs
+    names = ("root_states", "dof_state", "contact_forces", "torques", "actions")
+    host = [{k: fr[k].cpu().pin_memory() for k in names} for fr in frames]
+    dev = {k: torch.empty_like(frames[0][k]) for k in names}
+    env.bind_sim_tensors(**{k: dev[k] for k in names[:4]})
+    out_h = {"obs": torch.empty(env.obs_buf.shape, dtype=torch.float).pin_memory(),
+             "rew": torch.empty(N, dtype=torch.float).pin_memory(),
+             "reset": torch.empty(N, dtype=torch.bool).pin_memory()}
+    h2d = sum(host[0][k].numel() * host[0][k].element_size() for k in names)
+    d2h = sum(v.numel() * v.element_size() for v in out_h.values())
+
+    def one(i):
+        h = host[i % len(host)]
+        for k in names:
+            dev[k].copy_(h[k], non_blocking=True)
+        obs, _, rew, reset, _ = env.step(dev["actions"])
+        out_h["obs"].copy_(obs, non_blocking=True)
+        out_h["rew"].copy_(rew, non_blocking=True)
+        out_h["reset"].copy_(reset, non_blocking=True)
+        stream.synchronize()            # the caller consumes the step's result before the next one
+
+    steps = max(10, min(args.steps, 200))
+    with torch.cuda.stream(stream):
+        for i in range(3):
+            one(i)
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(steps):
+            one(i)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return {"value": round(N * world * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": round(ms / steps, 5),
+            "path": "pinned host buffers -> LeggedRobot.step() -> pinned host buffers, stream-synchronised every step"}
+
+
+def cpu_reference(envs, budget_s=20.0, steps=None, warmup=1):
+    """The reference's CPU implementation of the path (oracle port) on all host cores, bounded sample."""
+    import helpers
+    from legged_gym_b200.utils import synthetic
+    from oracle import legged_oracle as lo
+    torch.set_num_threads(os.cpu_count() or 1)
+    # size the sample from a short probe so the whole leg stays within the budget
+    probe_n = min(envs, 4096)
+    t_probe = _time_oracle(probe_n, 2, 1, helpers, synthetic, lo)
+    per_env = t_probe / probe_n
+    n = envs
+    if steps is None:
+        steps = 5
+    while n > 1024 and per_env * n * (steps + warmup) > budget_s:
+        n //= 2
+    t = _time_oracle(n, steps, warmup, helpers, synthetic, lo)
+    return {"value": round(n / t, 1), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} steps x {n} envs of the same workload after {warmup} warm-up (oracle/legged_oracle.py, "
+                      f"torch {torch.__version__} CPU kernels)", "ms_per_step": round(t * 1e3, 3)}
+
+
+def _time_oracle(n, steps, warmup, helpers, synthetic, lo):
+    env = helpers.make_env(SCENARIO, n, device="cpu", seed=1)
+    g = torch.Generator().manual_seed(99)
+    env.episode_length_buf = torch.randint(0, int(env.max_episode_length), (n,), generator=g)
+    p = lo.OracleParams.from_env(env)
+    s = lo.OracleState.from_env(env, p)
+    frames = synthetic.make_frames(env, 2, seed=3234)
+    taps = synthetic.make_taps(env, seed=5)
+    ts = []
+    for i in range(steps + warmup):
+        fr = frames[i % 2]
+        s.root_states.copy_(fr["root_states"]); s.dof_state.copy_(fr["dof_state"])
+        s.contact_forces.copy_(fr["contact_forces"].view_as(s.contact_forces)); s.torques.copy_(fr["torques"])
+        t0 = time.perf_counter()
+        taps["noise"] = torch.rand(n, env.num_obs)      # the reference draws its noise every step (:231)
+        lo.step(p, s, fr["actions"], taps)
+        ts.append(time.perf_counter() - t0)
+    ts = sorted(ts[warmup:])
+    return ts[len(ts) // 2]
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    t0 = time.perf_counter()
+    cpu = cpu_reference(args.envs, budget_s=max(30.0, min(150.0, 1.5 * (args.steps + args.warmup))),
+                        steps=max(1, min(args.steps, 20)), warmup=max(1, min(args.warmup, 3)))
+    n_sample = int(cpu["sample"].split(" x ")[1].split(" envs")[0])
+    line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cpu["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"Go1 rough terrain, 187-point height scan, full reward set, {args.envs} envs/GPU "
+                                   f"(CPU sample of {n_sample} envs per step)", "envs_per_gpu": args.envs},
+            "cpu_baseline": cpu, "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                                         "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": round(time.perf_counter() - t0, 1)}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--envs", type=int, default=65536, help="envs per GPU (BASELINE.json: 4096-65536)")
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=20.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

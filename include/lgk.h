@@ -78,24 +78,17 @@ typedef enum LgkRewardTerm {
   LGK_REW_COUNT
 } LgkRewardTerm;
 
-/* LgkConsts.index_math -- the two device-dependent roundings on the height-index path
- * (legged_robot.py:839-842, utils/math.py:38-42).  torch evaluates them differently on CPU and
- * on CUDA, and a last-bit difference moves ~2e-5 of the truncated indices, so the caller names
- * the torch device it must agree with bit-for-bit.
- *  bit 0    (p / horizontal_scale): 0 = IEEE division (torch CPU), 1 = multiply by the fp32
- *           reciprocal (torch CUDA div-by-scalar).
- *  bits 1-2 norm([0,0,qz,qw]): 0 = sqrtf(fma(w,w,z*z)), 1 = sqrtf(z*z + w*w) with separately
- *           rounded squares, 2 = sqrtf(fma(z,z,w*w)), 3 = (float)sqrt((double)(z*z + w*w)) with
- *           separately rounded squares (what torch 2.11 CPU computes; measured). */
+/* LgkConsts.index_math -- the one device-dependent rounding on the height-index path
+ * (legged_robot.py:842): (p / horizontal_scale).long().  torch-CPU performs an IEEE division,
+ * torch-CUDA multiplies by the fp32 reciprocal of the python scalar; the truncated indices differ
+ * in ~2e-6 of samples (measured on the B200 box), so the caller names the torch device it must
+ * agree with bit-for-bit.  Everything else on that path -- normalize([0,0,qz,qw]) as
+ * sqrtf(z*z + w*w) with separately rounded squares, quat_apply without contraction -- was measured
+ * to be identical on both devices (tools/calibrate_norm.py). */
 typedef enum LgkIndexMath {
-  LGK_INDEX_DIV = 0,
-  LGK_INDEX_MUL_RCP = 1,
-  LGK_NORM_FMA_W = 0 << 1,
-  LGK_NORM_SEPARATE = 1 << 1,
-  LGK_NORM_FMA_Z = 2 << 1,
-  LGK_NORM_SEPARATE_F64SQRT = 3 << 1
+  LGK_INDEX_DIV = 0,      /* torch CPU  */
+  LGK_INDEX_MUL_RCP = 1   /* torch CUDA */
 } LgkIndexMath;
-#define LGK_INDEX_MATH_TORCH_CPU (LGK_INDEX_DIV | LGK_NORM_SEPARATE_F64SQRT)
 
 /* random-number source */
 typedef enum LgkRngMode {
@@ -281,6 +274,11 @@ int lgk_reset_all(const LgkConsts* c, const LgkBuffers* b, void* stream);
 /* Sets the device copy of common_step_counter (legged_robot.py:119,527) held in the workspace;
  * the step kernel increments it itself.  Not capturable in a CUDA graph. */
 int lgk_set_step_counter(void* workspace, int64_t value, void* stream);
+
+/* Calibration probe: out[i] = (qz, qw) / norm([0,0,qz,qw]) for quat [n,4], computed exactly as the
+ * step kernel does (norm_mode 1); modes 0, 2, 3 are the alternatives that were ruled out
+ * (fma-contracted sums, double-precision sqrt).  Lets a test pin the formula against torch. */
+int lgk_debug_yaw_quat(const float* quat, int32_t n, int32_t norm_mode, float* out, void* stream);
 
 /* sizeof(LgkConsts) / sizeof(LgkBuffers) as compiled, for binding self-checks */
 int64_t lgk_sizeof_consts(void);

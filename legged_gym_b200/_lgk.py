@@ -28,10 +28,10 @@ REWARD_ID = {n: i for i, n in enumerate(REWARD_TERMS)}
 REW_EXTERNAL = len(REWARD_TERMS)
 
 INDEX_DIV, INDEX_MUL_RCP = 0, 1
-NORM_FMA_W, NORM_SEPARATE, NORM_FMA_Z, NORM_SEPARATE_F64SQRT = 0 << 1, 1 << 1, 2 << 1, 3 << 1
-INDEX_MATH_TORCH_CPU = INDEX_DIV | NORM_SEPARATE_F64SQRT
-# what torch CUDA evaluates on B200 (calibrated by tests/test_gpu_index_math.py)
-INDEX_MATH_TORCH_CUDA = INDEX_MUL_RCP | NORM_FMA_W
+# (p / horizontal_scale).long(): torch-CPU divides, torch-CUDA multiplies by the fp32 reciprocal
+# (measured on B200: tools/calibrate_index_math.py)
+INDEX_MATH_TORCH_CPU = INDEX_DIV
+INDEX_MATH_TORCH_CUDA = INDEX_MUL_RCP
 
 RNG_PHILOX, RNG_TAPS = 0, 1
 
@@ -151,6 +151,7 @@ def load():
         "lgk_reset_idx": (C.c_int, [cp, bp, fp, C.c_int32, fp]),
         "lgk_reset_all": (C.c_int, [cp, bp, fp]),
         "lgk_set_step_counter": (C.c_int, [fp, C.c_int64, fp]),
+        "lgk_debug_yaw_quat": (C.c_int, [fp, C.c_int32, C.c_int32, fp, fp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)   # AttributeError if the library does not export a declared symbol
@@ -169,7 +170,7 @@ def load():
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
     "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_compute_torques", "lgk_actuator_advance",
-    "lgk_post_physics_step", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter",
+    "lgk_post_physics_step", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]
 
 

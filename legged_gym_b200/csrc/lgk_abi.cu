@@ -10,6 +10,7 @@ int lgk_build_height_min3_impl(const int16_t*, int, int, int16_t*, int, cudaStre
 int lgk_clip_actions_impl(const float*, float*, long long, float, cudaStream_t);
 int lgk_compute_poses_impl(const LgkConsts*, const float*, float*, cudaStream_t);
 int lgk_compute_torques_impl(const LgkConsts*, const float*, const float*, const float*, float*, cudaStream_t);
+int lgk_debug_yaw_quat_impl(const float*, int, int, float*, cudaStream_t);
 int lgk_actuator_advance_impl(int, const float*, const float*, float*, float*, float*, const float*, const float*,
                               float*, cudaStream_t);
 }
@@ -160,6 +161,13 @@ int lgk_reset_idx(const LgkConsts* c, const LgkBuffers* b, const int64_t* env_id
 int lgk_reset_all(const LgkConsts* c, const LgkBuffers* b, void* stream) {
   if (!c) return LGK_ERR_NULL;
   return lgk_reset_idx(c, b, nullptr, c->num_envs, stream);
+}
+
+int lgk_debug_yaw_quat(const float* quat, int32_t n, int32_t norm_mode, float* out, void* stream) {
+  if (!quat || !out) return LGK_ERR_NULL;
+  if (n <= 0 || norm_mode < 0 || norm_mode > 3) return LGK_ERR_DIM;
+  g_launches += 1;
+  return lgk_debug_yaw_quat_impl(quat, n, norm_mode, out, (cudaStream_t)stream);
 }
 
 /* device-side common_step_counter (legged_robot.py:119,527) */

@@ -24,6 +24,28 @@ extern "C" int lgk_build_height_min3_impl(const int16_t* hs, int rows, int cols,
 }
 
 // ---------------------------------------------------------------------------------------------
+// Calibration probe: normalize([0,0,qz,qw]) in each LgkIndexMath norm mode, so a test can find the
+// mode that reproduces torch's `x / x.norm(p=2, dim=-1).clamp(min=eps)` bit-for-bit on a device.
+__global__ void lgk_yaw_quat_kernel(const float* __restrict__ quat, int n, int mode, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float z = quat[4 * i + 2], w = quat[4 * i + 3];
+  const float zz = mul_rn(z, z), ww = mul_rn(w, w);
+  float nn;
+  if (mode == 0) nn = sqrtf(fmaf(w, w, zz));
+  else if (mode == 1) nn = sqrtf(add_rn(zz, ww));
+  else if (mode == 2) nn = sqrtf(fmaf(z, z, ww));
+  else nn = (float)sqrt((double)add_rn(zz, ww));
+  nn = fmaxf(nn, 1e-9f);
+  out[2 * i] = __fdiv_rn(z, nn);
+  out[2 * i + 1] = __fdiv_rn(w, nn);
+}
+extern "C" int lgk_debug_yaw_quat_impl(const float* quat, int n, int mode, float* out, cudaStream_t st) {
+  lgk_yaw_quat_kernel<<<(n + 255) / 256, 256, 0, st>>>(quat, n, mode, out);
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
 __global__ void lgk_clip_kernel(const float* __restrict__ in, float* __restrict__ out, long long n, float lim) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long n4 = n >> 2;

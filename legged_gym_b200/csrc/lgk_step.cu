@@ -183,14 +183,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     cmd_rew = cmd;
     // yaw-only quaternion of quat_apply_yaw (utils/math.py:38-42): normalize([0,0,qz,qw])
     {
-      const int nm = (c.index_math >> 1) & 3;
-      const float zz = mul_rn(q[2], q[2]), ww = mul_rn(q[3], q[3]);
-      float n;
-      if (nm == 0) n = sqrtf(fmaf(q[3], q[3], zz));
-      else if (nm == 1) n = sqrtf(add_rn(zz, ww));
-      else if (nm == 2) n = sqrtf(fmaf(q[2], q[2], ww));
-      else n = (float)sqrt((double)add_rn(zz, ww));
-      n = fmaxf(n, 1e-9f);
+      // x.norm(p=2, dim=-1): separately rounded squares, correctly rounded sqrt (same on torch CPU/CUDA)
+      const float n = fmaxf(sqrtf(add_rn(mul_rn(q[2], q[2]), mul_rn(q[3], q[3]))), 1e-9f);
       yaw_z = __fdiv_rn(q[2], n);
       yaw_w = __fdiv_rn(q[3], n);
     }
@@ -429,7 +423,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   {
     const bool add_noise = flags & LGK_F_ADD_NOISE;
     const bool plane = flags & LGK_F_TERRAIN_PLANE;
-    const bool mul_rcp = c.index_math & LGK_INDEX_MUL_RCP;
+    const bool mul_rcp = c.index_math == LGK_INDEX_MUL_RCP;
     const float inv_hs = 1.0f / c.horizontal_scale;
     const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
     // this lane's scan offsets (same for every env)
