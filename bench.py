@@ -205,6 +205,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     value = N * world * args.steps / (ms_total * 1e-3)
+    env._dev_step_counter = -1      # graph replays advanced the device step counter: reseed it on the next eager step
 
     # ---- dominant kernel alone: events around the fused post-physics launch ---------------------
     import ctypes as C

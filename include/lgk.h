@@ -206,8 +206,10 @@ typedef struct LgkBuffers {
   int32_t*     reset_ids;          /* [N] ascending env ids reset this step                */
   int32_t*     resample_ids;       /* [N] ascending env ids whose command was resampled    */
   int32_t*     counts;             /* [2] {n_reset, n_resample}; counts_host mirrors it    */
-  float*       episode_stats;      /* [R(+1)+3]: sum over reset ids of episode_sums[k],
-                                      then n_reset, sum(terrain_levels), spare             */
+  float*       episode_stats;      /* [2*(R'+4)], R' = R(+1): first half = this step: sum over reset
+                                      ids of episode_sums[k], then n_reset, sum(terrain_levels), N;
+                                      second half = the same sums accumulated over steps until
+                                      the caller zeroes them (multi-GPU all-reduce payload)      */
   float*       extras;             /* [R(+1)+2]: rew_<k> means / max_episode_length_s,
                                       terrain_level mean; only rewritten when n_reset > 0  */
   const float* ext_rewards;        /* [n_ext, N] values of LGK_REW_EXTERNAL terms or NULL  */

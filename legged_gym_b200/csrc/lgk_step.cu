@@ -614,6 +614,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     if ((int)threadIdx.x < num_rows) {
       const float s = st[threadIdx.x];
       b.episode_stats[threadIdx.x] = s;
+      b.episode_stats[num_rows + 4 + threadIdx.x] += s;   // running sums since the host last cleared them
       if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
         b.extras[threadIdx.x] = (s / (float)n_reset) / c.max_episode_length_s;
       ws->stats[parity ^ 1][threadIdx.x] = 0.f;   // next step's accumulators
@@ -624,6 +625,9 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       b.episode_stats[num_rows] = (float)n_reset;
       b.episode_stats[num_rows + 1] = (float)level_sum;
       b.episode_stats[num_rows + 2] = (float)N;
+      b.episode_stats[2 * num_rows + 4] += (float)n_reset;
+      b.episode_stats[2 * num_rows + 5] = (float)level_sum;
+      b.episode_stats[2 * num_rows + 6] = (float)N;
       if (n_reset > 0 && (flags & LGK_F_TERRAIN_CURRICULUM))
         b.extras[num_rows] = (float)level_sum / (float)N;   // mean(terrain_levels.float()) (:188)
       ws->level_sum[parity ^ 1] = 0;

@@ -405,7 +405,7 @@ class LeggedRobot(BaseTask):
         # dict in the reference's key order (reward_scales order); values are rows of one [R,N] buffer
         self.episode_sums = {name: self._episode_sums_buf[self._sum_row[name]] for name in self.reward_scales.keys()}
         self._extras_buf = torch.zeros(self._num_sum_rows + 4, dtype=torch.float, device=self.device)
-        self.episode_stats = torch.zeros(self._num_sum_rows + 4, dtype=torch.float, device=self.device)
+        self.episode_stats = torch.zeros(2 * (self._num_sum_rows + 4), dtype=torch.float, device=self.device)
         if self._external_terms:
             self._ext_rewards = torch.zeros(len(self._external_terms), self.num_envs, dtype=torch.float,
                                             device=self.device)
@@ -764,6 +764,26 @@ class LeggedRobot(BaseTask):
             self._bufs = self.build_buffers(self._taps)
         if index_math is not None:
             self._consts.index_math = index_math
+
+    def bind_sim_tensors(self, root_states=None, dof_state=None, contact_forces=None, torques=None):
+        """Point the env at other storage for the simulator-owned tensors (a backend that hands out a
+        different buffer per frame, or pre-generated frames resident in HBM) without copying."""
+        self._kernels()
+        N, D = self.num_envs, self.num_dof
+        if root_states is not None:
+            self.root_states = root_states.view(N, 13)
+            self.base_quat = self.root_states[:, 3:7]
+        if dof_state is not None:
+            self.dof_state = dof_state.view(N * D, 2)
+            self.dof_pos = self.dof_state.view(N, D, 2)[..., 0]
+            self.dof_vel = self.dof_state.view(N, D, 2)[..., 1]
+        if contact_forces is not None:
+            self.contact_forces = contact_forces.view(N, -1, 3)
+        if torques is not None:
+            self.torques = torques.view(N, self.num_actions)
+        P = _lgk.ptr
+        self._bufs.root_states, self._bufs.dof_state = P(self.root_states), P(self.dof_state)
+        self._bufs.contact_forces, self._bufs.torques = P(self.contact_forces), P(self.torques)
 
     def _ensure_dev_counter(self, want: int):
         """Device copy of common_step_counter: the step kernel increments it itself, so it is
