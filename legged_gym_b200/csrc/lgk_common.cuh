@@ -47,13 +47,14 @@ __device__ __forceinline__ float u01(unsigned int x) { return (float)(x >> 8) * 
 
 // RNG "sites" of one env-step; each owns a range of Philox blocks
 enum : unsigned int {
-  LGK_SITE_NOISE = 0,        // blocks 0..63: lane + 32*k
-  LGK_SITE_CMD_CB = 64,
-  LGK_SITE_CMD_RESET = 65,
-  LGK_SITE_PUSH = 66,
-  LGK_SITE_LEVEL = 67,
-  LGK_SITE_ROOT = 68,        // 2 blocks: xy(2) + vel(6)
-  LGK_SITE_DOF = 70          // ceil(D/4) blocks
+  LGK_SITE_NOISE = 0,        // blocks 0..95: 3 * lane + k (head A, head B, then one word per scan pass)
+  LGK_SITE_CMD_CB = 96,
+  LGK_SITE_CMD_RESET = 97,
+  LGK_SITE_PUSH = 98,
+  LGK_SITE_LEVEL = 99,
+  LGK_SITE_ROOT = 100,       // 2 blocks: xy(2) + vel(6)
+  LGK_SITE_DOF = 102,        // ceil(D/4) blocks
+  LGK_SITE_RESET_IDX = 256   // offset added by lgk_reset_idx (draws disjoint from the step's)
 };
 __device__ __forceinline__ uint4 lgk_philox(const uint64_t seed, unsigned long long step, unsigned int env_global,
                                             unsigned int block) {
@@ -115,3 +116,44 @@ __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fm
     cudaError_t e__ = (err);               \
     if (e__ != cudaSuccess) return (int)e__; \
   } while (0)
+
+// ---- sm_100a async-proxy helpers: 1-D bulk copies (TMA engine, SASS UBLKCP) + mbarrier ----------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok = 0;
+  const uint32_t addr = smem_u32(bar);
+  while (!ok) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  }
+}
+// global -> shared, completion counted in bytes on `bar`; dst/src 16-byte aligned, bytes % 16 == 0
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(__cvta_generic_to_global(src_gmem)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// shared -> global (bulk async-group)
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(__cvta_generic_to_global(dst_gmem)),
+               "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// generic-proxy shared-memory writes -> visible to the async proxy (before a bulk store reads them)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

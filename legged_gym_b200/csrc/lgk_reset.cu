@@ -24,7 +24,7 @@ lgk_reset_kernel(const __grid_constant__ ResetArgs a) {
   const unsigned long long csc = ws->step_counter;
   const int parity = (int)((csc + 1ull) & 1ull);   // accumulators the next step kernel will NOT use... see finalize
   const unsigned eg = (unsigned)(c.env_id_offset + env);
-  const unsigned SITE = 128u;   // philox blocks disjoint from the step kernel's
+  const unsigned SITE = LGK_SITE_RESET_IDX;   // philox blocks disjoint from the step kernel's
 
   int level_contrib = 0;
   if (active) {

@@ -1,4 +1,4 @@
-// Fused post_physics_step kernel (sm_100a).
+// Fused post_physics_step kernel (sm_100a), tile version.
 //
 // One launch replaces everything LeggedRobot.post_physics_step() does per env
 // (reference legged_robot.py:109-141): episode counters, body-frame velocities / projected
@@ -7,65 +7,60 @@
 // curriculum, dof / root state, commands), the noisy scaled observation row, last_* copies,
 // ascending compacted reset / resample id lists and the episode statistics behind extras.
 //
-// Work decomposition: a warp owns `epw` consecutive envs.
-//   S0  lane e does the per-env scalar work of env e (contacts staged through shared memory so
-//       global traffic stays coalesced; 12-wide dof rows read as float4).
-//   A   the warp walks its envs one at a time; lanes cover the 48-wide observation head and the
-//       H scan points of that env (coalesced obs stores, one int16 gather per point from the
-//       precomputed min-of-three-neighbours table).
-//   S1  lane e sums the reward terms of env e in the reference's order and updates episode sums.
-//   The last CTA to finish scans the per-warp reset / resample bitmasks into ascending id lists
+// Work decomposition: one CTA (4 warps) owns a tile of 32 consecutive envs.
+//   load    every per-env input row of the tile is contiguous in HBM ([N,13], [N,D,2], [N,B,3], ...):
+//           one thread issues 1-D bulk async copies (cp.async.bulk -> SASS UBLKCP, the TMA engine)
+//           into shared memory, completion counted on an mbarrier.  No register staging, full
+//           coalescing, ~22 KB in flight per CTA.
+//   stage 1 the four warps run four different per-env jobs with lane = env (no divergence inside a
+//           warp): W0 base state / commands / termination / reset of the root, W1 + W2 the joints,
+//           W3 contacts + feet air time.  The reset flag is cheap and is recomputed by each warp.
+//   stage 2 each warp takes 8 envs; lanes cover the columns of one env at a time: noise on the
+//           observation head, then the H scan points (one int16 gather per point from the
+//           precomputed min-of-three-neighbours table).  The observation tile is built in shared memory.
+//   stage 3 W0 (lane = env) sums the reward terms in the reference's order and updates episode sums.
+//   store   obs tile, last_actions, last_dof_vel and the episode-sum rows leave through bulk async
+//           stores; small per-env outputs are written directly.
+//   The last CTA to finish scans the per-tile reset / resample bitmasks into ascending id lists
 //   and finalises the statistics.
 #include "lgk_common.cuh"
+
+#define TILE 32
+
+struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
+  int root, dof, act, ldv, cmd, fat, ep, lvl, sums, head, scr, cf, tq, lact, obs, total;
+};
 
 struct StepArgs {
   LgkConsts c;
   LgkBuffers b;
-  int epw;         // envs per warp (4, 8, 16 or 32)
-  int head_stride; // shared-memory row stride of the staged observation head (odd)
-  int row_floats;  // floats of shared memory per env  = max(3B, head_stride)
-  int num_warps;   // warps with work
+  TileLayout L;
+  int num_tiles;
+  int head_stride;   // odd row stride of the staged observation head
+  int air_active;    // feet_air_time term active (:945-948 only run then)
+  int bh_active;     // base_height term active
+  int tma_ok;        // every tiled array 16-byte aligned and N % 4 == 0
+  int num_rows;      // episode_sums rows: num_rewards (+1 with termination)
 };
+
+// scratch fields (SoA, [field][TILE]) exchanged between the stages
+enum { SC_ES = 0,            // 8 floats per env (AoS): rx ry rz zo | yaw_z yaw_w - -
+       SC_J1 = 8, SC_J2 = 18,  // joint partial sums of W1 / W2 (10 each)
+       SC_COLL = 28, SC_FFP, SC_RAIR, SC_STUMBLE, SC_NOFLY, SC_BH, SC_FIELDS };
 
 // ---------------------------------------------------------------------------------------------
-struct ContactSummary {
-  bool term;          // any termination body with |f| > 1           (:146)
-  float collisions;   // # penalised bodies with |f| > 0.1            (:897)
-  unsigned contact_bits;  // feet with f_z > 1                        (:943)
-  int nofly_contacts; // feet with f_z > 0.1                          (cassie.py:44)
-  bool stumble;       // any foot with |f_xy| > 5 |f_z|               (:953)
-  float feet_force_pen;   // sum max(|f| - max_contact_force, 0)      (:962)
-};
-
 __device__ __forceinline__ float norm3(float x, float y, float z) {
   return sqrtf(fmaf(z, z, fmaf(y, y, x * x)));
 }
 
-__device__ __forceinline__ ContactSummary summarise_contacts(const LgkConsts& c, const float* __restrict__ cf) {
-  ContactSummary s;
-  s.term = false;
-  for (int t = 0; t < c.num_term; ++t) {
-    const float* f = cf + 3 * c.term_idx[t];
-    s.term |= norm3(f[0], f[1], f[2]) > 1.0f;
+// any termination body with |f| > 1 (:146)
+__device__ __forceinline__ bool term_contact(const LgkConsts& c, const float* __restrict__ cf) {
+  bool t = false;
+  for (int k = 0; k < c.num_term; ++k) {
+    const float* f = cf + 3 * c.term_idx[k];
+    t |= norm3(f[0], f[1], f[2]) > 1.0f;
   }
-  s.collisions = 0.f;
-  for (int p = 0; p < c.num_pen; ++p) {
-    const float* f = cf + 3 * c.pen_idx[p];
-    s.collisions += (norm3(f[0], f[1], f[2]) > 0.1f) ? 1.f : 0.f;
-  }
-  s.contact_bits = 0;
-  s.nofly_contacts = 0;
-  s.stumble = false;
-  s.feet_force_pen = 0.f;
-  for (int k = 0; k < c.num_feet; ++k) {
-    const float* f = cf + 3 * c.feet_idx[k];
-    const float fx = f[0], fy = f[1], fz = f[2];
-    if (fz > 1.0f) s.contact_bits |= 1u << k;
-    s.nofly_contacts += (fz > 0.1f) ? 1 : 0;
-    s.stumble |= sqrtf(fmaf(fy, fy, fx * fx)) > 5.0f * fabsf(fz);
-    s.feet_force_pen += fmaxf(norm3(fx, fy, fz) - c.max_contact_force, 0.f);
-  }
-  return s;
+  return t;
 }
 
 // _resample_commands for one env (legged_robot.py:354-368); cr = (lo, hi-lo) pairs
@@ -81,398 +76,469 @@ __device__ __forceinline__ void resample_command(float4& cmd, const float* __res
 }
 
 struct DofAcc {   // per-env sums over joints feeding the reward terms (:874-916, :956-966)
-  float tq2, energy, qd2, acc2, arate, poslim, vellim, tqlim, stand, hip;
+  float v[10];    // tq2, energy, qd2, acc2, arate, poslim, vellim, tqlim, stand, hip
 };
+enum { A_TQ2 = 0, A_ENERGY, A_QD2, A_ACC2, A_ARATE, A_POSLIM, A_VELLIM, A_TQLIM, A_STAND, A_HIP };
 
-template <int DT>
+// one joint: reward partial sums on the pre-reset state, reset values, observation head columns
+__device__ __forceinline__ void joint_update(const LgkConsts& c, int d, int D, unsigned hip_mask, bool reset,
+                                             float inv_dt, float av, float lav, float tqv, float ldvv, float& p,
+                                             float& v, float u, DofAcc& acc, float* __restrict__ head_row) {
+  acc.v[A_TQ2] = fmaf(tqv, tqv, acc.v[A_TQ2]);
+  const float pw = tqv * v;
+  acc.v[A_ENERGY] = fmaf(pw, pw, acc.v[A_ENERGY]);
+  acc.v[A_QD2] = fmaf(v, v, acc.v[A_QD2]);
+  const float ja = (ldvv - v) * inv_dt;
+  acc.v[A_ACC2] = fmaf(ja, ja, acc.v[A_ACC2]);
+  const float da = lav - av;
+  acc.v[A_ARATE] = fmaf(da, da, acc.v[A_ARATE]);
+  acc.v[A_POSLIM] += -fminf(p - c.dof_pos_lo[d], 0.f) + fmaxf(p - c.dof_pos_hi[d], 0.f);
+  acc.v[A_VELLIM] += clampf(fabsf(v) - c.dof_vel_limits[d] * c.soft_dof_vel_limit, 0.f, 1.f);
+  acc.v[A_TQLIM] += fmaxf(fabsf(tqv) - c.torque_limits[d] * c.soft_torque_limit, 0.f);
+  const float dev = fabsf(p - c.default_dof_pos[d]);
+  acc.v[A_STAND] += dev;
+  if ((hip_mask >> d) & 1u) acc.v[A_HIP] += dev;
+  if (reset) {   // _reset_dofs (:399-408): default * U(0.5, 1.5), zero velocity
+    p = mul_rn(c.default_dof_pos[d], rand_affine(1.0f, 0.5f, u));
+    v = 0.f;
+  }
+  head_row[12 + d] = (p - c.default_dof_pos[d]) * c.obs_scale_dof_pos;
+  head_row[12 + D + d] = v * c.obs_scale_dof_vel;
+  head_row[12 + 2 * D + d] = av;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int DT, bool TAPS, bool MUL_RCP>
 __global__ void __launch_bounds__(LGK_CTA_THREADS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
+  const TileLayout& L = a.L;
   constexpr bool VEC = (DT > 0) && (DT % 4 == 0);
   const int D = DT > 0 ? DT : c.num_dof;
   const int N = c.num_envs;
   const int B3 = c.num_bodies * 3;
+  const int F = c.num_feet;
   const int H = c.num_height_points;
   const int O = c.num_obs;
   const int OH = 12 + 3 * D;               // width of the observation head (:217-224)
+  const int HS = a.head_stride;
   const unsigned flags = c.flags;
-  const bool taps = c.rng_mode == LGK_RNG_TAPS;
   const bool heading_mode = flags & LGK_F_HEADING_COMMAND;
+  const int num_rows = a.num_rows;
 
-  extern __shared__ float smem[];
-  const int lane = threadIdx.x & 31;
-  const int wic = threadIdx.x >> 5;
-  const int gwarp = blockIdx.x * LGK_WARPS_PER_CTA + wic;
-  const int epw = a.epw;
-  const int env0 = gwarp * epw;
-  const int tile_envs = max(0, min(epw, N - env0));
-  float* wsm = smem + (size_t)wic * epw * a.row_floats;
+  extern __shared__ __align__(16) float sm[];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ unsigned s_is_last;
+  __shared__ int s_scan[2][LGK_WARPS_PER_CTA + 1];
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int wic = tid >> 5;
+  const int tile = blockIdx.x;
+  const int env0 = tile * TILE;
+  const int ne = min(TILE, N - env0);
+  const bool full = (ne == TILE) && a.tma_ok;
+  const bool has_levels = b.terrain_levels != nullptr;
 
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
   const int parity = (int)(csc & 1ull);
   const bool push_step = (flags & LGK_F_PUSH_ROBOTS) && (csc % (unsigned long long)c.push_interval == 0ull);
 
-  const bool active = lane < tile_envs;
+  // ---- load the tile ------------------------------------------------------------------------
+  if (full) {
+    if (tid == 0) {
+      mbar_init(&s_bar, 1);
+      const unsigned f4 = TILE * 4;   // bytes per float column of the tile
+      unsigned bytes = f4 * (13 + 2 * D + B3 + 3 * D + D + 4 + F + 2 + num_rows) + (has_levels ? f4 * 2 : 0);
+      mbar_expect_tx(&s_bar, bytes);
+      bulk_g2s(sm + L.root, b.root_states + (size_t)env0 * 13, f4 * 13, &s_bar);
+      bulk_g2s(sm + L.ep, b.episode_length_buf + env0, f4 * 2, &s_bar);
+      bulk_g2s(sm + L.cf, b.contact_forces + (size_t)env0 * B3, f4 * B3, &s_bar);
+      bulk_g2s(sm + L.cmd, b.commands + (size_t)env0 * 4, f4 * 4, &s_bar);
+      bulk_g2s(sm + L.dof, b.dof_state + (size_t)env0 * 2 * D, f4 * 2 * D, &s_bar);
+      bulk_g2s(sm + L.act, b.actions + (size_t)env0 * D, f4 * D, &s_bar);
+      bulk_g2s(sm + L.lact, b.last_actions + (size_t)env0 * D, f4 * D, &s_bar);
+      bulk_g2s(sm + L.tq, b.torques + (size_t)env0 * D, f4 * D, &s_bar);
+      bulk_g2s(sm + L.ldv, b.last_dof_vel + (size_t)env0 * D, f4 * D, &s_bar);
+      bulk_g2s(sm + L.fat, b.feet_air_time + (size_t)env0 * F, f4 * F, &s_bar);
+      if (has_levels) bulk_g2s(sm + L.lvl, b.terrain_levels + env0, f4 * 2, &s_bar);
+      for (int r = 0; r < num_rows; ++r)
+        bulk_g2s(sm + L.sums + r * TILE, b.episode_sums + (size_t)r * N + env0, f4, &s_bar);
+    }
+    __syncthreads();          // barrier initialised before anyone polls it
+    mbar_wait(&s_bar, 0);
+  } else {
+    auto ld = [&](int off, const void* g, int words_per_env) {
+      const unsigned* src = reinterpret_cast<const unsigned*>(g);
+      unsigned* dst = reinterpret_cast<unsigned*>(sm + off);
+      for (int i = tid; i < ne * words_per_env; i += LGK_CTA_THREADS) dst[i] = src[i];
+    };
+    ld(L.root, b.root_states + (size_t)env0 * 13, 13);
+    ld(L.ep, b.episode_length_buf + env0, 2);
+    ld(L.cf, b.contact_forces + (size_t)env0 * B3, B3);
+    ld(L.cmd, b.commands + (size_t)env0 * 4, 4);
+    ld(L.dof, b.dof_state + (size_t)env0 * 2 * D, 2 * D);
+    ld(L.act, b.actions + (size_t)env0 * D, D);
+    ld(L.lact, b.last_actions + (size_t)env0 * D, D);
+    ld(L.tq, b.torques + (size_t)env0 * D, D);
+    ld(L.ldv, b.last_dof_vel + (size_t)env0 * D, D);
+    ld(L.fat, b.feet_air_time + (size_t)env0 * F, F);
+    if (has_levels) ld(L.lvl, b.terrain_levels + env0, 2);
+    for (int i = tid; i < num_rows * TILE; i += LGK_CTA_THREADS) {
+      const int r = i / TILE, e = i % TILE;
+      if (e < ne) sm[L.sums + i] = b.episode_sums[(size_t)r * N + env0 + e];
+    }
+    __syncthreads();
+  }
+
+  const bool active = lane < ne;
   const int env = env0 + (active ? lane : 0);
   const unsigned env_global = (unsigned)(c.env_id_offset + env);
+  float* scr = sm + L.scr;
+  float* head_row = sm + L.head + lane * HS;
+  const float* cf_row = sm + L.cf + lane * B3;
+  const long long ep_in = reinterpret_cast<const long long*>(sm + L.ep)[lane];
 
-  // ---- stage this warp's contact rows (contiguous, coalesced) --------------------------
-  {
-    const int total = tile_envs * B3;
-    const float* src = b.contact_forces + (size_t)env0 * B3;
-    if (((B3 * epw) & 3) == 0 && tile_envs == epw) {
-      const float4* s4 = reinterpret_cast<const float4*>(src);
-      float4* d4 = reinterpret_cast<float4*>(wsm);
-      for (int i = lane; i < (total >> 2); i += 32) d4[i] = __ldg(s4 + i);
-    } else {
-      for (int i = lane; i < total; i += 32) wsm[i] = __ldg(src + i);
-    }
+  // the reset decision (:143-148) is cheap: every stage-1 warp forms it for its own lane
+  bool time_out = false, reset = false;
+  if (active) {
+    time_out = (ep_in + 1) > c.max_episode_length;
+    reset = term_contact(c, cf_row) || time_out;
   }
-  __syncwarp();
 
-  // per-env values that outlive S0
-  float root_x = 0.f, root_y = 0.f, z_pre = 0.f, zobs = 0.f, yaw_z = 0.f, yaw_w = 1.f;
+  // values W0 keeps in registers from stage 1 to stage 3
   float blv[3] = {0, 0, 0}, bav[3] = {0, 0, 0}, grav[3] = {0, 0, 0};
   float4 cmd_rew = make_float4(0, 0, 0, 0);
-  ContactSummary cs = {};
-  DofAcc acc = {};
-  float r_air = 0.f;
-  bool reset = false, time_out = false, resample_cb = false;
-  float head[12];   // first 12 obs columns; the 3D joint columns go straight to shared memory
-  int level_contrib = 0;
+  float z_pre = 0.f;
+  unsigned reset_mask = 0u;
 
-  if (active) cs = summarise_contacts(c, wsm + lane * B3);
-  __syncwarp();   // every lane is done with the contact rows: the region is reused for obs heads
-  float* head_row = wsm + lane * a.head_stride;
-
-  if (active) {
-    // ---- prologue (:118-125) ------------------------------------------------------------
-    float root[13];
-    const float* rp = b.root_states + (size_t)env * 13;
+  // =========================================== stage 1 ===========================================
+  if (wic == 0) {
+    // ---- W0: base state, commands, termination, root reset, per-env outputs ----------------------
+    bool resample_cb = false;
+    int level_contrib = 0;
+    if (active) {
+      float root[13];
+      const float* rp = sm + L.root + lane * 13;
 #pragma unroll
-    for (int i = 0; i < 13; ++i) root[i] = rp[i];
-    long long ep = b.episode_length_buf[env] + 1;
-    const float q[4] = {root[3], root[4], root[5], root[6]};
-    quat_rotate_inverse(q, root[7], root[8], root[9], blv);
-    quat_rotate_inverse(q, root[10], root[11], root[12], bav);
-    quat_rotate_inverse(q, 0.f, 0.f, -1.f, grav);
-    float4 cmd = *reinterpret_cast<const float4*>(b.commands + (size_t)env * 4);
-    const float* cr = b.command_ranges;
+      for (int i = 0; i < 13; ++i) root[i] = rp[i];
+      long long ep = ep_in + 1;                                   // (:118)
+      const float q[4] = {root[3], root[4], root[5], root[6]};
+      quat_rotate_inverse(q, root[7], root[8], root[9], blv);     // (:123-125)
+      quat_rotate_inverse(q, root[10], root[11], root[12], bav);
+      quat_rotate_inverse(q, 0.f, 0.f, -1.f, grav);
+      float4 cmd = *reinterpret_cast<const float4*>(sm + L.cmd + lane * 4);
+      const float* cr = b.command_ranges;
 
-    // ---- _post_physics_step_callback (:337-352) -----------------------------------------
-    resample_cb = (ep % c.resample_interval) == 0;
-    if (resample_cb) {
-      float u0, u1, u2;
-      if (taps) {
-        const float* t = b.tap_cmd_callback + (size_t)env * 3;
-        u0 = t[0]; u1 = t[1]; u2 = t[2];
+      // ---- _post_physics_step_callback (:337-352) ---------------------------------------------
+      resample_cb = (ep % c.resample_interval) == 0;
+      if (resample_cb) {
+        float u0, u1, u2;
+        if (TAPS) {
+          const float* t = b.tap_cmd_callback + (size_t)env * 3;
+          u0 = t[0]; u1 = t[1]; u2 = t[2];
+        } else {
+          const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_CMD_CB);
+          u0 = u01(r.x); u1 = u01(r.y); u2 = u01(r.z);
+        }
+        resample_command(cmd, cr, heading_mode, u0, u1, u2);
+      }
+      if (heading_mode) {
+        float fwd[3];
+        quat_apply(q, 1.f, 0.f, 0.f, fwd);
+        const float heading = atan2f(fwd[1], fwd[0]);
+        cmd.z = clampf(0.5f * wrap_to_pi(cmd.w - heading), -1.f, 1.f);
+      }
+      cmd_rew = cmd;
+      // yaw-only quaternion of quat_apply_yaw (utils/math.py:38-42): normalize([0,0,qz,qw]);
+      // x.norm(p=2): separately rounded squares, correctly rounded sqrt (same on torch CPU / CUDA)
+      float yaw_z, yaw_w;
+      {
+        const float n = fmaxf(sqrtf(add_rn(mul_rn(q[2], q[2]), mul_rn(q[3], q[3]))), 1e-9f);
+        yaw_z = __fdiv_rn(q[2], n);
+        yaw_w = __fdiv_rn(q[3], n);
+      }
+      z_pre = root[2];
+      const float root_x = root[0], root_y = root[1];
+      float rvel[6] = {root[7], root[8], root[9], root[10], root[11], root[12]};
+      if (push_step) {   // _push_robots (:436-441): every env, after the body-frame velocities
+        float u0, u1;
+        if (TAPS) { u0 = b.tap_push[(size_t)env * 2]; u1 = b.tap_push[(size_t)env * 2 + 1]; }
+        else { const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_PUSH); u0 = u01(r.x); u1 = u01(r.y); }
+        const float range = 2.0f * c.max_push_vel_xy;
+        rvel[0] = rand_affine(range, -c.max_push_vel_xy, u0);
+        rvel[1] = rand_affine(range, -c.max_push_vel_xy, u1);
+      }
+
+      // ---- terrain curriculum + new origin for reset envs (:443-463) ---------------------------
+      float origin[3] = {0, 0, 0};
+      long long level = has_levels ? reinterpret_cast<const long long*>(sm + L.lvl)[lane] : 0;
+      if (reset) {
+        const float* op = b.env_origins + (size_t)env * 3;
+        origin[0] = op[0]; origin[1] = op[1]; origin[2] = op[2];
+        if ((flags & LGK_F_TERRAIN_CURRICULUM) && (flags & LGK_F_INIT_DONE) && has_levels) {
+          const float dx = root[0] - origin[0], dy = root[1] - origin[1];
+          const float dist = sqrtf(fmaf(dy, dy, dx * dx));
+          const bool up = dist > c.half_env_length;
+          const float cn = sqrtf(fmaf(cmd.y, cmd.y, cmd.x * cmd.x));
+          const bool down = (dist < mul_rn(mul_rn(cn, c.max_episode_length_s), 0.5f)) && !up;
+          level += (up ? 1 : 0) - (down ? 1 : 0);
+          if (level >= c.max_terrain_level) {
+            if (TAPS) level = b.tap_level[env];
+            else level = (long long)(lgk_philox(c.seed, csc, env_global, LGK_SITE_LEVEL).x % (unsigned)c.max_terrain_level);
+          } else if (level < 0) {
+            level = 0;
+          }
+          b.terrain_levels[env] = level;
+          const float* to = b.terrain_origins + ((size_t)level * c.num_terrain_types + (size_t)b.terrain_types[env]) * 3;
+          origin[0] = to[0]; origin[1] = to[1]; origin[2] = to[2];
+          float* ow = b.env_origins + (size_t)env * 3;
+          ow[0] = origin[0]; ow[1] = origin[1]; ow[2] = origin[2];
+        }
+      }
+      level_contrib = (int)level;
+
+      // ---- reset of the root state and the command (:414-434, :173) ---------------------------
+      if (reset) {
+        float u[8];
+        if (TAPS) {
+          u[0] = b.tap_root_xy[(size_t)env * 2]; u[1] = b.tap_root_xy[(size_t)env * 2 + 1];
+          for (int i = 0; i < 6; ++i) u[2 + i] = b.tap_root_vel[(size_t)env * 6 + i];
+        } else {
+          const uint4 r0 = lgk_philox(c.seed, csc, env_global, LGK_SITE_ROOT);
+          const uint4 r1 = lgk_philox(c.seed, csc, env_global, LGK_SITE_ROOT + 1);
+          u[0] = u01(r0.x); u[1] = u01(r0.y); u[2] = u01(r0.z); u[3] = u01(r0.w);
+          u[4] = u01(r1.x); u[5] = u01(r1.y); u[6] = u01(r1.z); u[7] = u01(r1.w);
+        }
+#pragma unroll
+        for (int i = 0; i < 13; ++i) root[i] = c.base_init_state[i];
+        root[0] = add_rn(root[0], origin[0]);
+        root[1] = add_rn(root[1], origin[1]);
+        root[2] = add_rn(root[2], origin[2]);
+        if (flags & LGK_F_CUSTOM_ORIGINS) {   // xy within 1 m of the platform centre (:425)
+          root[0] = add_rn(root[0], rand_affine(2.0f, -1.0f, u[0]));
+          root[1] = add_rn(root[1], rand_affine(2.0f, -1.0f, u[1]));
+        }
+#pragma unroll
+        for (int i = 0; i < 6; ++i) { rvel[i] = rand_affine(1.0f, -0.5f, u[2 + i]); root[7 + i] = rvel[i]; }
+        float* rw = b.root_states + (size_t)env * 13;
+#pragma unroll
+        for (int i = 0; i < 13; ++i) rw[i] = root[i];
+        float c0, c1, c2;
+        if (TAPS) { const float* t = b.tap_cmd_reset + (size_t)env * 3; c0 = t[0]; c1 = t[1]; c2 = t[2]; }
+        else { const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_CMD_RESET); c0 = u01(r.x); c1 = u01(r.y); c2 = u01(r.z); }
+        resample_command(cmd, cr, heading_mode, c0, c1, c2);
+        ep = 0;
+      } else if (push_step) {
+        float* rw = b.root_states + (size_t)env * 13;
+        rw[7] = rvel[0];
+        rw[8] = rvel[1];
+      }
+
+      // ---- per-env stores ---------------------------------------------------------------------------
+      b.episode_length_buf[env] = ep;
+      b.reset_buf[env] = reset ? 1 : 0;
+      b.time_out_buf[env] = time_out ? 1 : 0;
+      *reinterpret_cast<float4*>(b.commands + (size_t)env * 4) = cmd;
+      {
+        float* p = b.base_lin_vel + (size_t)env * 3; p[0] = blv[0]; p[1] = blv[1]; p[2] = blv[2];
+        p = b.base_ang_vel + (size_t)env * 3;        p[0] = bav[0]; p[1] = bav[1]; p[2] = bav[2];
+        p = b.projected_gravity + (size_t)env * 3;   p[0] = grav[0]; p[1] = grav[1]; p[2] = grav[2];
+        float2* lr = reinterpret_cast<float2*>(b.last_root_vel + (size_t)env * 6);   // (:138)
+        lr[0] = make_float2(rvel[0], rvel[1]); lr[1] = make_float2(rvel[2], rvel[3]); lr[2] = make_float2(rvel[4], rvel[5]);
+      }
+      // obs head columns 0..11 (:217-220), post-reset commands
+      head_row[0] = blv[0] * c.obs_scale_lin_vel; head_row[1] = blv[1] * c.obs_scale_lin_vel; head_row[2] = blv[2] * c.obs_scale_lin_vel;
+      head_row[3] = bav[0] * c.obs_scale_ang_vel; head_row[4] = bav[1] * c.obs_scale_ang_vel; head_row[5] = bav[2] * c.obs_scale_ang_vel;
+      head_row[6] = grav[0]; head_row[7] = grav[1]; head_row[8] = grav[2];
+      head_row[9] = cmd.x * c.commands_scale[0]; head_row[10] = cmd.y * c.commands_scale[1]; head_row[11] = cmd.z * c.commands_scale[2];
+      // scalars of the height scan: pre-reset position / yaw, post-reset z for the observation (:227)
+      float4* es = reinterpret_cast<float4*>(scr + SC_ES * TILE + lane * 8);
+      es[0] = make_float4(root_x, root_y, z_pre, sub_rn(root[2], 0.5f));
+      es[1] = make_float4(yaw_z, yaw_w, 0.f, 0.f);
+    }
+    // ---- tile bookkeeping: bitmasks for the ordered compaction, level sum ----------------------
+    reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
+    const unsigned resample_mask = __ballot_sync(LGK_FULL_MASK, active && resample_cb);
+    unsigned* mask_base = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + LGK_WS_HEADER_BYTES);
+    if (lane == 0) {
+      mask_base[tile] = reset_mask;
+      mask_base[lgk_max_warps(N) + tile] = resample_mask;
+    }
+    if ((flags & LGK_F_TERRAIN_CURRICULUM) && has_levels) {
+      const int s = warp_sum_int(active ? level_contrib : 0);
+      if (lane == 0 && s != 0) atomicAdd(&ws->level_sum[parity], s);
+    }
+  }
+  else if (wic == 1 || wic == 2) {
+    // ---- W1 / W2: joints (:874-916, :956-966 sums; :399-408 reset; obs head; last_dof_vel) -------
+    DofAcc acc;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) acc.v[i] = 0.f;
+    if (active) {
+      const float inv_dt = 1.0f / c.dt;
+      unsigned hip_mask = 0u;
+      for (int h = 0; h < c.num_hip; ++h) hip_mask |= 1u << c.hip_idx[h];
+      const float* act_p = sm + L.act + lane * D;
+      const float* lact_p = sm + L.lact + lane * D;
+      const float* tq_p = sm + L.tq + lane * D;
+      float* ldv_p = sm + L.ldv + lane * D;            // in: last_dof_vel, out: dof_vel (staged for the store)
+      const float* dof_p = sm + L.dof + lane * 2 * D;
+      float* dof_g = b.dof_state + (size_t)env * D * 2;
+      if constexpr (VEC) {
+        constexpr int NC = DT / 4, NC1 = (NC + 1) / 2;
+        const int cb = (wic == 1) ? 0 : NC1, ce = (wic == 1) ? NC1 : NC;
+#pragma unroll
+        for (int ch = 0; ch < NC; ++ch) {
+          if (ch < cb || ch >= ce) continue;
+          const int d0 = ch * 4;
+          const float4 a4 = *reinterpret_cast<const float4*>(act_p + d0);
+          const float4 la4 = *reinterpret_cast<const float4*>(lact_p + d0);
+          const float4 tq4 = *reinterpret_cast<const float4*>(tq_p + d0);
+          const float4 ldv4 = *reinterpret_cast<const float4*>(ldv_p + d0);
+          float4 s0 = *reinterpret_cast<const float4*>(dof_p + 2 * d0);       // p0 v0 p1 v1
+          float4 s1 = *reinterpret_cast<const float4*>(dof_p + 2 * d0 + 4);   // p2 v2 p3 v3
+          float u[4] = {0, 0, 0, 0};
+          if (reset) {
+            if (TAPS) {
+              const float* t = b.tap_dof + (size_t)env * D + d0;
+              u[0] = t[0]; u[1] = t[1]; u[2] = t[2]; u[3] = t[3];
+            } else {
+              const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_DOF + ch);
+              u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
+            }
+          }
+          joint_update(c, d0 + 0, D, hip_mask, reset, inv_dt, a4.x, la4.x, tq4.x, ldv4.x, s0.x, s0.y, u[0], acc, head_row);
+          joint_update(c, d0 + 1, D, hip_mask, reset, inv_dt, a4.y, la4.y, tq4.y, ldv4.y, s0.z, s0.w, u[1], acc, head_row);
+          joint_update(c, d0 + 2, D, hip_mask, reset, inv_dt, a4.z, la4.z, tq4.z, ldv4.z, s1.x, s1.y, u[2], acc, head_row);
+          joint_update(c, d0 + 3, D, hip_mask, reset, inv_dt, a4.w, la4.w, tq4.w, ldv4.w, s1.z, s1.w, u[3], acc, head_row);
+          *reinterpret_cast<float4*>(ldv_p + d0) = make_float4(s0.y, s0.w, s1.y, s1.w);   // last_dof_vel = dof_vel (:137)
+          if (reset) {
+            *reinterpret_cast<float4*>(dof_g + 2 * d0) = s0;
+            *reinterpret_cast<float4*>(dof_g + 2 * d0 + 4) = s1;
+          }
+        }
       } else {
-        const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_CMD_CB);
-        u0 = u01(r.x); u1 = u01(r.y); u2 = u01(r.z);
-      }
-      resample_command(cmd, cr, heading_mode, u0, u1, u2);
-    }
-    if (heading_mode) {
-      float fwd[3];
-      quat_apply(q, 1.f, 0.f, 0.f, fwd);
-      const float heading = atan2f(fwd[1], fwd[0]);
-      cmd.z = clampf(0.5f * wrap_to_pi(cmd.w - heading), -1.f, 1.f);
-    }
-    cmd_rew = cmd;
-    // yaw-only quaternion of quat_apply_yaw (utils/math.py:38-42): normalize([0,0,qz,qw])
-    {
-      // x.norm(p=2, dim=-1): separately rounded squares, correctly rounded sqrt (same on torch CPU/CUDA)
-      const float n = fmaxf(sqrtf(add_rn(mul_rn(q[2], q[2]), mul_rn(q[3], q[3]))), 1e-9f);
-      yaw_z = __fdiv_rn(q[2], n);
-      yaw_w = __fdiv_rn(q[3], n);
-    }
-    root_x = root[0]; root_y = root[1]; z_pre = root[2];
-    float rvel[6] = {root[7], root[8], root[9], root[10], root[11], root[12]};
-    if (push_step) {   // _push_robots (:436-441): every env, after the body-frame velocities
-      float u0, u1;
-      if (taps) { u0 = b.tap_push[(size_t)env * 2]; u1 = b.tap_push[(size_t)env * 2 + 1]; }
-      else { const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_PUSH); u0 = u01(r.x); u1 = u01(r.y); }
-      const float range = 2.0f * c.max_push_vel_xy;
-      rvel[0] = rand_affine(range, -c.max_push_vel_xy, u0);
-      rvel[1] = rand_affine(range, -c.max_push_vel_xy, u1);
-    }
-
-    // ---- check_termination (:143-148) ---------------------------------------------------
-    time_out = ep > c.max_episode_length;
-    reset = cs.term || time_out;
-
-    // ---- terrain curriculum + new origin for reset envs (:443-463) --------------------
-    float origin[3] = {0, 0, 0};
-    const bool has_levels = b.terrain_levels != nullptr;
-    long long level = has_levels ? b.terrain_levels[env] : 0;
-    if (reset) {
-      const float* op = b.env_origins + (size_t)env * 3;
-      origin[0] = op[0]; origin[1] = op[1]; origin[2] = op[2];
-      if ((flags & LGK_F_TERRAIN_CURRICULUM) && (flags & LGK_F_INIT_DONE) && has_levels) {
-        const float dx = root[0] - origin[0], dy = root[1] - origin[1];
-        const float dist = sqrtf(fmaf(dy, dy, dx * dx));
-        const bool up = dist > c.half_env_length;
-        const float cn = sqrtf(fmaf(cmd.y, cmd.y, cmd.x * cmd.x));
-        const bool down = (dist < mul_rn(mul_rn(cn, c.max_episode_length_s), 0.5f)) && !up;
-        level += (up ? 1 : 0) - (down ? 1 : 0);
-        if (level >= c.max_terrain_level) {
-          if (taps) level = b.tap_level[env];
-          else level = (long long)(lgk_philox(c.seed, csc, env_global, LGK_SITE_LEVEL).x % (unsigned)c.max_terrain_level);
-        } else if (level < 0) {
-          level = 0;
+        const int half = (D + 1) / 2;
+        const int db = (wic == 1) ? 0 : half, de = (wic == 1) ? half : D;
+        for (int d = db; d < de; ++d) {
+          const float av = act_p[d], lav = lact_p[d], tqv = tq_p[d], ldvv = ldv_p[d];
+          float p = dof_p[2 * d], v = dof_p[2 * d + 1];
+          float u = 0.f;
+          if (reset) {
+            if (TAPS) u = b.tap_dof[(size_t)env * D + d];
+            else {
+              const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_DOF + (d >> 2));
+              const unsigned rr[4] = {r.x, r.y, r.z, r.w};
+              u = u01(rr[d & 3]);
+            }
+          }
+          joint_update(c, d, D, hip_mask, reset, inv_dt, av, lav, tqv, ldvv, p, v, u, acc, head_row);
+          ldv_p[d] = v;
+          if (reset) { dof_g[2 * d] = p; dof_g[2 * d + 1] = v; }
         }
-        b.terrain_levels[env] = level;
-        const float* to = b.terrain_origins + ((size_t)level * c.num_terrain_types + (size_t)b.terrain_types[env]) * 3;
-        origin[0] = to[0]; origin[1] = to[1]; origin[2] = to[2];
-        float* ow = b.env_origins + (size_t)env * 3;
-        ow[0] = origin[0]; ow[1] = origin[1]; ow[2] = origin[2];
       }
     }
-    level_contrib = (int)level;
-
-    // ---- joints: reward sums, reset values, obs head, last_* (:176-177,:399-408,:136-137) --
-    float feet_air[LGK_MAX_FEET];
-    const float inv_dt = 1.0f / c.dt;
-    const float* act_p = b.actions + (size_t)env * D;
-    const float* lact_p = b.last_actions + (size_t)env * D;
-    const float* tq_p = b.torques + (size_t)env * D;
-    const float* ldv_p = b.last_dof_vel + (size_t)env * D;
-    float* dof_p = b.dof_state + (size_t)env * D * 2;
-    float* lact_w = b.last_actions + (size_t)env * D;
-    float* ldv_w = b.last_dof_vel + (size_t)env * D;
-
-    unsigned hip_mask = 0u;
-    for (int h = 0; h < c.num_hip; ++h) hip_mask |= 1u << c.hip_idx[h];
-    auto joint = [&](int d, float av, float lav, float tqv, float ldvv, float& p, float& v, float u) {
-      // rewards see the pre-reset joint state
-      acc.tq2 = fmaf(tqv, tqv, acc.tq2);
-      const float pw = tqv * v;
-      acc.energy = fmaf(pw, pw, acc.energy);
-      acc.qd2 = fmaf(v, v, acc.qd2);
-      const float ja = (ldvv - v) * inv_dt;
-      acc.acc2 = fmaf(ja, ja, acc.acc2);
-      const float da = lav - av;
-      acc.arate = fmaf(da, da, acc.arate);
-      acc.poslim += -fminf(p - c.dof_pos_lo[d], 0.f) + fmaxf(p - c.dof_pos_hi[d], 0.f);
-      acc.vellim += clampf(fabsf(v) - c.dof_vel_limits[d] * c.soft_dof_vel_limit, 0.f, 1.f);
-      acc.tqlim += fmaxf(fabsf(tqv) - c.torque_limits[d] * c.soft_torque_limit, 0.f);
-      const float dev = fabsf(p - c.default_dof_pos[d]);
-      acc.stand += dev;
-      if ((hip_mask >> d) & 1u) acc.hip += dev;
-      if (reset) {   // _reset_dofs: default * U(0.5, 1.5), zero velocity
-        p = mul_rn(c.default_dof_pos[d], rand_affine(1.0f, 0.5f, u));
-        v = 0.f;
-      }
-      head_row[12 + d] = (p - c.default_dof_pos[d]) * c.obs_scale_dof_pos;
-      head_row[12 + D + d] = v * c.obs_scale_dof_vel;
-      head_row[12 + 2 * D + d] = av;
-    };
-
-    if constexpr (VEC) {
+    float* jp = scr + ((wic == 1) ? SC_J1 : SC_J2) * TILE + lane;
 #pragma unroll
-      for (int d0 = 0; d0 < DT; d0 += 4) {
-        const float4 a4 = __ldg(reinterpret_cast<const float4*>(act_p + d0));
-        const float4 la4 = *reinterpret_cast<const float4*>(lact_p + d0);
-        const float4 tq4 = __ldg(reinterpret_cast<const float4*>(tq_p + d0));
-        const float4 ldv4 = *reinterpret_cast<const float4*>(ldv_p + d0);
-        float4 s0 = *reinterpret_cast<const float4*>(dof_p + 2 * d0);       // p0 v0 p1 v1
-        float4 s1 = *reinterpret_cast<const float4*>(dof_p + 2 * d0 + 4);   // p2 v2 p3 v3
-        float u[4] = {0, 0, 0, 0};
-        if (reset) {
-          if (taps) {
-            const float* t = b.tap_dof + (size_t)env * D + d0;
-            u[0] = t[0]; u[1] = t[1]; u[2] = t[2]; u[3] = t[3];
-          } else {
-            const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_DOF + (d0 >> 2));
-            u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
-          }
-        }
-        joint(d0 + 0, a4.x, la4.x, tq4.x, ldv4.x, s0.x, s0.y, u[0]);
-        joint(d0 + 1, a4.y, la4.y, tq4.y, ldv4.y, s0.z, s0.w, u[1]);
-        joint(d0 + 2, a4.z, la4.z, tq4.z, ldv4.z, s1.x, s1.y, u[2]);
-        joint(d0 + 3, a4.w, la4.w, tq4.w, ldv4.w, s1.z, s1.w, u[3]);
-        *reinterpret_cast<float4*>(lact_w + d0) = a4;                              // last_actions = actions
-        *reinterpret_cast<float4*>(ldv_w + d0) = make_float4(s0.y, s0.w, s1.y, s1.w);  // last_dof_vel = dof_vel
-        if (reset) {
-          *reinterpret_cast<float4*>(dof_p + 2 * d0) = s0;
-          *reinterpret_cast<float4*>(dof_p + 2 * d0 + 4) = s1;
-        }
+    for (int i = 0; i < 10; ++i) jp[i * TILE] = acc.v[i];
+  } else {
+    // ---- W3: contacts (:895-897, :951-962, cassie.py:43-46) and feet air time (:941-949) ---------
+    float collisions = 0.f, ffp = 0.f, r_air = 0.f;
+    bool stumble = false;
+    int nofly = 0;
+    if (active) {
+      for (int p = 0; p < c.num_pen; ++p) {
+        const float* f = cf_row + 3 * c.pen_idx[p];
+        collisions += (norm3(f[0], f[1], f[2]) > 0.1f) ? 1.f : 0.f;
       }
-    } else {
-      for (int d = 0; d < D; ++d) {
-        const float av = act_p[d], lav = lact_p[d], tqv = tq_p[d], ldvv = ldv_p[d];
-        float p = dof_p[2 * d], v = dof_p[2 * d + 1];
-        float u = 0.f;
-        if (reset) {
-          if (taps) u = b.tap_dof[(size_t)env * D + d];
-          else {
-            const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_DOF + (d >> 2));
-            const unsigned rr[4] = {r.x, r.y, r.z, r.w};
-            u = u01(rr[d & 3]);
-          }
-        }
-        joint(d, av, lav, tqv, ldvv, p, v, u);
-        lact_w[d] = av;
-        ldv_w[d] = v;
-        if (reset) { dof_p[2 * d] = p; dof_p[2 * d + 1] = v; }
-      }
-    }
-
-    // ---- feet_air_time reward state (:941-949); only advanced when the term is active -------
-    bool air_active = false;
-    for (int i = 0; i < c.num_rewards; ++i) air_active |= (c.rewards[i].term == LGK_REW_FEET_AIR_TIME);
-    {
-      const int F = c.num_feet;
-      float* fa = b.feet_air_time + (size_t)env * F;
-      const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
+      const float* fa_in = sm + L.fat + lane * F;
+      float* fa_out = b.feet_air_time + (size_t)env * F;
       for (int k = 0; k < F; ++k) {
-        float t = fa[k];
-        if (air_active) {
-          const bool contact = (cs.contact_bits >> k) & 1u;
+        const float* f = cf_row + 3 * c.feet_idx[k];
+        const float fx = f[0], fy = f[1], fz = f[2];
+        const bool contact = fz > 1.0f;
+        nofly += (fz > 0.1f) ? 1 : 0;
+        stumble |= sqrtf(fmaf(fy, fy, fx * fx)) > 5.0f * fabsf(fz);
+        ffp += fmaxf(norm3(fx, fy, fz) - c.max_contact_force, 0.f);
+        float t = fa_in[k];
+        if (a.air_active) {   // the state only advances inside _reward_feet_air_time
           const bool first = (t > 0.f) && contact;
           t = add_rn(t, c.dt);
           r_air += first ? (t - 0.5f) : 0.f;
           if (contact) t = 0.f;
         }
-        feet_air[k] = reset ? 0.f : t;
+        if (a.air_active || reset) fa_out[k] = reset ? 0.f : t;   // zeroed on reset (:178)
       }
-      r_air *= (cn > 0.1f) ? 1.f : 0.f;
-      if (air_active || reset)
-        for (int k = 0; k < F; ++k) fa[k] = feet_air[k];
     }
-
-    // ---- reset_idx for this env (:150-193) --------------------------------------------------
-    if (reset) {
-      float u[8];
-      if (taps) {
-        u[0] = b.tap_root_xy[(size_t)env * 2]; u[1] = b.tap_root_xy[(size_t)env * 2 + 1];
-        for (int i = 0; i < 6; ++i) u[2 + i] = b.tap_root_vel[(size_t)env * 6 + i];
-      } else {
-        const uint4 r0 = lgk_philox(c.seed, csc, env_global, LGK_SITE_ROOT);
-        const uint4 r1 = lgk_philox(c.seed, csc, env_global, LGK_SITE_ROOT + 1);
-        u[0] = u01(r0.x); u[1] = u01(r0.y); u[2] = u01(r0.z); u[3] = u01(r0.w);
-        u[4] = u01(r1.x); u[5] = u01(r1.y); u[6] = u01(r1.z); u[7] = u01(r1.w);
-      }
-#pragma unroll
-      for (int i = 0; i < 13; ++i) root[i] = c.base_init_state[i];
-      root[0] = add_rn(root[0], origin[0]);
-      root[1] = add_rn(root[1], origin[1]);
-      root[2] = add_rn(root[2], origin[2]);
-      if (flags & LGK_F_CUSTOM_ORIGINS) {   // xy within 1 m of the platform centre (:425)
-        root[0] = add_rn(root[0], rand_affine(2.0f, -1.0f, u[0]));
-        root[1] = add_rn(root[1], rand_affine(2.0f, -1.0f, u[1]));
-      }
-#pragma unroll
-      for (int i = 0; i < 6; ++i) { rvel[i] = rand_affine(1.0f, -0.5f, u[2 + i]); root[7 + i] = rvel[i]; }
-      float* rw = b.root_states + (size_t)env * 13;
-#pragma unroll
-      for (int i = 0; i < 13; ++i) rw[i] = root[i];
-      // commands for the new episode (:173)
-      float c0, c1, c2;
-      if (taps) { const float* t = b.tap_cmd_reset + (size_t)env * 3; c0 = t[0]; c1 = t[1]; c2 = t[2]; }
-      else { const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_CMD_RESET); c0 = u01(r.x); c1 = u01(r.y); c2 = u01(r.z); }
-      resample_command(cmd, cr, heading_mode, c0, c1, c2);
-      ep = 0;
-    } else if (push_step) {
-      float* rw = b.root_states + (size_t)env * 13;
-      rw[7] = rvel[0];
-      rw[8] = rvel[1];
-    }
-    zobs = sub_rn(root[2], 0.5f);   // root z after a possible reset, minus 0.5 (:227)
-
-    // ---- per-env stores -------------------------------------------------------------------------
-    b.episode_length_buf[env] = ep;
-    b.reset_buf[env] = reset ? 1 : 0;
-    b.time_out_buf[env] = time_out ? 1 : 0;
-    *reinterpret_cast<float4*>(b.commands + (size_t)env * 4) = cmd;
-    {
-      float* p = b.base_lin_vel + (size_t)env * 3; p[0] = blv[0]; p[1] = blv[1]; p[2] = blv[2];
-      p = b.base_ang_vel + (size_t)env * 3;        p[0] = bav[0]; p[1] = bav[1]; p[2] = bav[2];
-      p = b.projected_gravity + (size_t)env * 3;   p[0] = grav[0]; p[1] = grav[1]; p[2] = grav[2];
-      float2* lr = reinterpret_cast<float2*>(b.last_root_vel + (size_t)env * 6);   // (:138)
-      lr[0] = make_float2(rvel[0], rvel[1]); lr[1] = make_float2(rvel[2], rvel[3]); lr[2] = make_float2(rvel[4], rvel[5]);
-    }
-    // obs head columns 0..11 (:217-220), post-reset commands
-    head[0] = blv[0] * c.obs_scale_lin_vel; head[1] = blv[1] * c.obs_scale_lin_vel; head[2] = blv[2] * c.obs_scale_lin_vel;
-    head[3] = bav[0] * c.obs_scale_ang_vel; head[4] = bav[1] * c.obs_scale_ang_vel; head[5] = bav[2] * c.obs_scale_ang_vel;
-    head[6] = grav[0]; head[7] = grav[1]; head[8] = grav[2];
-    head[9] = cmd.x * c.commands_scale[0]; head[10] = cmd.y * c.commands_scale[1]; head[11] = cmd.z * c.commands_scale[2];
-#pragma unroll
-    for (int i = 0; i < 12; ++i) head_row[i] = head[i];
+    scr[SC_COLL * TILE + lane] = collisions;
+    scr[SC_FFP * TILE + lane] = ffp;
+    scr[SC_RAIR * TILE + lane] = r_air;       // masked by |cmd_xy| > 0.1 in stage 3
+    scr[SC_STUMBLE * TILE + lane] = stumble ? 1.f : 0.f;
+    scr[SC_NOFLY * TILE + lane] = (nofly == 1) ? 1.f : 0.f;
   }
-  __syncwarp();
+  __syncthreads();
 
-  // ---- warp-wide bookkeeping: bitmasks for the ordered compaction, level sum -------------------
-  const unsigned reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
-  const unsigned resample_mask = __ballot_sync(LGK_FULL_MASK, active && resample_cb);
-  unsigned* mask_base = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + LGK_WS_HEADER_BYTES);
-  const int max_warps = lgk_max_warps(N);
-  if (lane == 0 && gwarp < max_warps) {
-    mask_base[gwarp] = reset_mask;
-    mask_base[max_warps + gwarp] = resample_mask;
-  }
-  if ((flags & LGK_F_TERRAIN_CURRICULUM) && b.terrain_levels != nullptr) {
-    const int s = warp_sum_int(active ? level_contrib : 0);
-    if (lane == 0 && s != 0) atomicAdd(&ws->level_sum[parity], s);
-  }
-
-  // ---- phase A: observation row + height scan, one env at a time, lanes over columns ----------
-  float bh_sum = 0.f;   // sum_h (root_z - measured_height) of this lane's env (:871)
+  // =========================================== stage 2 ===========================================
+  // observation tile (aliases the contact / torque / last_actions rows, all consumed in stage 1)
+  float* obs_t = sm + L.obs;
   {
     const bool add_noise = flags & LGK_F_ADD_NOISE;
     const bool plane = flags & LGK_F_TERRAIN_PLANE;
-    const bool mul_rcp = c.index_math == LGK_INDEX_MUL_RCP;
     const float inv_hs = 1.0f / c.horizontal_scale;
     const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
-    // this lane's scan offsets (same for every env)
-    float px_l[8], py_l[8];
+    const float clip_obs = c.clip_obs;
+    // this lane's scan offsets and noise amplitudes (same for every env)
+    float px_l[8], py_l[8], ns_h[8];
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int h = it * 32 + lane;
       const bool ok = h < H;
       px_l[it] = ok ? __ldg(b.height_points_xy + 2 * h) : 0.f;
       py_l[it] = ok ? __ldg(b.height_points_xy + 2 * h + 1) : 0.f;
+      ns_h[it] = (ok && add_noise) ? __ldg(b.noise_scale_vec + OH + h) : 0.f;
     }
-    for (int e = 0; e < tile_envs; ++e) {
-      const int env_e = env0 + e;
-      const float rx = __shfl_sync(LGK_FULL_MASK, root_x, e);
-      const float ry = __shfl_sync(LGK_FULL_MASK, root_y, e);
-      const float rz = __shfl_sync(LGK_FULL_MASK, z_pre, e);
-      const float zo = __shfl_sync(LGK_FULL_MASK, zobs, e);
-      const float qz = __shfl_sync(LGK_FULL_MASK, yaw_z, e);
-      const float qw = __shfl_sync(LGK_FULL_MASK, yaw_w, e);
-      float* orow = b.obs_buf + (size_t)env_e * O;
-      const float* trow = taps ? b.tap_noise + (size_t)env_e * O : nullptr;
-      uint4 rnd = make_uint4(0, 0, 0, 0);
-      const unsigned eg = (unsigned)(c.env_id_offset + env_e);
-      auto noisy = [&](float v, int col, unsigned rbits) {
-        if (add_noise) {
-          const float u = taps ? __ldg(trow + col) : u01(rbits);
-          // obs += (2*rand - 1) * noise_scale_vec   (:231)
-          v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, u), 1.0f), __ldg(b.noise_scale_vec + col)));
-        }
-        return clampf(v, -c.clip_obs, c.clip_obs);   // step(): clip(obs, +-clip_observations) (:104)
-      };
-      if (add_noise && !taps) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + lane);
-      // head: columns 0..OH-1 (OH <= 64)
-      {
-        const float* hrow = wsm + e * a.head_stride;
-        if (lane < OH) orow[lane] = noisy(hrow[lane], lane, rnd.x);
-        if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], lane + 32, rnd.y);
+    const float ns_a = (add_noise && lane < OH) ? __ldg(b.noise_scale_vec + lane) : 0.f;
+    const float ns_b = (add_noise && lane + 32 < OH) ? __ldg(b.noise_scale_vec + lane + 32) : 0.f;
+    // obs = clip(v + (2*rand - 1) * noise_scale_vec, +-clip_observations)   (:231, :104)
+    auto noisy = [&](float v, const float* __restrict__ trow, int col, unsigned rbits, float ns) {
+      if (add_noise) {
+        if (TAPS) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
+        else v = fmaf(fmaf((float)(rbits >> 8), 1.1920928955078125e-07f, -1.0f), ns, v);   // 2 * u01 - 1
       }
-      // scan points: column OH + h
+      return clampf(v, -clip_obs, clip_obs);
+    };
+    const int e_end = min(wic * 8 + 8, ne);
+    for (int e = wic * 8; e < e_end; ++e) {
+      const int env_e = env0 + e;
+      const float4 es0 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8);
+      const float4 es1 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8 + 4);
+      const float rx = es0.x, ry = es0.y, rz = es0.z, zo = es0.w, qz = es1.x, qw = es1.y;
+      float* orow = obs_t + e * O;
+      const float* trow = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
+      const unsigned eg = (unsigned)(c.env_id_offset + env_e);
+      uint4 rnd = make_uint4(0, 0, 0, 0);
+      if (!TAPS && add_noise) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane);
+      {
+        const float* hrow = sm + L.head + e * HS;
+        if (lane < OH) orow[lane] = noisy(hrow[lane], trow, lane, rnd.x, ns_a);
+        if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], trow, lane + 32, rnd.y, ns_b);
+      }
       float part = 0.f;
       if (H > 0) {
         const float qz2 = mul_rn(qz, 2.0f);
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
           if (it * 32 >= H) break;
-          if (it == 2 && add_noise && !taps) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 32 + lane);
-          if (it == 6 && add_noise && !taps) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 64 + lane);
+          if (!TAPS && add_noise) {
+            if (it == 2) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
+            if (it == 6) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 2);
+          }
+          const int w = (it + 2) & 3;
+          const unsigned rbits = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
           const int h = it * 32 + lane;
-          const unsigned rbits = (it & 3) == 0 ? rnd.z : (it & 3) == 1 ? rnd.w : (it & 3) == 2 ? rnd.x : rnd.y;
           if (h < H) {
             float hgt = 0.f;
             if (!plane) {
@@ -485,8 +551,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
               wx = add_rn(add_rn(wx, rx), c.border_size);
               wy = add_rn(add_rn(wy, ry), c.border_size);
               // (points / horizontal_scale).long(): truncation toward zero (:842)
-              const float sx = mul_rcp ? mul_rn(wx, inv_hs) : __fdiv_rn(wx, c.horizontal_scale);
-              const float sy = mul_rcp ? mul_rn(wy, inv_hs) : __fdiv_rn(wy, c.horizontal_scale);
+              const float sx = MUL_RCP ? mul_rn(wx, inv_hs) : __fdiv_rn(wx, c.horizontal_scale);
+              const float sy = MUL_RCP ? mul_rn(wy, inv_hs) : __fdiv_rn(wy, c.horizontal_scale);
               int ix = __float2int_rz(sx), iy = __float2int_rz(sy);
               ix = min(max(ix, 0), max_px);
               iy = min(max(iy, 0), max_py);
@@ -496,130 +562,179 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
             if (b.measured_heights != nullptr) b.measured_heights[(size_t)env_e * H + h] = hgt;
             part += sub_rn(rz, hgt);
             const float v = clampf(sub_rn(zo, hgt), -1.f, 1.f) * c.obs_scale_height;
-            orow[OH + h] = noisy(v, OH + h, rbits);
+            orow[OH + h] = noisy(v, trow, OH + h, rbits, ns_h[it]);
           }
         }
       }
-      part = warp_sum(part);
-      if (lane == e) bh_sum = part;
+      if (a.bh_active) {   // sum_h (root_z - measured_height) for _reward_base_height (:871)
+        part = warp_sum(part);
+        if (lane == 0) scr[SC_BH * TILE + e] = part;
+      }
     }
+  }
+  fence_proxy_async_smem();   // obs tile / last_dof_vel rows -> visible to the bulk stores
+  __syncthreads();
+
+  // ---- tile outputs that do not depend on the rewards: issued by W1 while W0 runs stage 3 ---------
+  if (full) {
+    if (tid == 32) {
+      bulk_s2g(b.obs_buf + (size_t)env0 * O, obs_t, TILE * 4 * O);
+      bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, TILE * 4 * D);   // last_actions = actions (:136)
+      bulk_s2g(b.last_dof_vel + (size_t)env0 * D, sm + L.ldv, TILE * 4 * D);
+      bulk_commit();
+    }
+  } else if (wic > 0) {
+    const int t = tid - 32, nt = LGK_CTA_THREADS - 32;
+    float* og = b.obs_buf + (size_t)env0 * O;
+    for (int i = t; i < ne * O; i += nt) og[i] = obs_t[i];
+    float* la = b.last_actions + (size_t)env0 * D;
+    float* lv = b.last_dof_vel + (size_t)env0 * D;
+    for (int i = t; i < ne * D; i += nt) { la[i] = sm[L.act + i]; lv[i] = sm[L.ldv + i]; }
   }
 
-  // ---- S1: reward terms in the reference's order (:195-212), episode sums, statistics -----------
-  const bool any_reset = reset_mask != 0u;
-  const int num_rows = c.num_rewards + ((flags & LGK_F_HAS_TERMINATION) ? 1 : 0);
-  float rew = 0.f;
-  int ext_k = 0;
-  for (int i = 0; i < num_rows; ++i) {
-    float r = 0.f;
-    if (i < c.num_rewards) {
-      float v = 0.f;
-      const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
-      switch (c.rewards[i].term) {
-        case LGK_REW_ACTION_RATE: v = acc.arate; break;
-        case LGK_REW_ANG_VEL_XY: v = fmaf(bav[1], bav[1], bav[0] * bav[0]); break;
-        case LGK_REW_BASE_HEIGHT: {
-          const float bh = H > 0 ? bh_sum / (float)H : z_pre;
-          const float d = bh - c.base_height_target;
-          v = d * d;
-        } break;
-        case LGK_REW_COLLISION: v = cs.collisions; break;
-        case LGK_REW_DOF_ACC: v = acc.acc2; break;
-        case LGK_REW_DOF_POS_LIMITS: v = acc.poslim; break;
-        case LGK_REW_DOF_VEL: v = acc.qd2; break;
-        case LGK_REW_DOF_VEL_LIMITS: v = acc.vellim; break;
-        case LGK_REW_ENERGY: v = acc.energy; break;
-        case LGK_REW_FEET_AIR_TIME: v = r_air; break;
-        case LGK_REW_FEET_CONTACT_FORCES: v = cs.feet_force_pen; break;
-        case LGK_REW_HIP_MOTION: v = acc.hip; break;
-        case LGK_REW_LIN_VEL_Z: v = blv[2] * blv[2]; break;
-        case LGK_REW_NO_FLY: v = (cs.nofly_contacts == 1) ? 1.f : 0.f; break;
-        case LGK_REW_ORIENTATION: v = fmaf(grav[1], grav[1], grav[0] * grav[0]); break;
-        case LGK_REW_STAND_STILL: v = acc.stand * ((cn < 0.1f) ? 1.f : 0.f); break;
-        case LGK_REW_STUMBLE: v = cs.stumble ? 1.f : 0.f; break;
-        case LGK_REW_TORQUE_LIMITS: v = acc.tqlim; break;
-        case LGK_REW_TORQUES: v = acc.tq2; break;
-        case LGK_REW_TRACKING_ANG_VEL: {
-          const float e = cmd_rew.z - bav[2];
-          v = expf(-(e * e) / c.tracking_sigma);
-        } break;
-        case LGK_REW_TRACKING_LIN_VEL: {
-          const float ex = cmd_rew.x - blv[0], ey = cmd_rew.y - blv[1];
-          v = expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma);
-        } break;
-        case LGK_REW_EXTERNAL:
-          v = (active && b.ext_rewards != nullptr) ? b.ext_rewards[(size_t)ext_k * N + env] : 0.f;
-          ++ext_k;
-          break;
-        default: break;
+  // =========================================== stage 3 ===========================================
+  // W0, lane = env: reward terms in the reference's order (:195-212), episode sums, statistics
+  if (wic == 0) {
+    DofAcc acc;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) acc.v[i] = scr[(SC_J1 + i) * TILE + lane] + scr[(SC_J2 + i) * TILE + lane];
+    const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
+    const float r_air = scr[SC_RAIR * TILE + lane] * ((cn > 0.1f) ? 1.f : 0.f);
+    const bool any_reset = reset_mask != 0u;
+    float* sums = sm + L.sums;
+    float rew = 0.f;
+    int ext_k = 0;
+    for (int i = 0; i < num_rows; ++i) {
+      float r = 0.f;
+      if (i < c.num_rewards) {
+        float v = 0.f;
+        switch (c.rewards[i].term) {
+          case LGK_REW_ACTION_RATE: v = acc.v[A_ARATE]; break;
+          case LGK_REW_ANG_VEL_XY: v = fmaf(bav[1], bav[1], bav[0] * bav[0]); break;
+          case LGK_REW_BASE_HEIGHT: {
+            const float bh = H > 0 ? scr[SC_BH * TILE + lane] / (float)H : z_pre;
+            const float d = bh - c.base_height_target;
+            v = d * d;
+          } break;
+          case LGK_REW_COLLISION: v = scr[SC_COLL * TILE + lane]; break;
+          case LGK_REW_DOF_ACC: v = acc.v[A_ACC2]; break;
+          case LGK_REW_DOF_POS_LIMITS: v = acc.v[A_POSLIM]; break;
+          case LGK_REW_DOF_VEL: v = acc.v[A_QD2]; break;
+          case LGK_REW_DOF_VEL_LIMITS: v = acc.v[A_VELLIM]; break;
+          case LGK_REW_ENERGY: v = acc.v[A_ENERGY]; break;
+          case LGK_REW_FEET_AIR_TIME: v = r_air; break;
+          case LGK_REW_FEET_CONTACT_FORCES: v = scr[SC_FFP * TILE + lane]; break;
+          case LGK_REW_HIP_MOTION: v = acc.v[A_HIP]; break;
+          case LGK_REW_LIN_VEL_Z: v = blv[2] * blv[2]; break;
+          case LGK_REW_NO_FLY: v = scr[SC_NOFLY * TILE + lane]; break;
+          case LGK_REW_ORIENTATION: v = fmaf(grav[1], grav[1], grav[0] * grav[0]); break;
+          case LGK_REW_STAND_STILL: v = acc.v[A_STAND] * ((cn < 0.1f) ? 1.f : 0.f); break;
+          case LGK_REW_STUMBLE: v = scr[SC_STUMBLE * TILE + lane]; break;
+          case LGK_REW_TORQUE_LIMITS: v = acc.v[A_TQLIM]; break;
+          case LGK_REW_TORQUES: v = acc.v[A_TQ2]; break;
+          case LGK_REW_TRACKING_ANG_VEL: {
+            const float e = cmd_rew.z - bav[2];
+            v = expf(-(e * e) / c.tracking_sigma);
+          } break;
+          case LGK_REW_TRACKING_LIN_VEL: {
+            const float ex = cmd_rew.x - blv[0], ey = cmd_rew.y - blv[1];
+            v = expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma);
+          } break;
+          case LGK_REW_EXTERNAL:
+            v = (active && b.ext_rewards != nullptr) ? b.ext_rewards[(size_t)ext_k * N + env] : 0.f;
+            ++ext_k;
+            break;
+          default: break;
+        }
+        r = mul_rn(v, c.rewards[i].scale);
+        rew = add_rn(rew, r);
+      } else {
+        // termination term is added after the positive clip (:206-212)
+        if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
+        r = mul_rn((reset && !time_out) ? 1.f : 0.f, c.termination_scale);
+        rew = add_rn(rew, r);
       }
-      r = mul_rn(v, c.rewards[i].scale);
-      rew = add_rn(rew, r);
-    } else {
-      // termination term is added after the positive clip (:206-212)
-      if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
-      r = mul_rn((reset && !time_out) ? 1.f : 0.f, c.termination_scale);
-      rew = add_rn(rew, r);
+      float total = 0.f;
+      if (active) {
+        total = add_rn(sums[i * TILE + lane], r);
+        const float keep = reset ? 0.f : total;    // zeroed for reset envs after the statistics read it (:184-185)
+        sums[i * TILE + lane] = keep;
+        if (!full) b.episode_sums[(size_t)i * N + env] = keep;
+      }
+      if (any_reset) {
+        const float s = warp_sum((active && reset) ? total : 0.f);
+        if (lane == 0) atomicAdd(&ws->stats[parity][i], s);
+      }
     }
-    float total = 0.f;
-    if (active) {
-      float* sp = b.episode_sums + (size_t)i * N + env;
-      total = add_rn(*sp, r);
-      *sp = reset ? 0.f : total;    // zeroed for reset envs after the statistics read it (:184-185)
+    if (!(flags & LGK_F_HAS_TERMINATION) && (flags & LGK_F_ONLY_POSITIVE)) rew = fmaxf(rew, 0.f);
+    if (active) b.rew_buf[env] = rew;
+    if (full) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        for (int r = 0; r < num_rows; ++r)
+          bulk_s2g(b.episode_sums + (size_t)r * N + env0, sums + r * TILE, TILE * 4);
+        bulk_commit();
+      }
     }
-    if (any_reset) {
-      const float s = warp_sum((active && reset) ? total : 0.f);
-      if (lane == 0) atomicAdd(&ws->stats[parity][i], s);
+    // ---- completion ticket: masks / statistics of this tile are published before it is taken -----
+    if (lane == 0) {
+      __threadfence();
+      s_is_last = (atomicAdd(&ws->done_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
     }
   }
-  if (!(flags & LGK_F_HAS_TERMINATION) && (flags & LGK_F_ONLY_POSITIVE)) rew = fmaxf(rew, 0.f);
-  if (active) b.rew_buf[env] = rew;
+  __syncthreads();
+  // shared memory must outlive the bulk stores that read it
+  if (full && (tid == 0 || tid == 32)) bulk_wait_read_all();
+  if (!s_is_last) return;
 
   // ---- last CTA: ordered compaction of the id lists, statistics, counters ---------------------
-  __shared__ unsigned s_is_last;
-  __shared__ int s_scan[2][LGK_CTA_THREADS + 1];
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) s_is_last = (atomicAdd(&ws->done_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
-  __syncthreads();
-  if (!s_is_last) return;
   __threadfence();
   {
-    const int nw = a.num_warps;
-    const int per = (nw + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
-    const int w0 = min(nw, (int)threadIdx.x * per), w1 = min(nw, w0 + per);
+    const int nt = a.num_tiles;
+    const int max_warps = lgk_max_warps(N);
+    const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
     const volatile unsigned* rm = mask_base;
-    const volatile unsigned* sm = mask_base + max_warps;
+    const volatile unsigned* sv = mask_base + max_warps;
+    const int per = (nt + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
+    const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
     int c0 = 0, c1 = 0;
-    for (int w = w0; w < w1; ++w) { c0 += __popc(rm[w]); c1 += __popc(sm[w]); }
-    s_scan[0][threadIdx.x + 1] = c0;
-    s_scan[1][threadIdx.x + 1] = c1;
-    if (threadIdx.x == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
-    __syncthreads();
-    if (threadIdx.x < 2) {   // serial scan of 128 partials per list: negligible next to the loads
-      int* s = s_scan[threadIdx.x];
-      for (int i = 1; i <= LGK_CTA_THREADS; ++i) s[i] += s[i - 1];
+    for (int t = t0; t < t1; ++t) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
+    // block-wide exclusive scan of (c0, c1): shuffles inside a warp, 4 warp totals through shared memory
+    int i0 = c0, i1 = c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y0 = __shfl_up_sync(LGK_FULL_MASK, i0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, i1, o);
+      if (lane >= o) { i0 += y0; i1 += y1; }
     }
+    if (lane == 31) { s_scan[0][wic + 1] = i0; s_scan[1][wic + 1] = i1; }
+    if (tid == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
     __syncthreads();
-    int o0 = s_scan[0][threadIdx.x], o1 = s_scan[1][threadIdx.x];
-    for (int w = w0; w < w1; ++w) {
-      unsigned m = rm[w];
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = w * epw + bit; }
-      m = sm[w];
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = w * epw + bit; }
+    int base0 = 0, base1 = 0, n_reset = 0, n_resample = 0;
+#pragma unroll
+    for (int w = 0; w < LGK_WARPS_PER_CTA; ++w) {
+      if (w < wic) { base0 += s_scan[0][w + 1]; base1 += s_scan[1][w + 1]; }
+      n_reset += s_scan[0][w + 1];
+      n_resample += s_scan[1][w + 1];
     }
-    const int n_reset = s_scan[0][LGK_CTA_THREADS], n_resample = s_scan[1][LGK_CTA_THREADS];
+    int o0 = base0 + i0 - c0, o1 = base1 + i1 - c1;
+    for (int t = t0; t < t1; ++t) {
+      unsigned m = rm[t];
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = t * TILE + bit; }
+      m = sv[t];
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = t * TILE + bit; }
+    }
     const int level_sum = ((volatile int*)ws->level_sum)[parity];
     volatile float* st = ws->stats[parity];
-    if ((int)threadIdx.x < num_rows) {
-      const float s = st[threadIdx.x];
-      b.episode_stats[threadIdx.x] = s;
-      b.episode_stats[num_rows + 4 + threadIdx.x] += s;   // running sums since the host last cleared them
+    if (tid < num_rows) {
+      const float s = st[tid];
+      b.episode_stats[tid] = s;
+      b.episode_stats[num_rows + 4 + tid] += s;   // running sums since the host last cleared them
       if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
-        b.extras[threadIdx.x] = (s / (float)n_reset) / c.max_episode_length_s;
-      ws->stats[parity ^ 1][threadIdx.x] = 0.f;   // next step's accumulators
+        b.extras[tid] = (s / (float)n_reset) / c.max_episode_length_s;
+      ws->stats[parity ^ 1][tid] = 0.f;   // next step's accumulators
     }
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       b.counts[0] = n_reset;
       b.counts[1] = n_resample;
       b.episode_stats[num_rows] = (float)n_reset;
@@ -638,37 +753,74 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-static int pick_envs_per_warp(int num_envs, int requested) {
-  if (requested == 4 || requested == 8 || requested == 16 || requested == 32) return requested;
-  // enough warps to populate 148 SMs a few times over, else trade scalar-phase efficiency for spread
-  if (num_envs >= 32 * 148 * 8) return 32;
-  if (num_envs >= 16 * 148 * 8) return 16;
-  if (num_envs >= 8 * 148 * 4) return 8;
-  return 4;
+static inline int up4(int x) { return (x + 3) & ~3; }
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <int DT, bool TAPS, bool MUL_RCP>
+static int launch_step(const StepArgs& args, int grid, size_t smem, cudaStream_t stream) {
+  auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP>;
+  static size_t configured = 0;   // per instantiation
+  if (smem > 48 * 1024 && smem > configured) {
+    LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  kern<<<grid, LGK_CTA_THREADS, smem, stream>>>(args);
+  return (int)cudaGetLastError();
 }
 
 extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* b, cudaStream_t stream) {
   StepArgs args;
   args.c = *c;
   args.b = *b;
-  args.epw = pick_envs_per_warp(c->num_envs, c->envs_per_warp);
-  const int OH = 12 + 3 * c->num_dof;
+  const int D = c->num_dof, B3 = c->num_bodies * 3, F = c->num_feet, O = c->num_obs;
+  const int OH = 12 + 3 * D;
+  args.num_rows = c->num_rewards + ((c->flags & LGK_F_HAS_TERMINATION) ? 1 : 0);
   args.head_stride = OH | 1;
-  int row = c->num_bodies * 3;
-  if (row < args.head_stride) row = args.head_stride;
-  row = (row + 3) & ~3;   // keep every warp's region 16-byte aligned
-  args.row_floats = row;
-  args.num_warps = (c->num_envs + args.epw - 1) / args.epw;
-  const int grid = (args.num_warps + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA;
-  const size_t smem = (size_t)LGK_WARPS_PER_CTA * args.epw * row * sizeof(float);
-  if (c->num_dof == 12) {
-    if (smem > 48 * 1024)
-      LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_step_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lgk_step_kernel<12><<<grid, LGK_CTA_THREADS, smem, stream>>>(args);
-  } else {
-    if (smem > 48 * 1024)
-      LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_step_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lgk_step_kernel<0><<<grid, LGK_CTA_THREADS, smem, stream>>>(args);
+  args.num_tiles = (c->num_envs + TILE - 1) / TILE;
+  args.air_active = 0;
+  args.bh_active = 0;
+  for (int i = 0; i < c->num_rewards; ++i) {
+    args.air_active |= (c->rewards[i].term == LGK_REW_FEET_AIR_TIME);
+    args.bh_active |= (c->rewards[i].term == LGK_REW_BASE_HEIGHT);
   }
-  return (int)cudaGetLastError();
+  // shared-memory layout (floats); every region starts on a 16-byte boundary
+  TileLayout& L = args.L;
+  int o = 0;
+  L.root = o; o += up4(TILE * 13);
+  L.dof = o;  o += up4(TILE * 2 * D);
+  L.act = o;  o += up4(TILE * D);
+  L.ldv = o;  o += up4(TILE * D);
+  L.cmd = o;  o += TILE * 4;
+  L.fat = o;  o += up4(TILE * (F > 0 ? F : 1));
+  L.ep = o;   o += TILE * 2;
+  L.lvl = o;  o += TILE * 2;
+  L.sums = o; o += TILE * (args.num_rows > 0 ? args.num_rows : 1);
+  L.head = o; o += up4(TILE * args.head_stride);
+  L.scr = o;  o += TILE * SC_FIELDS;
+  // union: {contacts, torques, last_actions} (stage 1)  /  observation tile (stage 2 on)
+  const int u0 = o;
+  L.cf = o;   o += up4(TILE * B3);
+  L.tq = o;   o += up4(TILE * D);
+  L.lact = o; o += up4(TILE * D);
+  L.obs = u0;
+  const int obs_end = u0 + up4(TILE * O);
+  L.total = o > obs_end ? o : obs_end;
+  const size_t smem = (size_t)L.total * sizeof(float);
+  if (smem > 200 * 1024) return LGK_ERR_DIM;
+  // bulk (TMA) path: all tile base addresses and the episode-sum rows must be 16-byte aligned
+  args.tma_ok = (c->num_envs % 4 == 0) && al16(b->root_states) && al16(b->dof_state) && al16(b->contact_forces) &&
+                al16(b->torques) && al16(b->actions) && al16(b->last_actions) && al16(b->last_dof_vel) &&
+                al16(b->commands) && al16(b->feet_air_time) && al16(b->episode_length_buf) &&
+                al16(b->episode_sums) && al16(b->obs_buf) && (b->terrain_levels == nullptr || al16(b->terrain_levels));
+  const int grid = args.num_tiles;
+  const bool taps = c->rng_mode == LGK_RNG_TAPS;
+  const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
+#define LGK_DISPATCH(DT)                                                            \
+  (taps ? (mul ? launch_step<DT, true, true>(args, grid, smem, stream)              \
+               : launch_step<DT, true, false>(args, grid, smem, stream))            \
+        : (mul ? launch_step<DT, false, true>(args, grid, smem, stream)             \
+               : launch_step<DT, false, false>(args, grid, smem, stream)))
+  if (D == 12) return LGK_DISPATCH(12);
+  return LGK_DISPATCH(0);
+#undef LGK_DISPATCH
 }

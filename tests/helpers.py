@@ -129,3 +129,156 @@ def run_parity(scenario, num_envs, steps, oracle_device="cpu", index_math=None, 
         assert_close("target_poses", env.target_poses, target)
         total_resets += int(env.step_counts[0])
     return total_resets
+
+
+# ---------------------------------------------------------------------------------------------
+# golden fixtures: outputs of the reference's own code (tests/golden/make_golden.py)
+import os
+import zlib
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN_OUT = ("obs_buf", "rew_buf", "commands", "root_states", "dof_state", "last_actions", "last_dof_vel",
+              "last_root_vel", "feet_air_time", "base_lin_vel", "base_ang_vel", "projected_gravity", "env_origins",
+              "target_poses")
+GOLDEN_EXACT = ("reset_buf", "time_out_buf", "episode_length_buf")
+
+
+def load_golden(name):
+    d = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    return {k: d[k] for k in d.files}
+
+
+def _crc(t):
+    return zlib.crc32(np.ascontiguousarray(t.detach().cpu().numpy()).tobytes()) & 0xFFFFFFFF
+
+
+def golden_env(name, g, device):
+    """This repo's env built for the fixture's scenario, put into the fixture's initial state."""
+    N = int(g["meta_envs"])
+    env = make_env(name, N, device=device, seed=int(g["meta_seed"]))
+    if int(g["meta_terrain_crc"]) != 0:
+        assert _crc(env.height_samples) == int(g["meta_terrain_crc"]), "terrain height field differs from the reference's"
+        assert _crc(env.terrain_origins) == int(g["meta_origins_crc"]), "terrain origins differ from the reference's"
+    assert list(env.reward_names) == [str(x) for x in g["meta_reward_names"]], "reward evaluation order differs"
+    keys = [str(x) for x in g["meta_sum_keys"]]
+    assert list(env.episode_sums.keys()) == keys, "episode_sums key order differs"
+    T = lambda a: torch.from_numpy(np.asarray(a)).to(device)
+    env.episode_length_buf = T(g["init_episode_length_buf"])
+    for k in ("commands", "feet_air_time", "last_actions", "last_dof_vel", "env_origins"):
+        getattr(env, k).copy_(T(g["init_" + k]))
+    for i, k in enumerate(keys):
+        env.episode_sums[k].copy_(T(g["init_episode_sums"][i]))
+    if g["init_terrain_levels"].size:
+        env.terrain_levels.copy_(T(g["init_terrain_levels"]))
+        assert torch.equal(env.terrain_types.cpu(), torch.from_numpy(g["init_terrain_types"])), "terrain_types differ"
+    env.common_step_counter = int(g["init_common_step_counter"])
+    return env, keys
+
+
+def golden_frame(g, it, device):
+    T = lambda a: torch.from_numpy(np.asarray(a)).to(device)
+    fr = {k: T(g["in_" + k][it]) for k in ("root_states", "dof_state", "contact_forces", "torques", "actions")}
+    taps = {k[4:]: T(g[k][it]) for k in g if k.startswith("tap_")}
+    return fr, taps
+
+
+def compare_to_golden(get, g, it, keys, tag, float_names=GOLDEN_OUT):
+    """`get(name)` returns the candidate's buffer; compares against the reference's step-`it` outputs."""
+    T = lambda a: torch.from_numpy(np.asarray(a))
+    for name in GOLDEN_EXACT:
+        assert_close(f"{tag}{name}", get(name).reshape(-1), T(g["out_" + name][it]).reshape(-1), exact=True)
+    for name in float_names:
+        assert_close(f"{tag}{name}", get(name).reshape(-1), T(g["out_" + name][it]).reshape(-1))
+    sums = get("episode_sums")
+    for i, k in enumerate(keys):
+        assert_close(f"{tag}episode_sums[{k}]", sums[k], T(g["out_episode_sums"][it][i]))
+    if g["out_terrain_levels"][it].size:
+        assert_close(f"{tag}terrain_levels", get("terrain_levels"), T(g["out_terrain_levels"][it]), exact=True)
+    if g["out_measured_heights"][it].size:
+        mh = get("measured_heights")
+        if torch.is_tensor(mh):
+            assert_close(f"{tag}measured_heights", mh, T(g["out_measured_heights"][it]), exact=True)
+    want = g["out_reset_ids"][it]
+    want = want[want >= 0]
+    got = get("reset_ids")
+    assert_close(f"{tag}reset_ids", got.to(torch.int64).reshape(-1), T(want), exact=True)
+    want = g["out_resample_ids"][it]
+    want = want[want >= 0]
+    assert_close(f"{tag}resample_ids", get("resample_ids").to(torch.int64).reshape(-1), T(want), exact=True)
+    ex = get("extras")
+    if ex is not None:
+        row = g["out_extras"][it]
+        for i, k in enumerate(keys + ["terrain_level"]):
+            if not np.isnan(row[i]):
+                name = ("rew_" + k) if i < len(keys) else k
+                assert_close(f"{tag}extras[{name}]", torch.as_tensor(ex[name]).float().reshape(1), T(row[i:i + 1]))
+
+
+def replay_golden_oracle(name, device="cpu"):
+    """Oracle restatement vs the reference's recorded outputs."""
+    from oracle import legged_oracle as lo
+    g = load_golden(name)
+    env, keys = golden_env(name, g, "cpu")
+    fr0, _ = golden_frame(g, 0, "cpu")
+    synthetic.load_frame(env, fr0)
+    p = lo.OracleParams.from_env(env, device=device)
+    s = lo.OracleState.from_env(env, p, device=device)
+    act = None
+    if "out_dvel" in g:
+        from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
+        act = lo.ActuatorOracle(env.num_envs, random_mlp_state_dict(0), device=device)
+    n = 0
+    for it in range(int(g["meta_steps"])):
+        fr, taps = golden_frame(g, it, device)
+        s.root_states.copy_(fr["root_states"]); s.dof_state.copy_(fr["dof_state"])
+        s.contact_forces.copy_(fr["contact_forces"].view_as(s.contact_forces)); s.torques.copy_(fr["torques"])
+        if act is not None:
+            a = torch.clip(fr["actions"], -p.clip_actions, p.clip_actions)
+            for k in range(p.decimation):
+                dv = act.advance(a, s.dof_pos, s.dof_vel)
+                assert_close(f"[{name} step {it}.{k}] dVel", dv, torch.from_numpy(g["out_dvel"][it, k]))
+        target = lo.step(p, s, fr["actions"].clone(), taps)
+
+        def get(nm):
+            if nm == "target_poses":
+                return target
+            if nm == "reset_ids":
+                return s.reset_env_ids
+            if nm == "resample_ids":
+                return s.resample_env_ids
+            if nm == "extras":
+                return s.extras.get("episode") if len(s.reset_env_ids) else None
+            return getattr(s, nm)
+        compare_to_golden(get, g, it, keys, f"[oracle {name} step {it}] ")
+        n += len(s.reset_env_ids)
+    return n
+
+
+def replay_golden_env(name, index_math=None):
+    """This repo's CUDA path (through the C ABI) vs the reference's recorded outputs."""
+    from legged_gym_b200 import _lgk
+    g = load_golden(name)
+    env, keys = golden_env(name, g, "cuda:0")
+    n = 0
+    for it in range(int(g["meta_steps"])):
+        fr, taps = golden_frame(g, it, "cuda:0")
+        synthetic.load_frame(env, fr)
+        # the fixtures were produced by torch-CPU: its (p / horizontal_scale) is an IEEE division
+        env.use_rng_taps(taps, index_math=_lgk.INDEX_MATH_TORCH_CPU if index_math is None else index_math)
+        env.step(fr["actions"].clone())
+        torch.cuda.synchronize()
+        if "out_dvel" in g:
+            assert_close(f"[{name} step {it}] dVel", env.dVel, torch.from_numpy(g["out_dvel"][it, -1]))
+        nr, ns = int(env.step_counts[0]), int(env.step_counts[1])
+
+        def get(nm):
+            if nm == "reset_ids":
+                return env.reset_ids[:nr]
+            if nm == "resample_ids":
+                return env.resample_ids[:ns]
+            if nm == "extras":
+                return env.extras.get("episode") if nr else None
+            return getattr(env, nm)
+        compare_to_golden(get, g, it, keys, f"[cuda {name} step {it}] ")
+        n += nr
+    return n

@@ -1,0 +1,296 @@
+"""GPU tier: the CUDA path, called through the C ABI (liblgk.so), against
+  (1) the reference's own recorded outputs (tests/golden),
+  (2) the oracle restatement on identical frames + RNG taps (torch-CPU and torch-CUDA variants), and
+  (3) size-independent properties at the full BASELINE.json size (65536 envs).
+Tolerances (north star): bit-exact for terminations, id lists, height-field indices / measured heights,
+episode lengths, terrain levels; |a-b| <= 1e-5*max(|a|,|b|) + 1e-6 for fp32 outputs (helpers.RTOL/ATOL)."""
+import ctypes as C
+
+import pytest
+import torch
+
+import helpers
+from legged_gym_b200 import _lgk
+from legged_gym_b200.utils import scenarios, synthetic
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_cuda():
+    assert torch.cuda.is_available(), "GPU tier needs a CUDA device"
+    _lgk.load()
+
+
+# ------------------------------------------------------------------------------------------- (1) golden
+@pytest.mark.parametrize("name", list(scenarios.SCENARIOS))
+def test_cuda_path_matches_reference_golden(name):
+    assert helpers.replay_golden_env(name) >= 6
+
+
+# ------------------------------------------------------------------------------------------- (2) oracle
+@pytest.mark.parametrize("oracle_device", ["cpu", "cuda:0"])
+@pytest.mark.parametrize("name", list(scenarios.SCENARIOS))
+def test_step_matches_oracle(name, oracle_device):
+    n = helpers.run_parity(name, num_envs=1024, steps=6, oracle_device=oracle_device)
+    assert n > 0
+
+
+@pytest.mark.parametrize("num_envs", [1, 3, 33, 127, 1800])
+def test_ragged_env_counts(num_envs):
+    """env counts that are not multiples of the warp / CTA tile (config 1 uses 1800)."""
+    helpers.run_parity("go1_rough_full", num_envs=num_envs, steps=4, oracle_device="cpu", seed=2)
+    helpers.run_parity("go1_flat", num_envs=num_envs, steps=3, oracle_device="cpu", seed=3)
+
+
+def test_heights_not_materialised_gives_same_observations():
+    def nomat(cfg):
+        cfg.terrain.materialize_heights = False
+    a = helpers.make_env("go1_rough_full", 512, device=DEV, seed=5)
+    b = helpers.make_env("go1_rough_full", 512, device=DEV, seed=5, extra=nomat)
+    assert torch.is_tensor(a.measured_heights) and not torch.is_tensor(b.measured_heights)
+    fr = synthetic.make_frames(a, 1, seed=11)[0]
+    taps = synthetic.make_taps(a, seed=4)
+    for env in (a, b):
+        helpers.randomise_env_state(env, 5)
+        synthetic.load_frame(env, fr)
+        env.use_rng_taps(taps)
+        env.step(fr["actions"].clone())
+    assert torch.equal(a.obs_buf, b.obs_buf) and torch.equal(a.rew_buf, b.rew_buf)
+
+
+def test_robots_outside_the_terrain_are_clipped_like_the_reference():
+    from oracle import legged_oracle as lo
+    env = helpers.make_env("go1_rough_full", 256, device=DEV, seed=1)
+    helpers.randomise_env_state(env, 1)
+    fr = synthetic.make_frames(env, 1, seed=5)[0]
+    fr["root_states"][:, 0] = torch.linspace(-80., 220., 256, device=DEV)
+    fr["root_states"][:, 1] = torch.linspace(330., -90., 256, device=DEV)
+    synthetic.load_frame(env, fr)
+    taps = synthetic.make_taps(env, seed=2)
+    p = lo.OracleParams.from_env(env, device=DEV)
+    s = lo.OracleState.from_env(env, p, device=DEV)
+    env.use_rng_taps(taps, index_math=_lgk.INDEX_MATH_TORCH_CUDA)
+    env.step(fr["actions"].clone())
+    lo.step(p, s, fr["actions"].clone(), taps)
+    helpers.compare_env_to_oracle(env, s, tag="[outside] ")
+
+
+# ------------------------------------------------------------------------------------------- control
+@pytest.mark.parametrize("control_type", ["P", "V", "T"])
+def test_compute_torques(control_type):
+    from oracle import legged_oracle as lo
+
+    def ct(cfg):
+        cfg.control.control_type = control_type
+    env = helpers.make_env("go1_flat", 777, device=DEV, extra=ct)
+    fr = synthetic.make_frames(env, 1, seed=3)[0]
+    synthetic.load_frame(env, fr)
+    env.last_dof_vel[:] = torch.randn_like(env.last_dof_vel)
+    p = lo.OracleParams.from_env(env, device="cpu")
+    s = lo.OracleState.from_env(env, p, device="cpu")
+    a = (3 * torch.randn(777, 12, device=DEV))
+    got = env._compute_torques(a)
+    want = lo.compute_torques(p, s, a.cpu())
+    helpers.assert_close(f"torques[{control_type}]", got, want)
+    assert (got.abs() <= env.torque_limits + 1e-6).all()
+
+
+def test_unknown_control_type_raises_name_error():
+    env = helpers.make_env("go1_flat", 8, device=DEV)
+    env.cfg.control.control_type = "Q"
+    with pytest.raises(NameError):
+        env._compute_torques(torch.zeros(8, 12, device=DEV))
+
+
+@pytest.mark.parametrize("n", [1, 5, 4096])
+def test_clip_actions_and_poses(n):
+    from oracle import legged_oracle as lo
+    env = helpers.make_env("cassie_flat", n, device=DEV)
+    lib = _lgk.load()
+    a = 200 * torch.randn(n, 12, device=DEV)
+    out = torch.empty_like(a)
+    _lgk.check("clip", lib.lgk_clip_actions(_lgk.ptr(a), _lgk.ptr(out), a.numel(), 100.0, _lgk.current_stream(DEV)))
+    assert torch.equal(out, a.clip(-100, 100))
+    # unaligned views take the scalar kernel
+    flat = torch.empty(n * 12 + 1, device=DEV)
+    _lgk.check("clip", lib.lgk_clip_actions(_lgk.ptr(a), C.c_void_p(flat.data_ptr() + 4), a.numel(), 1.0,
+                                            _lgk.current_stream(DEV)))
+    assert torch.equal(flat[1:].view(n, 12), a.clip(-1, 1))
+    p = lo.OracleParams.from_env(env, device="cpu")
+    helpers.assert_close("target_poses", env._compute_poses(out), lo.compute_poses(p, out.cpu()))
+
+
+def test_actuator_net_matches_oracle_over_substeps():
+    from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
+    from oracle import legged_oracle as lo
+    n = 1000
+    env = helpers.make_env("go1_rough_actuator", n, device=DEV)
+    act = lo.ActuatorOracle(n, random_mlp_state_dict(0))
+    frames = synthetic.make_frames(env, 7, seed=8)
+    for it, fr in enumerate(frames):       # > LEN_HIST substeps so the whole window is exercised
+        synthetic.load_frame(env, fr)
+        a = fr["actions"]
+        got = env.actuator_advance(a)
+        want = act.advance(a.cpu(), env.dof_pos.cpu(), env.dof_vel.cpu())
+        helpers.assert_close(f"dVel[{it}]", got, want)
+        helpers.assert_close(f"model_ins[{it}]", env.model_ins, act.model_ins)
+        assert torch.equal(env.pos_err_buffs.cpu().double(), torch.from_numpy(act.pos_err_buffs)) or \
+            torch.allclose(env.pos_err_buffs.cpu().double(), torch.from_numpy(act.pos_err_buffs), rtol=1e-6, atol=1e-7)
+
+
+# ------------------------------------------------------------------------------------------- resets
+def test_reset_idx_subset_and_reset_all():
+    from oracle import legged_oracle as lo
+    env = helpers.make_env("go1_rough_full", 500, device=DEV, seed=4)
+    helpers.randomise_env_state(env, 4)
+    fr = synthetic.make_frames(env, 1, seed=6)[0]
+    synthetic.load_frame(env, fr)
+    taps = synthetic.make_taps(env, seed=12)
+    p = lo.OracleParams.from_env(env, device="cpu")
+    s = lo.OracleState.from_env(env, p, device="cpu")
+    ids = torch.tensor([0, 7, 31, 32, 33, 250, 499], device=DEV)
+    env.use_rng_taps(taps)
+    env.reset_idx(ids)
+    torch.cuda.synchronize()
+    lo.reset_idx(p, s, ids.cpu(), {k: v.cpu() for k, v in taps.items()})
+    for name in ("root_states", "dof_state", "commands", "feet_air_time", "env_origins"):
+        helpers.assert_close(name, getattr(env, name).reshape(-1), getattr(s, name).reshape(-1))
+    helpers.assert_close("episode_length_buf", env.episode_length_buf, s.episode_length_buf, exact=True)
+    helpers.assert_close("terrain_levels", env.terrain_levels, s.terrain_levels, exact=True)
+    helpers.assert_close("reset_ids", env.reset_ids[:7].long(), ids, exact=True)
+    for k, v in s.extras["episode"].items():
+        helpers.assert_close(f"extras[{k}]", env.extras["episode"][k].reshape(1), torch.as_tensor(v).float().reshape(1))
+    for k in env.episode_sums:
+        helpers.assert_close(f"sums[{k}]", env.episode_sums[k], s.episode_sums[k])
+    env.reset_idx(torch.zeros(0, dtype=torch.long, device=DEV))       # empty list: early-out (:160)
+    obs, priv = env.reset()                                            # reset_idx(all) + zero-action step
+    assert obs is env.obs_buf and priv is None and torch.isfinite(obs).all()
+    assert (env.episode_length_buf <= 1).all()
+
+
+# ------------------------------------------------------------------------------------------- tables / probes
+def test_height_min3_table():
+    env = helpers.make_env("go1_rough_full", 8, device=DEV)
+    env._kernels()
+    hs = env.height_samples.cpu()
+    want = torch.min(torch.min(hs[:-1, :-1], hs[1:, :-1]), hs[:-1, 1:])
+    assert torch.equal(env._height_min3.cpu()[:-1, :hs.shape[1] - 1], want)
+
+
+def test_yaw_quaternion_formula_is_torch_exact():
+    lib = _lgk.load()
+    g = torch.Generator().manual_seed(0)
+    q = torch.randn(200000, 4, generator=g)
+    q = (q / q.norm(dim=1, keepdim=True)).to(DEV)
+    out = torch.empty(200000, 2, device=DEV)
+    _lgk.check("yaw", lib.lgk_debug_yaw_quat(_lgk.ptr(q), 200000, 1, _lgk.ptr(out), _lgk.current_stream(DEV)))
+    yq = q.clone()
+    yq[:, :2] = 0
+    for dev in ("cpu", DEV):
+        y = yq.to(dev)
+        want = (y / y.norm(p=2, dim=-1).clamp(min=1e-9).unsqueeze(-1))[:, 2:]
+        assert torch.equal(out.to(dev), want), f"normalize([0,0,qz,qw]) differs from torch on {dev}"
+
+
+# ------------------------------------------------------------------------------------------- (3) full size
+def _full_env(seed, n=65536):
+    env = helpers.make_env("go1_rough_full", n, device=DEV, seed=seed)
+    g = torch.Generator().manual_seed(77)
+    env.episode_length_buf = torch.randint(0, 1002, (n,), generator=g).to(DEV)
+    return env
+
+
+def test_full_size_properties_with_in_kernel_rng():
+    from oracle import legged_oracle as lo
+    N = 65536
+    env = _full_env(1)
+    frames = synthetic.make_frames(env, 2, seed=21)
+    p = lo.OracleParams.from_env(env, device=DEV)
+    n_resets = 0
+    for it in range(4):
+        fr = frames[it % 2]
+        synthetic.load_frame(env, fr)
+        ep_before = env.episode_length_buf.clone()
+        s = lo.OracleState.from_env(env, p, device=DEV)
+        env.step(fr["actions"].clone())
+        torch.cuda.synchronize()
+        # terminations / id lists: exact against the oracle's check_termination on the same inputs
+        s.episode_length_buf += 1
+        lo.check_termination(p, s)
+        assert torch.equal(env.reset_buf, s.reset_buf) and torch.equal(env.time_out_buf, s.time_out_buf)
+        nr, ns = int(env.step_counts[0]), int(env.step_counts[1])
+        ids = env.reset_buf.nonzero().flatten()
+        assert nr == len(ids) and torch.equal(env.reset_ids[:nr].long(), ids)          # ascending, complete
+        rs = ((ep_before + 1) % 500 == 0).nonzero().flatten()
+        assert ns == len(rs) and torch.equal(env.resample_ids[:ns].long(), rs)
+        # height-field indices at full size: measured_heights == int16 table * 0.005f exactly
+        s.root_states.copy_(fr["root_states"])
+        want_h = lo.get_heights(p, s)
+        assert torch.equal(env.measured_heights, want_h)
+        # episode bookkeeping
+        assert (env.episode_length_buf[ids] == 0).all()
+        keep = ~env.reset_buf
+        assert torch.equal(env.episode_length_buf[keep], ep_before[keep] + 1)
+        assert (env.feet_air_time[ids] == 0).all() and (env.dof_vel[ids] == 0).all()
+        for k in env.episode_sums:
+            assert (env.episode_sums[k][ids] == 0).all()
+        # reset poses: within 1 m of the (new) platform centre, joints in default * [0.5, 1.5]
+        d = (env.root_states[ids, :2] - env.env_origins[ids, :2]).abs()
+        assert (d <= 1.0 + 1e-5).all() and (env.root_states[ids, 7:13].abs() <= 0.5).all()
+        ratio = env.dof_pos[ids] / env.default_dof_pos
+        assert (ratio >= 0.5 - 1e-5).all() and (ratio <= 1.5 + 1e-5).all()
+        # observations: finite, clipped, noise bounded by the noise vector around the noiseless value
+        assert torch.isfinite(env.obs_buf).all() and (env.obs_buf.abs() <= 100).all()
+        clean = torch.clip(env.root_states[:, 2:3] - 0.5 - env.measured_heights, -1, 1) * 5.0
+        dev_h = (env.obs_buf[:, 48:] - clean).abs()
+        assert (dev_h[keep] <= 0.5 + 1e-5).all() and dev_h[keep].mean() > 0.2        # U(-0.5, 0.5): mean |x| = 0.25
+        noise_h = (env.obs_buf[:, 48:] - clean)[keep]
+        assert abs(float(noise_h.mean())) < 2e-3 and abs(float(noise_h.var()) - 1 / 12) < 2e-3
+        assert torch.equal(env.obs_buf[:, 36:48], env.actions)                        # zero noise scale columns
+        assert torch.equal(env.last_actions, env.actions) and torch.equal(env.last_dof_vel, env.dof_vel)
+        assert (env.rew_buf[keep] >= 0).all()                                         # only_positive_rewards
+        n_resets += nr
+    assert n_resets > 1000
+
+
+def test_in_kernel_rng_is_deterministic_per_seed_and_decorrelated_across_steps():
+    outs = []
+    for seed in (1, 1, 2):
+        env = _full_env(seed, n=8192)
+        frames = synthetic.make_frames(env, 1, seed=21)
+        rows = []
+        for it in range(2):
+            synthetic.load_frame(env, frames[0])
+            env.episode_length_buf = torch.full((8192,), 10 + it, device=DEV)
+            env.step(frames[0]["actions"].clone())
+            rows.append(env.obs_buf.clone())
+        outs.append(rows)
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert not torch.equal(outs[0][0][:, :3], outs[2][0][:, :3])
+    a = outs[0][0][:, 48:] - outs[0][1][:, 48:]            # same state, different step -> different noise
+    assert (a != 0).float().mean() > 0.99
+    n0 = (outs[0][0][:, 100] - outs[2][0][:, 100])
+    n1 = (outs[0][1][:, 100] - outs[2][1][:, 100])
+    assert abs(float(torch.corrcoef(torch.stack([n0, n1]))[0, 1])) < 0.05
+
+
+def test_step_is_graph_capturable_and_sync_free():
+    env = helpers.make_env("go1_rough_full", 4096, device=DEV, seed=9)
+    frames = synthetic.make_frames(env, 1, seed=2)
+    synthetic.load_frame(env, frames[0])
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            env.step(frames[0]["actions"])
+        st.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            env.step(frames[0]["actions"])
+        ep0 = env.episode_length_buf.clone()
+        for _ in range(5):
+            g.replay()
+        st.synchronize()
+    keep = env.episode_length_buf > 4
+    assert keep.any() and torch.equal(env.episode_length_buf[keep], ep0[keep] + 5)

@@ -1,0 +1,135 @@
+"""CPU tier: the host-side mirror of the reference interface -- registry, cfg -> constants, reward
+registration order and error behaviour, sharding of terrain types, no-CPU-path guarantees."""
+import copy
+import ctypes as C
+
+import pytest
+import torch
+
+import helpers
+from legged_gym_b200 import _lgk
+from legged_gym_b200.envs import LeggedRobot
+from legged_gym_b200.utils.task_registry import task_registry
+
+
+def test_registry_holds_the_reference_tasks():
+    names = {"anymal_c_rough", "anymal_c_flat", "anymal_b", "a1", "cassie", "a1_src", "go1", "aliengo"}
+    assert names <= set(task_registry.task_classes)
+    assert issubclass(task_registry.get_task_class("go1"), LeggedRobot)
+    with pytest.raises(ValueError, match="was not registered"):
+        task_registry.make_env("nope", args=object())
+
+
+def test_vecenv_surface_and_dtypes():
+    env = helpers.make_env("go1_rough_full", 48)
+    assert (env.num_envs, env.num_obs, env.num_actions, env.num_privileged_obs) == (48, 235, 12, None)
+    assert env.obs_buf.shape == (48, 235) and env.obs_buf.dtype == torch.float32
+    assert env.rew_buf.shape == (48,) and env.reset_buf.dtype == torch.bool
+    assert env.episode_length_buf.dtype == torch.int64 and env.time_out_buf.dtype == torch.bool
+    assert env.get_observations() is env.obs_buf and env.get_privileged_observations() is None
+    assert float(env.max_episode_length) == 1000.0 and abs(env.dt - 0.02) < 1e-12
+    assert env.num_bodies == 17 and env.feet_indices.tolist() == [4, 8, 12, 16]
+    assert len(env.penalised_contact_indices) == 8 and len(env.termination_contact_indices) == 1
+    assert env.height_samples.dtype == torch.int16 and tuple(env.height_samples.shape) == (1300, 2100)
+    assert env.height_points.shape == (48, 187, 3)
+    assert env.terrain_levels.dtype == torch.int64 and env.terrain_types.dtype == torch.int64
+    # rsl_rl re-binds episode_length_buf (scripts/train.py:43): assignment must write through
+    addr = env.episode_length_buf.data_ptr()
+    env.episode_length_buf = torch.arange(48)
+    assert env.episode_length_buf.data_ptr() == addr and env.episode_length_buf[5] == 5
+
+
+def test_reward_registration_is_alphabetical_and_scaled_by_dt():
+    env = helpers.make_env("go1_rough_full", 16)
+    assert env.reward_names == sorted(env.reward_names) and len(env.reward_names) == 20
+    assert "termination" in env.reward_scales and "termination" not in env.reward_names
+    assert abs(env.reward_scales["tracking_lin_vel"] - 1.0 * env.dt) < 1e-9
+    assert list(env.episode_sums.keys()) == list(env.reward_scales.keys())
+    flat = helpers.make_env("go1_flat", 16)
+    assert flat.reward_names == ["action_rate", "ang_vel_xy", "collision", "dof_acc", "dof_pos_limits",
+                                 "feet_air_time", "lin_vel_z", "torques", "tracking_ang_vel", "tracking_lin_vel"]
+    cassie = helpers.make_env("cassie_flat", 16)
+    assert "no_fly" in cassie.reward_names and cassie.num_obs == 169 and cassie.num_bodies == 13
+
+
+def test_unknown_reward_and_control_type_raise_like_the_reference():
+    def stumble(cfg):
+        cfg.rewards.scales.feet_stumble = -1.0       # no _reward_feet_stumble exists (legged_robot.py:593)
+    with pytest.raises(AttributeError, match="_reward_feet_stumble"):
+        helpers.make_env("go1_flat", 8, extra=stumble)
+    env = helpers.make_env("go1_flat", 8)
+    env.cfg.control.control_type = "X"
+    with pytest.raises(NameError, match="Unknown controller type"):
+        env.build_consts()
+
+
+def test_noise_scale_vector():
+    env = helpers.make_env("go1_rough_full", 8)
+    v = env.noise_scale_vec
+    assert torch.allclose(v[:3], torch.full((3,), 0.1 * 2.0)) and torch.allclose(v[3:6], torch.full((3,), 0.2 * 0.25))
+    assert torch.allclose(v[6:9], torch.full((3,), 0.05)) and (v[9:12] == 0).all() and (v[36:48] == 0).all()
+    assert torch.allclose(v[12:24], torch.full((12,), 0.01)) and torch.allclose(v[24:36], torch.full((12,), 1.5 * 0.05))
+    assert torch.allclose(v[48:], torch.full((187,), 0.1 * 5.0))
+
+
+def test_constant_block_mirrors_cfg():
+    env = helpers.make_env("go1_rough_full", 64)
+    c = env.build_consts()
+    assert c.struct_size == C.sizeof(_lgk.LgkConsts)
+    assert (c.num_envs, c.num_dof, c.num_bodies, c.num_feet, c.num_pen, c.num_term) == (64, 12, 17, 4, 8, 1)
+    assert (c.num_height_points, c.num_obs, c.num_rewards) == (187, 235, 20)
+    assert c.flags & _lgk.F_HAS_TERMINATION and c.flags & _lgk.F_ONLY_POSITIVE and c.flags & _lgk.F_TERRAIN_CURRICULUM
+    assert c.flags & _lgk.F_HEADING_COMMAND and c.flags & _lgk.F_CUSTOM_ORIGINS and not c.flags & _lgk.F_TERRAIN_PLANE
+    assert (c.max_episode_length, c.resample_interval, c.push_interval) == (1000, 500, 750)
+    assert [c.rewards[i].term for i in range(20)] == [_lgk.REWARD_ID[n] for n in env.reward_names]
+    assert abs(c.rewards[0].scale - env.reward_scales["action_rate"]) < 1e-10      # fp32 of the python float
+    assert (c.terrain_rows, c.terrain_cols, c.terrain_pitch) == (1300, 2100, 2104)
+    assert list(c.hip_idx) == [0, 3, 6, 9]
+    cas = helpers.make_env("cassie_flat", 8).build_consts()
+    assert cas.flags & _lgk.F_TERRAIN_PLANE and cas.num_height_points == 121 and cas.num_feet == 2
+
+
+def test_sharded_terrain_types_follow_the_global_env_index():
+    def shard(rank):
+        def f(cfg):
+            cfg.env.shard_rank, cfg.env.shard_world = rank, 4
+        return f
+    whole = helpers.make_env("go1_rough_full", 256)
+    parts = [helpers.make_env("go1_rough_full", 64, extra=shard(r)) for r in range(4)]
+    assert torch.equal(torch.cat([p.terrain_types for p in parts]), whole.terrain_types)
+    assert [p.env_id_offset for p in parts] == [0, 64, 128, 192]
+    seeds = {p.build_consts().seed for p in parts}
+    assert len(seeds) == 4         # independent Philox streams per rank
+
+
+def test_there_is_no_cpu_step_path():
+    env = helpers.make_env("go1_flat", 8, device="cpu")
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        env.step(torch.zeros(8, 12))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        env.reset()
+
+
+def test_fused_hooks_cannot_be_overridden_silently():
+    class Bad(LeggedRobot):
+        def check_termination(self):
+            pass
+    cfg = copy.deepcopy(task_registry.env_cfgs["a1"])
+    cfg.env.num_envs = 4
+    from legged_gym_b200.sim import gymapi, gymutil
+    from legged_gym_b200.utils.helpers import class_to_dict
+    sp = gymapi.SimParams()
+    gymutil.parse_sim_config(class_to_dict(cfg.sim), sp)
+    with pytest.raises(NotImplementedError, match="check_termination"):
+        Bad(cfg=cfg, sim_params=sp, physics_engine=gymapi.SIM_PHYSX, sim_device="cpu", headless=True)
+
+
+def test_product_code_never_imports_the_oracle():
+    import os
+    import re
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "legged_gym_b200")
+    for dp, _, files in os.walk(root):
+        for f in files:
+            if f.endswith(".py"):
+                src = open(os.path.join(dp, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports oracle/"

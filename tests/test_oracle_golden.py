@@ -1,0 +1,38 @@
+"""CPU tier: the oracle restatement against the reference's own recorded outputs (tests/golden, produced by
+tests/golden/make_golden.py from /root/reference) and, where /root/reference exists, against the reference
+run live.  Pins the oracle before the GPU tier trusts it."""
+import pytest
+import torch
+
+import helpers
+from legged_gym_b200.utils import scenarios
+from oracle import reference_loader
+
+
+@pytest.mark.parametrize("name", list(scenarios.SCENARIOS))
+def test_oracle_matches_reference_golden(name):
+    n_resets = helpers.replay_golden_oracle(name)
+    assert n_resets >= 6      # every fixture exercises resets (time-outs + contact terminations)
+
+
+@pytest.mark.reference
+@pytest.mark.skipif(not reference_loader.reference_available(), reason="/root/reference only exists in the build container")
+@pytest.mark.parametrize("name", ["go1_rough_full", "cassie_flat"])
+def test_oracle_bit_identical_to_live_reference(name):
+    from oracle import validate_against_reference as v
+    assert v.run_scenario(name, num_envs=96, steps=6, seed=3, verbose=False) > 0
+
+
+def test_golden_fixtures_cover_the_edge_cases():
+    """resample on step 0, time-outs on steps 0 and 2, push on step 2, contact terminations somewhere."""
+    g = helpers.load_golden("go1_rough_full")
+    assert (g["out_resample_ids"][0] >= 0).sum() >= 8
+    assert g["out_time_out_buf"][0].sum() >= 3 and g["out_time_out_buf"][2].sum() >= 2
+    assert (g["out_reset_buf"] & ~g["out_time_out_buf"]).sum() >= 1
+    # the push rewrites root lin vel xy of every env on the third step (common_step_counter % 750 == 0)
+    assert not (g["out_root_states"][2][:, 7:9] == g["in_root_states"][2][:, 7:9]).all(axis=1).any()
+    nores = ~g["out_reset_buf"][1]
+    assert (g["out_root_states"][1][nores, 7:9] == g["in_root_states"][1][nores, 7:9]).all()
+    # heights are int16 * 0.005f
+    mh = g["out_measured_heights"][0]
+    assert mh.shape == (64, 187) and (mh != 0).any()
