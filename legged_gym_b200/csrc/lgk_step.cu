@@ -26,6 +26,9 @@
 #include "lgk_common.cuh"
 
 #define TILE 32
+#ifndef LGK_MIN_CTAS
+#define LGK_MIN_CTAS 6   // register cap 85: six 128-thread CTAs per SM
+#endif
 
 struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
   int root, dof, act, ldv, cmd, fat, ep, lvl, sums, head, scr, cf, tq, lact, obs, total;
@@ -108,8 +111,8 @@ __device__ __forceinline__ void joint_update(const LgkConsts& c, int d, int D, u
 }
 
 // ---------------------------------------------------------------------------------------------
-template <int DT, bool TAPS, bool MUL_RCP>
-__global__ void __launch_bounds__(LGK_CTA_THREADS)
+template <int DT, bool TAPS, bool MUL_RCP, int NP>
+__global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_MIN_CTAS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
@@ -482,18 +485,19 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   __syncthreads();
 
   // =========================================== stage 2 ===========================================
-  // observation tile (aliases the contact / torque / last_actions rows, all consumed in stage 1)
-  float* obs_t = sm + L.obs;
+  // one env at a time per warp, lanes over observation columns: noise on the head, then the H scan
+  // points in NP passes of 32.  All gathers of an env are issued before any is consumed.
   {
     const bool add_noise = flags & LGK_F_ADD_NOISE;
     const bool plane = flags & LGK_F_TERRAIN_PLANE;
+    const bool materialise = b.measured_heights != nullptr;
     const float inv_hs = 1.0f / c.horizontal_scale;
     const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
     const float clip_obs = c.clip_obs;
-    // this lane's scan offsets and noise amplitudes (same for every env)
-    float px_l[8], py_l[8], ns_h[8];
+    // this lane's scan offsets and noise amplitudes (same for every env); lanes past H repeat point 0
+    float px_l[NP > 0 ? NP : 1], py_l[NP > 0 ? NP : 1], ns_h[NP > 0 ? NP : 1];
 #pragma unroll
-    for (int it = 0; it < 8; ++it) {
+    for (int it = 0; it < NP; ++it) {
       const int h = it * 32 + lane;
       const bool ok = h < H;
       px_l[it] = ok ? __ldg(b.height_points_xy + 2 * h) : 0.f;
@@ -504,9 +508,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     const float ns_b = (add_noise && lane + 32 < OH) ? __ldg(b.noise_scale_vec + lane + 32) : 0.f;
     // obs = clip(v + (2*rand - 1) * noise_scale_vec, +-clip_observations)   (:231, :104)
     auto noisy = [&](float v, const float* __restrict__ trow, int col, unsigned rbits, float ns) {
-      if (add_noise) {
-        if (TAPS) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
-        else v = fmaf(fmaf((float)(rbits >> 8), 1.1920928955078125e-07f, -1.0f), ns, v);   // 2 * u01 - 1
+      if (TAPS) {
+        if (add_noise) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
+      } else {
+        v = fmaf(fmaf((float)(rbits >> 8), 1.1920928955078125e-07f, -1.0f), ns, v);   // (2 * u01 - 1) * ns, ns = 0 without noise
       }
       return clampf(v, -clip_obs, clip_obs);
     };
@@ -516,7 +521,34 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       const float4 es0 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8);
       const float4 es1 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8 + 4);
       const float rx = es0.x, ry = es0.y, rz = es0.z, zo = es0.w, qz = es1.x, qw = es1.y;
-      float* orow = obs_t + e * O;
+      // ---- phase A: height-field indices of every pass, gathers in flight --------------------------
+      int raw[NP > 0 ? NP : 1];
+      if (NP > 0 && !plane) {
+        const float qz2 = mul_rn(qz, 2.0f);
+#pragma unroll
+        for (int it = 0; it < NP; ++it) {
+          // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op-for-op (no contraction):
+          //   t = 2 * cross(xyz, p); r = p + w*t + cross(xyz, t)
+          const float bx = px_l[it], by = py_l[it];
+          const float tx = -mul_rn(qz2, by), ty = mul_rn(qz2, bx);
+          float wx = add_rn(add_rn(bx, mul_rn(qw, tx)), -mul_rn(qz, ty));
+          float wy = add_rn(add_rn(by, mul_rn(qw, ty)), mul_rn(qz, tx));
+          wx = add_rn(add_rn(wx, rx), c.border_size);
+          wy = add_rn(add_rn(wy, ry), c.border_size);
+          // (points / horizontal_scale).long(): truncation toward zero (:842)
+          const float sx = MUL_RCP ? mul_rn(wx, inv_hs) : __fdiv_rn(wx, c.horizontal_scale);
+          const float sy = MUL_RCP ? mul_rn(wy, inv_hs) : __fdiv_rn(wy, c.horizontal_scale);
+          int ix = __float2int_rz(sx), iy = __float2int_rz(sy);
+          ix = min(max(ix, 0), max_px);
+          iy = min(max(iy, 0), max_py);
+          raw[it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
+        }
+      } else {
+#pragma unroll
+        for (int it = 0; it < (NP > 0 ? NP : 1); ++it) raw[it] = 0;
+      }
+      // ---- observation head (covers the gather latency) --------------------------------------------
+      float* orow = b.obs_buf + (size_t)env_e * O;
       const float* trow = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
       const unsigned eg = (unsigned)(c.env_id_offset + env_e);
       uint4 rnd = make_uint4(0, 0, 0, 0);
@@ -526,44 +558,25 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         if (lane < OH) orow[lane] = noisy(hrow[lane], trow, lane, rnd.x, ns_a);
         if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], trow, lane + 32, rnd.y, ns_b);
       }
+      // ---- phase B: heights -> observation columns -----------------------------------------------
       float part = 0.f;
-      if (H > 0) {
-        const float qz2 = mul_rn(qz, 2.0f);
 #pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          if (it * 32 >= H) break;
-          if (!TAPS && add_noise) {
-            if (it == 2) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
-            if (it == 6) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 2);
-          }
-          const int w = (it + 2) & 3;
-          const unsigned rbits = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
-          const int h = it * 32 + lane;
-          if (h < H) {
-            float hgt = 0.f;
-            if (!plane) {
-              // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op-for-op (no contraction):
-              //   t = 2 * cross(xyz, p); r = p + w*t + cross(xyz, t)
-              const float bx = px_l[it], by = py_l[it];
-              const float tx = -mul_rn(qz2, by), ty = mul_rn(qz2, bx);
-              float wx = add_rn(add_rn(bx, mul_rn(qw, tx)), -mul_rn(qz, ty));
-              float wy = add_rn(add_rn(by, mul_rn(qw, ty)), mul_rn(qz, tx));
-              wx = add_rn(add_rn(wx, rx), c.border_size);
-              wy = add_rn(add_rn(wy, ry), c.border_size);
-              // (points / horizontal_scale).long(): truncation toward zero (:842)
-              const float sx = MUL_RCP ? mul_rn(wx, inv_hs) : __fdiv_rn(wx, c.horizontal_scale);
-              const float sy = MUL_RCP ? mul_rn(wy, inv_hs) : __fdiv_rn(wy, c.horizontal_scale);
-              int ix = __float2int_rz(sx), iy = __float2int_rz(sy);
-              ix = min(max(ix, 0), max_px);
-              iy = min(max(iy, 0), max_py);
-              const int raw = __ldg(b.height_min3 + (size_t)ix * c.terrain_pitch + iy);
-              hgt = mul_rn((float)raw, c.vertical_scale);
-            }
-            if (b.measured_heights != nullptr) b.measured_heights[(size_t)env_e * H + h] = hgt;
-            part += sub_rn(rz, hgt);
-            const float v = clampf(sub_rn(zo, hgt), -1.f, 1.f) * c.obs_scale_height;
-            orow[OH + h] = noisy(v, trow, OH + h, rbits, ns_h[it]);
-          }
+      for (int it = 0; it < NP; ++it) {
+        if (!TAPS && add_noise) {
+          if (it == 2) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
+          if (it == 6) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 2);
+        }
+        const int w = (it + 2) & 3;
+        const unsigned rbits = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
+        const int h = it * 32 + lane;
+        const bool ok = h < H;
+        const float hgt = mul_rn((float)raw[it], c.vertical_scale);
+        part += ok ? sub_rn(rz, hgt) : 0.f;
+        const float v = clampf(sub_rn(zo, hgt), -1.f, 1.f) * c.obs_scale_height;
+        const float o = noisy(v, trow, ok ? OH + h : 0, rbits, ns_h[it]);
+        if (ok) {
+          orow[OH + h] = o;
+          if (materialise) b.measured_heights[(size_t)env_e * H + h] = hgt;
         }
       }
       if (a.bh_active) {   // sum_h (root_z - measured_height) for _reward_base_height (:871)
@@ -572,21 +585,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       }
     }
   }
-  fence_proxy_async_smem();   // obs tile / last_dof_vel rows -> visible to the bulk stores
+  fence_proxy_async_smem();   // last_dof_vel rows -> visible to the bulk store
   __syncthreads();
 
   // ---- tile outputs that do not depend on the rewards: issued by W1 while W0 runs stage 3 ---------
   if (full) {
     if (tid == 32) {
-      bulk_s2g(b.obs_buf + (size_t)env0 * O, obs_t, TILE * 4 * O);
       bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, TILE * 4 * D);   // last_actions = actions (:136)
       bulk_s2g(b.last_dof_vel + (size_t)env0 * D, sm + L.ldv, TILE * 4 * D);
       bulk_commit();
     }
   } else if (wic > 0) {
     const int t = tid - 32, nt = LGK_CTA_THREADS - 32;
-    float* og = b.obs_buf + (size_t)env0 * O;
-    for (int i = t; i < ne * O; i += nt) og[i] = obs_t[i];
     float* la = b.last_actions + (size_t)env0 * D;
     float* lv = b.last_dof_vel + (size_t)env0 * D;
     for (int i = t; i < ne * D; i += nt) { la[i] = sm[L.act + i]; lv[i] = sm[L.ldv + i]; }
@@ -756,9 +766,9 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 static inline int up4(int x) { return (x + 3) & ~3; }
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-template <int DT, bool TAPS, bool MUL_RCP>
+template <int DT, bool TAPS, bool MUL_RCP, int NP>
 static int launch_step(const StepArgs& args, int grid, size_t smem, cudaStream_t stream) {
-  auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP>;
+  auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP, NP>;
   static size_t configured = 0;   // per instantiation
   if (smem > 48 * 1024 && smem > configured) {
     LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -797,14 +807,11 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   L.sums = o; o += TILE * (args.num_rows > 0 ? args.num_rows : 1);
   L.head = o; o += up4(TILE * args.head_stride);
   L.scr = o;  o += TILE * SC_FIELDS;
-  // union: {contacts, torques, last_actions} (stage 1)  /  observation tile (stage 2 on)
-  const int u0 = o;
   L.cf = o;   o += up4(TILE * B3);
   L.tq = o;   o += up4(TILE * D);
   L.lact = o; o += up4(TILE * D);
-  L.obs = u0;
-  const int obs_end = u0 + up4(TILE * O);
-  L.total = o > obs_end ? o : obs_end;
+  L.obs = 0;
+  L.total = o;
   const size_t smem = (size_t)L.total * sizeof(float);
   if (smem > 200 * 1024) return LGK_ERR_DIM;
   // bulk (TMA) path: all tile base addresses and the episode-sum rows must be 16-byte aligned
@@ -815,12 +822,16 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   const int grid = args.num_tiles;
   const bool taps = c->rng_mode == LGK_RNG_TAPS;
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
-#define LGK_DISPATCH(DT)                                                            \
-  (taps ? (mul ? launch_step<DT, true, true>(args, grid, smem, stream)              \
-               : launch_step<DT, true, false>(args, grid, smem, stream))            \
-        : (mul ? launch_step<DT, false, true>(args, grid, smem, stream)             \
-               : launch_step<DT, false, false>(args, grid, smem, stream)))
-  if (D == 12) return LGK_DISPATCH(12);
-  return LGK_DISPATCH(0);
+  const int H = c->num_height_points;
+  const int np = (H + 31) / 32;   // scan passes of 32 points
+#define LGK_DISPATCH(DT, NP)                                                            \
+  (taps ? (mul ? launch_step<DT, true, true, NP>(args, grid, smem, stream)              \
+               : launch_step<DT, true, false, NP>(args, grid, smem, stream))            \
+        : (mul ? launch_step<DT, false, true, NP>(args, grid, smem, stream)             \
+               : launch_step<DT, false, false, NP>(args, grid, smem, stream)))
+  if (D == 12 && np == 6) return LGK_DISPATCH(12, 6);   // 187-point scan
+  if (D == 12 && np == 0) return LGK_DISPATCH(12, 0);   // blind
+  if (D == 12 && np <= 4) return LGK_DISPATCH(12, 4);   // Cassie's 121 points
+  return LGK_DISPATCH(0, 8);
 #undef LGK_DISPATCH
 }
