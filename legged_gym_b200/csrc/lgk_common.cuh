@@ -62,6 +62,15 @@ __device__ __forceinline__ uint4 lgk_philox(const uint64_t seed, unsigned long l
                          make_uint2((unsigned int)seed, (unsigned int)(seed >> 32)));
 }
 
+// same generator with the 10 round keys precomputed on the host (they depend on the seed only)
+__device__ __forceinline__ uint4 philox_keyed(const unsigned int (&pk)[20], unsigned long long step,
+                                              unsigned int env_global, unsigned int block) {
+  uint4 ctr = make_uint4(env_global, block, (unsigned int)step, (unsigned int)(step >> 32));
+#pragma unroll
+  for (int r = 0; r < 10; ++r) ctr = Philox::round(ctr, make_uint2(pk[2 * r], pk[2 * r + 1]));
+  return ctr;
+}
+
 // ---- exact-order fp32 helpers (no contraction) ----------------------------------------
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }

@@ -44,6 +44,7 @@ struct StepArgs {
   int bh_active;     // base_height term active
   int tma_ok;        // every tiled array 16-byte aligned and N % 4 == 0
   int num_rows;      // episode_sums rows: num_rewards (+1 with termination)
+  unsigned pk[20];   // Philox4x32-10 round keys of c.seed
 };
 
 // scratch fields (SoA, [field][TILE]) exchanged between the stages
@@ -243,7 +244,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           const float* t = b.tap_cmd_callback + (size_t)env * 3;
           u0 = t[0]; u1 = t[1]; u2 = t[2];
         } else {
-          const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_CMD_CB);
+          const uint4 r = philox_keyed(a.pk, csc, env_global, LGK_SITE_CMD_CB);
           u0 = u01(r.x); u1 = u01(r.y); u2 = u01(r.z);
         }
         resample_command(cmd, cr, heading_mode, u0, u1, u2);
@@ -269,7 +270,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (push_step) {   // _push_robots (:436-441): every env, after the body-frame velocities
         float u0, u1;
         if (TAPS) { u0 = b.tap_push[(size_t)env * 2]; u1 = b.tap_push[(size_t)env * 2 + 1]; }
-        else { const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_PUSH); u0 = u01(r.x); u1 = u01(r.y); }
+        else { const uint4 r = philox_keyed(a.pk, csc, env_global, LGK_SITE_PUSH); u0 = u01(r.x); u1 = u01(r.y); }
         const float range = 2.0f * c.max_push_vel_xy;
         rvel[0] = rand_affine(range, -c.max_push_vel_xy, u0);
         rvel[1] = rand_affine(range, -c.max_push_vel_xy, u1);
@@ -290,7 +291,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           level += (up ? 1 : 0) - (down ? 1 : 0);
           if (level >= c.max_terrain_level) {
             if (TAPS) level = b.tap_level[env];
-            else level = (long long)(lgk_philox(c.seed, csc, env_global, LGK_SITE_LEVEL).x % (unsigned)c.max_terrain_level);
+            else level = (long long)(philox_keyed(a.pk, csc, env_global, LGK_SITE_LEVEL).x % (unsigned)c.max_terrain_level);
           } else if (level < 0) {
             level = 0;
           }
@@ -310,8 +311,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           u[0] = b.tap_root_xy[(size_t)env * 2]; u[1] = b.tap_root_xy[(size_t)env * 2 + 1];
           for (int i = 0; i < 6; ++i) u[2 + i] = b.tap_root_vel[(size_t)env * 6 + i];
         } else {
-          const uint4 r0 = lgk_philox(c.seed, csc, env_global, LGK_SITE_ROOT);
-          const uint4 r1 = lgk_philox(c.seed, csc, env_global, LGK_SITE_ROOT + 1);
+          const uint4 r0 = philox_keyed(a.pk, csc, env_global, LGK_SITE_ROOT);
+          const uint4 r1 = philox_keyed(a.pk, csc, env_global, LGK_SITE_ROOT + 1);
           u[0] = u01(r0.x); u[1] = u01(r0.y); u[2] = u01(r0.z); u[3] = u01(r0.w);
           u[4] = u01(r1.x); u[5] = u01(r1.y); u[6] = u01(r1.z); u[7] = u01(r1.w);
         }
@@ -331,7 +332,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         for (int i = 0; i < 13; ++i) rw[i] = root[i];
         float c0, c1, c2;
         if (TAPS) { const float* t = b.tap_cmd_reset + (size_t)env * 3; c0 = t[0]; c1 = t[1]; c2 = t[2]; }
-        else { const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_CMD_RESET); c0 = u01(r.x); c1 = u01(r.y); c2 = u01(r.z); }
+        else { const uint4 r = philox_keyed(a.pk, csc, env_global, LGK_SITE_CMD_RESET); c0 = u01(r.x); c1 = u01(r.y); c2 = u01(r.z); }
         resample_command(cmd, cr, heading_mode, c0, c1, c2);
         ep = 0;
       } else if (push_step) {
@@ -409,7 +410,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
               const float* t = b.tap_dof + (size_t)env * D + d0;
               u[0] = t[0]; u[1] = t[1]; u[2] = t[2]; u[3] = t[3];
             } else {
-              const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_DOF + ch);
+              const uint4 r = philox_keyed(a.pk, csc, env_global, LGK_SITE_DOF + ch);
               u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
             }
           }
@@ -433,7 +434,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           if (reset) {
             if (TAPS) u = b.tap_dof[(size_t)env * D + d];
             else {
-              const uint4 r = lgk_philox(c.seed, csc, env_global, LGK_SITE_DOF + (d >> 2));
+              const uint4 r = philox_keyed(a.pk, csc, env_global, LGK_SITE_DOF + (d >> 2));
               const unsigned rr[4] = {r.x, r.y, r.z, r.w};
               u = u01(rr[d & 3]);
             }
@@ -486,22 +487,25 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 
   // =========================================== stage 2 ===========================================
   // one env at a time per warp, lanes over observation columns: noise on the head, then the H scan
-  // points in NP passes of 32.  All gathers of an env are issued before any is consumed.
+  // points in NP passes of 32.  All gathers of an env are issued before any is consumed.  The index
+  // chain runs on packed f32x2 instructions (x and y of a point share every operation; each packed
+  // op rounds its halves like the scalar op, so the result is bit-identical to the op-by-op chain).
   {
+    constexpr int NPA = NP > 0 ? NP : 1;
     const bool add_noise = flags & LGK_F_ADD_NOISE;
     const bool plane = flags & LGK_F_TERRAIN_PLANE;
-    const bool materialise = b.measured_heights != nullptr;
     const float inv_hs = 1.0f / c.horizontal_scale;
     const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
     const float clip_obs = c.clip_obs;
     // this lane's scan offsets and noise amplitudes (same for every env); lanes past H repeat point 0
-    float px_l[NP > 0 ? NP : 1], py_l[NP > 0 ? NP : 1], ns_h[NP > 0 ? NP : 1];
+    float2 pxy_l[NPA];
+    float ns_h[NPA];
 #pragma unroll
     for (int it = 0; it < NP; ++it) {
       const int h = it * 32 + lane;
       const bool ok = h < H;
-      px_l[it] = ok ? __ldg(b.height_points_xy + 2 * h) : 0.f;
-      py_l[it] = ok ? __ldg(b.height_points_xy + 2 * h + 1) : 0.f;
+      pxy_l[it].x = ok ? __ldg(b.height_points_xy + 2 * h) : 0.f;
+      pxy_l[it].y = ok ? __ldg(b.height_points_xy + 2 * h + 1) : 0.f;
       ns_h[it] = (ok && add_noise) ? __ldg(b.noise_scale_vec + OH + h) : 0.f;
     }
     const float ns_a = (add_noise && lane < OH) ? __ldg(b.noise_scale_vec + lane) : 0.f;
@@ -515,73 +519,81 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       }
       return clampf(v, -clip_obs, clip_obs);
     };
+    const float2 border2 = make_float2(c.border_size, c.border_size);
+    const float2 inv2 = make_float2(inv_hs, inv_hs);
     const int e_end = min(wic * 8 + 8, ne);
     for (int e = wic * 8; e < e_end; ++e) {
       const int env_e = env0 + e;
       const float4 es0 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8);
       const float4 es1 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8 + 4);
-      const float rx = es0.x, ry = es0.y, rz = es0.z, zo = es0.w, qz = es1.x, qw = es1.y;
+      const float rz = es0.z, zo = es0.w, qz = es1.x, qw = es1.y;
       // ---- phase A: height-field indices of every pass, gathers in flight --------------------------
-      int raw[NP > 0 ? NP : 1];
+      int raw[NPA];
       if (NP > 0 && !plane) {
+        // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op for op (no contraction):
+        //   t = 2 * cross(xyz, p) = (-2qz*py, 2qz*px); r = p + w*t + cross(xyz, t) = p + qw*t + (-qz*ty, qz*tx)
         const float qz2 = mul_rn(qz, 2.0f);
+        const float2 k_t = make_float2(-qz2, qz2), k_ts = make_float2(qz2, -qz2);
+        const float2 qw2 = make_float2(qw, qw), k_c = make_float2(-qz, qz), r2 = make_float2(es0.x, es0.y);
 #pragma unroll
         for (int it = 0; it < NP; ++it) {
-          // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op-for-op (no contraction):
-          //   t = 2 * cross(xyz, p); r = p + w*t + cross(xyz, t)
-          const float bx = px_l[it], by = py_l[it];
-          const float tx = -mul_rn(qz2, by), ty = mul_rn(qz2, bx);
-          float wx = add_rn(add_rn(bx, mul_rn(qw, tx)), -mul_rn(qz, ty));
-          float wy = add_rn(add_rn(by, mul_rn(qw, ty)), mul_rn(qz, tx));
-          wx = add_rn(add_rn(wx, rx), c.border_size);
-          wy = add_rn(add_rn(wy, ry), c.border_size);
+          const float2 p = pxy_l[it], pyx = make_float2(p.y, p.x);
+          const float2 t = __fmul2_rn(k_t, pyx);     // (tx, ty)
+          const float2 ts = __fmul2_rn(k_ts, p);     // (ty, tx)
+          float2 w = __fadd2_rn(p, __fmul2_rn(qw2, t));
+          w = __fadd2_rn(w, __fmul2_rn(k_c, ts));
+          w = __fadd2_rn(__fadd2_rn(w, r2), border2);
           // (points / horizontal_scale).long(): truncation toward zero (:842)
-          const float sx = MUL_RCP ? mul_rn(wx, inv_hs) : __fdiv_rn(wx, c.horizontal_scale);
-          const float sy = MUL_RCP ? mul_rn(wy, inv_hs) : __fdiv_rn(wy, c.horizontal_scale);
-          int ix = __float2int_rz(sx), iy = __float2int_rz(sy);
+          float2 sxy;
+          if (MUL_RCP) sxy = __fmul2_rn(w, inv2);
+          else sxy = make_float2(__fdiv_rn(w.x, c.horizontal_scale), __fdiv_rn(w.y, c.horizontal_scale));
+          int ix = __float2int_rz(sxy.x), iy = __float2int_rz(sxy.y);
           ix = min(max(ix, 0), max_px);
           iy = min(max(iy, 0), max_py);
           raw[it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
         }
       } else {
 #pragma unroll
-        for (int it = 0; it < (NP > 0 ? NP : 1); ++it) raw[it] = 0;
+        for (int it = 0; it < NPA; ++it) raw[it] = 0;
       }
       // ---- observation head (covers the gather latency) --------------------------------------------
       float* orow = b.obs_buf + (size_t)env_e * O;
       const float* trow = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
       const unsigned eg = (unsigned)(c.env_id_offset + env_e);
       uint4 rnd = make_uint4(0, 0, 0, 0);
-      if (!TAPS && add_noise) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane);
+      if (!TAPS && add_noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane);
       {
         const float* hrow = sm + L.head + e * HS;
         if (lane < OH) orow[lane] = noisy(hrow[lane], trow, lane, rnd.x, ns_a);
         if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], trow, lane + 32, rnd.y, ns_b);
       }
       // ---- phase B: heights -> observation columns -----------------------------------------------
-      float part = 0.f;
+      float hsum = 0.f;
 #pragma unroll
       for (int it = 0; it < NP; ++it) {
         if (!TAPS && add_noise) {
-          if (it == 2) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
-          if (it == 6) rnd = lgk_philox(c.seed, csc, eg, LGK_SITE_NOISE + 3 * lane + 2);
+          if (it == 2) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
+          if (it == 6) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane + 2);
         }
         const int w = (it + 2) & 3;
         const unsigned rbits = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
         const int h = it * 32 + lane;
         const bool ok = h < H;
         const float hgt = mul_rn((float)raw[it], c.vertical_scale);
-        part += ok ? sub_rn(rz, hgt) : 0.f;
+        hsum += ok ? hgt : 0.f;
         const float v = clampf(sub_rn(zo, hgt), -1.f, 1.f) * c.obs_scale_height;
         const float o = noisy(v, trow, ok ? OH + h : 0, rbits, ns_h[it]);
-        if (ok) {
-          orow[OH + h] = o;
-          if (materialise) b.measured_heights[(size_t)env_e * H + h] = hgt;
-        }
+        if (ok) orow[OH + h] = o;
       }
-      if (a.bh_active) {   // sum_h (root_z - measured_height) for _reward_base_height (:871)
-        part = warp_sum(part);
-        if (lane == 0) scr[SC_BH * TILE + e] = part;
+      if (b.measured_heights != nullptr) {   // optional materialisation of measured_heights [N,H]
+        float* mrow = b.measured_heights + (size_t)env_e * H;
+#pragma unroll
+        for (int it = 0; it < NP; ++it)
+          if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn((float)raw[it], c.vertical_scale);
+      }
+      if (a.bh_active) {   // mean_h(root_z - measured_height) = root_z - mean_h(height), _reward_base_height (:871)
+        hsum = warp_sum(hsum);
+        if (lane == 0) scr[SC_BH * TILE + e] = H > 0 ? rz - hsum / (float)H : rz;
       }
     }
   }
@@ -605,11 +617,42 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   // =========================================== stage 3 ===========================================
   // W0, lane = env: reward terms in the reference's order (:195-212), episode sums, statistics
   if (wic == 0) {
-    DofAcc acc;
-#pragma unroll
-    for (int i = 0; i < 10; ++i) acc.v[i] = scr[(SC_J1 + i) * TILE + lane] + scr[(SC_J2 + i) * TILE + lane];
     const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
-    const float r_air = scr[SC_RAIR * TILE + lane] * ((cn > 0.1f) ? 1.f : 0.f);
+    // every term's value for this lane's env -> table [term][lane] (the contact rows are dead by now)
+    float* rv = sm + L.cf;
+    {
+      auto J = [&](int k) { return scr[(SC_J1 + k) * TILE + lane] + scr[(SC_J2 + k) * TILE + lane]; };
+      auto put = [&](int term, float v) { rv[term * TILE + lane] = v; };
+      put(LGK_REW_ACTION_RATE, J(A_ARATE));
+      put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
+      {
+        const float d = scr[SC_BH * TILE + lane] - c.base_height_target;
+        put(LGK_REW_BASE_HEIGHT, d * d);
+      }
+      put(LGK_REW_COLLISION, scr[SC_COLL * TILE + lane]);
+      put(LGK_REW_DOF_ACC, J(A_ACC2));
+      put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
+      put(LGK_REW_DOF_VEL, J(A_QD2));
+      put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
+      put(LGK_REW_ENERGY, J(A_ENERGY));
+      put(LGK_REW_FEET_AIR_TIME, scr[SC_RAIR * TILE + lane] * ((cn > 0.1f) ? 1.f : 0.f));
+      put(LGK_REW_FEET_CONTACT_FORCES, scr[SC_FFP * TILE + lane]);
+      put(LGK_REW_HIP_MOTION, J(A_HIP));
+      put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
+      put(LGK_REW_NO_FLY, scr[SC_NOFLY * TILE + lane]);
+      put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
+      put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
+      put(LGK_REW_STUMBLE, scr[SC_STUMBLE * TILE + lane]);
+      put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
+      put(LGK_REW_TORQUES, J(A_TQ2));
+      {
+        const float e = cmd_rew.z - bav[2];
+        put(LGK_REW_TRACKING_ANG_VEL, expf(-(e * e) / c.tracking_sigma));
+        const float ex = cmd_rew.x - blv[0], ey = cmd_rew.y - blv[1];
+        put(LGK_REW_TRACKING_LIN_VEL, expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma));
+      }
+    }
+    __syncwarp();
     const bool any_reset = reset_mask != 0u;
     float* sums = sm + L.sums;
     float rew = 0.f;
@@ -617,44 +660,13 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     for (int i = 0; i < num_rows; ++i) {
       float r = 0.f;
       if (i < c.num_rewards) {
-        float v = 0.f;
-        switch (c.rewards[i].term) {
-          case LGK_REW_ACTION_RATE: v = acc.v[A_ARATE]; break;
-          case LGK_REW_ANG_VEL_XY: v = fmaf(bav[1], bav[1], bav[0] * bav[0]); break;
-          case LGK_REW_BASE_HEIGHT: {
-            const float bh = H > 0 ? scr[SC_BH * TILE + lane] / (float)H : z_pre;
-            const float d = bh - c.base_height_target;
-            v = d * d;
-          } break;
-          case LGK_REW_COLLISION: v = scr[SC_COLL * TILE + lane]; break;
-          case LGK_REW_DOF_ACC: v = acc.v[A_ACC2]; break;
-          case LGK_REW_DOF_POS_LIMITS: v = acc.v[A_POSLIM]; break;
-          case LGK_REW_DOF_VEL: v = acc.v[A_QD2]; break;
-          case LGK_REW_DOF_VEL_LIMITS: v = acc.v[A_VELLIM]; break;
-          case LGK_REW_ENERGY: v = acc.v[A_ENERGY]; break;
-          case LGK_REW_FEET_AIR_TIME: v = r_air; break;
-          case LGK_REW_FEET_CONTACT_FORCES: v = scr[SC_FFP * TILE + lane]; break;
-          case LGK_REW_HIP_MOTION: v = acc.v[A_HIP]; break;
-          case LGK_REW_LIN_VEL_Z: v = blv[2] * blv[2]; break;
-          case LGK_REW_NO_FLY: v = scr[SC_NOFLY * TILE + lane]; break;
-          case LGK_REW_ORIENTATION: v = fmaf(grav[1], grav[1], grav[0] * grav[0]); break;
-          case LGK_REW_STAND_STILL: v = acc.v[A_STAND] * ((cn < 0.1f) ? 1.f : 0.f); break;
-          case LGK_REW_STUMBLE: v = scr[SC_STUMBLE * TILE + lane]; break;
-          case LGK_REW_TORQUE_LIMITS: v = acc.v[A_TQLIM]; break;
-          case LGK_REW_TORQUES: v = acc.v[A_TQ2]; break;
-          case LGK_REW_TRACKING_ANG_VEL: {
-            const float e = cmd_rew.z - bav[2];
-            v = expf(-(e * e) / c.tracking_sigma);
-          } break;
-          case LGK_REW_TRACKING_LIN_VEL: {
-            const float ex = cmd_rew.x - blv[0], ey = cmd_rew.y - blv[1];
-            v = expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma);
-          } break;
-          case LGK_REW_EXTERNAL:
-            v = (active && b.ext_rewards != nullptr) ? b.ext_rewards[(size_t)ext_k * N + env] : 0.f;
-            ++ext_k;
-            break;
-          default: break;
+        const int term = c.rewards[i].term;
+        float v;
+        if (term == LGK_REW_EXTERNAL) {
+          v = (active && b.ext_rewards != nullptr) ? b.ext_rewards[(size_t)ext_k * N + env] : 0.f;
+          ++ext_k;
+        } else {
+          v = rv[term * TILE + lane];
         }
         r = mul_rn(v, c.rewards[i].scale);
         rew = add_rn(rew, r);
@@ -787,6 +799,10 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   args.num_rows = c->num_rewards + ((c->flags & LGK_F_HAS_TERMINATION) ? 1 : 0);
   args.head_stride = OH | 1;
   args.num_tiles = (c->num_envs + TILE - 1) / TILE;
+  for (int r = 0; r < 10; ++r) {
+    args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
+    args.pk[2 * r + 1] = (unsigned)(c->seed >> 32) + (unsigned)r * 0xBB67AE85u;
+  }
   args.air_active = 0;
   args.bh_active = 0;
   for (int i = 0; i < c->num_rewards; ++i) {
@@ -807,7 +823,7 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   L.sums = o; o += TILE * (args.num_rows > 0 ? args.num_rows : 1);
   L.head = o; o += up4(TILE * args.head_stride);
   L.scr = o;  o += TILE * SC_FIELDS;
-  L.cf = o;   o += up4(TILE * B3);
+  L.cf = o;   o += (up4(TILE * B3) > TILE * LGK_REW_COUNT) ? up4(TILE * B3) : TILE * LGK_REW_COUNT;   // later: reward table
   L.tq = o;   o += up4(TILE * D);
   L.lact = o; o += up4(TILE * D);
   L.obs = 0;
