@@ -12,7 +12,7 @@
 struct LgkWorkspace {
   unsigned long long step_counter;   // == reference common_step_counter (legged_robot.py:119)
   unsigned int done_ticket;          // CTAs finished in the current launch
-  unsigned int pad0;
+  unsigned int mask_ticket;          // CTAs that have published their reset / resample masks
   int level_sum[2];                  // sum(terrain_levels) accumulators, indexed by step parity
   unsigned int pad1[2];
   float stats[2][LGK_MAX_REWARDS + 4];   // per-parity: sum over reset ids of episode_sums[k]

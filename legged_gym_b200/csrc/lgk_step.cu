@@ -152,24 +152,29 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 
   // ---- load the tile ------------------------------------------------------------------------
   if (full) {
-    if (tid == 0) {
-      mbar_init(&s_bar, 1);
+    if (wic == 0) {
       const unsigned f4 = TILE * 4;   // bytes per float column of the tile
-      unsigned bytes = f4 * (13 + 2 * D + B3 + 3 * D + D + 4 + F + 2 + num_rows) + (has_levels ? f4 * 2 : 0);
-      mbar_expect_tx(&s_bar, bytes);
-      bulk_g2s(sm + L.root, b.root_states + (size_t)env0 * 13, f4 * 13, &s_bar);
-      bulk_g2s(sm + L.ep, b.episode_length_buf + env0, f4 * 2, &s_bar);
-      bulk_g2s(sm + L.cf, b.contact_forces + (size_t)env0 * B3, f4 * B3, &s_bar);
-      bulk_g2s(sm + L.cmd, b.commands + (size_t)env0 * 4, f4 * 4, &s_bar);
-      bulk_g2s(sm + L.dof, b.dof_state + (size_t)env0 * 2 * D, f4 * 2 * D, &s_bar);
-      bulk_g2s(sm + L.act, b.actions + (size_t)env0 * D, f4 * D, &s_bar);
-      bulk_g2s(sm + L.lact, b.last_actions + (size_t)env0 * D, f4 * D, &s_bar);
-      bulk_g2s(sm + L.tq, b.torques + (size_t)env0 * D, f4 * D, &s_bar);
-      bulk_g2s(sm + L.ldv, b.last_dof_vel + (size_t)env0 * D, f4 * D, &s_bar);
-      bulk_g2s(sm + L.fat, b.feet_air_time + (size_t)env0 * F, f4 * F, &s_bar);
-      if (has_levels) bulk_g2s(sm + L.lvl, b.terrain_levels + env0, f4 * 2, &s_bar);
-      for (int r = 0; r < num_rows; ++r)
-        bulk_g2s(sm + L.sums + r * TILE, b.episode_sums + (size_t)r * N + env0, f4, &s_bar);
+      if (lane == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_expect_tx(&s_bar, f4 * (13 + 2 * D + B3 + 3 * D + D + 4 + F + 2 + num_rows) + (has_levels ? f4 * 2 : 0));
+      }
+      __syncwarp();
+      switch (lane) {   // one bulk copy per lane: the issue cost is spread instead of serialised on one thread
+        case 0: bulk_g2s(sm + L.root, b.root_states + (size_t)env0 * 13, f4 * 13, &s_bar); break;
+        case 1: bulk_g2s(sm + L.ep, b.episode_length_buf + env0, f4 * 2, &s_bar); break;
+        case 2: bulk_g2s(sm + L.cf, b.contact_forces + (size_t)env0 * B3, f4 * B3, &s_bar); break;
+        case 3: bulk_g2s(sm + L.cmd, b.commands + (size_t)env0 * 4, f4 * 4, &s_bar); break;
+        case 4: bulk_g2s(sm + L.dof, b.dof_state + (size_t)env0 * 2 * D, f4 * 2 * D, &s_bar); break;
+        case 5: bulk_g2s(sm + L.act, b.actions + (size_t)env0 * D, f4 * D, &s_bar); break;
+        case 6: bulk_g2s(sm + L.lact, b.last_actions + (size_t)env0 * D, f4 * D, &s_bar); break;
+        case 7: bulk_g2s(sm + L.tq, b.torques + (size_t)env0 * D, f4 * D, &s_bar); break;
+        case 8: bulk_g2s(sm + L.ldv, b.last_dof_vel + (size_t)env0 * D, f4 * D, &s_bar); break;
+        case 9: bulk_g2s(sm + L.fat, b.feet_air_time + (size_t)env0 * F, f4 * F, &s_bar); break;
+        case 10: if (has_levels) bulk_g2s(sm + L.lvl, b.terrain_levels + env0, f4 * 2, &s_bar); break;
+        default:
+          for (int r = lane - 11; r < num_rows; r += 21)
+            bulk_g2s(sm + L.sums + r * TILE, b.episode_sums + (size_t)r * N + env0, f4, &s_bar);
+      }
     }
     __syncthreads();          // barrier initialised before anyone polls it
     mbar_wait(&s_bar, 0);
@@ -367,13 +372,16 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
     const unsigned resample_mask = __ballot_sync(LGK_FULL_MASK, active && resample_cb);
     unsigned* mask_base = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + LGK_WS_HEADER_BYTES);
-    if (lane == 0) {
-      mask_base[tile] = reset_mask;
-      mask_base[lgk_max_warps(N) + tile] = resample_mask;
-    }
     if ((flags & LGK_F_TERRAIN_CURRICULUM) && has_levels) {
       const int s = warp_sum_int(active ? level_contrib : 0);
       if (lane == 0 && s != 0) atomicAdd(&ws->level_sum[parity], s);
+    }
+    if (lane == 0) {
+      mask_base[tile] = reset_mask;
+      mask_base[lgk_max_warps(N) + tile] = resample_mask;
+      // mask ticket: the CTA that publishes the last pair of masks compacts the id lists (below)
+      __threadfence();
+      s_is_last = (atomicAdd(&ws->mask_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
     }
   }
   else if (wic == 1 || wic == 2) {
@@ -483,7 +491,65 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     scr[SC_STUMBLE * TILE + lane] = stumble ? 1.f : 0.f;
     scr[SC_NOFLY * TILE + lane] = (nofly == 1) ? 1.f : 0.f;
   }
+  fence_proxy_async_smem();   // last_dof_vel rows (W1 / W2) -> visible to the bulk store
   __syncthreads();
+
+  // ---- tile outputs that are complete after stage 1 -------------------------------------------------
+  if (full) {
+    if (tid == 32) {
+      bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, TILE * 4 * D);   // last_actions = actions (:136)
+      bulk_s2g(b.last_dof_vel + (size_t)env0 * D, sm + L.ldv, TILE * 4 * D);
+      bulk_commit();
+    }
+  } else if (wic > 0) {
+    const int t = tid - 32, nt = LGK_CTA_THREADS - 32;
+    float* la = b.last_actions + (size_t)env0 * D;
+    float* lv = b.last_dof_vel + (size_t)env0 * D;
+    for (int i = t; i < ne * D; i += nt) { la[i] = sm[L.act + i]; lv[i] = sm[L.ldv + i]; }
+  }
+
+  // ---- ordered compaction of the reset / resample id lists (one CTA per launch gets here) ----------
+  if (s_is_last) {
+    __threadfence();
+    const int nt = a.num_tiles;
+    const int max_warps = lgk_max_warps(N);
+    const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
+    const volatile unsigned* rm = mask_base;
+    const volatile unsigned* sv = mask_base + max_warps;
+    const int per = (nt + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
+    const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
+    int c0 = 0, c1 = 0;
+    for (int t = t0; t < t1; ++t) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
+    // block-wide exclusive scan of (c0, c1): shuffles inside a warp, 4 warp totals through shared memory
+    int i0 = c0, i1 = c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y0 = __shfl_up_sync(LGK_FULL_MASK, i0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, i1, o);
+      if (lane >= o) { i0 += y0; i1 += y1; }
+    }
+    if (lane == 31) { s_scan[0][wic + 1] = i0; s_scan[1][wic + 1] = i1; }
+    if (tid == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
+    __syncthreads();
+    int base0 = 0, base1 = 0, n_reset = 0, n_resample = 0;
+#pragma unroll
+    for (int w = 0; w < LGK_WARPS_PER_CTA; ++w) {
+      if (w < wic) { base0 += s_scan[0][w + 1]; base1 += s_scan[1][w + 1]; }
+      n_reset += s_scan[0][w + 1];
+      n_resample += s_scan[1][w + 1];
+    }
+    int o0 = base0 + i0 - c0, o1 = base1 + i1 - c1;
+    for (int t = t0; t < t1; ++t) {
+      unsigned m = rm[t];
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = t * TILE + bit; }
+      m = sv[t];
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = t * TILE + bit; }
+    }
+    if (tid == 0) {
+      b.counts[0] = n_reset;
+      b.counts[1] = n_resample;
+      ws->mask_ticket = 0u;
+    }
+  }
 
   // =========================================== stage 2 ===========================================
   // one env at a time per warp, lanes over observation columns: noise on the head, then the H scan
@@ -597,26 +663,17 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       }
     }
   }
-  fence_proxy_async_smem();   // last_dof_vel rows -> visible to the bulk store
-  __syncthreads();
-
-  // ---- tile outputs that do not depend on the rewards: issued by W1 while W0 runs stage 3 ---------
-  if (full) {
-    if (tid == 32) {
-      bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, TILE * 4 * D);   // last_actions = actions (:136)
-      bulk_s2g(b.last_dof_vel + (size_t)env0 * D, sm + L.ldv, TILE * 4 * D);
-      bulk_commit();
-    }
-  } else if (wic > 0) {
-    const int t = tid - 32, nt = LGK_CTA_THREADS - 32;
-    float* la = b.last_actions + (size_t)env0 * D;
-    float* lv = b.last_dof_vel + (size_t)env0 * D;
-    for (int i = t; i < ne * D; i += nt) { la[i] = sm[L.act + i]; lv[i] = sm[L.ldv + i]; }
+  // W1..W3 are done: they signal the base-height partial sums and leave; W0 waits for all of them
+  if (wic != 0) {
+    asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
+    if (full && tid == 32) bulk_wait_read_all();   // shared memory must outlive the bulk stores that read it
+    return;
   }
+  asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
 
   // =========================================== stage 3 ===========================================
   // W0, lane = env: reward terms in the reference's order (:195-212), episode sums, statistics
-  if (wic == 0) {
+  {
     const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
     // every term's value for this lane's env -> table [term][lane] (the contact rows are dead by now)
     float* rv = sm + L.cf;
@@ -699,66 +756,28 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         bulk_commit();
       }
     }
-    // ---- completion ticket: masks / statistics of this tile are published before it is taken -----
+    // ---- statistics ticket: the last W0 to get here finalises the episode statistics --------------
+    unsigned last = 0u;
     if (lane == 0) {
       __threadfence();
-      s_is_last = (atomicAdd(&ws->done_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+      last = (atomicAdd(&ws->done_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+      if (full) bulk_wait_read_all();   // shared memory must outlive the bulk stores that read it
     }
-  }
-  __syncthreads();
-  // shared memory must outlive the bulk stores that read it
-  if (full && (tid == 0 || tid == 32)) bulk_wait_read_all();
-  if (!s_is_last) return;
-
-  // ---- last CTA: ordered compaction of the id lists, statistics, counters ---------------------
-  __threadfence();
-  {
-    const int nt = a.num_tiles;
-    const int max_warps = lgk_max_warps(N);
-    const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
-    const volatile unsigned* rm = mask_base;
-    const volatile unsigned* sv = mask_base + max_warps;
-    const int per = (nt + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
-    const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
-    int c0 = 0, c1 = 0;
-    for (int t = t0; t < t1; ++t) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
-    // block-wide exclusive scan of (c0, c1): shuffles inside a warp, 4 warp totals through shared memory
-    int i0 = c0, i1 = c1;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y0 = __shfl_up_sync(LGK_FULL_MASK, i0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, i1, o);
-      if (lane >= o) { i0 += y0; i1 += y1; }
-    }
-    if (lane == 31) { s_scan[0][wic + 1] = i0; s_scan[1][wic + 1] = i1; }
-    if (tid == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
-    __syncthreads();
-    int base0 = 0, base1 = 0, n_reset = 0, n_resample = 0;
-#pragma unroll
-    for (int w = 0; w < LGK_WARPS_PER_CTA; ++w) {
-      if (w < wic) { base0 += s_scan[0][w + 1]; base1 += s_scan[1][w + 1]; }
-      n_reset += s_scan[0][w + 1];
-      n_resample += s_scan[1][w + 1];
-    }
-    int o0 = base0 + i0 - c0, o1 = base1 + i1 - c1;
-    for (int t = t0; t < t1; ++t) {
-      unsigned m = rm[t];
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = t * TILE + bit; }
-      m = sv[t];
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = t * TILE + bit; }
-    }
+    last = __shfl_sync(LGK_FULL_MASK, last, 0);
+    if (!last) return;
+    __threadfence();
+    const int n_reset = ((volatile int*)b.counts)[0];
     const int level_sum = ((volatile int*)ws->level_sum)[parity];
     volatile float* st = ws->stats[parity];
-    if (tid < num_rows) {
-      const float s = st[tid];
-      b.episode_stats[tid] = s;
-      b.episode_stats[num_rows + 4 + tid] += s;   // running sums since the host last cleared them
+    if (lane < num_rows) {
+      const float s = st[lane];
+      b.episode_stats[lane] = s;
+      b.episode_stats[num_rows + 4 + lane] += s;   // running sums since the host last cleared them
       if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
-        b.extras[tid] = (s / (float)n_reset) / c.max_episode_length_s;
-      ws->stats[parity ^ 1][tid] = 0.f;   // next step's accumulators
+        b.extras[lane] = (s / (float)n_reset) / c.max_episode_length_s;
+      ws->stats[parity ^ 1][lane] = 0.f;   // next step's accumulators
     }
-    if (tid == 0) {
-      b.counts[0] = n_reset;
-      b.counts[1] = n_resample;
+    if (lane == 0) {
       b.episode_stats[num_rows] = (float)n_reset;
       b.episode_stats[num_rows + 1] = (float)level_sum;
       b.episode_stats[num_rows + 2] = (float)N;
