@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LGK_ABI_VERSION 3
+#define LGK_ABI_VERSION 4
 
 #define LGK_MAX_DOF     16   /* num_dof = num_actions (12 for every shipped robot)        */
 #define LGK_MAX_FEET     8
@@ -135,7 +135,7 @@ typedef struct LgkConsts {
   int32_t  control_type;      /* LgkControlType                                            */
   int32_t  index_math;        /* LgkIndexMath                                              */
   int32_t  rng_mode;          /* LgkRngMode                                                */
-  int32_t  envs_per_warp;     /* 0 = library picks                                         */
+  int32_t  envs_per_cta;      /* envs per persistent CTA; 0 = library balances over the SMs */
   /* timing */
   float    dt;                /* decimation * sim.dt                                       */
   float    sim_dt;

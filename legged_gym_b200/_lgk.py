@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-LGK_ABI_VERSION = 3
+LGK_ABI_VERSION = 4
 LGK_MAX_DOF = 16
 LGK_MAX_FEET = 8
 LGK_MAX_PEN = 16
@@ -64,7 +64,7 @@ class LgkConsts(C.Structure):
         ("num_envs", _I), ("num_dof", _I), ("num_bodies", _I), ("num_feet", _I), ("num_pen", _I), ("num_term", _I),
         ("num_height_points", _I), ("num_obs", _I), ("num_rewards", _I), ("num_commands", _I),
         ("env_id_offset", _I), ("flags", C.c_uint32), ("control_type", _I), ("index_math", _I), ("rng_mode", _I),
-        ("envs_per_warp", _I),
+        ("envs_per_cta", _I),
         ("dt", _F), ("sim_dt", _F),
         ("max_episode_length", C.c_int64), ("resample_interval", C.c_int64), ("push_interval", C.c_int64),
         ("max_episode_length_s", _F), ("max_push_vel_xy", _F),
@@ -118,7 +118,7 @@ class LgkError(RuntimeError):
 
 
 _LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "liblgk.so")
+LIB_PATH = os.environ.get("LGK_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "liblgk.so")
 
 
 def lib_path() -> str:

@@ -38,7 +38,8 @@ struct StepArgs {
   LgkConsts c;
   LgkBuffers b;
   TileLayout L;
-  int num_tiles;
+  int per;           // envs per CTA (multiple of 4): CTA c owns envs [c*per, (c+1)*per), in sub-tiles of <= 32
+  int max_sub;       // sub-tiles per CTA = ceil(per / 32)
   int head_stride;   // odd row stride of the staged observation head
   int air_active;    // feet_air_time term active (:945-948 only run then)
   int bh_active;     // base_height term active
@@ -139,10 +140,9 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int tid = threadIdx.x;
   const int lane = tid & 31;
   const int wic = tid >> 5;
-  const int tile = blockIdx.x;
-  const int env0 = tile * TILE;
-  const int ne = min(TILE, N - env0);
-  const bool full = (ne == TILE) && a.tma_ok;
+  const int cta_env0 = blockIdx.x * a.per;
+  const int cta_ne = min(a.per, N - cta_env0);
+  const int nsub = (cta_ne + TILE - 1) / TILE;
   const bool has_levels = b.terrain_levels != nullptr;
 
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
@@ -150,12 +150,28 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int parity = (int)(csc & 1ull);
   const bool push_step = (flags & LGK_F_PUSH_ROBOTS) && (csc % (unsigned long long)c.push_interval == 0ull);
 
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    s_is_last = 0u;
+  }
+  __syncthreads();          // barrier initialised before anyone polls it
+
+  // Persistent CTA: sub-tiles of its env range, one after the other (grid = resident CTA slots, so
+  // every slot gets the same number of envs and all finish together -- no partial last wave).
+  for (int sub = 0; sub < nsub; ++sub) {
+  const int env0 = cta_env0 + sub * TILE;
+  const int ne = min(TILE, cta_ne - sub * TILE);
+  const bool full = a.tma_ok && ((ne & 3) == 0);   // bulk copies need 16-byte multiples: 4 envs x 4 B
+  const int tile = blockIdx.x * a.max_sub + sub;   // slot of this sub-tile's reset / resample masks
+  const bool last_sub = sub == nsub - 1;
+
   // ---- load the tile ------------------------------------------------------------------------
   if (full) {
     if (wic == 0) {
-      const unsigned f4 = TILE * 4;   // bytes per float column of the tile
+      const unsigned f4 = ne * 4;   // bytes per float column of the tile
       if (lane == 0) {
-        mbar_init(&s_bar, 1);
+        bulk_wait_read_all();       // the previous sub-tile's episode-sum stores have left shared memory
+        fence_proxy_async_smem();   // generic reads of the previous sub-tile before the async writes
         mbar_expect_tx(&s_bar, f4 * (13 + 2 * D + B3 + 3 * D + D + 4 + F + 2 + num_rows) + (has_levels ? f4 * 2 : 0));
       }
       __syncwarp();
@@ -176,9 +192,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
             bulk_g2s(sm + L.sums + r * TILE, b.episode_sums + (size_t)r * N + env0, f4, &s_bar);
       }
     }
-    __syncthreads();          // barrier initialised before anyone polls it
-    mbar_wait(&s_bar, 0);
+    mbar_wait(&s_bar, sub & 1);
   } else {
+    if (tid == 0) bulk_wait_read_all();
+    __syncthreads();          // W0 may still be in stage 3 of the previous sub-tile
     auto ld = [&](int off, const void* g, int words_per_env) {
       const unsigned* src = reinterpret_cast<const unsigned*>(g);
       unsigned* dst = reinterpret_cast<unsigned*>(sm + off);
@@ -380,8 +397,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       mask_base[tile] = reset_mask;
       mask_base[lgk_max_warps(N) + tile] = resample_mask;
       // mask ticket: the CTA that publishes the last pair of masks compacts the id lists (below)
-      __threadfence();
-      s_is_last = (atomicAdd(&ws->mask_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+      if (last_sub) {
+        __threadfence();
+        s_is_last = (atomicAdd(&ws->mask_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+      }
     }
   }
   else if (wic == 1 || wic == 2) {
@@ -497,8 +516,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   // ---- tile outputs that are complete after stage 1 -------------------------------------------------
   if (full) {
     if (tid == 32) {
-      bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, TILE * 4 * D);   // last_actions = actions (:136)
-      bulk_s2g(b.last_dof_vel + (size_t)env0 * D, sm + L.ldv, TILE * 4 * D);
+      bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, ne * 4 * D);   // last_actions = actions (:136)
+      bulk_s2g(b.last_dof_vel + (size_t)env0 * D, sm + L.ldv, ne * 4 * D);
       bulk_commit();
     }
   } else if (wic > 0) {
@@ -511,15 +530,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   // ---- ordered compaction of the reset / resample id lists (one CTA per launch gets here) ----------
   if (s_is_last) {
     __threadfence();
-    const int nt = a.num_tiles;
+    const int nt = gridDim.x * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
     const int max_warps = lgk_max_warps(N);
     const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
     const volatile unsigned* rm = mask_base;
     const volatile unsigned* sv = mask_base + max_warps;
     const int per = (nt + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
     const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
+    // slots of sub-tiles past a CTA's range were never written this launch: skip them
+    auto slot_env0 = [&](int t) { const int cta = t / a.max_sub, k = t - cta * a.max_sub; return cta * a.per + k * TILE; };
+    auto slot_ok = [&](int t) { const int cta = t / a.max_sub, k = t - cta * a.max_sub; return k * TILE < min(a.per, N - cta * a.per); };
     int c0 = 0, c1 = 0;
-    for (int t = t0; t < t1; ++t) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
+    for (int t = t0; t < t1; ++t) if (slot_ok(t)) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
     // block-wide exclusive scan of (c0, c1): shuffles inside a warp, 4 warp totals through shared memory
     int i0 = c0, i1 = c1;
 #pragma unroll
@@ -539,10 +561,12 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     }
     int o0 = base0 + i0 - c0, o1 = base1 + i1 - c1;
     for (int t = t0; t < t1; ++t) {
+      if (!slot_ok(t)) continue;
+      const int e0 = slot_env0(t);
       unsigned m = rm[t];
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = t * TILE + bit; }
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
       m = sv[t];
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = t * TILE + bit; }
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = e0 + bit; }
     }
     if (tid == 0) {
       b.counts[0] = n_reset;
@@ -587,8 +611,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     };
     const float2 border2 = make_float2(c.border_size, c.border_size);
     const float2 inv2 = make_float2(inv_hs, inv_hs);
-    const int e_end = min(wic * 8 + 8, ne);
-    for (int e = wic * 8; e < e_end; ++e) {
+    for (int e = wic; e < ne; e += LGK_WARPS_PER_CTA) {   // envs of the sub-tile dealt round-robin to the warps
       const int env_e = env0 + e;
       const float4 es0 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8);
       const float4 es1 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8 + 4);
@@ -665,9 +688,9 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   }
   // W1..W3 are done: they signal the base-height partial sums and leave; W0 waits for all of them
   if (wic != 0) {
+    if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows: W0 may refill them
     asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
-    if (full && tid == 32) bulk_wait_read_all();   // shared memory must outlive the bulk stores that read it
-    return;
+    continue;
   }
   asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
 
@@ -752,16 +775,20 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       __syncwarp();
       if (lane == 0) {
         for (int r = 0; r < num_rows; ++r)
-          bulk_s2g(b.episode_sums + (size_t)r * N + env0, sums + r * TILE, TILE * 4);
+          bulk_s2g(b.episode_sums + (size_t)r * N + env0, sums + r * TILE, ne * 4);
         bulk_commit();
       }
     }
+  }
+  }   // sub-tiles
+  if (wic != 0) return;
+  {
     // ---- statistics ticket: the last W0 to get here finalises the episode statistics --------------
     unsigned last = 0u;
     if (lane == 0) {
       __threadfence();
       last = (atomicAdd(&ws->done_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
-      if (full) bulk_wait_read_all();   // shared memory must outlive the bulk stores that read it
+      bulk_wait_read_all();   // shared memory must outlive the bulk stores that read it
     }
     last = __shfl_sync(LGK_FULL_MASK, last, 0);
     if (!last) return;
@@ -817,7 +844,6 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   const int OH = 12 + 3 * D;
   args.num_rows = c->num_rewards + ((c->flags & LGK_F_HAS_TERMINATION) ? 1 : 0);
   args.head_stride = OH | 1;
-  args.num_tiles = (c->num_envs + TILE - 1) / TILE;
   for (int r = 0; r < 10; ++r) {
     args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
     args.pk[2 * r + 1] = (unsigned)(c->seed >> 32) + (unsigned)r * 0xBB67AE85u;
@@ -854,7 +880,23 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
                 al16(b->torques) && al16(b->actions) && al16(b->last_actions) && al16(b->last_dof_vel) &&
                 al16(b->commands) && al16(b->feet_air_time) && al16(b->episode_length_buf) &&
                 al16(b->episode_sums) && al16(b->obs_buf) && (b->terrain_levels == nullptr || al16(b->terrain_levels));
-  const int grid = args.num_tiles;
+  // persistent grid: one CTA per resident slot, equal env ranges (multiples of 4 envs)
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0;
+    LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
+    LGK_CUDA_RETURN_IF(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  int per_sm = (int)((227u * 1024u) / (smem + 1024u));
+  if (per_sm > LGK_MIN_CTAS) per_sm = LGK_MIN_CTAS;
+  if (per_sm < 1) per_sm = 1;
+  const int slots = num_sms * per_sm;
+  int per = (c->num_envs + slots - 1) / slots;
+  per = (per + 3) & ~3;
+  if (c->envs_per_cta > 0) per = (c->envs_per_cta + 3) & ~3;   // caller's choice (tests force multi-sub-tile ranges)
+  args.per = per;
+  args.max_sub = (per + TILE - 1) / TILE;
+  const int grid = (c->num_envs + per - 1) / per;
   const bool taps = c->rng_mode == LGK_RNG_TAPS;
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
   const int H = c->num_height_points;

@@ -644,7 +644,7 @@ class LeggedRobot(BaseTask):
             index_math = int(getattr(cfg.env, "index_math", _lgk.INDEX_MATH_TORCH_CUDA))
         c.index_math = index_math
         c.rng_mode = rng_mode
-        c.envs_per_warp = int(getattr(cfg.env, "envs_per_warp", 0))
+        c.envs_per_cta = int(getattr(cfg.env, "envs_per_cta", 0))
         c.dt, c.sim_dt = self.dt, self.sim_params.dt
         c.max_episode_length = int(self.max_episode_length)
         c.resample_interval = int(cfg.commands.resampling_time / self.dt)

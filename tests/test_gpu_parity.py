@@ -44,6 +44,35 @@ def test_ragged_env_counts(num_envs):
     helpers.run_parity("go1_flat", num_envs=num_envs, steps=3, oracle_device="cpu", seed=3)
 
 
+@pytest.mark.parametrize("per_cta", [4, 40, 76, 200])
+def test_persistent_cta_ranges(per_cta):
+    """envs per persistent CTA: one partial sub-tile, 32+8, 32+32+12 (the 65536-env shape), many sub-tiles."""
+    def force(cfg):
+        cfg.env.envs_per_cta = per_cta
+    env = helpers.make_env("go1_rough_full", 1000, device=DEV, seed=6, extra=force)
+    ref = helpers.make_env("go1_rough_full", 1000, device=DEV, seed=6)
+    fr = synthetic.make_frames(env, 2, seed=13)
+    for it in range(3):
+        taps = synthetic.make_taps(env, seed=40 + it)
+        for e in (env, ref):
+            if it == 0:
+                helpers.randomise_env_state(e, 6)
+            synthetic.load_frame(e, fr[it % 2])
+            e.use_rng_taps(taps)
+            e.step(fr[it % 2]["actions"].clone())
+        torch.cuda.synchronize()
+        for name in ("obs_buf", "rew_buf", "reset_buf", "episode_length_buf", "root_states", "dof_state", "commands",
+                     "last_dof_vel", "last_actions", "feet_air_time", "terrain_levels", "measured_heights"):
+            assert torch.equal(getattr(env, name), getattr(ref, name)), f"{name} differs at per_cta={per_cta}, step {it}"
+        n = int(ref.step_counts[0])
+        assert int(env.step_counts[0]) == n and torch.equal(env.reset_ids[:n], ref.reset_ids[:n])
+        for k in env.episode_sums:
+            assert torch.equal(env.episode_sums[k], ref.episode_sums[k])
+        for k, v in ref.extras["episode"].items():
+            if torch.is_tensor(v):
+                helpers.assert_close(f"extras[{k}]", env.extras["episode"][k].reshape(1), v.reshape(1))
+
+
 def test_heights_not_materialised_gives_same_observations():
     def nomat(cfg):
         cfg.terrain.materialize_heights = False
