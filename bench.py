@@ -127,6 +127,7 @@ def _build_env(envs, device, rank, world):
     def extra(cfg):
         cfg.env.shard_rank, cfg.env.shard_world = rank, world
         cfg.terrain.materialize_heights = False     # measured_heights stays in registers (algorithmic bytes)
+        cfg.env.envs_per_cta = int(os.environ.get("LGK_ENVS_PER_CTA", "0"))
     env = helpers.make_env(SCENARIO, envs, device=device, seed=1 + rank, extra=extra)
     g = torch.Generator().manual_seed(99 + rank)
     env.episode_length_buf = torch.randint(0, int(env.max_episode_length), (envs,), generator=g).to(device)

@@ -1,0 +1,34 @@
+"""Development: per-phase cycle counts of the step kernel (needs the -DLGK_PROFILE build in build/liblgk_prof.so)."""
+import ctypes as C, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+os.environ["LGK_LIB_PATH"] = os.path.join(ROOT, "build", "liblgk_prof.so")
+import torch, helpers
+from legged_gym_b200 import _lgk
+from legged_gym_b200.utils import synthetic
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
+per = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+def extra(cfg):
+    cfg.terrain.materialize_heights = False
+    cfg.env.envs_per_cta = per
+env = helpers.make_env("go1_rough_full", N, device="cuda:0", seed=1, extra=extra)
+fr = synthetic.make_frames(env, 2, seed=3)
+for i in range(6):
+    synthetic.load_frame(env, fr[i % 2]); env.step(fr[i % 2]["actions"])
+torch.cuda.synchronize()
+lib = _lgk.load()
+n = 2048 * 2 * 8
+buf = (C.c_longlong * n)()
+lib.lgk_debug_read_prof.argtypes = [C.c_void_p, C.c_int]
+assert lib.lgk_debug_read_prof(buf, n) == 0
+t = torch.tensor(list(buf), dtype=torch.float64).view(2048, 2, 8)
+ncta = min(2048, (N + per - 1) // per)
+t = t[:ncta]
+t0 = t[:, 0, 0].min()
+names = ["load", "stage1", "barrier1", "stage2", "wait_w123", "stage3"]
+for w in (0, 1):
+    d = t[:, w, 1:7] - t[:, w, 0:6]
+    print(f"warp {w}: " + "  ".join(f"{names[k]} {d[:, k].mean():8.0f}" for k in range(6 if w == 0 else 4)), " total", float((t[:, w, 6 if w == 0 else 4] - t[:, w, 0]).mean()))
+d7 = t[:, 0, 7] - t[:, 0, 5]
+print("stage3 reward-table part", float(d7.mean()), " loop part", float((t[:, 0, 6] - t[:, 0, 7]).mean()))
+print("kernel span cycles", float(t[:, 0, 6].max() - t0), " first-wave CTAs start spread", float(t[:, 0, 0].max() - t0))
