@@ -48,8 +48,17 @@ __device__ long long lgk_prof[2048 * 2 * 8];
 extern "C" int lgk_debug_read_prof(long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, lgk_prof, sizeof(long long) * n);
 }
+// CTA timeline: [cta][globaltimer at start, globaltimer when W0 leaves, SM id, 0]
+__device__ long long lgk_prof_cta[2048 * 4];
+static __device__ __forceinline__ long long lgk_gtime() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+static __device__ __forceinline__ int lgk_smid() { int r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
+#define LGK_CTA_STAMP(k) do { if (blockIdx.x < 2048) { lgk_prof_cta[blockIdx.x * 4 + (k)] = lgk_gtime(); lgk_prof_cta[blockIdx.x * 4 + 2] = lgk_smid(); } } while (0)
+extern "C" int lgk_debug_read_prof_cta(long long* out, int n) {
+  return (int)cudaMemcpyFromSymbol(out, lgk_prof_cta, sizeof(long long) * n);
+}
 #else
 #define LGK_STAMP(k) do {} while (0)
+#define LGK_CTA_STAMP(k) do {} while (0)
 #endif
 
 struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
@@ -255,9 +264,9 @@ static __device__ __noinline__ void tile_load_fallback(const StepArgs& a, float*
     if (e < ne) sm[L.sums + r * RS + e] = b.episode_sums[(size_t)r * N + env0 + e];
   }
 }
-static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const float* sm, int env0, int ne) {
+static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const float* sm, int env0, int ne, int tid) {
   const int D = a.c.num_dof;
-  const int t = threadIdx.x - 32, nt = LGK_CTA_THREADS - 32;   // warps 1..3
+  const int t = tid - 32, nt = LGK_CTA_THREADS - 32;   // warps 1..3
   float* la = a.b.last_actions + (size_t)env0 * D;
   float* lv = a.b.last_dof_vel + (size_t)env0 * D;
 #pragma unroll 1
@@ -273,16 +282,37 @@ static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace*
   __threadfence();
   const int nt = gridDim.x * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
   const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
-  const volatile unsigned* rm = mask_base;
-  const volatile unsigned* sv = mask_base + lgk_max_warps(N);
+  const unsigned* rm = mask_base;                      // read with ld.global.cg: the masks were published through L2
+  const unsigned* sv = mask_base + lgk_max_warps(N);
   const int per = (nt + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
   const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
   // slots of sub-tiles past a CTA's range were never written this launch: skip them
-  auto slot_env0 = [&](int t) { const int cta = t / a.max_sub, k = t - cta * a.max_sub; return cta * a.per + k * TILE; };
-  auto slot_ok = [&](int t) { const int cta = t / a.max_sub, k = t - cta * a.max_sub; return k * TILE < min(a.per, N - cta * a.per); };
+  const bool one_sub = a.max_sub == 1;
+  auto slot_env0 = [&](int t) {
+    if (one_sub) return t * a.per;
+    const int cta = t / a.max_sub, k = t - cta * a.max_sub;
+    return cta * a.per + k * TILE;
+  };
+  auto slot_ok = [&](int t) {
+    if (one_sub) return true;
+    const int cta = t / a.max_sub, k = t - cta * a.max_sub;
+    return k * TILE < min(a.per, N - cta * a.per);
+  };
+  // this launch's serial tail: keep eight slots (sixteen L2 loads) in flight per thread
+  constexpr int U = 8;
   int c0 = 0, c1 = 0;
 #pragma unroll 1
-  for (int t = t0; t < t1; ++t) if (slot_ok(t)) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
+  for (int t = t0; t < t1; t += U) {
+    unsigned mr[U], ms[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const bool ok = t + k < t1 && slot_ok(t + k);
+      mr[k] = ok ? __ldcg(rm + t + k) : 0u;
+      ms[k] = ok ? __ldcg(sv + t + k) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) { c0 += __popc(mr[k]); c1 += __popc(ms[k]); }
+  }
   // block-wide exclusive scan of (c0, c1): shuffles inside a warp, 4 warp totals through shared memory
   int i0 = c0, i1 = c1;
 #pragma unroll
@@ -301,14 +331,26 @@ static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace*
     n_resample += s_scan[1][w + 1];
   }
   int o0 = base0 + i0 - c0, o1 = base1 + i1 - c1;
+  if (c0 + c1 != 0) {
 #pragma unroll 1
-  for (int t = t0; t < t1; ++t) {
-    if (!slot_ok(t)) continue;
-    const int e0 = slot_env0(t);
-    unsigned m = rm[t];
-    while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
-    m = sv[t];
-    while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = e0 + bit; }
+    for (int t = t0; t < t1; t += U) {
+      unsigned mr[U], ms[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const bool ok = t + k < t1 && slot_ok(t + k);
+        mr[k] = ok ? __ldcg(rm + t + k) : 0u;
+        ms[k] = ok ? __ldcg(sv + t + k) : 0u;
+      }
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        if ((mr[k] | ms[k]) == 0u) continue;
+        const int e0 = slot_env0(t + k);
+        unsigned m = mr[k];
+        while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
+        m = ms[k];
+        while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = e0 + bit; }
+      }
+    }
   }
   if (tid == 0) {
     b.counts[0] = n_reset;
@@ -374,9 +416,11 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ unsigned s_is_last;
 
-  const int tid = threadIdx.x;
-  const int lane = tid & 31;
-  const int wic = tid >> 5;
+  // roles go by the logical warp index wic: rotated per CTA so that the W0s of the CTAs resident on an
+  // SM (the longest role, and the only one running in stage 3) do not all sit on the same scheduler
+  const int lane = threadIdx.x & 31;
+  const int wic = ((int)(threadIdx.x >> 5) + (int)((blockIdx.x * 2654435761u) >> 30)) & (LGK_WARPS_PER_CTA - 1);
+  const int tid = wic * 32 + lane;
   const int cta_env0 = blockIdx.x * a.per;
   const int cta_ne = min(a.per, N - cta_env0);
   const int nsub = (cta_ne + TILE - 1) / TILE;
@@ -393,6 +437,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     s_row_ext[lane] = __popc(xm & ((1u << lane) - 1u));
     s_row_scale[lane] = in ? c.rewards[lane].scale : c.termination_scale;
   }
+  if (tid == 0) LGK_CTA_STAMP(0);
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
   const int parity = (int)(csc & 1ull);
@@ -718,7 +763,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         bulk_commit();
       }
     } else if (wic > 0) {
-      tile_store_fallback(a, sm, env0, ne);
+      tile_store_fallback(a, sm, env0, ne, tid);
     }
     if (s_is_last) compact_ids(a, ws);
 
@@ -939,6 +984,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   LGK_STAMP(6);
   }   // sub-tiles
   if (wic != 0) return;
+  if (lane == 0) LGK_CTA_STAMP(1);
   // ---- statistics ticket: the last W0 to get here finalises the episode statistics ----------------
   unsigned last = 0u;
   if (lane == 0) {

@@ -32,3 +32,21 @@ for w in (0, 1):
 d7 = t[:, 0, 7] - t[:, 0, 5]
 print("stage3 reward-table part", float(d7.mean()), " loop part", float((t[:, 0, 6] - t[:, 0, 7]).mean()))
 print("kernel span cycles", float(t[:, 0, 6].max() - t0), " first-wave CTAs start spread", float(t[:, 0, 0].max() - t0))
+
+# CTA timeline (globaltimer, ns): waves per SM, tail
+m = 2048 * 4
+buf2 = (C.c_longlong * m)()
+lib.lgk_debug_read_prof_cta.argtypes = [C.c_void_p, C.c_int]
+assert lib.lgk_debug_read_prof_cta(buf2, m) == 0
+g = torch.tensor(list(buf2), dtype=torch.float64).view(2048, 4)[:ncta]
+g0 = g[:, 0].min()
+st, en, smid = g[:, 0] - g0, g[:, 1] - g0, g[:, 2].long()
+print(f"timeline (us): last CTA start {st.max() / 1e3:.1f}  last W0 end {en.max() / 1e3:.1f}  mean CTA life {(en - st).mean() / 1e3:.1f}")
+print("  SMs used", int(smid.unique().numel()), " CTAs per SM min/max", int(torch.bincount(smid).clamp(min=0)[smid.unique()].min()), int(torch.bincount(smid).max()))
+qs = torch.tensor([0.1, 0.25, 0.5, 0.75, 0.9, 1.0], dtype=torch.float64)
+print("  start quantiles us", [round(float(x) / 1e3, 1) for x in torch.quantile(st, qs)])
+print("  end   quantiles us", [round(float(x) / 1e3, 1) for x in torch.quantile(en, qs)])
+life = (en - st)
+order = torch.argsort(st)
+k = max(ncta // 4, 1)
+print("  CTA life by start order (us): first quarter %.1f  second %.1f  third %.1f  last %.1f" % tuple(float(life[order[i * k:(i + 1) * k]].mean()) / 1e3 for i in range(4)))
