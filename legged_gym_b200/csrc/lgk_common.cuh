@@ -14,11 +14,20 @@ struct LgkWorkspace {
   unsigned int done_ticket;          // CTAs finished in the current launch
   unsigned int mask_ticket;          // CTAs that have published their reset / resample masks
   int level_sum[2];                  // sum(terrain_levels) accumulators, indexed by step parity
-  unsigned int pad1[2];
+  int reset_count[2];                // number of reset envs, indexed by step parity
   float stats[2][LGK_MAX_REWARDS + 4];   // per-parity: sum over reset ids of episode_sums[k]
   // followed by: uint32 reset_mask[max_warps]; uint32 resample_mask[max_warps];
 };
 #define LGK_WS_HEADER_BYTES 512
+#ifdef __CUDACC__
+// ticket counters: release-ordered increment (MEMBAR.ALL.GPU + ATOMG; no L1 invalidation, unlike
+// __threadfence() + atomicAdd), so everything the CTA wrote before it is visible to whoever draws the last ticket
+__device__ __forceinline__ unsigned int ticket_release(unsigned int* p) {
+  unsigned int old;
+  asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
+  return old;
+}
+#endif
 static_assert(sizeof(LgkWorkspace) <= LGK_WS_HEADER_BYTES, "workspace header too large");
 
 __host__ __device__ inline int lgk_max_warps(int num_envs) { return (num_envs + 3) / 4 + LGK_WARPS_PER_CTA; }

@@ -36,6 +36,7 @@
 #include "lgk_common.cuh"
 
 #define TILE 32
+#define HP_OFF (((RS * (LGK_REW_COUNT + 1)) + 3) & ~3)   // base-height partial sums, after the reward table
 #define RS (TILE + 1)   // row stride of the [row][env] reward tables: conflict-free by row and by env
 #ifndef LGK_MIN_CTAS
 #define LGK_MIN_CTAS 6   // register cap 85: six 128-thread CTAs per SM
@@ -82,7 +83,7 @@ struct StepArgs {
 // scratch fields (SoA, [field][TILE]) exchanged between the stages
 enum { SC_ES = 0,            // 8 floats per env (AoS): rx ry rz zo | yaw_z yaw_w - -
        SC_J1 = 8, SC_J2 = 18,  // joint partial sums of W1 / W2 (10 each)
-       SC_COLL = 28, SC_FFP, SC_RAIR, SC_STUMBLE, SC_NOFLY, SC_BH, SC_FIELDS };
+       SC_COLL = 28, SC_FFP, SC_RAIR, SC_STUMBLE, SC_NOFLY, SC_FIELDS };
 
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float norm3(float x, float y, float z) {
@@ -274,17 +275,18 @@ static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const
 }
 
 // ordered compaction of the reset / resample masks into ascending id lists (one CTA per launch)
-static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace* ws) {
+static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace* ws, int tid) {
+  constexpr int NT = LGK_CTA_THREADS - 32;   // run by W1..W3: tid in [0, 96)
   __shared__ int s_scan[2][LGK_WARPS_PER_CTA + 1];
   const LgkBuffers& b = a.b;
   const int N = a.c.num_envs;
-  const int tid = threadIdx.x, lane = tid & 31, wic = tid >> 5;
+  const int lane = tid & 31, wic = tid >> 5;
   __threadfence();
   const int nt = gridDim.x * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
   const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
   const unsigned* rm = mask_base;                      // read with ld.global.cg: the masks were published through L2
   const unsigned* sv = mask_base + lgk_max_warps(N);
-  const int per = (nt + LGK_CTA_THREADS - 1) / LGK_CTA_THREADS;
+  const int per = (nt + NT - 1) / NT;
   const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
   // slots of sub-tiles past a CTA's range were never written this launch: skip them
   const bool one_sub = a.max_sub == 1;
@@ -322,10 +324,10 @@ static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace*
   }
   if (lane == 31) { s_scan[0][wic + 1] = i0; s_scan[1][wic + 1] = i1; }
   if (tid == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
-  __syncthreads();
+  asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
   int base0 = 0, base1 = 0, n_reset = 0, n_resample = 0;
 #pragma unroll
-  for (int w = 0; w < LGK_WARPS_PER_CTA; ++w) {
+  for (int w = 0; w < LGK_WARPS_PER_CTA - 1; ++w) {
     if (w < wic) { base0 += s_scan[0][w + 1]; base1 += s_scan[1][w + 1]; }
     n_reset += s_scan[0][w + 1];
     n_resample += s_scan[1][w + 1];
@@ -366,7 +368,7 @@ static __device__ __noinline__ void finalize_stats(const StepArgs& a, LgkWorkspa
   const int lane = threadIdx.x & 31, num_rows = a.num_rows, N = c.num_envs;
   const int parity = (int)(csc & 1ull);
   __threadfence();
-  const int n_reset = ((volatile int*)b.counts)[0];
+  const int n_reset = ((volatile int*)ws->reset_count)[parity];
   const int level_sum = ((volatile int*)ws->level_sum)[parity];
   volatile float* st = ws->stats[parity];
   if (lane < num_rows) {
@@ -387,6 +389,7 @@ static __device__ __noinline__ void finalize_stats(const StepArgs& a, LgkWorkspa
     if (n_reset > 0 && (c.flags & LGK_F_TERRAIN_CURRICULUM))
       b.extras[num_rows] = (float)level_sum / (float)N;   // mean(terrain_levels.float()) (:188)
     ws->level_sum[parity ^ 1] = 0;
+    ws->reset_count[parity ^ 1] = 0;
     ws->step_counter = csc;
     ws->done_ticket = 0u;
   }
@@ -441,7 +444,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
   const int parity = (int)(csc & 1ull);
-  const bool push_step = (flags & LGK_F_PUSH_ROBOTS) && (csc % (unsigned long long)c.push_interval == 0ull);
+  bool push_step = false;   // W0 only; 32-bit remainder unless the counter has outgrown it
+  if (wic == 0 && (flags & LGK_F_PUSH_ROBOTS))
+    push_step = (csc >> 32) == 0ull ? ((unsigned)csc % (unsigned)c.push_interval == 0u)
+                                    : (csc % (unsigned long long)c.push_interval == 0ull);
 
   // W0: lane i issues the bulk copy of input array i (rows r = i - 11, i + 10 of the episode sums for
   // i >= 11); source base, shared-memory offset and bytes per env are fixed for the whole launch
@@ -470,6 +476,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   }
   __syncthreads();          // barrier initialised before anyone polls it
 
+  bool stats_last = false;
   for (int sub = 0; sub < nsub; ++sub) {
     const int env0 = cta_env0 + sub * TILE;
     const int ne = min(TILE, cta_ne - sub * TILE);
@@ -545,7 +552,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         float4 cmd = *reinterpret_cast<const float4*>(sm + L.cmd + lane * 4);
 
         // ---- _post_physics_step_callback (:337-352) -------------------------------------------
-        resample_cb = (ep % c.resample_interval) == 0;
+        resample_cb = (unsigned long long)ep < 0x80000000ull ? ((int)ep % c.resample_interval) == 0
+                                                             : (ep % c.resample_interval) == 0;
         if (resample_cb) {
           float u0, u1, u2;
           if (TAPS) {
@@ -633,10 +641,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         unsigned* mask_base = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + LGK_WS_HEADER_BYTES);
         mask_base[slot] = reset_mask;
         mask_base[lgk_max_warps(N) + slot] = resample_mask;
-        if (last_sub) {   // mask ticket: the CTA that publishes the last masks compacts the id lists
-          __threadfence();
-          s_is_last = (atomicAdd(&ws->mask_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
-        }
+        const int nr = __popc(reset_mask);
+        if (nr != 0) atomicAdd(&ws->reset_count[parity], nr);
       }
     }
     else if (wic == 1 || wic == 2) {
@@ -765,7 +771,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     } else if (wic > 0) {
       tile_store_fallback(a, sm, env0, ne, tid);
     }
-    if (s_is_last) compact_ids(a, ws);
+    // mask ticket (release: W0's masks are ordered before it by the barrier above); W3 looks at the
+    // answer after its stage 2, so nobody waits for the round trip
+    unsigned mask_old = 0u;
+    if (last_sub && tid == 96) mask_old = ticket_release(&ws->mask_ticket);
 
   // =========================================== stage 2 ===========================================
   // one env at a time per warp, lanes over observation columns: noise on the head, then the H scan
@@ -797,17 +806,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (TAPS) {
         if (add_noise) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
       } else {
-        v = fmaf(fmaf((float)(rbits >> 8), 1.1920928955078125e-07f, -1.0f), ns, v);   // (2 * u01 - 1) * ns, ns = 0 without noise
+        v = fmaf(fmaf((float)rbits, 3.0517578125e-05f, -0.9999847412109375f), ns, v);   // (2 * u - 1) * ns, u = (r16 + 0.5) / 2^16; ns = 0 without noise
       }
       return clampf(v, -clip_obs, clip_obs);
     };
+    float* hpart = sm + L.cf + HP_OFF;   // [env][RS]; torques / last_actions rows are dead after stage 1
     const float2 border2 = make_float2(c.border_size, c.border_size);
     const float2 inv2 = make_float2(inv_hs, inv_hs);
     for (int e = wic; e < ne; e += LGK_WARPS_PER_CTA) {   // envs of the sub-tile dealt round-robin to the warps
       const int env_e = env0 + e;
       const float4 es0 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8);
       const float4 es1 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8 + 4);
-      const float rz = es0.z, zo = es0.w, qz = es1.x, qw = es1.y;
+      const float zo = es0.w, qz = es1.x, qw = es1.y;
       // ---- phase A: height-field indices of every pass, gathers in flight --------------------------
       int raw[NPA];
       if (NP > 0 && !plane) {
@@ -829,8 +839,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           if (MUL_RCP) sxy = __fmul2_rn(w, inv2);
           else sxy = make_float2(__fdiv_rn(w.x, c.horizontal_scale), __fdiv_rn(w.y, c.horizontal_scale));
           int ix = __float2int_rz(sxy.x), iy = __float2int_rz(sxy.y);
-          ix = min(max(ix, 0), max_px);
-          iy = min(max(iy, 0), max_py);
+          ix = __vimin_s32_relu(ix, max_px);   // clip(0, max): one VIMNMX.RELU
+          iy = __vimin_s32_relu(iy, max_py);
           raw[it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
         }
       } else {
@@ -842,26 +852,27 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       const float* trow = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
       const unsigned eg = (unsigned)(c.env_id_offset + env_e);
       uint4 rnd = make_uint4(0, 0, 0, 0);
+      // noise field j of this lane (head: j = 0, 1; scan pass it: j = 2 + it) = 16-bit half (j & 1) of
+      // word (j % 8) / 2 of Philox block LGK_SITE_NOISE + 3 * lane + j / 8: one block covers 6 passes
       if (!TAPS && add_noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane);
       {
         const float* hrow = sm + L.head + e * HS;
-        if (lane < OH) orow[lane] = noisy(hrow[lane], trow, lane, rnd.x, ns_a);
-        if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], trow, lane + 32, rnd.y, ns_b);
+        if (lane < OH) orow[lane] = noisy(hrow[lane], trow, lane, rnd.x & 0xffffu, ns_a);
+        if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], trow, lane + 32, rnd.x >> 16, ns_b);
       }
       // ---- phase B: heights -> observation columns -----------------------------------------------
       float hsum = 0.f;
 #pragma unroll
       for (int it = 0; it < NP; ++it) {
-        if (!TAPS && add_noise) {
-          if (it == 2) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
-          if (it == 6) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane + 2);
-        }
-        const int w = (it + 2) & 3;
-        const unsigned rbits = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
+        if (!TAPS && add_noise && it == 6) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
+        const int w = ((it + 2) >> 1) & 3;
+        const unsigned rw = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
+        const unsigned rbits = (it & 1) ? rw >> 16 : rw & 0xffffu;
         const int h = it * 32 + lane;
         const bool ok = h < H;
         const float hgt = mul_rn((float)raw[it], c.vertical_scale);
-        hsum += ok ? hgt : 0.f;
+        if ((it + 1) * 32 <= H) hsum += hgt;   // only the last pass can hold lanes past H
+        else hsum += ok ? hgt : 0.f;
         const float v = clampf(sub_rn(zo, hgt), -1.f, 1.f) * c.obs_scale_height;
         const float o = noisy(v, trow, ok ? OH + h : 0, rbits, ns_h[it]);
         if (ok) orow[OH + h] = o;
@@ -872,10 +883,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         for (int it = 0; it < NP; ++it)
           if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn((float)raw[it], c.vertical_scale);
       }
-      if (a.bh_active) {   // mean_h(root_z - measured_height) = root_z - mean_h(height), _reward_base_height (:871)
-        hsum = warp_sum(hsum);
-        if (lane == 0) scr[SC_BH * TILE + e] = H > 0 ? rz - hsum / (float)H : rz;
-      }
+      // _reward_base_height (:871) needs mean_h(height): this lane's partial sum; W0 adds them in stage 3
+      if (a.bh_active) hpart[e * RS + lane] = hsum;
     }
   }
   LGK_STAMP(4);
@@ -884,6 +893,11 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   if (wic != 0) {
     if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows: W0 may refill them
     asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
+    if (last_sub) {   // the CTA whose mask ticket was the launch's last compacts the id lists (W1..W3)
+      if (tid == 96) s_is_last = (mask_old == gridDim.x - 1) ? 1u : 0u;
+      asm volatile("bar.sync 2, %0;" ::"n"(LGK_CTA_THREADS - 32) : "memory");
+      if (s_is_last) compact_ids(a, ws, tid - 32);
+    }
     continue;
   }
   asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
@@ -905,8 +919,16 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       auto put = [&](int term, float v) { rv[term * RS + lane] = v; };
       put(LGK_REW_ACTION_RATE, J(A_ARATE));
       put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
-      {
-        const float d = scr[SC_BH * TILE + lane] - c.base_height_target;
+      {   // mean_h(root_z - measured_height) = root_z - mean_h(height)
+        float bh = scr[SC_ES * TILE + lane * 8 + 2];   // root z before the reset
+        if (a.bh_active && H > 0) {
+          const float* hp = sm + L.cf + HP_OFF + lane * RS;
+          float hs = 0.f;
+#pragma unroll 8
+          for (int k = 0; k < 32; ++k) hs += hp[k];
+          bh -= hs / (float)H;
+        }
+        const float d = bh - c.base_height_target;
         put(LGK_REW_BASE_HEIGHT, d * d);
       }
       put(LGK_REW_COLLISION, scr[SC_COLL * TILE + lane]);
@@ -974,6 +996,12 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
     // termination term is added after the positive clip (:206-212)
     if (flags & LGK_F_HAS_TERMINATION) rew = add_rn(rew, rr[nrew * RS + lane]);
+    // statistics ticket (release) before this warp's last stores: the finaliser only reads the statistics
+    if (last_sub) {
+      unsigned old = 0u;
+      if (lane == 0) old = ticket_release(&ws->done_ticket);
+      stats_last = __shfl_sync(LGK_FULL_MASK, old, 0) == gridDim.x - 1;
+    }
     if (active) {
       b.rew_buf[env] = rew;
       float* grow = b.episode_sums + env;
@@ -985,14 +1013,8 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   }   // sub-tiles
   if (wic != 0) return;
   if (lane == 0) LGK_CTA_STAMP(1);
-  // ---- statistics ticket: the last W0 to get here finalises the episode statistics ----------------
-  unsigned last = 0u;
-  if (lane == 0) {
-    __threadfence();
-    last = (atomicAdd(&ws->done_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
-  }
-  last = __shfl_sync(LGK_FULL_MASK, last, 0);
-  if (last) finalize_stats(a, ws, csc);
+  // the last W0 of the launch to take the statistics ticket finalises the episode statistics
+  if (stats_last) finalize_stats(a, ws, csc);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1043,7 +1065,12 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   L.sums = o; o += up4(RS * (args.num_rows > 0 ? args.num_rows : 1));
   L.head = o; o += (TILE * args.head_stride > RS * args.num_rows) ? up4(TILE * args.head_stride) : up4(RS * args.num_rows);   // later: reward rows
   L.scr = o;  o += TILE * SC_FIELDS;
-  L.cf = o;   o += (TILE * B3 > RS * (LGK_REW_COUNT + 1)) ? up4(TILE * B3) : up4(RS * (LGK_REW_COUNT + 1));   // later: reward table
+  // contact rows; later the reward table [LGK_REW_COUNT + 1][RS] and, running on into the torque /
+  // last_actions rows, the base-height partial sums [TILE][RS]
+  {
+    const int need = HP_OFF + TILE * RS - 2 * up4(TILE * D);
+    L.cf = o; o += up4(TILE * B3 > need ? TILE * B3 : need);
+  }
   L.tq = o;   o += up4(TILE * D);
   L.lact = o; o += up4(TILE * D);
   L.total = o;
