@@ -44,16 +44,16 @@
 
 #ifdef LGK_PROFILE
 // development build only: per-CTA phase timestamps (clock64) of the first sub-tile, [cta][warp 0 / 1][8]
-__device__ long long lgk_prof[2048 * 2 * 8];
-#define LGK_STAMP(k) do { if (sub == 0 && lane == 0 && wic < 2 && blockIdx.x < 2048) lgk_prof[(blockIdx.x * 2 + wic) * 8 + (k)] = clock64(); } while (0)
+__device__ long long lgk_prof[4096 * 2 * 8];
+#define LGK_STAMP(k) do { if (sub == 0 && lane == 0 && wic < 2 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 2 + wic) * 8 + (k)] = clock64(); } while (0)
 extern "C" int lgk_debug_read_prof(long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, lgk_prof, sizeof(long long) * n);
 }
 // CTA timeline: [cta][globaltimer at start, globaltimer when W0 leaves, SM id, 0]
-__device__ long long lgk_prof_cta[2048 * 4];
+__device__ long long lgk_prof_cta[4096 * 4];
 static __device__ __forceinline__ long long lgk_gtime() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 static __device__ __forceinline__ int lgk_smid() { int r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
-#define LGK_CTA_STAMP(k) do { if (blockIdx.x < 2048) { lgk_prof_cta[blockIdx.x * 4 + (k)] = lgk_gtime(); lgk_prof_cta[blockIdx.x * 4 + 2] = lgk_smid(); } } while (0)
+#define LGK_CTA_STAMP(k) do { if (blockIdx.x < 4096) { lgk_prof_cta[blockIdx.x * 4 + (k)] = lgk_gtime(); lgk_prof_cta[blockIdx.x * 4 + 2] = lgk_smid(); } } while (0)
 extern "C" int lgk_debug_read_prof_cta(long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, lgk_prof_cta, sizeof(long long) * n);
 }
@@ -66,11 +66,14 @@ struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared
   int root, dof, act, ldv, cmd, fat, ep, lvl, sums, head, scr, cf, tq, lact, total;
 };
 
+#define LGK_LD_ARRAYS 11
 struct StepArgs {
   LgkConsts c;
   LgkBuffers b;
   TileLayout L;
-  int per;           // envs per CTA (multiple of 4): CTA c owns envs [c*per, (c+1)*per), in sub-tiles of <= 32
+  int per;           // envs per CTA (multiple of 4) of the first n_big CTAs, walked in sub-tiles of <= 32
+  int n_big;         // CTAs past n_big own per_small envs each: the launch's last, partial wave runs on
+  int per_small;     //   smaller tiles so that it is shorter than a full wave (per_small <= 32)
   int max_sub;       // sub-tiles per CTA = ceil(per / 32)
   int head_stride;   // odd row stride of the staged observation head
   int air_active;    // feet_air_time term active (:945-948 only run then)
@@ -78,6 +81,11 @@ struct StepArgs {
   int tma_ok;        // every tiled array 16-byte aligned and N % 4 == 0
   int num_rows;      // episode_sums rows: num_rewards (+1 with termination)
   unsigned pk[20];   // Philox4x32-10 round keys of c.seed
+  // bulk-load table: lane i of W0 copies input array i of a sub-tile (source base, offset into shared
+  // memory in floats, bytes per env); src == nullptr: nothing to copy
+  const char* ld_src[LGK_LD_ARRAYS];
+  unsigned ld_off[LGK_LD_ARRAYS], ld_bpe[LGK_LD_ARRAYS];
+  unsigned ld_bytes_per_env;   // sum of ld_bpe
 };
 
 // scratch fields (SoA, [field][TILE]) exchanged between the stages
@@ -259,11 +267,6 @@ static __device__ __noinline__ void tile_load_fallback(const StepArgs& a, float*
   ld(L.ldv, b.last_dof_vel + (size_t)env0 * D, D);
   ld(L.fat, b.feet_air_time + (size_t)env0 * F, F);
   if (b.terrain_levels != nullptr) ld(L.lvl, b.terrain_levels + env0, 2);
-#pragma unroll 1
-  for (int i = tid; i < a.num_rows * TILE; i += LGK_CTA_THREADS) {
-    const int r = i / TILE, e = i % TILE;
-    if (e < ne) sm[L.sums + r * RS + e] = b.episode_sums[(size_t)r * N + env0 + e];
-  }
 }
 static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const float* sm, int env0, int ne, int tid) {
   const int D = a.c.num_dof;
@@ -291,7 +294,7 @@ static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace*
   // slots of sub-tiles past a CTA's range were never written this launch: skip them
   const bool one_sub = a.max_sub == 1;
   auto slot_env0 = [&](int t) {
-    if (one_sub) return t * a.per;
+    if (one_sub) return t < a.n_big ? t * a.per : a.n_big * a.per + (t - a.n_big) * a.per_small;
     const int cta = t / a.max_sub, k = t - cta * a.max_sub;
     return cta * a.per + k * TILE;
   };
@@ -424,11 +427,30 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int lane = threadIdx.x & 31;
   const int wic = ((int)(threadIdx.x >> 5) + (int)((blockIdx.x * 2654435761u) >> 30)) & (LGK_WARPS_PER_CTA - 1);
   const int tid = wic * 32 + lane;
-  const int cta_env0 = blockIdx.x * a.per;
-  const int cta_ne = min(a.per, N - cta_env0);
+  const bool big = (int)blockIdx.x < a.n_big;
+  const int cta_env0 = big ? blockIdx.x * a.per : a.n_big * a.per + ((int)blockIdx.x - a.n_big) * a.per_small;
+  const int cta_ne = min(big ? a.per : a.per_small, N - cta_env0);
   const int nsub = (cta_ne + TILE - 1) / TILE;
   const bool has_levels = b.terrain_levels != nullptr;
 
+  // ---- first thing: W0 sets the mbarrier up and gets the bulk loads of the first sub-tile going; the
+  // rest of the prologue runs under their latency.  Lane i copies input array i.
+  const char* ld_src = nullptr;
+  unsigned ld_off = 0, ld_bpe = 0;
+  if (wic == 0) {
+    if (lane < LGK_LD_ARRAYS) { ld_src = a.ld_src[lane]; ld_off = a.ld_off[lane]; ld_bpe = a.ld_bpe[lane]; }
+    if (lane == 0) {
+      mbar_init(&s_bar, 1);
+      s_is_last = 0u;
+    }
+    __syncwarp();
+    const int ne0 = min(TILE, cta_ne);
+    if (a.tma_ok && (ne0 & 3) == 0) {
+      if (lane == 0) mbar_expect_tx(&s_bar, (unsigned)ne0 * a.ld_bytes_per_env);
+      __syncwarp();
+      if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)cta_env0 * ld_bpe, (unsigned)ne0 * ld_bpe, &s_bar);
+    }
+  }
   // stage 3, pass B: lane l of W0 owns episode-sum row l (term, scale, index among the external terms)
   __shared__ int s_row_term[32], s_row_ext[32];
   __shared__ float s_row_scale[32];
@@ -441,6 +463,12 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     s_row_scale[lane] = in ? c.rewards[lane].scale : c.termination_scale;
   }
   if (tid == 0) LGK_CTA_STAMP(0);
+#ifdef LGK_STAGGER_NS   // experiment: de-phase the CTAs that start together on an SM
+  if (blockIdx.x < 888) {
+    const unsigned k = min(blockIdx.x / 148u, 5u);
+    for (unsigned i = 0; i < k; ++i) __nanosleep(LGK_STAGGER_NS);
+  }
+#endif
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
   const int parity = (int)(csc & 1ull);
@@ -449,34 +477,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     push_step = (csc >> 32) == 0ull ? ((unsigned)csc % (unsigned)c.push_interval == 0u)
                                     : (csc % (unsigned long long)c.push_interval == 0ull);
 
-  // W0: lane i issues the bulk copy of input array i (rows r = i - 11, i + 10 of the episode sums for
-  // i >= 11); source base, shared-memory offset and bytes per env are fixed for the whole launch
-  const char* ld_src = nullptr;
-  unsigned ld_off = 0, ld_bpe = 0;
-  if (wic == 0) {
-    switch (lane) {
-      case 0: ld_src = (const char*)b.root_states; ld_off = L.root; ld_bpe = 13 * 4; break;
-      case 1: ld_src = (const char*)b.episode_length_buf; ld_off = L.ep; ld_bpe = 8; break;
-      case 2: ld_src = (const char*)b.contact_forces; ld_off = L.cf; ld_bpe = B3 * 4; break;
-      case 3: ld_src = (const char*)b.commands; ld_off = L.cmd; ld_bpe = 16; break;
-      case 4: ld_src = (const char*)b.dof_state; ld_off = L.dof; ld_bpe = D * 8; break;
-      case 5: ld_src = (const char*)b.actions; ld_off = L.act; ld_bpe = D * 4; break;
-      case 6: ld_src = (const char*)b.last_actions; ld_off = L.lact; ld_bpe = D * 4; break;
-      case 7: ld_src = (const char*)b.torques; ld_off = L.tq; ld_bpe = D * 4; break;
-      case 8: ld_src = (const char*)b.last_dof_vel; ld_off = L.ldv; ld_bpe = D * 4; break;
-      case 9: ld_src = (const char*)b.feet_air_time; ld_off = L.fat; ld_bpe = F * 4; break;
-      case 10: ld_src = has_levels ? (const char*)b.terrain_levels : nullptr; ld_off = L.lvl; ld_bpe = 8; break;
-      default: break;
-    }
-  }
-
-  if (tid == 0) {
-    mbar_init(&s_bar, 1);
-    s_is_last = 0u;
-  }
-  __syncthreads();          // barrier initialised before anyone polls it
+  __syncthreads();          // barrier initialised before anyone polls it, row table written
 
   bool stats_last = false;
+  unsigned mask_old = 0u;
   for (int sub = 0; sub < nsub; ++sub) {
     const int env0 = cta_env0 + sub * TILE;
     const int ne = min(TILE, cta_ne - sub * TILE);
@@ -487,28 +491,20 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     LGK_STAMP(0);
     // ---- load the sub-tile --------------------------------------------------------------------
     if (full) {
-      if (wic == 0) {
-        if (lane == 0) {
-          fence_proxy_async_smem();   // generic reads of the previous sub-tile before the async writes
-          mbar_expect_tx(&s_bar, (unsigned)ne * 4u * (13 + 2 * D + B3 + 4 * D + 4 + F + 2 + (has_levels ? 2 : 0)));
+      if (sub > 0) {            // (the first sub-tile's loads were issued at the top of the kernel)
+        __syncthreads();        // every warp is through stage 3 of the previous sub-tile
+        if (wic == 0) {
+          if (lane == 0) {
+            fence_proxy_async_smem();   // generic reads of the previous sub-tile before the async writes
+            mbar_expect_tx(&s_bar, (unsigned)ne * a.ld_bytes_per_env);
+          }
+          __syncwarp();
+          if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)env0 * ld_bpe, (unsigned)ne * ld_bpe, &s_bar);
         }
-        __syncwarp();
-        if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)env0 * ld_bpe, (unsigned)ne * ld_bpe, &s_bar);
       }
       mbar_wait(&s_bar, sub & 1);
-      if (wic == 3 && lane < ne) {
-        // episode-sum rows ([R, N], 128 B per row and tile): 4-byte cp.async per lane instead of R bulk
-        // copies; issued once W0 is past stage 3 of the previous sub-tile, awaited before the stage-1 barrier
-        const float* src = b.episode_sums + env0 + lane;
-        const unsigned dst = smem_u32(sm + L.sums + lane);
-#pragma unroll 1
-        for (int r = 0; r < num_rows; ++r)
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + (unsigned)r * (RS * 4)),
-                       "l"(src + (size_t)r * N) : "memory");
-        asm volatile("cp.async.commit_group;" ::: "memory");
-      }
     } else {
-      __syncthreads();          // W0 may still be in stage 3 of the previous sub-tile
+      __syncthreads();          // every warp is through stage 3 of the previous sub-tile
       tile_load_fallback(a, sm, env0, ne);
       __syncthreads();
     }
@@ -532,7 +528,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     // values W0 keeps in registers from stage 1 to stage 3
     float blv[3] = {0, 0, 0}, bav[3] = {0, 0, 0}, grav[3] = {0, 0, 0};
     float4 cmd_rew = make_float4(0, 0, 0, 0);
-    unsigned reset_mask = 0u;
+    const unsigned reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
 
     // =========================================== stage 1 =========================================
     if (wic == 0) {
@@ -631,7 +627,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         es[1] = make_float4(yaw_z, yaw_w, 0.f, 0.f);
       }
       // ---- sub-tile bookkeeping: bitmasks for the ordered compaction, level sum --------------------
-      reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
       const unsigned resample_mask = __ballot_sync(LGK_FULL_MASK, active && resample_cb);
       if ((flags & LGK_F_TERRAIN_CURRICULUM) && has_levels) {
         const int s = warp_sum_int(active ? level_contrib : 0);
@@ -754,7 +749,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       scr[SC_RAIR * TILE + lane] = r_air;       // masked by |cmd_xy| > 0.1 in stage 3
       scr[SC_STUMBLE * TILE + lane] = stumble ? 1.f : 0.f;
       scr[SC_NOFLY * TILE + lane] = (nofly == 1) ? 1.f : 0.f;
-      asm volatile("cp.async.wait_group 0;" ::: "memory");   // this lane's episode-sum words have landed
     }
     LGK_STAMP(2);
     fence_proxy_async_smem();   // last_dof_vel rows (W1 / W2) -> visible to the bulk store
@@ -773,8 +767,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     }
     // mask ticket (release: W0's masks are ordered before it by the barrier above); W3 looks at the
     // answer after its stage 2, so nobody waits for the round trip
-    unsigned mask_old = 0u;
     if (last_sub && tid == 96) mask_old = ticket_release(&ws->mask_ticket);
+    if (wic == 3 && lane < ne) {
+      // episode-sum rows ([R, N], 128 B per row and tile): 4-byte cp.async (LDGSTS) per lane and row into
+      // rows the joints no longer need; in flight during stage 2, awaited before the stage-3 barrier
+      const float* src = b.episode_sums + env0 + lane;
+      const unsigned dst = smem_u32(sm + L.sums + lane);
+#pragma unroll 1
+      for (int r = 0; r < num_rows; ++r)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + (unsigned)r * (RS * 4)),
+                     "l"(src + (size_t)r * N) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
 
   // =========================================== stage 2 ===========================================
   // one env at a time per warp, lanes over observation columns: noise on the head, then the H scan
@@ -888,75 +892,76 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     }
   }
   LGK_STAMP(4);
-  // W1..W3 are done with this sub-tile: they signal the base-height sums and go on to wait for the next
-  // loads; W0 waits for all of them and runs stage 3
-  if (wic != 0) {
-    if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows: W0 may refill them
-    asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
-    if (last_sub) {   // the CTA whose mask ticket was the launch's last compacts the id lists (W1..W3)
-      if (tid == 96) s_is_last = (mask_old == gridDim.x - 1) ? 1u : 0u;
-      asm volatile("bar.sync 2, %0;" ::"n"(LGK_CTA_THREADS - 32) : "memory");
-      if (s_is_last) compact_ids(a, ws, tid - 32);
-    }
-    continue;
-  }
-  asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
-  LGK_STAMP(5);
-
   // =========================================== stage 3 ===========================================
-  // W0: reward terms in the reference's order (:195-212), episode sums, statistics, in three passes:
-  //   A (lane = env)  every term's value -> table rv[term][env]
+  // reward terms in the reference's order (:195-212), episode sums, statistics; all four warps:
+  //   A (lane = env)  each warp puts its share of the term values into the table rv[term][env]
+  //   -- barrier --
+  //   then warp w alone for the envs [w * epw, (w + 1) * epw) of the sub-tile:
   //   B (lane = row)  r = value * scale, episode sum += r, statistics over the reset envs; the lanes
   //                   work on independent rows, so nothing here waits on a neighbour or on a constant
-  //   C (lane = env)  reward = ordered sum of the rows' r; 128-byte coalesced stores of the sums
+  //   C (lane = (row group, env))  reward = ordered sum of the rows' r; the sums leave in 32-byte sectors
   {
-    const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
+    if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows before anything refills them
     float* rv = sm + L.cf;     // [LGK_REW_COUNT + 1][RS]   (the contact rows are dead by now)
-    float* rr = sm + L.head;   // [num_rows][RS]            (the observation heads left in stage 2)
+    float* rr = sm + L.head;   // [num_rows][RS]            (written after the barrier: the heads have left)
     float* sums = sm + L.sums; // [num_rows][RS]
     {
       auto J = [&](int k) { return scr[(SC_J1 + k) * TILE + lane] + scr[(SC_J2 + k) * TILE + lane]; };
       auto put = [&](int term, float v) { rv[term * RS + lane] = v; };
-      put(LGK_REW_ACTION_RATE, J(A_ARATE));
-      put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
-      {   // mean_h(root_z - measured_height) = root_z - mean_h(height)
-        float bh = scr[SC_ES * TILE + lane * 8 + 2];   // root z before the reset
-        if (a.bh_active && H > 0) {
-          const float* hp = sm + L.cf + HP_OFF + lane * RS;
-          float hs = 0.f;
-#pragma unroll 8
-          for (int k = 0; k < 32; ++k) hs += hp[k];
-          bh -= hs / (float)H;
-        }
-        const float d = bh - c.base_height_target;
-        put(LGK_REW_BASE_HEIGHT, d * d);
-      }
-      put(LGK_REW_COLLISION, scr[SC_COLL * TILE + lane]);
-      put(LGK_REW_DOF_ACC, J(A_ACC2));
-      put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
-      put(LGK_REW_DOF_VEL, J(A_QD2));
-      put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
-      put(LGK_REW_ENERGY, J(A_ENERGY));
-      put(LGK_REW_FEET_AIR_TIME, scr[SC_RAIR * TILE + lane] * ((cn > 0.1f) ? 1.f : 0.f));
-      put(LGK_REW_FEET_CONTACT_FORCES, scr[SC_FFP * TILE + lane]);
-      put(LGK_REW_HIP_MOTION, J(A_HIP));
-      put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
-      put(LGK_REW_NO_FLY, scr[SC_NOFLY * TILE + lane]);
-      put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
-      put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
-      put(LGK_REW_STUMBLE, scr[SC_STUMBLE * TILE + lane]);
-      put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
-      put(LGK_REW_TORQUES, J(A_TQ2));
-      {
+      if (wic == 0) {          // the terms on W0's registers
+        const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
+        put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
+        put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
+        put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
+        put(LGK_REW_FEET_AIR_TIME, scr[SC_RAIR * TILE + lane] * ((cn > 0.1f) ? 1.f : 0.f));
+        put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
         const float e = cmd_rew.z - bav[2];
         put(LGK_REW_TRACKING_ANG_VEL, expf(-(e * e) / c.tracking_sigma));
         const float ex = cmd_rew.x - blv[0], ey = cmd_rew.y - blv[1];
         put(LGK_REW_TRACKING_LIN_VEL, expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma));
+      } else if (wic == 1) {
+        put(LGK_REW_ACTION_RATE, J(A_ARATE));
+        put(LGK_REW_DOF_ACC, J(A_ACC2));
+        put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
+        put(LGK_REW_DOF_VEL, J(A_QD2));
+        put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
+      } else if (wic == 2) {
+        put(LGK_REW_ENERGY, J(A_ENERGY));
+        put(LGK_REW_HIP_MOTION, J(A_HIP));
+        put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
+        put(LGK_REW_TORQUES, J(A_TQ2));
+      } else {
+        put(LGK_REW_COLLISION, scr[SC_COLL * TILE + lane]);
+        put(LGK_REW_FEET_CONTACT_FORCES, scr[SC_FFP * TILE + lane]);
+        put(LGK_REW_NO_FLY, scr[SC_NOFLY * TILE + lane]);
+        put(LGK_REW_STUMBLE, scr[SC_STUMBLE * TILE + lane]);
+        put(LGK_REW_COUNT, (reset && !time_out) ? 1.f : 0.f);   // the termination row's value (:210-212)
       }
-      put(LGK_REW_COUNT, (reset && !time_out) ? 1.f : 0.f);   // the termination row's value (:210-212)
+    }
+    if (wic == 3) asm volatile("cp.async.wait_group 0;" ::: "memory");   // this lane's episode-sum words have landed
+    __syncthreads();   // table and base-height partial sums complete, observation heads consumed
+    LGK_STAMP(5);
+    const int epw = (ne + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA;   // envs per warp (<= 8)
+    const int e_lo = wic * epw, e_hi = min(e_lo + epw, ne);
+    const int el = lane & 7, q = lane >> 3;
+    {   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height);
+        // lane (q, el) adds a quarter of the partial sums of env e_lo + el
+      const int e = min(e_lo + el, TILE - 1);
+      float bh = scr[SC_ES * TILE + e * 8 + 2];   // root z before the reset
+      if (a.bh_active && H > 0) {
+        const float* hp = sm + L.cf + HP_OFF + e * RS + q * 8;
+        float hs = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) hs += hp[k];
+        hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 8);
+        hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 16);
+        bh -= hs / (float)H;
+      }
+      const float d = bh - c.base_height_target;
+      if (q == 0 && e_lo + el < e_hi) rv[LGK_REW_BASE_HEIGHT * RS + e] = d * d;
     }
     __syncwarp();
-    LGK_STAMP(7);
+    const unsigned my_resets = reset_mask & (e_hi > e_lo ? ((0xffffffffu >> (32 - (e_hi - e_lo))) << e_lo) : 0u);
     if (lane < num_rows) {
       const int row_term = s_row_term[lane];
       const float row_scale = s_row_scale[lane];
@@ -966,7 +971,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (row_term != LGK_REW_EXTERNAL) {
         const float* vrow = rv + row_term * RS;
 #pragma unroll 4
-        for (int e = 0; e < ne; ++e) {
+        for (int e = e_lo; e < e_hi; ++e) {
           const float r = mul_rn(vrow[e], row_scale);
           const float total = add_rn(srow[e], r);
           const bool rs = (reset_mask >> e) & 1u;
@@ -977,7 +982,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       } else {
         const float* xrow = b.ext_rewards != nullptr ? b.ext_rewards + (size_t)s_row_ext[lane] * N + env0 : nullptr;
 #pragma unroll 1
-        for (int e = 0; e < ne; ++e) {
+        for (int e = e_lo; e < e_hi; ++e) {
           const float r = mul_rn(xrow != nullptr ? xrow[e] : 0.f, row_scale);
           const float total = add_rn(srow[e], r);
           const bool rs = (reset_mask >> e) & 1u;
@@ -986,34 +991,50 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           stat += rs ? total : 0.f;
         }
       }
-      if (reset_mask != 0u) atomicAdd(&ws->stats[parity][lane], stat);
+      if (my_resets != 0u) atomicAdd(&ws->stats[parity][lane], stat);
+    }
+    // statistics ticket (release), drawn by W3 once every warp's contributions are on their way and
+    // before its own last stores: the finaliser only reads the statistics
+    if (last_sub) {
+      if (wic != 3) {
+        asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
+      } else {
+        asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
+        unsigned old = 0u;
+        if (lane == 0) old = ticket_release(&ws->done_ticket);
+        stats_last = __shfl_sync(LGK_FULL_MASK, old, 0) == gridDim.x - 1;
+      }
     }
     __syncwarp();
-    float rew = 0.f;
-    const int nrew = c.num_rewards;
+    LGK_STAMP(7);
+    const int e_mine = e_lo + el;
+    if (e_mine < e_hi) {
+      if (q == 0) {
+        float rew = 0.f;
+        const int nrew = c.num_rewards;
 #pragma unroll 4
-    for (int i = 0; i < nrew; ++i) rew = add_rn(rew, rr[i * RS + lane]);
-    if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
-    // termination term is added after the positive clip (:206-212)
-    if (flags & LGK_F_HAS_TERMINATION) rew = add_rn(rew, rr[nrew * RS + lane]);
-    // statistics ticket (release) before this warp's last stores: the finaliser only reads the statistics
-    if (last_sub) {
-      unsigned old = 0u;
-      if (lane == 0) old = ticket_release(&ws->done_ticket);
-      stats_last = __shfl_sync(LGK_FULL_MASK, old, 0) == gridDim.x - 1;
-    }
-    if (active) {
-      b.rew_buf[env] = rew;
-      float* grow = b.episode_sums + env;
-#pragma unroll 4
-      for (int i = 0; i < num_rows; ++i) grow[(size_t)i * N] = sums[i * RS + lane];
+        for (int i = 0; i < nrew; ++i) rew = add_rn(rew, rr[i * RS + e_mine]);
+        if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
+        // termination term is added after the positive clip (:206-212)
+        if (flags & LGK_F_HAS_TERMINATION) rew = add_rn(rew, rr[nrew * RS + e_mine]);
+        b.rew_buf[env0 + e_mine] = rew;
+      }
+      float* grow = b.episode_sums + env0 + e_mine;
+#pragma unroll 2
+      for (int i = q; i < num_rows; i += 4) grow[(size_t)i * N] = sums[i * RS + e_mine];
     }
   }
   LGK_STAMP(6);
   }   // sub-tiles
-  if (wic != 0) return;
-  if (lane == 0) LGK_CTA_STAMP(1);
-  // the last W0 of the launch to take the statistics ticket finalises the episode statistics
+  if (wic == 0) {
+    if (lane == 0) LGK_CTA_STAMP(1);
+    return;
+  }
+  // the CTA whose mask ticket was the launch's last compacts the id lists (W1..W3)
+  if (tid == 96) s_is_last = (mask_old == gridDim.x - 1) ? 1u : 0u;
+  asm volatile("bar.sync 2, %0;" ::"n"(LGK_CTA_THREADS - 32) : "memory");
+  if (s_is_last) compact_ids(a, ws, tid - 32);
+  // the W3 that drew the launch's last statistics ticket finalises the episode statistics
   if (stats_last) finalize_stats(a, ws, csc);
 }
 
@@ -1062,7 +1083,6 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   L.fat = o;  o += up4(TILE * (F > 0 ? F : 1));
   L.ep = o;   o += TILE * 2;
   L.lvl = o;  o += TILE * 2;
-  L.sums = o; o += up4(RS * (args.num_rows > 0 ? args.num_rows : 1));
   L.head = o; o += (TILE * args.head_stride > RS * args.num_rows) ? up4(TILE * args.head_stride) : up4(RS * args.num_rows);   // later: reward rows
   L.scr = o;  o += TILE * SC_FIELDS;
   // contact rows; later the reward table [LGK_REW_COUNT + 1][RS] and, running on into the torque /
@@ -1073,22 +1093,62 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   }
   L.tq = o;   o += up4(TILE * D);
   L.lact = o; o += up4(TILE * D);
+  // episode-sum rows [num_rows][RS]: loaded after stage 1, over the dof_state rows when they fit
+  if (RS * args.num_rows <= up4(TILE * 2 * D)) L.sums = L.dof;
+  else { L.sums = o; o += up4(RS * args.num_rows); }
   L.total = o;
   const size_t smem = (size_t)L.total * sizeof(float);
   if (smem > 200 * 1024) return LGK_ERR_DIM;
+  {
+    const void* src[LGK_LD_ARRAYS] = {b->root_states, b->episode_length_buf, b->contact_forces, b->commands, b->dof_state,
+                                      b->actions, b->last_actions, b->torques, b->last_dof_vel, b->feet_air_time,
+                                      b->terrain_levels};
+    const int off[LGK_LD_ARRAYS] = {L.root, L.ep, L.cf, L.cmd, L.dof, L.act, L.lact, L.tq, L.ldv, L.fat, L.lvl};
+    const int bpe[LGK_LD_ARRAYS] = {13 * 4, 8, B3 * 4, 16, D * 8, D * 4, D * 4, D * 4, D * 4, F * 4, 8};
+    args.ld_bytes_per_env = 0;
+    for (int i = 0; i < LGK_LD_ARRAYS; ++i) {
+      const bool on = src[i] != nullptr && bpe[i] > 0;
+      args.ld_src[i] = on ? static_cast<const char*>(src[i]) : nullptr;
+      args.ld_off[i] = (unsigned)off[i];
+      args.ld_bpe[i] = on ? (unsigned)bpe[i] : 0u;
+      args.ld_bytes_per_env += args.ld_bpe[i];
+    }
+  }
   // bulk (TMA) path: all tile base addresses and the episode-sum rows must be 16-byte aligned
   args.tma_ok = (c->num_envs % 4 == 0) && al16(b->root_states) && al16(b->dof_state) && al16(b->contact_forces) &&
                 al16(b->torques) && al16(b->actions) && al16(b->last_actions) && al16(b->last_dof_vel) &&
                 al16(b->commands) && al16(b->feet_air_time) && al16(b->episode_length_buf) &&
                 al16(b->episode_sums) && al16(b->obs_buf) && (b->terrain_levels == nullptr || al16(b->terrain_levels));
-  // one 32-env tile per CTA by default: the tile is latency-bound, so short CTAs that the
-  // hardware scheduler backfills beat equal persistent ranges (0.105 ms vs 0.120 ms at 65536 envs).
-  // envs_per_cta > 0 gives each CTA a longer range that it walks in sub-tiles of 32.
-  int per = TILE;
-  if (c->envs_per_cta > 0) per = (c->envs_per_cta + 3) & ~3;
-  args.per = per;
-  args.max_sub = (per + TILE - 1) / TILE;
-  const int grid = (c->num_envs + per - 1) / per;
+  // Grid: the tile is latency-bound, so what counts is how many tiles are resident.  More
+  // envs than one wave of 32-env tiles: one tile per CTA, the hardware scheduler backfills the slots
+  // (measured at 65536 envs: 0.087 ms; equal persistent ranges 0.105 ms; smaller tiles for the last
+  // wave 0.094 ms).  Fewer: the envs are dealt to all the resident slots in equal smaller tiles (4096
+  // envs: 8-env tiles, 0.024 ms instead of 0.040 ms).  envs_per_cta > 0 overrides both.
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0;
+    LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
+    LGK_CUDA_RETURN_IF(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  int grid;
+  if (c->envs_per_cta > 0) {
+    args.per = (c->envs_per_cta + 3) & ~3;
+    grid = (c->num_envs + args.per - 1) / args.per;
+    args.n_big = grid;
+    args.per_small = args.per;
+  } else {
+    int per_sm = (int)((227u * 1024u) / (smem + 1024u));
+    if (per_sm > LGK_MIN_CTAS) per_sm = LGK_MIN_CTAS;
+    if (per_sm < 1) per_sm = 1;
+    const int slots = num_sms * per_sm;
+    args.per = TILE;
+    args.n_big = c->num_envs > TILE * slots ? (c->num_envs + TILE - 1) / TILE : 0;
+    const int rest = c->num_envs - args.n_big * TILE;   // > 0 only in the single-wave case
+    args.per_small = (((rest + slots - 1) / slots) + 3) & ~3;
+    if (args.per_small < 4) args.per_small = 4;
+    grid = args.n_big + (rest > 0 ? (rest + args.per_small - 1) / args.per_small : 0);
+  }
+  args.max_sub = (args.per + TILE - 1) / TILE;
   const bool taps = c->rng_mode == LGK_RNG_TAPS;
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
   const int H = c->num_height_points;

@@ -7,7 +7,7 @@ import torch, helpers
 from legged_gym_b200 import _lgk
 from legged_gym_b200.utils import synthetic
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 65536
-per = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+per = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 def extra(cfg):
     cfg.terrain.materialize_heights = False
     cfg.env.envs_per_cta = per
@@ -17,28 +17,28 @@ for i in range(6):
     synthetic.load_frame(env, fr[i % 2]); env.step(fr[i % 2]["actions"])
 torch.cuda.synchronize()
 lib = _lgk.load()
-n = 2048 * 2 * 8
+n = 4096 * 2 * 8
 buf = (C.c_longlong * n)()
 lib.lgk_debug_read_prof.argtypes = [C.c_void_p, C.c_int]
 assert lib.lgk_debug_read_prof(buf, n) == 0
-t = torch.tensor(list(buf), dtype=torch.float64).view(2048, 2, 8)
-ncta = min(2048, (N + per - 1) // per)
+t = torch.tensor(list(buf), dtype=torch.float64).view(4096, 2, 8)
+ncta = min(4096, (N + per - 1) // per) if per > 0 else int(sys.argv[3])   # per = 0: the library's own grid (first 4096 CTAs)
 t = t[:ncta]
 t0 = t[:, 0, 0].min()
-names = ["load", "stage1", "barrier1", "stage2", "wait_w123", "stage3"]
+names = ["load", "stage1", "barrier1", "stage2", "s3_A+barrier", "s3_BC"]
 for w in (0, 1):
     d = t[:, w, 1:7] - t[:, w, 0:6]
     print(f"warp {w}: " + "  ".join(f"{names[k]} {d[:, k].mean():8.0f}" for k in range(6 if w == 0 else 4)), " total", float((t[:, w, 6 if w == 0 else 4] - t[:, w, 0]).mean()))
 d7 = t[:, 0, 7] - t[:, 0, 5]
-print("stage3 reward-table part", float(d7.mean()), " loop part", float((t[:, 0, 6] - t[:, 0, 7]).mean()))
+print("stage3 pass B (+ticket wait for W3)", float(d7.mean()), " pass C", float((t[:, 0, 6] - t[:, 0, 7]).mean()))
 print("kernel span cycles", float(t[:, 0, 6].max() - t0), " first-wave CTAs start spread", float(t[:, 0, 0].max() - t0))
 
 # CTA timeline (globaltimer, ns): waves per SM, tail
-m = 2048 * 4
+m = 4096 * 4
 buf2 = (C.c_longlong * m)()
 lib.lgk_debug_read_prof_cta.argtypes = [C.c_void_p, C.c_int]
 assert lib.lgk_debug_read_prof_cta(buf2, m) == 0
-g = torch.tensor(list(buf2), dtype=torch.float64).view(2048, 4)[:ncta]
+g = torch.tensor(list(buf2), dtype=torch.float64).view(4096, 4)[:ncta]
 g0 = g[:, 0].min()
 st, en, smid = g[:, 0] - g0, g[:, 1] - g0, g[:, 2].long()
 print(f"timeline (us): last CTA start {st.max() / 1e3:.1f}  last W0 end {en.max() / 1e3:.1f}  mean CTA life {(en - st).mean() / 1e3:.1f}")
@@ -50,3 +50,17 @@ life = (en - st)
 order = torch.argsort(st)
 k = max(ncta // 4, 1)
 print("  CTA life by start order (us): first quarter %.1f  second %.1f  third %.1f  last %.1f" % tuple(float(life[order[i * k:(i + 1) * k]].mean()) / 1e3 for i in range(4)))
+
+if per == 0:
+    nb = int(sys.argv[4])
+    for name, sl in (("big", slice(0, nb)), ("small", slice(nb, ncta))):
+        print(f"  {name}: n {life[sl].numel()} life mean {life[sl].mean() / 1e3:.1f} us  start min {st[sl].min() / 1e3:.1f} max {st[sl].max() / 1e3:.1f}  end max {en[sl].max() / 1e3:.1f}")
+        for w in (0, 1):
+            d = t[sl, w, 1:7] - t[sl, w, 0:6]
+            print(f"    warp {w}: " + "  ".join(f"{names[k]} {d[:, k].mean():8.0f}" for k in range(6 if w == 0 else 4)))
+print("  smid of CTAs 0..23:", smid[:24].tolist())
+print("  smid of CTAs 148..159:", smid[148:160].tolist(), " 296..303:", smid[296:304].tolist())
+same = {}
+for b_ in range(min(ncta, 888)):
+    same.setdefault(int(smid[b_]), []).append(b_)
+print("  first-wave CTAs on SM of CTA 0:", same[int(smid[0])], " on SM of CTA 1:", same[int(smid[1])])
