@@ -81,6 +81,13 @@ __device__ __forceinline__ uint4 philox_keyed(const unsigned int (&pk)[20], unsi
 }
 
 // ---- exact-order fp32 helpers (no contraction) ----------------------------------------
+// int16 sample (sign-extended in a 32-bit register) -> float on the ALU's I2FP instead of the
+// quarter-rate conversion unit's I2F.S16 the compiler picks when it knows the range
+__device__ __forceinline__ float s16_to_float(int v) {
+  float f;
+  asm("cvt.rn.f32.s32 %0, %1;" : "=f"(f) : "r"(v));
+  return f;
+}
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }

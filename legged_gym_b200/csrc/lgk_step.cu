@@ -38,14 +38,20 @@
 #define TILE 32
 #define HP_OFF (((RS * (LGK_REW_COUNT + 1)) + 3) & ~3)   // base-height partial sums, after the reward table
 #define RS (TILE + 1)   // row stride of the [row][env] reward tables: conflict-free by row and by env
+#ifndef LGK_STAGE2_ENVS
+#define LGK_STAGE2_ENVS 1   // envs a warp keeps in flight in stage 2 (2 measured slower: stage 2 is issue-bound at full residency)
+#endif
 #ifndef LGK_MIN_CTAS
 #define LGK_MIN_CTAS 6   // register cap 85: six 128-thread CTAs per SM
 #endif
 
 #ifdef LGK_PROFILE
-// development build only: per-CTA phase timestamps (clock64) of the first sub-tile, [cta][warp 0 / 1][8]
-__device__ long long lgk_prof[4096 * 2 * 8];
-#define LGK_STAMP(k) do { if (sub == 0 && lane == 0 && wic < 2 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 2 + wic) * 8 + (k)] = clock64(); } while (0)
+// development build only: per-CTA phase timestamps (clock64) of the first sub-tile, [cta][warp][8]
+__device__ long long lgk_prof[4096 * 4 * 8];
+#ifndef LGK_PROF_SUB
+#define LGK_PROF_SUB 0
+#endif
+#define LGK_STAMP(k) do { if (sub == LGK_PROF_SUB && lane == 0 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 4 + wic) * 8 + (k)] = clock64(); } while (0)
 extern "C" int lgk_debug_read_prof(long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, lgk_prof, sizeof(long long) * n);
 }
@@ -89,9 +95,11 @@ struct StepArgs {
 };
 
 // scratch fields (SoA, [field][TILE]) exchanged between the stages
-enum { SC_ES = 0,            // 8 floats per env (AoS): rx ry rz zo | yaw_z yaw_w - -
-       SC_J1 = 8, SC_J2 = 18,  // joint partial sums of W1 / W2 (10 each)
-       SC_COLL = 28, SC_FFP, SC_RAIR, SC_STUMBLE, SC_NOFLY, SC_FIELDS };
+enum { SC_ES = 0,            // 12 floats per env (AoS), the scan's per-env operands as ready-made f32x2 pairs:
+                             //   (-2qz, 2qz) (2qz, -2qz) | (qw, qw) (-qz, qz) | (rx, ry) rz zo      (yaw-only unit quaternion)
+       ES_W = 12,
+       SC_J1 = 12, SC_J2 = 22,  // joint partial sums of W1 / W2 (10 each)
+       SC_COLL = 32, SC_FFP, SC_RAIR, SC_STUMBLE, SC_NOFLY, SC_FIELDS };
 
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float norm3(float x, float y, float z) {
@@ -622,9 +630,11 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         head_row[6] = grav[0]; head_row[7] = grav[1]; head_row[8] = grav[2];
         head_row[9] = cmd.x * c.commands_scale[0]; head_row[10] = cmd.y * c.commands_scale[1]; head_row[11] = cmd.z * c.commands_scale[2];
         // scalars of the height scan: pre-reset position / yaw, post-reset z for the observation (:227)
-        float4* es = reinterpret_cast<float4*>(scr + SC_ES * TILE + lane * 8);
-        es[0] = make_float4(root[0], root[1], root[2], sub_rn(z_obs, 0.5f));
-        es[1] = make_float4(yaw_z, yaw_w, 0.f, 0.f);
+        float4* es = reinterpret_cast<float4*>(scr + SC_ES * TILE + lane * ES_W);
+        const float yz2 = mul_rn(yaw_z, 2.0f);
+        es[0] = make_float4(-yz2, yz2, yz2, -yz2);
+        es[1] = make_float4(yaw_w, yaw_w, -yaw_z, yaw_z);
+        es[2] = make_float4(root[0], root[1], root[2], sub_rn(z_obs, 0.5f));
       }
       // ---- sub-tile bookkeeping: bitmasks for the ordered compaction, level sum --------------------
       const unsigned resample_mask = __ballot_sync(LGK_FULL_MASK, active && resample_cb);
@@ -810,85 +820,115 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (TAPS) {
         if (add_noise) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
       } else {
-        v = fmaf(fmaf((float)rbits, 3.0517578125e-05f, -0.9999847412109375f), ns, v);   // (2 * u - 1) * ns, u = (r16 + 0.5) / 2^16; ns = 0 without noise
+        // 2^23 + r16 as a float (one PRMT, no I2F on the quarter-rate conversion unit), then
+        // (2^23 + r16) * 2^-15 - 257 = r16 / 2^15 - 1, exact: uniform on [-1, 1) in steps of 2^-15; ns = 0 without noise
+        v = fmaf(fmaf(__uint_as_float(0x4b000000u | rbits), 3.0517578125e-05f, -257.0f), ns, v);
       }
       return clampf(v, -clip_obs, clip_obs);
     };
     float* hpart = sm + L.cf + HP_OFF;   // [env][RS]; torques / last_actions rows are dead after stage 1
     const float2 border2 = make_float2(c.border_size, c.border_size);
     const float2 inv2 = make_float2(inv_hs, inv_hs);
-    for (int e = wic; e < ne; e += LGK_WARPS_PER_CTA) {   // envs of the sub-tile dealt round-robin to the warps
-      const int env_e = env0 + e;
-      const float4 es0 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8);
-      const float4 es1 = *reinterpret_cast<const float4*>(scr + SC_ES * TILE + e * 8 + 4);
-      const float zo = es0.w, qz = es1.x, qw = es1.y;
+    // U envs in flight per warp (e, e + 4, ...): a single env's instruction stream is a chain of
+    // dependent latencies (index chain -> gather -> scale / noise -> store), so the warp interleaves U of them
+    constexpr int U = LGK_STAGE2_ENVS;
+    for (int e0 = wic; e0 < ne; e0 += LGK_WARPS_PER_CTA * U) {
+      int eu[U];
+      bool live[U];
+      float zo[U];
+      int raw[U][NPA];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        eu[u] = e0 + u * LGK_WARPS_PER_CTA;
+        live[u] = eu[u] < ne;
+        if (!live[u]) eu[u] = e0;   // a dead slot recomputes the first env; its stores are predicated off
+      }
       // ---- phase A: height-field indices of every pass, gathers in flight --------------------------
-      int raw[NPA];
-      if (NP > 0 && !plane) {
-        // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op for op (no contraction):
-        //   t = 2 * cross(xyz, p) = (-2qz*py, 2qz*px); r = p + w*t + cross(xyz, t) = p + qw*t + (-qz*ty, qz*tx)
-        const float qz2 = mul_rn(qz, 2.0f);
-        const float2 k_t = make_float2(-qz2, qz2), k_ts = make_float2(qz2, -qz2);
-        const float2 qw2 = make_float2(qw, qw), k_c = make_float2(-qz, qz), r2 = make_float2(es0.x, es0.y);
 #pragma unroll
-        for (int it = 0; it < NP; ++it) {
-          const float2 p = pxy_l[it], pyx = make_float2(p.y, p.x);
-          const float2 t = __fmul2_rn(k_t, pyx);     // (tx, ty)
-          const float2 ts = __fmul2_rn(k_ts, p);     // (ty, tx)
-          float2 w = __fadd2_rn(p, __fmul2_rn(qw2, t));
-          w = __fadd2_rn(w, __fmul2_rn(k_c, ts));
-          w = __fadd2_rn(__fadd2_rn(w, r2), border2);
-          // (points / horizontal_scale).long(): truncation toward zero (:842)
-          float2 sxy;
-          if (MUL_RCP) sxy = __fmul2_rn(w, inv2);
-          else sxy = make_float2(__fdiv_rn(w.x, c.horizontal_scale), __fdiv_rn(w.y, c.horizontal_scale));
-          int ix = __float2int_rz(sxy.x), iy = __float2int_rz(sxy.y);
-          ix = __vimin_s32_relu(ix, max_px);   // clip(0, max): one VIMNMX.RELU
-          iy = __vimin_s32_relu(iy, max_py);
-          raw[it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
+      for (int u = 0; u < U; ++u) {
+        const float4* es = reinterpret_cast<const float4*>(scr + SC_ES * TILE + eu[u] * ES_W);
+        const float4 esa = es[0], esb = es[1], esc = es[2];
+        zo[u] = esc.w;
+        if (NP > 0 && !plane) {
+          // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op for op (no contraction):
+          //   t = 2 * cross(xyz, p) = (-2qz*py, 2qz*px); r = p + w*t + cross(xyz, t) = p + qw*t + (-qz*ty, qz*tx)
+          const float2 k_t = make_float2(esa.x, esa.y), k_ts = make_float2(esa.z, esa.w);
+          const float2 qw2 = make_float2(esb.x, esb.y), k_c = make_float2(esb.z, esb.w), r2 = make_float2(esc.x, esc.y);
+#pragma unroll
+          for (int it = 0; it < NP; ++it) {
+            const float2 p = pxy_l[it], pyx = make_float2(p.y, p.x);
+            const float2 t = __fmul2_rn(k_t, pyx);     // (tx, ty)
+            const float2 ts = __fmul2_rn(k_ts, p);     // (ty, tx)
+            float2 w = __fadd2_rn(p, __fmul2_rn(qw2, t));
+            w = __fadd2_rn(w, __fmul2_rn(k_c, ts));
+            w = __fadd2_rn(__fadd2_rn(w, r2), border2);
+            // (points / horizontal_scale).long(): truncation toward zero (:842)
+            float2 sxy;
+            if (MUL_RCP) sxy = __fmul2_rn(w, inv2);
+            else sxy = make_float2(__fdiv_rn(w.x, c.horizontal_scale), __fdiv_rn(w.y, c.horizontal_scale));
+            int ix = __float2int_rz(sxy.x), iy = __float2int_rz(sxy.y);
+            ix = __vimin_s32_relu(ix, max_px);   // clip(0, max): one VIMNMX.RELU
+            iy = __vimin_s32_relu(iy, max_py);
+            raw[u][it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
+          }
+        } else {
+#pragma unroll
+          for (int it = 0; it < NPA; ++it) raw[u][it] = 0;
         }
-      } else {
-#pragma unroll
-        for (int it = 0; it < NPA; ++it) raw[it] = 0;
       }
       // ---- observation head (covers the gather latency) --------------------------------------------
-      float* orow = b.obs_buf + (size_t)env_e * O;
-      const float* trow = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
-      const unsigned eg = (unsigned)(c.env_id_offset + env_e);
-      uint4 rnd = make_uint4(0, 0, 0, 0);
       // noise field j of this lane (head: j = 0, 1; scan pass it: j = 2 + it) = 16-bit half (j & 1) of
       // word (j % 8) / 2 of Philox block LGK_SITE_NOISE + 3 * lane + j / 8: one block covers 6 passes
-      if (!TAPS && add_noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane);
-      {
-        const float* hrow = sm + L.head + e * HS;
-        if (lane < OH) orow[lane] = noisy(hrow[lane], trow, lane, rnd.x & 0xffffu, ns_a);
-        if (lane + 32 < OH) orow[lane + 32] = noisy(hrow[lane + 32], trow, lane + 32, rnd.x >> 16, ns_b);
+      uint4 rnd[U];
+      float* orow[U];
+      const float* trow[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int env_e = env0 + eu[u];
+        orow[u] = b.obs_buf + (size_t)env_e * O;
+        trow[u] = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
+        rnd[u] = make_uint4(0, 0, 0, 0);
+        if (!TAPS && add_noise) rnd[u] = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env_e), LGK_SITE_NOISE + 3 * lane);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float* hrow = sm + L.head + eu[u] * HS;
+        const float o0 = noisy(hrow[lane], trow[u], lane, rnd[u].x & 0xffffu, ns_a);
+        if (live[u] && lane < OH) orow[u][lane] = o0;
+        if (lane + 32 < OH) {
+          const float o1 = noisy(hrow[lane + 32], trow[u], lane + 32, rnd[u].x >> 16, ns_b);
+          if (live[u]) orow[u][lane + 32] = o1;
+        }
       }
       // ---- phase B: heights -> observation columns -----------------------------------------------
-      float hsum = 0.f;
 #pragma unroll
-      for (int it = 0; it < NP; ++it) {
-        if (!TAPS && add_noise && it == 6) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE + 3 * lane + 1);
-        const int w = ((it + 2) >> 1) & 3;
-        const unsigned rw = w == 0 ? rnd.x : w == 1 ? rnd.y : w == 2 ? rnd.z : rnd.w;
-        const unsigned rbits = (it & 1) ? rw >> 16 : rw & 0xffffu;
-        const int h = it * 32 + lane;
-        const bool ok = h < H;
-        const float hgt = mul_rn((float)raw[it], c.vertical_scale);
-        if ((it + 1) * 32 <= H) hsum += hgt;   // only the last pass can hold lanes past H
-        else hsum += ok ? hgt : 0.f;
-        const float v = clampf(sub_rn(zo, hgt), -1.f, 1.f) * c.obs_scale_height;
-        const float o = noisy(v, trow, ok ? OH + h : 0, rbits, ns_h[it]);
-        if (ok) orow[OH + h] = o;
-      }
-      if (b.measured_heights != nullptr) {   // optional materialisation of measured_heights [N,H]
-        float* mrow = b.measured_heights + (size_t)env_e * H;
+      for (int u = 0; u < U; ++u) {
+        float hsum = 0.f;
 #pragma unroll
-        for (int it = 0; it < NP; ++it)
-          if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn((float)raw[it], c.vertical_scale);
+        for (int it = 0; it < NP; ++it) {
+          if (!TAPS && add_noise && it == 6)
+            rnd[u] = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env0 + eu[u]), LGK_SITE_NOISE + 3 * lane + 1);
+          const int w = ((it + 2) >> 1) & 3;
+          const unsigned rw = w == 0 ? rnd[u].x : w == 1 ? rnd[u].y : w == 2 ? rnd[u].z : rnd[u].w;
+          const unsigned rbits = (it & 1) ? rw >> 16 : rw & 0xffffu;
+          const int h = it * 32 + lane;
+          // the specialised instantiations run with ceil(H / 32) == NP: only the last pass holds lanes past H
+          const bool ok = (DT > 0 && it < NP - 1) ? true : h < H;
+          const float hgt = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
+          hsum += ok ? hgt : 0.f;
+          const float v = clampf(sub_rn(zo[u], hgt), -1.f, 1.f) * c.obs_scale_height;
+          const float o = noisy(v, trow[u], ok ? OH + h : 0, rbits, ns_h[it]);
+          if (ok && live[u]) orow[u][OH + h] = o;
+        }
+        if (b.measured_heights != nullptr && live[u]) {   // optional materialisation of measured_heights [N,H]
+          float* mrow = b.measured_heights + (size_t)(env0 + eu[u]) * H;
+#pragma unroll
+          for (int it = 0; it < NP; ++it)
+            if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
+        }
+        // _reward_base_height (:871) needs mean_h(height): this lane's partial sum; added up in stage 3
+        if (a.bh_active && live[u]) hpart[eu[u] * RS + lane] = hsum;
       }
-      // _reward_base_height (:871) needs mean_h(height): this lane's partial sum; W0 adds them in stage 3
-      if (a.bh_active) hpart[e * RS + lane] = hsum;
     }
   }
   LGK_STAMP(4);
@@ -947,7 +987,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     {   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height);
         // lane (q, el) adds a quarter of the partial sums of env e_lo + el
       const int e = min(e_lo + el, TILE - 1);
-      float bh = scr[SC_ES * TILE + e * 8 + 2];   // root z before the reset
+      float bh = scr[SC_ES * TILE + e * ES_W + 10];   // root z before the reset
       if (a.bh_active && H > 0) {
         const float* hp = sm + L.cf + HP_OFF + e * RS + q * 8;
         float hs = 0.f;
@@ -1160,7 +1200,7 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
                : launch_step<DT, false, false, NP>(args, grid, smem, stream)))
   if (D == 12 && np == 6) return LGK_DISPATCH(12, 6);   // 187-point scan
   if (D == 12 && np == 0) return LGK_DISPATCH(12, 0);   // blind
-  if (D == 12 && np <= 4) return LGK_DISPATCH(12, 4);   // Cassie's 121 points
+  if (D == 12 && np == 4) return LGK_DISPATCH(12, 4);   // Cassie's 121 points
   return LGK_DISPATCH(0, 8);
 #undef LGK_DISPATCH
 }

@@ -2,7 +2,7 @@
 import ctypes as C, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
-os.environ["LGK_LIB_PATH"] = os.path.join(ROOT, "build", "liblgk_prof.so")
+os.environ["LGK_LIB_PATH"] = os.path.join(ROOT, "build", os.environ.get("LGK_PROF_LIB", "liblgk_prof.so"))
 import torch, helpers
 from legged_gym_b200 import _lgk
 from legged_gym_b200.utils import synthetic
@@ -17,18 +17,18 @@ for i in range(6):
     synthetic.load_frame(env, fr[i % 2]); env.step(fr[i % 2]["actions"])
 torch.cuda.synchronize()
 lib = _lgk.load()
-n = 4096 * 2 * 8
+n = 4096 * 4 * 8
 buf = (C.c_longlong * n)()
 lib.lgk_debug_read_prof.argtypes = [C.c_void_p, C.c_int]
 assert lib.lgk_debug_read_prof(buf, n) == 0
-t = torch.tensor(list(buf), dtype=torch.float64).view(4096, 2, 8)
+t = torch.tensor(list(buf), dtype=torch.float64).view(4096, 4, 8)
 ncta = min(4096, (N + per - 1) // per) if per > 0 else int(sys.argv[3])   # per = 0: the library's own grid (first 4096 CTAs)
 t = t[:ncta]
 t0 = t[:, 0, 0].min()
 names = ["load", "stage1", "barrier1", "stage2", "s3_A+barrier", "s3_BC"]
-for w in (0, 1):
+for w in (0, 1, 2, 3):
     d = t[:, w, 1:7] - t[:, w, 0:6]
-    print(f"warp {w}: " + "  ".join(f"{names[k]} {d[:, k].mean():8.0f}" for k in range(6 if w == 0 else 4)), " total", float((t[:, w, 6 if w == 0 else 4] - t[:, w, 0]).mean()))
+    print(f"warp {w}: " + "  ".join(f"{names[k]} {d[:, k].mean():8.0f}" for k in range(6)), " total", float((t[:, w, 6] - t[:, w, 0]).mean()))
 d7 = t[:, 0, 7] - t[:, 0, 5]
 print("stage3 pass B (+ticket wait for W3)", float(d7.mean()), " pass C", float((t[:, 0, 6] - t[:, 0, 7]).mean()))
 print("kernel span cycles", float(t[:, 0, 6].max() - t0), " first-wave CTAs start spread", float(t[:, 0, 0].max() - t0))
