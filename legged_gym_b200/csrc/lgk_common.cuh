@@ -20,12 +20,10 @@ struct LgkWorkspace {
 };
 #define LGK_WS_HEADER_BYTES 512
 #ifdef __CUDACC__
-// ticket counters: release-ordered increment (MEMBAR.ALL.GPU + ATOMG; no L1 invalidation, unlike
-// __threadfence() + atomicAdd), so everything the CTA wrote before it is visible to whoever draws the last ticket
-__device__ __forceinline__ unsigned int ticket_release(unsigned int* p) {
-  unsigned int old;
-  asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
-  return old;
+// ticket counters: release-ordered increment (MEMBAR.ALL.GPU + RED; no L1 invalidation, unlike
+// __threadfence() + atomicAdd), so everything the CTA wrote before it is visible to whoever sees the count
+__device__ __forceinline__ void ticket_release(unsigned int* p) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
 }
 #endif
 static_assert(sizeof(LgkWorkspace) <= LGK_WS_HEADER_BYTES, "workspace header too large");

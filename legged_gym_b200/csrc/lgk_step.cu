@@ -33,6 +33,9 @@
 //
 // Code size matters here (the four roles + two stages exceed the instruction cache when everything
 // is inlined): paths that run once per launch or only for ragged / unaligned tiles are __noinline__.
+#include <cmath>
+#include <limits>
+#include <type_traits>
 #include "lgk_common.cuh"
 
 #define TILE 32
@@ -47,11 +50,11 @@
 
 #ifdef LGK_PROFILE
 // development build only: per-CTA phase timestamps (clock64) of the first sub-tile, [cta][warp][8]
-__device__ long long lgk_prof[4096 * 4 * 8];
+__device__ long long lgk_prof[4096 * 4 * 16];
 #ifndef LGK_PROF_SUB
 #define LGK_PROF_SUB 0
 #endif
-#define LGK_STAMP(k) do { if (sub == LGK_PROF_SUB && lane == 0 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 4 + wic) * 8 + (k)] = clock64(); } while (0)
+#define LGK_STAMP(k) do { if (sub == LGK_PROF_SUB && lane == 0 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 4 + wic) * 16 + (k)] = clock64(); } while (0)
 extern "C" int lgk_debug_read_prof(long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, lgk_prof, sizeof(long long) * n);
 }
@@ -92,6 +95,9 @@ struct StepArgs {
   const char* ld_src[LGK_LD_ARRAYS];
   unsigned ld_off[LGK_LD_ARRAYS], ld_bpe[LGK_LD_ARRAYS];
   unsigned ld_bytes_per_env;   // sum of ld_bpe
+  // norm > c without the square root: sqrt is monotone and correctly rounded, so sqrtf(s) > c is the same
+  // predicate as s > thr(c), thr(c) = the largest float whose square root rounds to <= c (found on the host)
+  float thr_term, thr_pen, thr_ffp;   // c = 1 (:146), 0.1 (:897), max_contact_force (:962)
 };
 
 // scratch fields (SoA, [field][TILE]) exchanged between the stages
@@ -107,12 +113,13 @@ __device__ __forceinline__ float norm3(float x, float y, float z) {
 }
 
 // any termination body with |f| > 1 (:146)
-__device__ __forceinline__ bool term_contact(const LgkConsts& c, const float* __restrict__ cf) {
+__device__ __forceinline__ float sumsq3(float x, float y, float z) { return fmaf(z, z, fmaf(y, y, x * x)); }
+__device__ __forceinline__ bool term_contact(const LgkConsts& c, const float* __restrict__ cf, float thr_term) {
   bool t = false;
 #pragma unroll 1
   for (int k = 0; k < c.num_term; ++k) {
     const float* f = cf + 3 * c.term_idx[k];
-    t |= norm3(f[0], f[1], f[2]) > 1.0f;
+    t |= sumsq3(f[0], f[1], f[2]) > thr_term;   // norm > 1
   }
   return t;
 }
@@ -287,13 +294,13 @@ static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const
 
 // ordered compaction of the reset / resample masks into ascending id lists (one CTA per launch)
 static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace* ws, int tid) {
-  constexpr int NT = LGK_CTA_THREADS - 32;   // run by W1..W3: tid in [0, 96)
+  constexpr int NT = LGK_CTA_THREADS;   // run by the finisher CTA
   __shared__ int s_scan[2][LGK_WARPS_PER_CTA + 1];
   const LgkBuffers& b = a.b;
   const int N = a.c.num_envs;
   const int lane = tid & 31, wic = tid >> 5;
   __threadfence();
-  const int nt = gridDim.x * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
+  const int nt = ((int)gridDim.x - 1) * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
   const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
   const unsigned* rm = mask_base;                      // read with ld.global.cg: the masks were published through L2
   const unsigned* sv = mask_base + lgk_max_warps(N);
@@ -335,10 +342,10 @@ static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace*
   }
   if (lane == 31) { s_scan[0][wic + 1] = i0; s_scan[1][wic + 1] = i1; }
   if (tid == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
-  asm volatile("bar.sync 2, %0;" ::"n"(NT) : "memory");
+  __syncthreads();
   int base0 = 0, base1 = 0, n_reset = 0, n_resample = 0;
 #pragma unroll
-  for (int w = 0; w < LGK_WARPS_PER_CTA - 1; ++w) {
+  for (int w = 0; w < LGK_WARPS_PER_CTA; ++w) {
     if (w < wic) { base0 += s_scan[0][w + 1]; base1 += s_scan[1][w + 1]; }
     n_reset += s_scan[0][w + 1];
     n_resample += s_scan[1][w + 1];
@@ -407,6 +414,28 @@ static __device__ __noinline__ void finalize_stats(const StepArgs& a, LgkWorkspa
 }
 
 // ---------------------------------------------------------------------------------------------
+// The launch's last CTA (blockIdx = gridDim - 1) owns no envs: it waits for the tile CTAs' tickets and
+// does the two serial jobs of the step off their critical path - the ordered id lists once every tile
+// has published its masks (while the last wave is still scanning heights), the episode statistics
+// once every tile has added its sums.  It is dispatched after every tile CTA and nothing waits on it,
+// so the polling cannot hold anything up.
+static __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+static __device__ __noinline__ void finisher(const StepArgs& a, LgkWorkspace* ws, unsigned long long csc) {
+  const unsigned n_tiles = gridDim.x - 1;
+  const int tid = threadIdx.x;
+  if (tid == 0) while (ld_acquire_gpu(&ws->mask_ticket) != n_tiles) __nanosleep(200);
+  __syncthreads();
+  compact_ids(a, ws, tid);
+  if (tid >= 32) return;
+  if (tid == 0) while (ld_acquire_gpu(&ws->done_ticket) != n_tiles) __nanosleep(200);
+  __syncwarp();
+  finalize_stats(a, ws, csc);
+}
+
 template <int DT, bool TAPS, bool MUL_RCP, int NP>
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_MIN_CTAS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
@@ -428,7 +457,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 
   extern __shared__ __align__(16) float sm[];
   __shared__ __align__(8) uint64_t s_bar;
-  __shared__ unsigned s_is_last;
 
   // roles go by the logical warp index wic: rotated per CTA so that the W0s of the CTAs resident on an
   // SM (the longest role, and the only one running in stage 3) do not all sit on the same scheduler
@@ -441,16 +469,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int nsub = (cta_ne + TILE - 1) / TILE;
   const bool has_levels = b.terrain_levels != nullptr;
 
+  if (blockIdx.x == gridDim.x - 1) {   // the finisher CTA: id lists and statistics, no envs
+    LgkWorkspace* wsf = reinterpret_cast<LgkWorkspace*>(b.workspace);
+    finisher(a, wsf, wsf->step_counter + 1ull);
+    return;
+  }
   // ---- first thing: W0 sets the mbarrier up and gets the bulk loads of the first sub-tile going; the
   // rest of the prologue runs under their latency.  Lane i copies input array i.
   const char* ld_src = nullptr;
   unsigned ld_off = 0, ld_bpe = 0;
   if (wic == 0) {
     if (lane < LGK_LD_ARRAYS) { ld_src = a.ld_src[lane]; ld_off = a.ld_off[lane]; ld_bpe = a.ld_bpe[lane]; }
-    if (lane == 0) {
-      mbar_init(&s_bar, 1);
-      s_is_last = 0u;
-    }
+    if (lane == 0) mbar_init(&s_bar, 1);
     __syncwarp();
     const int ne0 = min(TILE, cta_ne);
     if (a.tma_ok && (ne0 & 3) == 0) {
@@ -487,8 +517,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 
   __syncthreads();          // barrier initialised before anyone polls it, row table written
 
-  bool stats_last = false;
-  unsigned mask_old = 0u;
   for (int sub = 0; sub < nsub; ++sub) {
     const int env0 = cta_env0 + sub * TILE;
     const int ne = min(TILE, cta_ne - sub * TILE);
@@ -530,7 +558,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     bool time_out = false, reset = false;
     if (active) {
       time_out = (ep_in + 1) > c.max_episode_length;
-      reset = term_contact(c, cf_row) || time_out;
+      reset = term_contact(c, cf_row, a.thr_term) || time_out;
     }
 
     // values W0 keeps in registers from stage 1 to stage 3
@@ -538,6 +566,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     float4 cmd_rew = make_float4(0, 0, 0, 0);
     const unsigned reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
 
+    LGK_STAMP(12);
     // =========================================== stage 1 =========================================
     if (wic == 0) {
       // ---- W0: base state, commands, termination, root reset, per-env outputs --------------------
@@ -729,21 +758,37 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       bool stumble = false;
       int nofly = 0;
       if (active) {
+        // four bodies per trip: the index loads (constant bank, dynamic offset), the row reads and the
+        // square roots of a trip are independent, so their latencies overlap instead of adding up
 #pragma unroll 1
-        for (int p = 0; p < c.num_pen; ++p) {
-          const float* f = cf_row + 3 * c.pen_idx[p];
-          collisions += (norm3(f[0], f[1], f[2]) > 0.1f) ? 1.f : 0.f;
+        for (int p0 = 0; p0 < c.num_pen; p0 += 4) {
+          float n[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float* f = cf_row + 3 * c.pen_idx[min(p0 + j, c.num_pen - 1)];
+            n[j] = sumsq3(f[0], f[1], f[2]);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) collisions += (p0 + j < c.num_pen && n[j] > a.thr_pen) ? 1.f : 0.f;   // norm > 0.1
         }
+        LGK_STAMP(10);
         const float* fa_in = sm + L.fat + lane * F;
         float* fa_out = b.feet_air_time + (size_t)env * F;
-#pragma unroll 1
+#pragma unroll 2
         for (int k = 0; k < F; ++k) {
           const float* f = cf_row + 3 * c.feet_idx[k];
           const float fx = f[0], fy = f[1], fz = f[2];
           const bool contact = fz > 1.0f;
           nofly += (fz > 0.1f) ? 1 : 0;
-          stumble |= sqrtf(fmaf(fy, fy, fx * fx)) > 5.0f * fabsf(fz);
-          ffp += fmaxf(norm3(fx, fy, fz) - c.max_contact_force, 0.f);
+          {   // |f_xy| > 5 |f_z| (:957): decided on the squares when they are not within rounding of each other
+            const float sxy = fmaf(fy, fy, fx * fx), r = 5.0f * fabsf(fz), r2 = r * r;
+            if (sxy > r2 * 1.00001f) stumble = true;
+            else if (sxy >= r2 * 0.99999f) stumble |= sqrtf(sxy) > r;
+          }
+          {   // clip(norm - max_contact_force, min=0) (:962): zero unless norm > max_contact_force
+            const float s3 = sumsq3(fx, fy, fz);
+            if (s3 > a.thr_ffp) ffp += fmaxf(sqrtf(s3) - c.max_contact_force, 0.f);
+          }
           float t = fa_in[k];
           if (a.air_active) {   // the state only advances inside _reward_feet_air_time
             const bool first = (t > 0.f) && contact;
@@ -754,6 +799,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           if (a.air_active || reset) fa_out[k] = reset ? 0.f : t;   // zeroed on reset (:178)
         }
       }
+      LGK_STAMP(11);
       scr[SC_COLL * TILE + lane] = collisions;
       scr[SC_FFP * TILE + lane] = ffp;
       scr[SC_RAIR * TILE + lane] = r_air;       // masked by |cmd_xy| > 0.1 in stage 3
@@ -775,9 +821,9 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     } else if (wic > 0) {
       tile_store_fallback(a, sm, env0, ne, tid);
     }
-    // mask ticket (release: W0's masks are ordered before it by the barrier above); W3 looks at the
-    // answer after its stage 2, so nobody waits for the round trip
-    if (last_sub && tid == 96) mask_old = ticket_release(&ws->mask_ticket);
+    // mask ticket (release: W0's masks are ordered before it by the barrier above); the finisher CTA
+    // compacts the id lists once all tickets are in
+    if (last_sub && tid == 96) ticket_release(&ws->mask_ticket);
     if (wic == 3 && lane < ne) {
       // episode-sum rows ([R, N], 128 B per row and tile): 4-byte cp.async (LDGSTS) per lane and row into
       // rows the joints no longer need; in flight during stage 2, awaited before the stage-3 barrier
@@ -816,16 +862,23 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     const float ns_a = (add_noise && lane < OH) ? __ldg(b.noise_scale_vec + lane) : 0.f;
     const float ns_b = (add_noise && lane + 32 < OH) ? __ldg(b.noise_scale_vec + lane + 32) : 0.f;
     // obs = clip(v + (2*rand - 1) * noise_scale_vec, +-clip_observations)   (:231, :104)
-    auto noisy = [&](float v, const float* __restrict__ trow, int col, unsigned rbits, float ns) {
+    auto noisy = [&](float v, const float* __restrict__ trow, int col, unsigned rw, int half, float ns, bool clip) {
       if (TAPS) {
         if (add_noise) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
       } else {
         // 2^23 + r16 as a float (one PRMT, no I2F on the quarter-rate conversion unit), then
         // (2^23 + r16) * 2^-15 - 257 = r16 / 2^15 - 1, exact: uniform on [-1, 1) in steps of 2^-15; ns = 0 without noise
-        v = fmaf(fmaf(__uint_as_float(0x4b000000u | rbits), 3.0517578125e-05f, -257.0f), ns, v);
+        const unsigned m = half ? __byte_perm(rw, 0x4b000000u, 0x7632) : __byte_perm(rw, 0x4b000000u, 0x7610);
+        v = fmaf(fmaf(__uint_as_float(m), 3.0517578125e-05f, -257.0f), ns, v);
       }
-      return clampf(v, -clip_obs, clip_obs);
+      return clip ? clampf(v, -clip_obs, clip_obs) : v;
     };
+    // the scan columns are bounded by obs_scale_height * 1 + noise: when that is inside clip_observations
+    // for every column (warp-uniform), their clip is the identity and is skipped
+    bool clip_h = false;
+#pragma unroll
+    for (int it = 0; it < NP; ++it) clip_h |= !(fabsf(c.obs_scale_height) + fabsf(ns_h[it]) <= clip_obs);
+    clip_h = __any_sync(LGK_FULL_MASK, clip_h);
     float* hpart = sm + L.cf + HP_OFF;   // [env][RS]; torques / last_actions rows are dead after stage 1
     const float2 border2 = make_float2(c.border_size, c.border_size);
     const float2 inv2 = make_float2(inv_hs, inv_hs);
@@ -866,7 +919,15 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
             float2 sxy;
             if (MUL_RCP) sxy = __fmul2_rn(w, inv2);
             else sxy = make_float2(__fdiv_rn(w.x, c.horizontal_scale), __fdiv_rn(w.y, c.horizontal_scale));
+#ifdef LGK_F2I_ON_XU
             int ix = __float2int_rz(sxy.x), iy = __float2int_rz(sxy.y);
+#else
+            // trunc toward zero without the quarter-rate conversion unit: 2^23 + s, rounded toward zero, holds
+            // trunc(s) in its mantissa for 0 <= s < 2^23; s < 0 lands below 2^23 (negative after the subtraction,
+            // clipped to 0 like trunc(s) would be), s >= 2^23 / NaN above the clip's upper bound
+            const float2 mg = __fadd2_rz(sxy, make_float2(8388608.0f, 8388608.0f));
+            int ix = __float_as_int(mg.x) - 0x4b000000, iy = __float_as_int(mg.y) - 0x4b000000;
+#endif
             ix = __vimin_s32_relu(ix, max_px);   // clip(0, max): one VIMNMX.RELU
             iy = __vimin_s32_relu(iy, max_py);
             raw[u][it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
@@ -893,42 +954,46 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const float* hrow = sm + L.head + eu[u] * HS;
-        const float o0 = noisy(hrow[lane], trow[u], lane, rnd[u].x & 0xffffu, ns_a);
+        const float o0 = noisy(hrow[lane], trow[u], lane, rnd[u].x, 0, ns_a, true);
         if (live[u] && lane < OH) orow[u][lane] = o0;
         if (lane + 32 < OH) {
-          const float o1 = noisy(hrow[lane + 32], trow[u], lane + 32, rnd[u].x >> 16, ns_b);
+          const float o1 = noisy(hrow[lane + 32], trow[u], lane + 32, rnd[u].x, 1, ns_b, true);
           if (live[u]) orow[u][lane + 32] = o1;
         }
       }
-      // ---- phase B: heights -> observation columns -----------------------------------------------
+      // ---- phase B: heights -> observation columns (two copies: with and without the final clip) ----
+      auto phase_b = [&](auto clip_tag) {
+        constexpr bool CLIP = decltype(clip_tag)::value;
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        float hsum = 0.f;
+        for (int u = 0; u < U; ++u) {
+          float hsum = 0.f;
 #pragma unroll
-        for (int it = 0; it < NP; ++it) {
-          if (!TAPS && add_noise && it == 6)
-            rnd[u] = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env0 + eu[u]), LGK_SITE_NOISE + 3 * lane + 1);
-          const int w = ((it + 2) >> 1) & 3;
-          const unsigned rw = w == 0 ? rnd[u].x : w == 1 ? rnd[u].y : w == 2 ? rnd[u].z : rnd[u].w;
-          const unsigned rbits = (it & 1) ? rw >> 16 : rw & 0xffffu;
-          const int h = it * 32 + lane;
-          // the specialised instantiations run with ceil(H / 32) == NP: only the last pass holds lanes past H
-          const bool ok = (DT > 0 && it < NP - 1) ? true : h < H;
-          const float hgt = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
-          hsum += ok ? hgt : 0.f;
-          const float v = clampf(sub_rn(zo[u], hgt), -1.f, 1.f) * c.obs_scale_height;
-          const float o = noisy(v, trow[u], ok ? OH + h : 0, rbits, ns_h[it]);
-          if (ok && live[u]) orow[u][OH + h] = o;
+          for (int it = 0; it < NP; ++it) {
+            if (!TAPS && add_noise && it == 6)
+              rnd[u] = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env0 + eu[u]), LGK_SITE_NOISE + 3 * lane + 1);
+            const int w = ((it + 2) >> 1) & 3;
+            const unsigned rw = w == 0 ? rnd[u].x : w == 1 ? rnd[u].y : w == 2 ? rnd[u].z : rnd[u].w;
+            const int h = it * 32 + lane;
+            // the specialised instantiations run with ceil(H / 32) == NP: only the last pass holds lanes past H
+            const bool ok = (DT > 0 && it < NP - 1) ? true : h < H;
+            const float hgt = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
+            hsum += ok ? hgt : 0.f;
+            const float v = clampf(sub_rn(zo[u], hgt), -1.f, 1.f) * c.obs_scale_height;
+            const float o = noisy(v, trow[u], ok ? OH + h : 0, rw, it & 1, ns_h[it], CLIP);
+            if (ok && live[u]) orow[u][OH + h] = o;
+          }
+          if (b.measured_heights != nullptr && live[u]) {   // optional materialisation of measured_heights [N,H]
+            float* mrow = b.measured_heights + (size_t)(env0 + eu[u]) * H;
+#pragma unroll
+            for (int it = 0; it < NP; ++it)
+              if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
+          }
+          // _reward_base_height (:871) needs mean_h(height): this lane's partial sum; added up in stage 3
+          if (a.bh_active && live[u]) hpart[eu[u] * RS + lane] = hsum;
         }
-        if (b.measured_heights != nullptr && live[u]) {   // optional materialisation of measured_heights [N,H]
-          float* mrow = b.measured_heights + (size_t)(env0 + eu[u]) * H;
-#pragma unroll
-          for (int it = 0; it < NP; ++it)
-            if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
-        }
-        // _reward_base_height (:871) needs mean_h(height): this lane's partial sum; added up in stage 3
-        if (a.bh_active && live[u]) hpart[eu[u] * RS + lane] = hsum;
-      }
+      };
+      if (clip_h) phase_b(std::true_type{});
+      else phase_b(std::false_type{});
     }
   }
   LGK_STAMP(4);
@@ -1001,6 +1066,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (q == 0 && e_lo + el < e_hi) rv[LGK_REW_BASE_HEIGHT * RS + e] = d * d;
     }
     __syncwarp();
+    LGK_STAMP(8);
     const unsigned my_resets = reset_mask & (e_hi > e_lo ? ((0xffffffffu >> (32 - (e_hi - e_lo))) << e_lo) : 0u);
     if (lane < num_rows) {
       const int row_term = s_row_term[lane];
@@ -1033,6 +1099,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       }
       if (my_resets != 0u) atomicAdd(&ws->stats[parity][lane], stat);
     }
+    LGK_STAMP(9);
     // statistics ticket (release), drawn by W3 once every warp's contributions are on their way and
     // before its own last stores: the finaliser only reads the statistics
     if (last_sub) {
@@ -1040,9 +1107,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
       } else {
         asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
-        unsigned old = 0u;
-        if (lane == 0) old = ticket_release(&ws->done_ticket);
-        stats_last = __shfl_sync(LGK_FULL_MASK, old, 0) == gridDim.x - 1;
+        if (lane == 0) ticket_release(&ws->done_ticket);
       }
     }
     __syncwarp();
@@ -1066,20 +1131,24 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   }
   LGK_STAMP(6);
   }   // sub-tiles
-  if (wic == 0) {
-    if (lane == 0) LGK_CTA_STAMP(1);
-    return;
-  }
-  // the CTA whose mask ticket was the launch's last compacts the id lists (W1..W3)
-  if (tid == 96) s_is_last = (mask_old == gridDim.x - 1) ? 1u : 0u;
-  asm volatile("bar.sync 2, %0;" ::"n"(LGK_CTA_THREADS - 32) : "memory");
-  if (s_is_last) compact_ids(a, ws, tid - 32);
-  // the W3 that drew the launch's last statistics ticket finalises the episode statistics
-  if (stats_last) finalize_stats(a, ws, csc);
+  if (wic == 0 && lane == 0) LGK_CTA_STAMP(1);
+#ifdef LGK_PROFILE
+  if (tid == 96 && blockIdx.x < 4096) lgk_prof_cta[blockIdx.x * 4 + 3] = lgk_gtime();   // W3 leaves
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
 static inline int up4(int x) { return (x + 3) & ~3; }
+// the largest float x with sqrtf(x) <= c  (c >= 0; host sqrtf is correctly rounded like the device's sqrt.rn)
+static float sqrt_le_threshold(float c) {
+  if (!(c >= 0.f)) return -1.f;   // sqrtf(s) > negative c: always (s >= 0)
+  if (std::isinf(c)) return c;
+  float x = c * c;
+  if (std::isinf(x)) x = std::numeric_limits<float>::max();
+  while (sqrtf(x) <= c && x < std::numeric_limits<float>::max()) x = std::nextafterf(x, INFINITY);
+  while (sqrtf(x) > c) x = std::nextafterf(x, -INFINITY);
+  return x;
+}
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 template <int DT, bool TAPS, bool MUL_RCP, int NP>
@@ -1106,6 +1175,9 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
     args.pk[2 * r + 1] = (unsigned)(c->seed >> 32) + (unsigned)r * 0xBB67AE85u;
   }
+  args.thr_term = sqrt_le_threshold(1.0f);
+  args.thr_pen = sqrt_le_threshold(0.1f);
+  args.thr_ffp = sqrt_le_threshold(c->max_contact_force);
   args.air_active = 0;
   args.bh_active = 0;
   for (int i = 0; i < c->num_rewards; ++i) {
@@ -1193,11 +1265,12 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
   const int H = c->num_height_points;
   const int np = (H + 31) / 32;   // scan passes of 32 points
+  // grid + 1: the last CTA is the finisher (id lists, episode statistics)
 #define LGK_DISPATCH(DT, NP)                                                            \
-  (taps ? (mul ? launch_step<DT, true, true, NP>(args, grid, smem, stream)              \
-               : launch_step<DT, true, false, NP>(args, grid, smem, stream))            \
-        : (mul ? launch_step<DT, false, true, NP>(args, grid, smem, stream)             \
-               : launch_step<DT, false, false, NP>(args, grid, smem, stream)))
+  (taps ? (mul ? launch_step<DT, true, true, NP>(args, grid + 1, smem, stream)              \
+               : launch_step<DT, true, false, NP>(args, grid + 1, smem, stream))            \
+        : (mul ? launch_step<DT, false, true, NP>(args, grid + 1, smem, stream)             \
+               : launch_step<DT, false, false, NP>(args, grid + 1, smem, stream)))
   if (D == 12 && np == 6) return LGK_DISPATCH(12, 6);   // 187-point scan
   if (D == 12 && np == 0) return LGK_DISPATCH(12, 0);   // blind
   if (D == 12 && np == 4) return LGK_DISPATCH(12, 4);   // Cassie's 121 points

@@ -101,11 +101,11 @@ def compare_env_to_oracle(env, s, tag=""):
                 assert_close(f"{tag}extras[{k}]", env.extras["episode"][k].reshape(1), torch.as_tensor(v).reshape(1).float())
 
 
-def run_parity(scenario, num_envs, steps, oracle_device="cpu", index_math=None, seed=0, materialize=True):
+def run_parity(scenario, num_envs, steps, oracle_device="cpu", index_math=None, seed=0, materialize=True, extra=None):
     """Steps this repo's env (CUDA kernels, taps) and the oracle on the same frames; compares every step."""
     from legged_gym_b200 import _lgk
     from oracle import legged_oracle as lo
-    env = make_env(scenario, num_envs, device="cuda:0", seed=seed)
+    env = make_env(scenario, num_envs, device="cuda:0", seed=seed, extra=extra)
     randomise_env_state(env, seed)
     frames = synthetic.make_frames(env, 4, seed=1234 + seed)
     synthetic.load_frame(env, frames[0])

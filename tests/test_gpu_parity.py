@@ -44,6 +44,15 @@ def test_ragged_env_counts(num_envs):
     helpers.run_parity("go1_flat", num_envs=num_envs, steps=3, oracle_device="cpu", seed=3)
 
 
+@pytest.mark.parametrize("clip", [0.75, 5.2])
+def test_tight_observation_clip(clip):
+    """clip_observations inside the range of the scan columns (5 * 1 + noise): the kernel's copy of the
+    scan loop that keeps the final clip runs (the default 100 lets it drop the clip)."""
+    def tight(cfg):
+        cfg.normalization.clip_observations = clip
+    helpers.run_parity("go1_rough_full", num_envs=300, steps=3, oracle_device="cpu", seed=5, extra=tight)
+
+
 @pytest.mark.parametrize("per_cta", [4, 40, 76, 200])
 def test_persistent_cta_ranges(per_cta):
     """envs per persistent CTA: one partial sub-tile, 32+8, 32+32+12 (the 65536-env shape), many sub-tiles."""
