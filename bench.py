@@ -281,24 +281,39 @@ def run_e2e(env, frames, args, world, device, stream):
     N = env.num_envs
     names = ("root_states", "dof_state", "contact_forces", "torques", "actions")
     host = [{k: fr[k].cpu().pin_memory() for k in names} for fr in frames]
-    dev = {k: torch.empty_like(frames[0][k]) for k in names}
-    env.bind_sim_tensors(**{k: dev[k] for k in names[:4]})
+    sim_names = names[:4]
+    # two device input sets: the simulator state of step i+1 travels host -> device on a copy stream while
+    # step i's results travel device -> host (PCIe is full duplex).  The actions of step i+1 depend on the
+    # observations of step i in a real loop, so they are copied only after the read-back has completed.
+    dev = [{k: torch.empty_like(frames[0][k]) for k in names} for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device)
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
     out_h = {"obs": torch.empty(env.obs_buf.shape, dtype=torch.float).pin_memory(),
              "rew": torch.empty(N, dtype=torch.float).pin_memory(),
              "reset": torch.empty(N, dtype=torch.bool).pin_memory()}
     h2d = sum(host[0][k].numel() * host[0][k].element_size() for k in names)
     d2h = sum(v.numel() * v.element_size() for v in out_h.values())
 
+    def prefetch(i):
+        h, d = host[i % len(host)], dev[i % 2]
+        with torch.cuda.stream(copy_stream):
+            for k in sim_names:
+                d[k].copy_(h[k], non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
     def one(i):
-        h = host[i % len(host)]
-        for k in names:
-            dev[k].copy_(h[k], non_blocking=True)
-        obs, _, rew, reset, _ = env.step(dev["actions"])
+        h, d = host[i % len(host)], dev[i % 2]
+        d["actions"].copy_(h["actions"], non_blocking=True)
+        stream.wait_event(ready[i % 2])
+        env.bind_sim_tensors(**{k: d[k] for k in sim_names})
+        obs, _, rew, reset, _ = env.step(d["actions"])
+        prefetch(i + 1)                 # the other input set: step i-1 finished with it before the last sync
         out_h["obs"].copy_(obs, non_blocking=True)
         out_h["rew"].copy_(rew, non_blocking=True)
         out_h["reset"].copy_(reset, non_blocking=True)
         stream.synchronize()            # the caller consumes the step's result before the next one
 
+    prefetch(0)
     steps = max(10, min(args.steps, 200))
     with torch.cuda.stream(stream):
         for i in range(3):
@@ -321,7 +336,8 @@ def run_e2e(env, frames, args, world, device, stream):
         ms = float(t.item())
     return {"value": round(N * world * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": round(ms / steps, 5),
-            "path": "pinned host buffers -> LeggedRobot.step() -> pinned host buffers, stream-synchronised every step"}
+            "path": "pinned host buffers -> LeggedRobot.step() -> pinned host buffers, stream-synchronised every step; "
+                    "next step's simulator state is copied in (second stream) while this step's results are copied out"}
 
 
 def cpu_reference(envs, budget_s=20.0, steps=None, warmup=1):

@@ -250,6 +250,11 @@ int lgk_clip_actions(const float* actions_in, float* actions_out, int64_t count,
 /* target_poses = clip(a*action_scale + default_dof_pos, lo, hi)  (legged_robot.py:394-397) */
 int lgk_compute_poses(const LgkConsts* c, const float* actions, float* target_poses, void* stream);
 
+/* The two above in one pass (step() with position control, legged_robot.py:85-86 then :94 -> :394-397):
+ * actions_out = clip(actions_in, +-c->clip_actions); target_poses = poses(actions_out). */
+int lgk_clip_actions_poses(const LgkConsts* c, const float* actions_in, float* actions_out, float* target_poses,
+                           void* stream);
+
 /* torques = clip(PD(...), +-torque_limits) for control_type P / V / T (legged_robot.py:370-392) */
 int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* dof_state,
                         const float* last_dof_vel, float* torques_out, void* stream);

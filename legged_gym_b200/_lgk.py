@@ -145,6 +145,7 @@ def load():
         "lgk_build_height_min3": (C.c_int, [fp, C.c_int32, C.c_int32, fp, C.c_int32, fp]),
         "lgk_clip_actions": (C.c_int, [fp, fp, C.c_int64, C.c_float, fp]),
         "lgk_compute_poses": (C.c_int, [cp, fp, fp, fp]),
+        "lgk_clip_actions_poses": (C.c_int, [cp, fp, fp, fp, fp]),
         "lgk_compute_torques": (C.c_int, [cp, fp, fp, fp, fp, fp]),
         "lgk_actuator_advance": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp, fp]),
         "lgk_post_physics_step": (C.c_int, [cp, bp, fp]),
@@ -169,7 +170,7 @@ def load():
 
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
-    "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_compute_torques", "lgk_actuator_advance",
+    "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
     "lgk_post_physics_step", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]
 

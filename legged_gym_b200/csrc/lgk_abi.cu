@@ -9,6 +9,7 @@ int lgk_reset_idx_impl(const LgkConsts*, const LgkBuffers*, const long long*, in
 int lgk_build_height_min3_impl(const int16_t*, int, int, int16_t*, int, cudaStream_t);
 int lgk_clip_actions_impl(const float*, float*, long long, float, cudaStream_t);
 int lgk_compute_poses_impl(const LgkConsts*, const float*, float*, cudaStream_t);
+int lgk_clip_actions_poses_impl(const LgkConsts*, const float*, float*, float*, cudaStream_t);
 int lgk_compute_torques_impl(const LgkConsts*, const float*, const float*, const float*, float*, cudaStream_t);
 int lgk_debug_yaw_quat_impl(const float*, int, int, float*, cudaStream_t);
 int lgk_actuator_advance_impl(int, const float*, const float*, float*, float*, float*, const float*, const float*,
@@ -117,6 +118,15 @@ int lgk_compute_poses(const LgkConsts* c, const float* actions, float* target_po
   if (!actions || !target_poses) return LGK_ERR_NULL;
   g_launches += 1;
   return lgk_compute_poses_impl(c, actions, target_poses, (cudaStream_t)stream);
+}
+
+int lgk_clip_actions_poses(const LgkConsts* c, const float* actions_in, float* actions_out, float* target_poses,
+                           void* stream) {
+  int rc = check_consts(c);
+  if (rc) return rc;
+  if (!actions_in || !actions_out || !target_poses) return LGK_ERR_NULL;
+  g_launches += 1;
+  return lgk_clip_actions_poses_impl(c, actions_in, actions_out, target_poses, (cudaStream_t)stream);
 }
 
 int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* dof_state, const float* last_dof_vel,

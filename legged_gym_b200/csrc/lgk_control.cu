@@ -132,6 +132,39 @@ extern "C" int lgk_compute_poses_impl(const LgkConsts* c, const float* actions, 
   return (int)cudaGetLastError();
 }
 
+// clip_actions (:85-86) and _compute_poses (:394-397) in one pass over the actions: 4 joints per thread
+__global__ void lgk_clip_poses_kernel(const __grid_constant__ CtrlArgs a, const float* __restrict__ in,
+                                      float* __restrict__ act_out, float* __restrict__ poses_out, long long n4,
+                                      float lim) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const int d = (int)((unsigned)(i % (unsigned)(a.D >> 2)) << 2);   // D % 4 == 0: a quad never straddles two envs
+  float4 v = __ldg(reinterpret_cast<const float4*>(in) + i);
+  v.x = clampf(v.x, -lim, lim); v.y = clampf(v.y, -lim, lim);
+  v.z = clampf(v.z, -lim, lim); v.w = clampf(v.w, -lim, lim);
+  reinterpret_cast<float4*>(act_out)[i] = v;
+  float4 p;
+  p.x = clampf(add_rn(mul_rn(v.x, a.action_scale), a.def[d]), a.lo[d], a.hi[d]);
+  p.y = clampf(add_rn(mul_rn(v.y, a.action_scale), a.def[d + 1]), a.lo[d + 1], a.hi[d + 1]);
+  p.z = clampf(add_rn(mul_rn(v.z, a.action_scale), a.def[d + 2]), a.lo[d + 2], a.hi[d + 2]);
+  p.w = clampf(add_rn(mul_rn(v.w, a.action_scale), a.def[d + 3]), a.lo[d + 3], a.hi[d + 3]);
+  reinterpret_cast<float4*>(poses_out)[i] = p;
+}
+extern "C" int lgk_clip_actions_poses_impl(const LgkConsts* c, const float* in, float* act_out, float* poses_out,
+                                           cudaStream_t st) {
+  const long long n = (long long)c->num_envs * c->num_dof;
+  const bool vec = (c->num_dof % 4 == 0) && ((((uintptr_t)in | (uintptr_t)act_out | (uintptr_t)poses_out) & 15) == 0);
+  if (!vec) {   // odd joint counts / unaligned views: the two separate kernels
+    const int rc = lgk_clip_actions_impl(in, act_out, n, c->clip_actions, st);
+    return rc != 0 ? rc : lgk_compute_poses_impl(c, act_out, poses_out, st);
+  }
+  CtrlArgs a;
+  fill_ctrl(c, a);
+  const long long n4 = n >> 2;
+  lgk_clip_poses_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(a, in, act_out, poses_out, n4, c->clip_actions);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int lgk_compute_torques_impl(const LgkConsts* c, const float* actions, const float* dof_state,
                                         const float* last_dof_vel, float* out, cudaStream_t st) {
   CtrlArgs a;

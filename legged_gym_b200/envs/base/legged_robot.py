@@ -74,11 +74,12 @@ class LeggedRobot(BaseTask):
         lib = self._kernels()
         actions = actions.to(self.device, dtype=torch.float).contiguous()
         st = _lgk.current_stream(self.device)
-        _lgk.check("lgk_clip_actions", lib.lgk_clip_actions(
-            _lgk.ptr(actions), _lgk.ptr(self.actions), actions.numel(),
-            float(self.cfg.normalization.clip_actions), st))
+        # the clip and the position targets of the clipped actions in one launch; _compute_poses() (and a
+        # subclass override that ends in super()._compute_poses(), like Go1's) finds the targets ready
+        _lgk.check("lgk_clip_actions_poses", lib.lgk_clip_actions_poses(
+            C.byref(self._consts), _lgk.ptr(actions), _lgk.ptr(self.actions), _lgk.ptr(self._target_poses_buf), st))
+        self._poses_fresh = True
         self.render()
-        self._poses_fresh = False
         for _ in range(self.cfg.control.decimation):
             # position control, as in this fork of the reference (:93-95)
             self.target_poses = self._compute_poses(self.actions).view(self.target_poses.shape)

@@ -38,12 +38,11 @@ class ShardedStats:
         return self.publish()
 
     def publish(self):
-        """Global extras["episode"] values (device tensors; no host sync)."""
+        """Global extras["episode"] values (device tensors; no host sync).  Two small kernels for the
+        whole vector; the dict entries are views into it."""
         r = self.reduced
-        n_reset = r[self.rows].clamp(min=1.0)
-        out = {}
-        for name, row in self.env._sum_row.items():
-            out['rew_' + name] = r[row] / n_reset / self.env.max_episode_length_s
+        means = r[:self.rows] / (r[self.rows].clamp(min=1.0) * self.env.max_episode_length_s)
+        out = {'rew_' + name: means[row] for name, row in self.env._sum_row.items()}
         if self.env.cfg.terrain.curriculum:
             out["terrain_level"] = r[self.rows + 1] / r[self.rows + 2].clamp(min=1.0)
         out["num_resets"] = r[self.rows]
