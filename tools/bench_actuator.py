@@ -1,0 +1,28 @@
+"""Times the Go1 actuator-net substep (history shift + 30-128-128-128-3 tanh MLP per leg)
+on config 3's shape (16384 envs) and reports it against the fp32 FFMA peak of the device.
+usage: gpurun -- 'python tools/bench_actuator.py [envs]'"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch, helpers
+from legged_gym_b200.utils import synthetic
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
+env = helpers.make_env("go1_rough_actuator", N, device="cuda:0", seed=1)
+fr = synthetic.make_frames(env, 1, seed=3)[0]
+synthetic.load_frame(env, fr)
+act = fr["actions"].clone()
+for _ in range(5):
+    env.actuator_advance(act)
+torch.cuda.synchronize()
+reps = 50
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(reps):
+    env.actuator_advance(act)
+e1.record(); torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / reps
+flop = 2 * (30 * 128 + 128 * 128 + 128 * 128 + 128 * 3) * 4 * N
+p = torch.cuda.get_device_properties(0)
+peak = p.multi_processor_count * 128 * 2 * 1.965e9
+print(f"actuator substep, {N} envs: {ms * 1e3:.1f} us  {flop / ms / 1e9:.2f} TFLOP/s fp32 = {100 * flop / (ms * 1e-3) / peak:.1f}% of the FFMA peak "
+      f"({peak / 1e12:.1f} TFLOP/s at 1965 MHz)  -> {N / ms * 1e3:.3e} env-substeps/s")
