@@ -155,7 +155,7 @@ int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* do
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream) {
   int rc = check_step(c, b);
   if (rc) return rc;
-  g_launches += 1;
+  g_launches += 2;   // tile kernel + epilogue
   return lgk_post_physics_step_impl(c, b, (cudaStream_t)stream);
 }
 

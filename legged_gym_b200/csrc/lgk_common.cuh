@@ -22,6 +22,9 @@ struct LgkWorkspace {
 #ifdef __CUDACC__
 // ticket counters: release-ordered increment (MEMBAR.ALL.GPU + RED; no L1 invalidation, unlike
 // __threadfence() + atomicAdd), so everything the CTA wrote before it is visible to whoever sees the count
+__device__ __forceinline__ void ticket_relaxed(unsigned int* p) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+}
 __device__ __forceinline__ void ticket_release(unsigned int* p) {
   asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
 }

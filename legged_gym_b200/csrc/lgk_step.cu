@@ -98,6 +98,7 @@ struct StepArgs {
   // norm > c without the square root: sqrt is monotone and correctly rounded, so sqrtf(s) > c is the same
   // predicate as s > thr(c), thr(c) = the largest float whose square root rounds to <= c (found on the host)
   float thr_term, thr_pen, thr_ffp;   // c = 1 (:146), 0.1 (:897), max_contact_force (:962)
+  unsigned hip_mask;                  // bit d set: joint d is a hip joint (_reward_hip_motion)
 };
 
 // scratch fields (SoA, [field][TILE]) exchanged between the stages
@@ -114,11 +115,18 @@ __device__ __forceinline__ float norm3(float x, float y, float z) {
 
 // any termination body with |f| > 1 (:146)
 __device__ __forceinline__ float sumsq3(float x, float y, float z) { return fmaf(z, z, fmaf(y, y, x * x)); }
-__device__ __forceinline__ bool term_contact(const LgkConsts& c, const float* __restrict__ cf, float thr_term) {
+// offsets (in floats) of the contact rows the kernel looks at, copied from the parameter block into shared
+// memory once per CTA: [0,8) feet, [8,24) penalised bodies, [24,32) termination bodies
+#define IDX_FEET 0
+#define IDX_PEN LGK_MAX_FEET
+#define IDX_TERM (LGK_MAX_FEET + LGK_MAX_PEN)
+static_assert(LGK_MAX_FEET + LGK_MAX_PEN + LGK_MAX_TERM == 32, "one lane per contact index");
+__device__ __forceinline__ bool term_contact(const LgkConsts& c, const int* __restrict__ s_idx,
+                                             const float* __restrict__ cf, float thr_term) {
   bool t = false;
 #pragma unroll 1
   for (int k = 0; k < c.num_term; ++k) {
-    const float* f = cf + 3 * c.term_idx[k];
+    const float* f = cf + s_idx[IDX_TERM + k];
     t |= sumsq3(f[0], f[1], f[2]) > thr_term;   // norm > 1
   }
   return t;
@@ -292,20 +300,28 @@ static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const
   for (int i = t; i < ne * D; i += nt) { la[i] = sm[a.L.act + i]; lv[i] = sm[a.L.ldv + i]; }
 }
 
-// ordered compaction of the reset / resample masks into ascending id lists (one CTA per launch)
-static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace* ws, int tid) {
-  constexpr int NT = LGK_CTA_THREADS;   // run by the finisher CTA
-  __shared__ int s_scan[2][LGK_WARPS_PER_CTA + 1];
+// ---------------------------------------------------------------------------------------------
+// Step epilogue: the two once-per-step serial jobs, as a second small launch behind the tile kernel
+// (one CTA of 1024 threads).  Being a separate launch, the kernel boundary orders it after every tile's
+// masks and statistics: the tile CTAs need no tickets, fences or polling, and the job runs on an idle GPU
+// instead of on one SM that is busy with tiles (there it took 16-20 us, most of it instruction fetch).
+//   1. ordered compaction of the per-tile reset / resample bitmasks into ascending id lists (:150, :342)
+//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119)
+#define EPI_THREADS 1024
+__global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const __grid_constant__ StepArgs a, int n_ctas) {
+  __shared__ int s_scan[2][EPI_THREADS / 32 + 1];
+  const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
-  const int N = a.c.num_envs;
-  const int lane = tid & 31, wic = tid >> 5;
-  __threadfence();
-  const int nt = ((int)gridDim.x - 1) * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
+  const int N = c.num_envs;
+  const int tid = threadIdx.x, lane = tid & 31, wic = tid >> 5;
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  const unsigned long long csc = ws->step_counter + 1ull;
+  const int parity = (int)(csc & 1ull);
+  // ---- id lists --------------------------------------------------------------------------------
+  const int nt = n_ctas * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
   const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
-  const unsigned* rm = mask_base;                      // read with ld.global.cg: the masks were published through L2
+  const unsigned* rm = mask_base;
   const unsigned* sv = mask_base + lgk_max_warps(N);
-  const int per = (nt + NT - 1) / NT;
-  const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
   // slots of sub-tiles past a CTA's range were never written this launch: skip them
   const bool one_sub = a.max_sub == 1;
   auto slot_env0 = [&](int t) {
@@ -318,79 +334,56 @@ static __device__ __noinline__ void compact_ids(const StepArgs& a, LgkWorkspace*
     const int cta = t / a.max_sub, k = t - cta * a.max_sub;
     return k * TILE < min(a.per, N - cta * a.per);
   };
-  // this launch's serial tail: keep eight slots (sixteen L2 loads) in flight per thread
-  constexpr int U = 8;
+  const int per = (nt + EPI_THREADS - 1) / EPI_THREADS;   // 2 at 65536 envs
+  const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
   int c0 = 0, c1 = 0;
-#pragma unroll 1
-  for (int t = t0; t < t1; t += U) {
-    unsigned mr[U], ms[U];
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
-      const bool ok = t + k < t1 && slot_ok(t + k);
-      mr[k] = ok ? __ldcg(rm + t + k) : 0u;
-      ms[k] = ok ? __ldcg(sv + t + k) : 0u;
-    }
-#pragma unroll
-    for (int k = 0; k < U; ++k) { c0 += __popc(mr[k]); c1 += __popc(ms[k]); }
-  }
-  // block-wide exclusive scan of (c0, c1): shuffles inside a warp, 4 warp totals through shared memory
+#pragma unroll 4
+  for (int t = t0; t < t1; ++t)
+    if (slot_ok(t)) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
+  // block-wide exclusive scan of (c0, c1): shuffles inside a warp, warp totals through shared memory
   int i0 = c0, i1 = c1;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const int y0 = __shfl_up_sync(LGK_FULL_MASK, i0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, i1, o);
     if (lane >= o) { i0 += y0; i1 += y1; }
   }
-  if (lane == 31) { s_scan[0][wic + 1] = i0; s_scan[1][wic + 1] = i1; }
-  if (tid == 0) { s_scan[0][0] = 0; s_scan[1][0] = 0; }
+  if (lane == 31) { s_scan[0][wic] = i0; s_scan[1][wic] = i1; }
   __syncthreads();
-  int base0 = 0, base1 = 0, n_reset = 0, n_resample = 0;
+  if (wic == 0) {   // exclusive scan of the 32 warp totals
+    int w0 = s_scan[0][lane], w1 = s_scan[1][lane];
+    const int t0w = w0, t1w = w1;
 #pragma unroll
-  for (int w = 0; w < LGK_WARPS_PER_CTA; ++w) {
-    if (w < wic) { base0 += s_scan[0][w + 1]; base1 += s_scan[1][w + 1]; }
-    n_reset += s_scan[0][w + 1];
-    n_resample += s_scan[1][w + 1];
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y0 = __shfl_up_sync(LGK_FULL_MASK, w0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, w1, o);
+      if (lane >= o) { w0 += y0; w1 += y1; }
+    }
+    s_scan[0][lane] = w0 - t0w;
+    s_scan[1][lane] = w1 - t1w;
+    if (lane == 31) { s_scan[0][32] = w0; s_scan[1][32] = w1; }
   }
-  int o0 = base0 + i0 - c0, o1 = base1 + i1 - c1;
+  __syncthreads();
+  int o0 = s_scan[0][wic] + i0 - c0, o1 = s_scan[1][wic] + i1 - c1;
   if (c0 + c1 != 0) {
 #pragma unroll 1
-    for (int t = t0; t < t1; t += U) {
-      unsigned mr[U], ms[U];
-#pragma unroll
-      for (int k = 0; k < U; ++k) {
-        const bool ok = t + k < t1 && slot_ok(t + k);
-        mr[k] = ok ? __ldcg(rm + t + k) : 0u;
-        ms[k] = ok ? __ldcg(sv + t + k) : 0u;
-      }
-#pragma unroll
-      for (int k = 0; k < U; ++k) {
-        if ((mr[k] | ms[k]) == 0u) continue;
-        const int e0 = slot_env0(t + k);
-        unsigned m = mr[k];
-        while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
-        m = ms[k];
-        while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.resample_ids[o1++] = e0 + bit; }
-      }
+    for (int t = t0; t < t1; ++t) {
+      if (!slot_ok(t)) continue;
+      unsigned m = rm[t], m2 = sv[t];
+      const int e0 = slot_env0(t);
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
+      while (m2) { const int bit = __ffs(m2) - 1; m2 &= m2 - 1; b.resample_ids[o1++] = e0 + bit; }
     }
   }
   if (tid == 0) {
-    b.counts[0] = n_reset;
-    b.counts[1] = n_resample;
-    ws->mask_ticket = 0u;
+    b.counts[0] = s_scan[0][32];
+    b.counts[1] = s_scan[1][32];
   }
-}
-
-// episode statistics behind extras (:182-190); run by the last warp 0 of the launch
-static __device__ __noinline__ void finalize_stats(const StepArgs& a, LgkWorkspace* ws, unsigned long long csc) {
-  const LgkConsts& c = a.c;
-  const LgkBuffers& b = a.b;
-  const int lane = threadIdx.x & 31, num_rows = a.num_rows, N = c.num_envs;
-  const int parity = (int)(csc & 1ull);
-  __threadfence();
-  const int n_reset = ((volatile int*)ws->reset_count)[parity];
-  const int level_sum = ((volatile int*)ws->level_sum)[parity];
-  volatile float* st = ws->stats[parity];
+  if (wic != 1) return;
+  // ---- episode statistics (one warp) ------------------------------------------------------------
+  const int num_rows = a.num_rows;
+  const int n_reset = ws->reset_count[parity];
+  const int level_sum = ws->level_sum[parity];
   if (lane < num_rows) {
-    const float s = st[lane];
+    const float s = ws->stats[parity][lane];
     b.episode_stats[lane] = s;
     b.episode_stats[num_rows + 4 + lane] += s;   // running sums since the host last cleared them
     if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
@@ -409,31 +402,7 @@ static __device__ __noinline__ void finalize_stats(const StepArgs& a, LgkWorkspa
     ws->level_sum[parity ^ 1] = 0;
     ws->reset_count[parity ^ 1] = 0;
     ws->step_counter = csc;
-    ws->done_ticket = 0u;
   }
-}
-
-// ---------------------------------------------------------------------------------------------
-// The launch's last CTA (blockIdx = gridDim - 1) owns no envs: it waits for the tile CTAs' tickets and
-// does the two serial jobs of the step off their critical path - the ordered id lists once every tile
-// has published its masks (while the last wave is still scanning heights), the episode statistics
-// once every tile has added its sums.  It is dispatched after every tile CTA and nothing waits on it,
-// so the polling cannot hold anything up.
-static __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-static __device__ __noinline__ void finisher(const StepArgs& a, LgkWorkspace* ws, unsigned long long csc) {
-  const unsigned n_tiles = gridDim.x - 1;
-  const int tid = threadIdx.x;
-  if (tid == 0) while (ld_acquire_gpu(&ws->mask_ticket) != n_tiles) __nanosleep(200);
-  __syncthreads();
-  compact_ids(a, ws, tid);
-  if (tid >= 32) return;
-  if (tid == 0) while (ld_acquire_gpu(&ws->done_ticket) != n_tiles) __nanosleep(200);
-  __syncwarp();
-  finalize_stats(a, ws, csc);
 }
 
 template <int DT, bool TAPS, bool MUL_RCP, int NP>
@@ -469,11 +438,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int nsub = (cta_ne + TILE - 1) / TILE;
   const bool has_levels = b.terrain_levels != nullptr;
 
-  if (blockIdx.x == gridDim.x - 1) {   // the finisher CTA: id lists and statistics, no envs
-    LgkWorkspace* wsf = reinterpret_cast<LgkWorkspace*>(b.workspace);
-    finisher(a, wsf, wsf->step_counter + 1ull);
-    return;
-  }
   // ---- first thing: W0 sets the mbarrier up and gets the bulk loads of the first sub-tile going; the
   // rest of the prologue runs under their latency.  Lane i copies input array i.
   const char* ld_src = nullptr;
@@ -490,12 +454,13 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     }
   }
   // stage 3, pass B: lane l of W0 owns episode-sum row l (term, scale, index among the external terms)
-  __shared__ int s_row_term[32], s_row_ext[32];
+  __shared__ int s_row_term[32], s_row_ext[32], s_idx[32];
   __shared__ float s_row_scale[32];
   if (wic == 0) {
     const bool in = lane < c.num_rewards;
     const int term = in ? c.rewards[lane].term : LGK_REW_COUNT;   // LGK_REW_COUNT: the termination row
     const unsigned xm = __ballot_sync(LGK_FULL_MASK, in && term == LGK_REW_EXTERNAL);
+    s_idx[lane] = 3 * (lane < IDX_PEN ? c.feet_idx[lane] : lane < IDX_TERM ? c.pen_idx[lane - IDX_PEN] : c.term_idx[lane - IDX_TERM]);
     s_row_term[lane] = term;
     s_row_ext[lane] = __popc(xm & ((1u << lane) - 1u));
     s_row_scale[lane] = in ? c.rewards[lane].scale : c.termination_scale;
@@ -558,7 +523,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     bool time_out = false, reset = false;
     if (active) {
       time_out = (ep_in + 1) > c.max_episode_length;
-      reset = term_contact(c, cf_row, a.thr_term) || time_out;
+      reset = term_contact(c, s_idx, cf_row, a.thr_term) || time_out;
     }
 
     // values W0 keeps in registers from stage 1 to stage 3
@@ -686,9 +651,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       for (int i = 0; i < 10; ++i) acc.v[i] = 0.f;
       if (active) {
         const float inv_dt = 1.0f / c.dt;
-        unsigned hip_mask = 0u;
-#pragma unroll 1
-        for (int h = 0; h < c.num_hip; ++h) hip_mask |= 1u << c.hip_idx[h];
+        const unsigned hip_mask = a.hip_mask;
         const float* act_p = sm + L.act + lane * D;
         const float* lact_p = sm + L.lact + lane * D;
         const float* tq_p = sm + L.tq + lane * D;
@@ -765,7 +728,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           float n[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float* f = cf_row + 3 * c.pen_idx[min(p0 + j, c.num_pen - 1)];
+            const float* f = cf_row + s_idx[IDX_PEN + min(p0 + j, c.num_pen - 1)];
             n[j] = sumsq3(f[0], f[1], f[2]);
           }
 #pragma unroll
@@ -776,7 +739,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         float* fa_out = b.feet_air_time + (size_t)env * F;
 #pragma unroll 2
         for (int k = 0; k < F; ++k) {
-          const float* f = cf_row + 3 * c.feet_idx[k];
+          const float* f = cf_row + s_idx[IDX_FEET + k];
           const float fx = f[0], fy = f[1], fz = f[2];
           const bool contact = fz > 1.0f;
           nofly += (fz > 0.1f) ? 1 : 0;
@@ -821,9 +784,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     } else if (wic > 0) {
       tile_store_fallback(a, sm, env0, ne, tid);
     }
-    // mask ticket (release: W0's masks are ordered before it by the barrier above); the finisher CTA
-    // compacts the id lists once all tickets are in
-    if (last_sub && tid == 96) ticket_release(&ws->mask_ticket);
     if (wic == 3 && lane < ne) {
       // episode-sum rows ([R, N], 128 B per row and tile): 4-byte cp.async (LDGSTS) per lane and row into
       // rows the joints no longer need; in flight during stage 2, awaited before the stage-3 barrier
@@ -1100,16 +1060,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (my_resets != 0u) atomicAdd(&ws->stats[parity][lane], stat);
     }
     LGK_STAMP(9);
-    // statistics ticket (release), drawn by W3 once every warp's contributions are on their way and
-    // before its own last stores: the finaliser only reads the statistics
-    if (last_sub) {
-      if (wic != 3) {
-        asm volatile("bar.arrive 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
-      } else {
-        asm volatile("bar.sync 1, %0;" ::"n"(LGK_CTA_THREADS) : "memory");
-        if (lane == 0) ticket_release(&ws->done_ticket);
-      }
-    }
     __syncwarp();
     LGK_STAMP(7);
     const int e_mine = e_lo + el;
@@ -1160,6 +1110,7 @@ static int launch_step(const StepArgs& args, int grid, size_t smem, cudaStream_t
     configured = smem;
   }
   kern<<<grid, LGK_CTA_THREADS, smem, stream>>>(args);
+  lgk_step_epilogue_kernel<<<1, EPI_THREADS, 0, stream>>>(args, grid);
   return (int)cudaGetLastError();
 }
 
@@ -1175,6 +1126,8 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
     args.pk[2 * r + 1] = (unsigned)(c->seed >> 32) + (unsigned)r * 0xBB67AE85u;
   }
+  args.hip_mask = 0u;
+  for (int h = 0; h < c->num_hip; ++h) args.hip_mask |= 1u << c->hip_idx[h];
   args.thr_term = sqrt_le_threshold(1.0f);
   args.thr_pen = sqrt_le_threshold(0.1f);
   args.thr_ffp = sqrt_le_threshold(c->max_contact_force);
@@ -1265,12 +1218,11 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
   const int H = c->num_height_points;
   const int np = (H + 31) / 32;   // scan passes of 32 points
-  // grid + 1: the last CTA is the finisher (id lists, episode statistics)
 #define LGK_DISPATCH(DT, NP)                                                            \
-  (taps ? (mul ? launch_step<DT, true, true, NP>(args, grid + 1, smem, stream)              \
-               : launch_step<DT, true, false, NP>(args, grid + 1, smem, stream))            \
-        : (mul ? launch_step<DT, false, true, NP>(args, grid + 1, smem, stream)             \
-               : launch_step<DT, false, false, NP>(args, grid + 1, smem, stream)))
+  (taps ? (mul ? launch_step<DT, true, true, NP>(args, grid, smem, stream)              \
+               : launch_step<DT, true, false, NP>(args, grid, smem, stream))            \
+        : (mul ? launch_step<DT, false, true, NP>(args, grid, smem, stream)             \
+               : launch_step<DT, false, false, NP>(args, grid, smem, stream)))
   if (D == 12 && np == 6) return LGK_DISPATCH(12, 6);   // 187-point scan
   if (D == 12 && np == 0) return LGK_DISPATCH(12, 0);   // blind
   if (D == 12 && np == 4) return LGK_DISPATCH(12, 4);   // Cassie's 121 points

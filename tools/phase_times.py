@@ -72,3 +72,4 @@ same = {}
 for b_ in range(min(ncta, 888)):
     same.setdefault(int(smid[b_]), []).append(b_)
 print("  first-wave CTAs on SM of CTA 0:", same[int(smid[0])], " on SM of CTA 1:", same[int(smid[1])])
+
