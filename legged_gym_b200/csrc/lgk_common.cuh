@@ -20,6 +20,12 @@ struct LgkWorkspace {
 };
 #define LGK_WS_HEADER_BYTES 512
 #ifdef __CUDACC__
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialisation attribute
+// may be scheduled once every CTA of the kernel before it has passed pdl_launch_dependents(); it must call
+// pdl_wait() before it touches global memory -- that returns when the earlier grid has completed and its
+// writes are visible.  Both are no-ops in a launch without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 // ticket counters: release-ordered increment (MEMBAR.ALL.GPU + RED; no L1 invalidation, unlike
 // __threadfence() + atomicAdd), so everything the CTA wrote before it is visible to whoever sees the count
 __device__ __forceinline__ void ticket_relaxed(unsigned int* p) {
@@ -27,6 +33,26 @@ __device__ __forceinline__ void ticket_relaxed(unsigned int* p) {
 }
 __device__ __forceinline__ void ticket_release(unsigned int* p) {
   asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+}
+#endif
+#ifdef __CUDACC__
+#include <cstdlib>
+// launch with the programmatic-serialisation attribute (LGK_NO_PDL=1 in the environment: plain launch)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t lgk_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                         Args... args) {
+  static const bool off = [] { const char* e = getenv("LGK_NO_PDL"); return e && e[0] == '1'; }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = off ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 #endif
 static_assert(sizeof(LgkWorkspace) <= LGK_WS_HEADER_BYTES, "workspace header too large");

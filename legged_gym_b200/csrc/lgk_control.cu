@@ -136,6 +136,7 @@ extern "C" int lgk_compute_poses_impl(const LgkConsts* c, const float* actions, 
 __global__ void lgk_clip_poses_kernel(const __grid_constant__ CtrlArgs a, const float* __restrict__ in,
                                       float* __restrict__ act_out, float* __restrict__ poses_out, long long n4,
                                       float lim) {
+  pdl_launch_dependents();   // the step kernel behind this one may take its SM slots now (it waits on entry)
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   const int d = (int)((unsigned)(i % (unsigned)(a.D >> 2)) << 2);   // D % 4 == 0: a quad never straddles two envs

@@ -315,6 +315,7 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
   const int N = c.num_envs;
   const int tid = threadIdx.x, lane = tid & 31, wic = tid >> 5;
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  pdl_wait();   // scheduled while the tile kernel drains; from here on every tile's writes are visible
   const unsigned long long csc = ws->step_counter + 1ull;
   const int parity = (int)(csc & 1ull);
   // ---- id lists --------------------------------------------------------------------------------
@@ -408,6 +409,8 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
 template <int DT, bool TAPS, bool MUL_RCP, int NP>
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_MIN_CTAS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
+  pdl_launch_dependents();   // the epilogue may be scheduled as soon as the last tile CTA has started
+  pdl_wait();                // launched behind clip_actions_poses: its writes (actions) are visible from here
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
   const TileLayout& L = a.L;
@@ -1109,8 +1112,8 @@ static int launch_step(const StepArgs& args, int grid, size_t smem, cudaStream_t
     LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  kern<<<grid, LGK_CTA_THREADS, smem, stream>>>(args);
-  lgk_step_epilogue_kernel<<<1, EPI_THREADS, 0, stream>>>(args, grid);
+  LGK_CUDA_RETURN_IF(lgk_launch_pdl(kern, dim3(grid), dim3(LGK_CTA_THREADS), smem, stream, args));
+  LGK_CUDA_RETURN_IF(lgk_launch_pdl(lgk_step_epilogue_kernel, dim3(1), dim3(EPI_THREADS), 0, stream, args, grid));
   return (int)cudaGetLastError();
 }
 
