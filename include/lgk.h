@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LGK_ABI_VERSION 4
+#define LGK_ABI_VERSION 5
 
 #define LGK_MAX_DOF     16   /* num_dof = num_actions (12 for every shipped robot)        */
 #define LGK_MAX_FEET     8
@@ -266,6 +266,36 @@ int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* d
 int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state,
                          float* pos_err_hist, float* vel_hist, float* model_ins,
                          const float* weights, const float* norm, float* dvel_out, void* stream);
+
+/* ANYmal series-elastic actuator net (envs/anymal_c/anymal.py:46-81, resources/actuator_nets/
+ * anydrive_v3_lstm.pt): per joint a 2-layer torch.nn.LSTM(input 2, hidden 8, batch_first) followed by
+ * Linear(8 -> 1); forward(x, (h, c)) = out_scale * linear(lstm(x * in_scale, (h, c))).  Parameter layout
+ * is torch's: gate rows ordered i, f, g, o.  HOST memory, read during the call only. */
+#define LGK_LSTM_HID 8
+typedef struct LgkLstmWeights {
+  float w_ih0[4 * LGK_LSTM_HID][2],            w_hh0[4 * LGK_LSTM_HID][LGK_LSTM_HID];
+  float b_ih0[4 * LGK_LSTM_HID],               b_hh0[4 * LGK_LSTM_HID];
+  float w_ih1[4 * LGK_LSTM_HID][LGK_LSTM_HID], w_hh1[4 * LGK_LSTM_HID][LGK_LSTM_HID];
+  float b_ih1[4 * LGK_LSTM_HID],               b_hh1[4 * LGK_LSTM_HID];
+  float lin_w[LGK_LSTM_HID], lin_b;
+  float in_scale[2], out_scale;
+} LgkLstmWeights;
+
+/* Anymal._compute_torques with use_actuator_network (anymal.py:71-81), one call per simulator substep:
+ *   sea_input[:,0,0] = actions*action_scale + default_dof_pos - dof_pos;  sea_input[:,0,1] = dof_vel;
+ *   torques, (hidden, cell) = net(sea_input, (hidden, cell))
+ * hidden / cell: sea_hidden_state / sea_cell_state [2, N*D, 8], updated in place; sea_input [N*D,1,2] may be
+ * NULL (not materialised); torques_out [N*D] (the reference returns them unclipped).  Uses num_envs,
+ * num_dof, action_scale and default_dof_pos of LgkConsts. */
+int lgk_lstm_actuator_advance(const LgkConsts* c, const LgkLstmWeights* weights_host, const float* actions,
+                              const float* dof_state, float* sea_input, float* hidden, float* cell,
+                              float* torques_out, void* stream);
+
+/* Anymal.reset_idx's extra lines (anymal.py:56-60): zero the hidden and cell state of the listed envs.
+ * env_ids: int32 ids on the device (NULL = 0..n-1).  The count is read on the device from count_dev when
+ * that is non-NULL (the step kernel's counts[0]: no host sync), else count_host is used. */
+int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_ids, const int32_t* count_dev,
+                          int32_t count_host, float* hidden, float* cell, void* stream);
 
 /* Everything post_physics_step() does for every env (legged_robot.py:109-141) in one launch. */
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream);

@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-LGK_ABI_VERSION = 4
+LGK_ABI_VERSION = 5
 LGK_MAX_DOF = 16
 LGK_MAX_FEET = 8
 LGK_MAX_PEN = 16
@@ -106,6 +106,17 @@ class LgkBuffers(C.Structure):
     _fields_ = [(name, _P) for name in BUFFER_FIELDS]
 
 
+LGK_LSTM_HID = 8
+
+
+class LgkLstmWeights(C.Structure):
+    """torch.nn.LSTM(2, 8, num_layers=2) + Linear(8, 1) + in/out scales (include/lgk.h)."""
+    _G = 4 * LGK_LSTM_HID
+    _fields_ = [("w_ih0", _F * (2 * _G)), ("w_hh0", _F * (LGK_LSTM_HID * _G)), ("b_ih0", _F * _G), ("b_hh0", _F * _G),
+                ("w_ih1", _F * (LGK_LSTM_HID * _G)), ("w_hh1", _F * (LGK_LSTM_HID * _G)), ("b_ih1", _F * _G),
+                ("b_hh1", _F * _G), ("lin_w", _F * LGK_LSTM_HID), ("lin_b", _F), ("in_scale", _F * 2), ("out_scale", _F)]
+
+
 class LgkLibraryMissing(ImportError):
     pass
 
@@ -148,6 +159,8 @@ def load():
         "lgk_clip_actions_poses": (C.c_int, [cp, fp, fp, fp, fp]),
         "lgk_compute_torques": (C.c_int, [cp, fp, fp, fp, fp, fp]),
         "lgk_actuator_advance": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp, fp]),
+        "lgk_lstm_actuator_advance": (C.c_int, [cp, C.POINTER(LgkLstmWeights), fp, fp, fp, fp, fp, fp, fp]),
+        "lgk_lstm_reset_hidden": (C.c_int, [C.c_int32, C.c_int32, fp, fp, C.c_int32, fp, fp, fp]),
         "lgk_post_physics_step": (C.c_int, [cp, bp, fp]),
         "lgk_reset_idx": (C.c_int, [cp, bp, fp, C.c_int32, fp]),
         "lgk_reset_all": (C.c_int, [cp, bp, fp]),
@@ -171,7 +184,7 @@ def load():
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
     "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
-    "lgk_post_physics_step", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
+    "lgk_lstm_actuator_advance", "lgk_lstm_reset_hidden", "lgk_post_physics_step", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]
 
 

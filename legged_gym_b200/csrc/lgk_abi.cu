@@ -14,6 +14,9 @@ int lgk_compute_torques_impl(const LgkConsts*, const float*, const float*, const
 int lgk_debug_yaw_quat_impl(const float*, int, int, float*, cudaStream_t);
 int lgk_actuator_advance_impl(int, const float*, const float*, float*, float*, float*, const float*, const float*,
                               float*, cudaStream_t);
+int lgk_lstm_actuator_advance_impl(const LgkConsts*, const LgkLstmWeights*, const float*, const float*, float*, float*,
+                                   float*, float*, cudaStream_t);
+int lgk_lstm_reset_hidden_impl(int, int, const int*, const int*, int, float*, float*, cudaStream_t);
 }
 
 static std::atomic<long long> g_launches{0};
@@ -150,6 +153,32 @@ int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* do
   g_launches += 2;
   return lgk_actuator_advance_impl(num_envs, actions, dof_state, pos_err_hist, vel_hist, model_ins, weights, norm,
                                    dvel_out, (cudaStream_t)stream);
+}
+
+int lgk_lstm_actuator_advance(const LgkConsts* c, const LgkLstmWeights* weights_host, const float* actions,
+                              const float* dof_state, float* sea_input, float* hidden, float* cell,
+                              float* torques_out, void* stream) {
+  int rc = check_consts(c);
+  if (rc) return rc;
+  if (!weights_host || !actions || !dof_state || !hidden || !cell || !torques_out) return LGK_ERR_NULL;
+  if (!aligned16(hidden) || !aligned16(cell) || (reinterpret_cast<uintptr_t>(dof_state) & 7u) != 0 ||
+      (sea_input && (reinterpret_cast<uintptr_t>(sea_input) & 7u) != 0))
+    return LGK_ERR_ALIGN;
+  g_launches += 1;
+  return lgk_lstm_actuator_advance_impl(c, weights_host, actions, dof_state, sea_input, hidden, cell, torques_out,
+                                        (cudaStream_t)stream);
+}
+
+int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_ids, const int32_t* count_dev,
+                          int32_t count_host, float* hidden, float* cell, void* stream) {
+  if (!hidden || !cell) return LGK_ERR_NULL;
+  if (num_envs <= 0 || num_dof <= 0 || num_dof > LGK_MAX_DOF) return LGK_ERR_DIM;
+  if (!count_dev && (count_host < 0 || count_host > num_envs)) return LGK_ERR_DIM;
+  if (!aligned16(hidden) || !aligned16(cell)) return LGK_ERR_ALIGN;
+  if (!count_dev && count_host == 0) return LGK_OK;
+  g_launches += 1;
+  return lgk_lstm_reset_hidden_impl(num_envs, num_dof, env_ids, count_dev, count_host, hidden, cell,
+                                    (cudaStream_t)stream);
 }
 
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream) {

@@ -225,17 +225,6 @@ struct MlpSmem {
   float act[2][ACT_HID][MLP_AS];   // [k][row]
 };
 
-// tanh to ~2 ulp with two MUFU ops instead of the ~25-instruction library routine: 1 - 2 / (exp(2x) + 1) away
-// from zero, the odd Taylor polynomial where that form cancels (|x| < 0.15: truncation error < 2e-9 relative)
-__device__ __forceinline__ float tanh_fast(float x) {
-  const float ax = fabsf(x);
-  const float e = exp2f(ax * 2.885390081777927f);          // exp(2|x|); inf for large |x| -> 1
-  const float big = 1.0f - __fdividef(2.0f, e + 1.0f);
-  const float x2 = x * x;
-  const float small = ax * fmaf(x2, fmaf(x2, fmaf(x2, -0.05396825396825397f, 0.13333333333333333f), -0.3333333333333333f), 1.0f);
-  return copysignf(ax < 0.15f ? small : big, x);
-}
-
 template <int K>
 __device__ __forceinline__ void mlp_layer(const float (*__restrict__ wt)[MLP_WS], const float* __restrict__ bias,
                                           const float (*__restrict__ in)[MLP_AS], float (*__restrict__ out)[MLP_AS],

@@ -196,7 +196,13 @@ class LeggedRobot(BaseTask):
                 self.gym.set_actor_root_state_tensor(self.sim, self.root_states)
             self.gym.set_dof_state_tensor_indexed(self.sim, self.dof_state, self.reset_ids, self.step_counts)
             self.gym.set_actor_root_state_tensor_indexed(self.sim, self.root_states, self.reset_ids, self.step_counts)
+        self._after_fused_resets()
         self._publish_extras()
+
+    def _after_fused_resets(self):
+        """Hook for subclasses whose reset_idx() override clears extra per-env state (Anymal's LSTM state,
+        anymal.py:56-60).  The per-step resets run inside the fused kernel, which leaves the ascending id
+        list in self.reset_ids and its length in self.step_counts[0] (both on the device)."""
 
     def _publish_extras(self):
         """extras["episode"] / extras["time_outs"] as device views (:182-193); the kernel rewrites the
@@ -785,6 +791,31 @@ class LeggedRobot(BaseTask):
         P = _lgk.ptr
         self._bufs.root_states, self._bufs.dof_state = P(self.root_states), P(self.dof_state)
         self._bufs.contact_forces, self._bufs.torques = P(self.contact_forces), P(self.torques)
+
+    def bind_output_tensors(self, obs_buf=None, rew_buf=None, reset_buf=None):
+        """Let the fused kernel write observations / rewards / resets straight into the caller's storage
+        (e.g. slot t of a [T,N,O] rollout buffer) instead of into env-owned buffers that the caller then
+        copies (the reference's runner does `storage.observations[t].copy_(obs)`,
+        a second pass over the largest tensor of the step).  Each tensor must be contiguous with the
+        same element count and width as the buffer it replaces; `reset_buf` may be bool or uint8.
+        step() returns the bound tensors."""
+        self._kernels()
+        N = self.num_envs
+        if obs_buf is not None:
+            if obs_buf.dtype != torch.float or obs_buf.numel() != N * self.num_obs or not obs_buf.is_contiguous():
+                raise ValueError(f"obs_buf must be contiguous float32 with {N}x{self.num_obs} elements")
+            self.obs_buf = obs_buf.view(N, self.num_obs)
+            self._bufs.obs_buf = _lgk.ptr(self.obs_buf)
+        if rew_buf is not None:
+            if rew_buf.dtype != torch.float or rew_buf.numel() != N or not rew_buf.is_contiguous():
+                raise ValueError(f"rew_buf must be contiguous float32 with {N} elements")
+            self.rew_buf = rew_buf.view(N)
+            self._bufs.rew_buf = _lgk.ptr(self.rew_buf)
+        if reset_buf is not None:
+            if reset_buf.dtype not in (torch.bool, torch.uint8) or reset_buf.numel() != N or not reset_buf.is_contiguous():
+                raise ValueError(f"reset_buf must be contiguous bool / uint8 with {N} elements")
+            self.reset_buf = reset_buf.view(N)
+            self._bufs.reset_buf = _lgk.ptr(self.reset_buf)
 
     def _ensure_dev_counter(self, want: int):
         """Device copy of common_step_counter: the step kernel increments it itself, so it is

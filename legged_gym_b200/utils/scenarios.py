@@ -49,12 +49,17 @@ def cassie_flat(cfg):
     """config 4: Cassie as shipped (plane, 121 zero heights, 169 obs, 10 terms + termination)."""
 
 
+def anymal_c_flat(cfg):
+    """ANYmal C as shipped (plane, blind, 48 obs) with the LSTM actuator net."""
+
+
 SCENARIOS = {
     "go1_flat": ("go1", go1_flat),
     "go1_rough_full": ("go1", go1_rough_full),
     "go1_rough_default": ("go1", go1_rough_default),
     "go1_rough_actuator": ("go1", go1_rough_actuator),
     "cassie_flat": ("cassie", cassie_flat),
+    "anymal_c_flat": ("anymal_c_flat", anymal_c_flat),
 }
 
 

@@ -327,6 +327,57 @@ class ActuatorOracle:
         return dVel * self.vel_std                                     # go1.py:102-105
 
 
+class SeaLstmOracle:
+    """ANYmal series-elastic actuator net: Anymal._init_buffers / _compute_torques / reset_idx
+    (envs/anymal_c/anymal.py:56-81) around the TorchScript module LSTMsea of
+    resources/actuator_nets/anydrive_v3_lstm.pt, whose forward is
+        x0 = x * in_scale; x1, hcn = lstm(x0, hc0); return out_scale * squeeze(linear(x1)), hcn
+    with lstm = torch.nn.LSTM(2, 8, num_layers=2, batch_first=True).  The LSTM cell is written out
+    (gate rows i, f, g, o; torch.nn.LSTM documentation) so that no step hides in aten::lstm."""
+    HID, LAYERS = 8, 2
+
+    def __init__(self, num_envs, num_actions, state_dict, device="cpu"):
+        self.N, self.D = num_envs, num_actions
+        self.sd = {k: v.detach().float().to(device) for k, v in state_dict.items()}
+        M = num_envs * num_actions
+        self.sea_input = torch.zeros(M, 1, 2, device=device)                       # anymal.py:65
+        self.sea_hidden_state = torch.zeros(self.LAYERS, M, self.HID, device=device)
+        self.sea_cell_state = torch.zeros(self.LAYERS, M, self.HID, device=device)
+        self.sea_hidden_state_per_env = self.sea_hidden_state.view(self.LAYERS, num_envs, num_actions, self.HID)
+        self.sea_cell_state_per_env = self.sea_cell_state.view(self.LAYERS, num_envs, num_actions, self.HID)
+
+    def network(self, x, hc):
+        sd = self.sd
+        h0, c0 = hc
+        inp = (x * sd["in_scale"])[:, 0, :]                                         # one time step
+        hn, cn = [], []
+        for l in range(self.LAYERS):
+            gates = (torch.nn.functional.linear(inp, sd[f"lstm.weight_ih_l{l}"], sd[f"lstm.bias_ih_l{l}"])
+                     + torch.nn.functional.linear(h0[l], sd[f"lstm.weight_hh_l{l}"], sd[f"lstm.bias_hh_l{l}"]))
+            i, f, g, o = gates.chunk(4, dim=1)
+            c = torch.sigmoid(f) * c0[l] + torch.sigmoid(i) * torch.tanh(g)
+            h = torch.sigmoid(o) * torch.tanh(c)
+            hn.append(h); cn.append(c)
+            inp = h
+        x1 = inp.unsqueeze(1)
+        out = sd["out_scale"] * torch.squeeze(torch.nn.functional.linear(x1, sd["linear.weight"], sd["linear.bias"]))
+        return out, (torch.stack(hn), torch.stack(cn))
+
+    def compute_torques(self, actions, action_scale, default_dof_pos, dof_pos, dof_vel):
+        """anymal.py:71-78 (use_actuator_network branch); returns the flat [N*D] network output."""
+        self.sea_input[:, 0, 0] = (actions * action_scale + default_dof_pos - dof_pos).flatten()
+        self.sea_input[:, 0, 1] = dof_vel.flatten()
+        torques, (h, c) = self.network(self.sea_input, (self.sea_hidden_state, self.sea_cell_state))
+        self.sea_hidden_state[:] = h
+        self.sea_cell_state[:] = c
+        return torques
+
+    def reset(self, env_ids):
+        """anymal.py:58-60"""
+        self.sea_hidden_state_per_env[:, env_ids] = 0.
+        self.sea_cell_state_per_env[:, env_ids] = 0.
+
+
 # ----------------------------------------------------------------------------------------------
 # post_physics_step and its parts (a5-a18)
 def get_heights(p: OracleParams, s: OracleState):

@@ -18,6 +18,12 @@ Fixture layout (numpy arrays; S = steps, N = envs):
   out_extras        [S, K+1] extras["episode"] values in episode_sums key order (+ terrain_level), NaN
                     where the reference did not rewrite them
   out_dvel          [S, decimation, N, 12] Go1 actuator-net output per substep (actuator scenario only)
+  in_sea_dof_state / out_sea_torques / out_sea_hidden / out_sea_cell / out_sea_input
+                    ANYmal scenario only: after step s the reference's Anymal._compute_torques(actions) is
+                    called `decimation` times on the dof states in_sea_dof_state[s, k]; torques per call
+                    [S, dec, N*12], LSTM state / sea_input after the last call of the step [S, 2, N*12, 8] /
+                    [S, N*12, 1, 2] (the resets of step s have zeroed the state of the reset envs through
+                    the reference's reset_idx override before the calls)
 """
 from __future__ import annotations
 
@@ -89,6 +95,28 @@ def generate(name, num_envs, steps, seed=0):
             dvel_log.append(np_(out))
             return out
         env.actuator_advance = logged
+    anymal = task.startswith("anymal") and bool(env.cfg.control.use_actuator_network)
+    sea = {k: [] for k in ("in_sea_dof_state", "out_sea_torques", "out_sea_hidden", "out_sea_cell", "out_sea_input")}
+    if anymal:
+        # the reference loaded its checkpoint (anymal.py:51-54); swap in seeded random weights of the same
+        # architecture (LSTMsea: x*in_scale -> LSTM(2,8,2 layers, batch_first) -> Linear(8,1) -> *out_scale)
+        from legged_gym_b200.envs.anymal_c.anymal import random_lstm_state_dict
+
+        class LSTMsea(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.lstm = torch.nn.LSTM(2, 8, num_layers=2, batch_first=True)
+                self.linear = torch.nn.Linear(8, 1)
+                self.register_buffer("in_scale", torch.ones(1, 1, 2))
+                self.register_buffer("out_scale", torch.ones(1))
+
+            def forward(self, x, hc0):
+                x1, hcn = self.lstm(torch.mul(x, self.in_scale), hc0)
+                return torch.mul(self.out_scale, torch.squeeze(self.linear(x1))), hcn
+        assert sorted(env.actuator_network.state_dict().keys()) == sorted(random_lstm_state_dict(0).keys())
+        net = LSTMsea()
+        net.load_state_dict(random_lstm_state_dict(0))
+        env.actuator_network = net
     randomise(env, seed)
     frames = synthetic.make_frames(env, steps, seed=1234 + seed)
     synthetic.load_frame(env, frames[0])
@@ -131,6 +159,19 @@ def generate(name, num_envs, steps, seed=0):
         pad = lambda ids: np.concatenate([np_(ids).astype(np.int64), -np.ones(num_envs - len(ids), np.int64)])
         outs["reset_ids"].append(pad(env.reset_buf.nonzero(as_tuple=False).flatten()))
         outs["resample_ids"].append(pad(resample))
+        if anymal:
+            g_sea = torch.Generator().manual_seed(7000 + 10 * seed + it)
+            for k in range(env.cfg.control.decimation):
+                ds = fr["dof_state"].clone().view(num_envs, env.num_dof, 2)
+                ds[..., 0] += 0.05 * torch.randn(num_envs, env.num_dof, generator=g_sea)
+                ds[..., 1] += 0.5 * torch.randn(num_envs, env.num_dof, generator=g_sea)
+                env.dof_state.copy_(ds.view_as(env.dof_state))
+                tq = env._compute_torques(env.actions)
+                sea["in_sea_dof_state"].append(np_(ds))
+                sea["out_sea_torques"].append(np_(tq))
+            sea["out_sea_hidden"].append(np_(env.sea_hidden_state))
+            sea["out_sea_cell"].append(np_(env.sea_cell_state))
+            sea["out_sea_input"].append(np_(env.sea_input))
         ep = env.extras.get("episode", {})
         row = [float(ep["rew_" + k]) if ("rew_" + k) in ep else float("nan") for k in keys]
         row.append(float(ep["terrain_level"]) if "terrain_level" in ep else float("nan"))
@@ -145,6 +186,11 @@ def generate(name, num_envs, steps, seed=0):
         dec = env.cfg.control.decimation
         d["out_dvel"] = np.stack(dvel_log).reshape(steps, dec, num_envs, 12)
         d["out_model_ins"] = np_(env.model_ins)
+    if anymal:
+        dec = env.cfg.control.decimation
+        for k, v in sea.items():
+            a = np.stack(v)
+            d[k] = a.reshape((steps, dec) + a.shape[1:]) if a.shape[0] == steps * dec else a
     n_reset = int((d["out_reset_ids"] >= 0).sum())
     path = os.path.join(HERE, name + ".npz")
     np.savez_compressed(path, **d)
@@ -155,9 +201,11 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--envs", type=int, default=64)
     ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--only", default=None, help="comma-separated scenario names (default: all)")
     a = ap.parse_args()
     for name in scenarios.SCENARIOS:
-        generate(name, a.envs, a.steps)
+        if a.only is None or name in a.only.split(","):
+            generate(name, a.envs, a.steps)
 
 
 if __name__ == "__main__":

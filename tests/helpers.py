@@ -21,7 +21,7 @@ def make_env(scenario: str, num_envs: int, device: str = "cpu", seed: int = 0, e
     cfg = copy.deepcopy(task_registry.env_cfgs[task])
     cfg.env.num_envs = num_envs
     cfg.seed = seed
-    if task in ("go1", "aliengo"):
+    if task in ("go1", "aliengo", "anymal_c_flat", "anymal_c_rough", "anymal_b"):
         cfg.control.actuator_net_random_seed = 0
     mutate(cfg)
     if extra is not None:
@@ -214,6 +214,28 @@ def compare_to_golden(get, g, it, keys, tag, float_names=GOLDEN_OUT):
                 assert_close(f"{tag}extras[{name}]", torch.as_tensor(ex[name]).float().reshape(1), T(row[i:i + 1]))
 
 
+def sea_setup(g, device):
+    """ANYmal fixture: the LSTM weights the fixture was made with and the torque tolerance.
+
+    torque = out_scale * (b + sum_k w_k h_k) with |h_k| < 1 cancels: its rounding error scales with the
+    summands, not with the result, so the absolute floor is 1e-5 of out_scale * (|b| + sum |w_k|) (the
+    north-star relative tolerance applied to the magnitude of the sum's operands)."""
+    from legged_gym_b200.envs.anymal_c.anymal import random_lstm_state_dict
+    sd = random_lstm_state_dict(0)
+    atol = RTOL * float(sd["out_scale"].abs().max() * (sd["linear.bias"].abs().sum() + sd["linear.weight"].abs().sum()))
+    return sd, atol
+
+
+def assert_close_abs(name, got, want, atol):
+    a, b = got.detach().cpu().double().reshape(-1), want.detach().cpu().double().reshape(-1)
+    assert a.shape == b.shape, f"{name}: shape {tuple(a.shape)} != {tuple(b.shape)}"
+    bad = (a - b).abs() > RTOL * torch.maximum(a.abs(), b.abs()) + atol
+    if bad.any():
+        i = int(bad.nonzero()[0])
+        raise AssertionError(f"{name}: {int(bad.sum())} of {bad.numel()} outside 1e-5 rel + {atol:.2e}; first at {i}: "
+                             f"got {a[i].item()!r} want {b[i].item()!r}")
+
+
 def replay_golden_oracle(name, device="cpu"):
     """Oracle restatement vs the reference's recorded outputs."""
     from oracle import legged_oracle as lo
@@ -227,6 +249,10 @@ def replay_golden_oracle(name, device="cpu"):
     if "out_dvel" in g:
         from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
         act = lo.ActuatorOracle(env.num_envs, random_mlp_state_dict(0), device=device)
+    sea = None
+    if "out_sea_torques" in g:
+        sd, sea_atol = sea_setup(g, device)
+        sea = lo.SeaLstmOracle(env.num_envs, env.num_actions, sd, device=device)
     n = 0
     for it in range(int(g["meta_steps"])):
         fr, taps = golden_frame(g, it, device)
@@ -251,6 +277,17 @@ def replay_golden_oracle(name, device="cpu"):
             return getattr(s, nm)
         compare_to_golden(get, g, it, keys, f"[oracle {name} step {it}] ")
         n += len(s.reset_env_ids)
+        if sea is not None:
+            sea.reset(s.reset_env_ids)                       # Anymal.reset_idx, anymal.py:56-60
+            a = torch.clip(fr["actions"], -p.clip_actions, p.clip_actions)
+            for k in range(p.decimation):
+                ds = torch.from_numpy(g["in_sea_dof_state"][it, k]).to(device)
+                tq = sea.compute_torques(a, p.action_scale, p.default_dof_pos, ds[..., 0], ds[..., 1])
+                assert_close_abs(f"[oracle {name} step {it}.{k}] sea torques", tq,
+                                 torch.from_numpy(g["out_sea_torques"][it, k]), sea_atol)
+            assert_close(f"[oracle {name} step {it}] sea_hidden_state", sea.sea_hidden_state, torch.from_numpy(g["out_sea_hidden"][it]))
+            assert_close(f"[oracle {name} step {it}] sea_cell_state", sea.sea_cell_state, torch.from_numpy(g["out_sea_cell"][it]))
+            assert_close(f"[oracle {name} step {it}] sea_input", sea.sea_input, torch.from_numpy(g["out_sea_input"][it]))
     return n
 
 
@@ -281,4 +318,18 @@ def replay_golden_env(name, index_math=None):
             return getattr(env, nm)
         compare_to_golden(get, g, it, keys, f"[cuda {name} step {it}] ")
         n += nr
+        if "out_sea_torques" in g:
+            # torque mode on top of the step: Anymal._compute_torques once per simulator substep; the resets of
+            # this step have already cleared the LSTM state of the reset envs (device-side id list)
+            _, sea_atol = sea_setup(g, "cpu")
+            for k in range(env.cfg.control.decimation):
+                ds = torch.from_numpy(g["in_sea_dof_state"][it, k]).to("cuda:0")
+                env.dof_state.copy_(ds.view_as(env.dof_state))
+                tq = env._compute_torques(env.actions)
+                torch.cuda.synchronize()
+                assert_close_abs(f"[cuda {name} step {it}.{k}] sea torques", tq,
+                                 torch.from_numpy(g["out_sea_torques"][it, k]), sea_atol)
+            assert_close(f"[cuda {name} step {it}] sea_hidden_state", env.sea_hidden_state, torch.from_numpy(g["out_sea_hidden"][it]))
+            assert_close(f"[cuda {name} step {it}] sea_cell_state", env.sea_cell_state, torch.from_numpy(g["out_sea_cell"][it]))
+            assert_close(f"[cuda {name} step {it}] sea_input", env.sea_input, torch.from_numpy(g["out_sea_input"][it]))
     return n

@@ -74,6 +74,12 @@ def test_argument_errors_are_status_codes_not_crashes():
     b = _lgk.LgkBuffers()
     assert lib.lgk_post_physics_step(C.byref(_consts(num_bodies=17, num_commands=4, num_obs=48)), C.byref(b), null) == -2
     assert lib.lgk_actuator_advance(0, one, one, one, one, one, one, one, one, null) == -2
+    w = _lgk.LgkLstmWeights()
+    assert lib.lgk_lstm_actuator_advance(C.byref(_consts()), None, one, one, null, one, one, one, null) == -1
+    assert lib.lgk_lstm_actuator_advance(C.byref(_consts()), C.byref(w), one, one, null, C.c_void_p(20), one, one, null) == -5
+    assert lib.lgk_lstm_reset_hidden(8, 12, null, null, 9, one, one, null) == -2      # more ids than envs
+    assert lib.lgk_lstm_reset_hidden(8, 12, null, null, 0, one, one, null) == 0       # empty list: no launch (anymal.py:56)
+    assert C.sizeof(w) == 4 * (64 + 256 + 64 + 256 + 256 + 64 + 8 + 1 + 2 + 1)
     assert lib.lgk_build_height_min3(null, 4, 4, null, 8, null) == -1
     assert lib.lgk_build_height_min3(one, 1, 4, one, 8, null) == -2
     assert lib.lgk_workspace_bytes(65536, 21) >= 512 + 2 * 4 * (65536 // 32)

@@ -178,6 +178,71 @@ def test_actuator_net_matches_oracle_over_substeps():
             torch.allclose(env.pos_err_buffs.cpu().double(), torch.from_numpy(act.pos_err_buffs), rtol=1e-6, atol=1e-7)
 
 
+def test_anymal_lstm_actuator_matches_oracle_free_running():
+    """Anymal._compute_torques (LSTM actuator net) over 8 free-running substeps, with a reset_idx() of a few
+    envs and a fused-step reset in between (both must clear exactly the reset envs' hidden / cell state)."""
+    from oracle import legged_oracle as lo
+    n = 1501                                  # 18012 actuators: not a multiple of the CTA size
+    env = helpers.make_env("anymal_c_flat", n, device=DEV)
+    sd, atol = helpers.sea_setup(None, "cpu")
+    sea = lo.SeaLstmOracle(n, env.num_actions, sd)
+    p = lo.OracleParams.from_env(env, device="cpu")
+    frames = synthetic.make_frames(env, 8, seed=21)
+    for it, fr in enumerate(frames):
+        synthetic.load_frame(env, fr)
+        a = fr["actions"].clip(-p.clip_actions, p.clip_actions)
+        got = env._compute_torques(a)
+        want = sea.compute_torques(a.cpu(), p.action_scale, p.default_dof_pos, env.dof_pos.cpu(), env.dof_vel.cpu())
+        assert got.shape == want.shape == (n * env.num_actions,)
+        helpers.assert_close_abs(f"sea torques[{it}]", got, want, atol)
+        helpers.assert_close(f"sea_input[{it}]", env.sea_input, sea.sea_input)
+        helpers.assert_close(f"sea_hidden_state[{it}]", env.sea_hidden_state, sea.sea_hidden_state)
+        helpers.assert_close(f"sea_cell_state[{it}]", env.sea_cell_state, sea.sea_cell_state)
+        if it == 2:
+            ids = torch.tensor([0, 5, 777, n - 1], device=DEV)
+            env.reset_idx(ids)
+            sea.reset(ids.cpu())
+        if it == 4:                            # resets decided inside the fused step kernel
+            env.episode_length_buf[10:20] = int(env.max_episode_length)
+            env.step(fr["actions"].clone())
+            torch.cuda.synchronize()
+            k = int(env.step_counts[0])
+            assert k >= 10
+            sea.reset(env.reset_ids[:k].long().cpu())
+            assert float(env.sea_hidden_state_per_env[:, 10:20].abs().sum()) == 0.0
+    assert float(env.sea_hidden_state.abs().sum()) > 0.0
+
+
+def test_outputs_written_straight_into_rollout_storage():
+    """with the env's output pointers moved into [T,N,O] storage the kernel's stores are
+    the only pass; the storage must equal what a plain env returns step by step (same seed, in-kernel RNG)."""
+    from legged_gym_b200.utils.rollout import RolloutStorageWriter
+    n, T = 333, 5
+    envs = [helpers.make_env("go1_rough_full", n, device=DEV, seed=9) for _ in range(2)]
+    for e in envs:
+        helpers.randomise_env_state(e, 9)
+    frames = synthetic.make_frames(envs[0], T, seed=77)
+    for e in envs:
+        synthetic.load_frame(e, frames[0])
+    plain, wr = envs[0], RolloutStorageWriter(envs[1], T)
+    for rollout in range(2):
+        for t in range(T):
+            for e in envs:
+                synthetic.load_frame(e, frames[t])
+            obs, _, rew, reset, _ = plain.step(frames[t]["actions"].clone())
+            o2, _, r2, d2, _ = wr.step(frames[t]["actions"].clone())
+            torch.cuda.synchronize()
+            assert o2.data_ptr() == wr.observations[t + 1].data_ptr()
+            assert torch.equal(wr.observations[t + 1], obs) and torch.equal(wr.rewards[t, :, 0], rew)
+            assert torch.equal(wr.dones[t, :, 0], reset) and torch.equal(d2, reset)
+        with pytest.raises(AssertionError, match="overflow"):
+            wr.step(frames[0]["actions"])
+        wr.clear()
+        assert torch.equal(wr.observations[0], plain.obs_buf)
+    with pytest.raises(ValueError):
+        plain.bind_output_tensors(obs_buf=torch.zeros(n, 7, device=DEV))
+
+
 # ------------------------------------------------------------------------------------------- resets
 def test_reset_idx_subset_and_reset_all():
     from oracle import legged_oracle as lo
