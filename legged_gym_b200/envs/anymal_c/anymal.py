@@ -114,6 +114,9 @@ class Anymal(LeggedRobot):
         self.sea_cell_state_per_env = self.sea_cell_state.view(SEA_LAYERS, self.num_envs, self.num_actions, SEA_HIDDEN)
         self._sea_torques = torch.zeros(M, **kw)
 
+    def _extra_state_tensors(self):
+        return {"sea_hidden_state": self.sea_hidden_state, "sea_cell_state": self.sea_cell_state}
+
     def _compute_torques(self, actions):
         # Choose between pd controller and actuator network (anymal.py:71-81)
         if self.cfg.control.use_actuator_network:

@@ -817,6 +817,56 @@ class LeggedRobot(BaseTask):
             self.reset_buf = reset_buf.view(N)
             self._bufs.reset_buf = _lgk.ptr(self.reset_buf)
 
+    # ------------------------------------------------------------------ env-state checkpoint
+    # the reference resumes the policy only (utils/helpers.py:103-125,
+    # task_registry.py:162-167) and restarts every env from scratch.  Here the whole env state is a fixed
+    # set of device buffers plus three host scalars, and the in-kernel RNG is counter-based -- keyed by
+    # (seed, common_step_counter, env id, site) -- so restoring the counter restores the random stream.
+    _STATE_TENSORS = ("root_states", "dof_state", "actions", "last_actions", "last_dof_vel", "last_root_vel",
+                      "commands", "feet_air_time", "env_origins", "obs_buf", "rew_buf", "reset_buf", "time_out_buf",
+                      "base_lin_vel", "base_ang_vel", "projected_gravity", "_episode_sums_buf", "episode_stats",
+                      "_extras_buf", "_episode_length_buf", "terrain_levels")
+
+    def _extra_state_tensors(self) -> Dict[str, torch.Tensor]:
+        """Per-env state a subclass adds (actuator histories, LSTM state)."""
+        return {}
+
+    def state_dict(self) -> dict:
+        """Everything needed to continue this env bit-for-bit: host copies of the state buffers, the step
+        counter, the (curriculum-mutable) command ranges and the seed."""
+        tensors = {n: getattr(self, n).detach().cpu().clone() for n in self._STATE_TENSORS
+                   if torch.is_tensor(getattr(self, n, None))}
+        tensors.update({"extra." + k: v.detach().cpu().clone() for k, v in self._extra_state_tensors().items()})
+        return {"version": 1, "task": type(self).__name__, "num_envs": self.num_envs, "num_obs": self.num_obs,
+                "seed": int(getattr(self.cfg, "seed", 1)), "env_id_offset": int(getattr(self, "env_id_offset", 0)),
+                "common_step_counter": int(self.common_step_counter),
+                "command_ranges": {k: [float(x) for x in v] for k, v in self.command_ranges.items()},
+                "reward_names": list(self.reward_names), "tensors": tensors}
+
+    def load_state_dict(self, sd: dict):
+        """Restore a state_dict() into this env's existing buffers (addresses stay as the kernels know
+        them).  The env must have been built from the same config."""
+        if sd.get("version") != 1:
+            raise ValueError(f"unknown env checkpoint version {sd.get('version')}")
+        for key in ("num_envs", "num_obs"):
+            if sd[key] != getattr(self, key):
+                raise ValueError(f"checkpoint {key}={sd[key]} != env {key}={getattr(self, key)}")
+        if list(sd["reward_names"]) != list(self.reward_names):
+            raise ValueError("checkpoint was taken with a different reward set")
+        extra = self._extra_state_tensors()
+        for name, t in sd["tensors"].items():
+            dst = extra.get(name[6:]) if name.startswith("extra.") else getattr(self, name, None)
+            if not torch.is_tensor(dst) or dst.numel() != t.numel() or dst.dtype != t.dtype:
+                raise ValueError(f"checkpoint tensor {name} does not fit this env")
+            dst.copy_(t.view(dst.shape))
+        for k, v in sd["command_ranges"].items():
+            self.command_ranges[k][0], self.command_ranges[k][1] = v[0], v[1]
+        self.common_step_counter = int(sd["common_step_counter"])
+        self._dev_step_counter = -1          # re-seed the device copy on the next step
+        self._ranges_cache = None
+        if self._lib is not None:
+            self._sync_host_scalars()
+
     def _ensure_dev_counter(self, want: int):
         """Device copy of common_step_counter: the step kernel increments it itself, so it is
         re-seeded only when the host value was changed from outside."""

@@ -84,6 +84,9 @@ class Go1(LeggedRobot):
         self.vel_buffs = torch.zeros(self.num_envs, self.num_actions, LEN_HIST, **kw)
         self.dVel = torch.zeros(self.num_envs, self.num_actions, **kw)
 
+    def _extra_state_tensors(self):
+        return {"pos_err_buffs": self.pos_err_buffs, "vel_buffs": self.vel_buffs, "model_ins": self.model_ins}
+
     def _compute_poses(self, actions):
         if getattr(self.cfg.control, "use_actuator_network", False):
             self.actuator_advance(actions)   # result unused, as in the reference (go1.py:70-73)

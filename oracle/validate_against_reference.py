@@ -83,6 +83,48 @@ def run_scenario(name, num_envs=256, steps=12, seed=0, verbose=True):
     return n_resets
 
 
+def run_sea_lstm(num_envs=64, steps=20, seed=0, verbose=True):
+    """ANYmal actuator net: the reference's Anymal._compute_torques / reset_idx with the SHIPPED TorchScript
+    checkpoint (resources/actuator_nets/anydrive_v3_lstm.pt, aten::lstm) against SeaLstmOracle's written-out
+    cell.  aten::lstm's CPU kernel orders the gate sums differently, so this is not bit-identical: each call
+    starts from the reference's state and must agree within a few ulp (state) / 1e-6 of the output-layer
+    operand magnitude (torques); the free-running drift is reported."""
+    env = make_reference_env("anymal_c_flat", None, num_envs=num_envs, seed=seed)
+    assert env.cfg.control.use_actuator_network
+    sd = dict(env.actuator_network.state_dict())
+    p = lo.OracleParams.from_env(env)
+    sea = lo.SeaLstmOracle(num_envs, env.num_actions, sd)
+    free = lo.SeaLstmOracle(num_envs, env.num_actions, sd)
+    atol = 1e-6 * float(sd["out_scale"].abs().max() * (sd["linear.bias"].abs().sum() + sd["linear.weight"].abs().sum()))
+    g = torch.Generator().manual_seed(seed)
+    frames = synthetic.make_frames(env, 4, seed=77 + seed)
+    worst_state = worst_tq = drift = 0.0
+    for it in range(steps):
+        synthetic.load_frame(env, frames[it % 4])
+        a = torch.randn(num_envs, env.num_actions, generator=g)
+        sea.sea_hidden_state.copy_(env.sea_hidden_state); sea.sea_cell_state.copy_(env.sea_cell_state)
+        want = env._compute_torques(a)
+        got = sea.compute_torques(a, p.action_scale, p.default_dof_pos, env.dof_pos, env.dof_vel)
+        fr = free.compute_torques(a, p.action_scale, p.default_dof_pos, env.dof_pos, env.dof_vel)
+        assert torch.equal(sea.sea_input, env.sea_input)
+        worst_state = max(worst_state, float((sea.sea_hidden_state - env.sea_hidden_state).abs().max()),
+                          float((sea.sea_cell_state - env.sea_cell_state).abs().max()))
+        worst_tq = max(worst_tq, float(((got - want).abs() - 1e-5 * want.abs()).max()))
+        drift = max(drift, float((free.sea_hidden_state - env.sea_hidden_state).abs().max()))
+        if it == steps // 2:                    # reset_idx override zeroes exactly the listed envs (:56-60)
+            ids = torch.tensor([0, 3, num_envs - 1])
+            env.sea_hidden_state_per_env[:, ids] = 0.; env.sea_cell_state_per_env[:, ids] = 0.
+            free.reset(ids)
+    assert worst_state < 1e-6, worst_state
+    assert worst_tq < atol, (worst_tq, atol)
+    assert drift < 1e-4, drift
+    if verbose:
+        print(f"  anymal LSTM (shipped checkpoint): {steps} calls x {num_envs * env.num_actions} actuators, per-call "
+              f"state error {worst_state:.1e}, torque error beyond 1e-5 rel {max(worst_tq, 0):.1e} (floor {atol:.1e}), "
+              f"free-running drift {drift:.1e}")
+    return worst_state
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--envs", type=int, default=256)
@@ -90,6 +132,7 @@ def main(argv=None):
     a = ap.parse_args(argv)
     for name in scenarios.SCENARIOS:
         run_scenario(name, a.envs, a.steps)
+    run_sea_lstm()
     print("oracle == reference on every scenario")
 
 

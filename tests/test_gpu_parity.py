@@ -243,6 +243,32 @@ def test_outputs_written_straight_into_rollout_storage():
         plain.bind_output_tensors(obs_buf=torch.zeros(n, 7, device=DEV))
 
 
+def test_env_state_checkpoint_resumes_bit_identically():
+    """A fresh env restored from state_dict() continues exactly like the env that kept running (in-kernel
+    Philox RNG is keyed by the step counter, so no generator state has to travel)."""
+    n = 700
+    a = helpers.make_env("go1_rough_full", n, device=DEV, seed=5)
+    helpers.randomise_env_state(a, 5)
+    frames = synthetic.make_frames(a, 6, seed=31)
+    for t in range(3):
+        synthetic.load_frame(a, frames[t])
+        a.step(frames[t]["actions"].clone())
+    sd = a.state_dict()
+    b = helpers.make_env("go1_rough_full", n, device=DEV, seed=5)
+    b.load_state_dict(sd)
+    for t in range(3, 6):
+        for e in (a, b):
+            synthetic.load_frame(e, frames[t])
+            e.step(frames[t]["actions"].clone())
+        torch.cuda.synchronize()
+        for name in ("obs_buf", "rew_buf", "reset_buf", "commands", "root_states", "dof_state", "feet_air_time",
+                     "episode_length_buf", "terrain_levels", "env_origins", "_episode_sums_buf", "step_counts"):
+            assert torch.equal(getattr(a, name), getattr(b, name)), f"step {t}: {name} differs after resume"
+        k = int(a.step_counts[0])
+        assert torch.equal(a.reset_ids[:k], b.reset_ids[:k])
+    assert int(a.reset_buf.sum()) >= 0 and a.common_step_counter == b.common_step_counter
+
+
 # ------------------------------------------------------------------------------------------- resets
 def test_reset_idx_subset_and_reset_all():
     from oracle import legged_oracle as lo

@@ -133,3 +133,30 @@ def test_product_code_never_imports_the_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dp, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports oracle/"
+
+
+@pytest.mark.parametrize("scenario", ["go1_rough_full", "go1_rough_actuator", "anymal_c_flat"])
+def test_env_state_checkpoint_roundtrip(scenario, tmp_path):
+    """state_dict() -> torch.save -> load_state_dict() restores every state buffer in place."""
+    env = helpers.make_env(scenario, 24, seed=2)
+    helpers.randomise_env_state(env, 2)
+    env.command_ranges["lin_vel_x"][1] = 1.5          # as the command curriculum would have left it
+    env.common_step_counter = 4711
+    extra = env._extra_state_tensors()
+    for t in extra.values():
+        t.copy_(torch.randn(t.shape))
+    sd = env.state_dict()
+    path = tmp_path / "env_state.pt"
+    torch.save(sd, path)
+    want = {n: t.clone() for n, t in sd["tensors"].items()}
+    other = helpers.make_env(scenario, 24, seed=2)
+    addr = other.commands.data_ptr()
+    other.load_state_dict(torch.load(path, weights_only=False))
+    assert other.common_step_counter == 4711 and other.command_ranges["lin_vel_x"][1] == 1.5
+    assert other.commands.data_ptr() == addr          # restored in place: kernel pointers stay valid
+    got = other.state_dict()["tensors"]
+    assert set(got) == set(want) and len(want) >= 18 + len(extra)
+    for n in want:
+        assert torch.equal(got[n], want[n]), n
+    with pytest.raises(ValueError, match="num_envs"):
+        helpers.make_env(scenario, 8).load_state_dict(sd)

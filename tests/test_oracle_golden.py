@@ -23,6 +23,13 @@ def test_oracle_bit_identical_to_live_reference(name):
     assert v.run_scenario(name, num_envs=96, steps=6, seed=3, verbose=False) > 0
 
 
+@pytest.mark.reference
+@pytest.mark.skipif(not reference_loader.reference_available(), reason="/root/reference only exists in the build container")
+def test_sea_lstm_oracle_matches_the_shipped_torchscript_checkpoint():
+    from oracle import validate_against_reference as v
+    assert v.run_sea_lstm(num_envs=32, steps=12, verbose=False) < 1e-6
+
+
 def test_golden_fixtures_cover_the_edge_cases():
     """resample on step 0, time-outs on steps 0 and 2, push on step 2, contact terminations somewhere."""
     g = helpers.load_golden("go1_rough_full")
