@@ -106,7 +106,9 @@ enum {                                   /* LgkConsts.flags                     
   LGK_F_CUSTOM_ORIGINS    = 1u << 6,     /* rough terrain: xy jitter on reset (:422-425)   */
   LGK_F_ONLY_POSITIVE     = 1u << 7,     /* cfg.rewards.only_positive_rewards              */
   LGK_F_HAS_TERMINATION   = 1u << 8,     /* 'termination' scale is non-zero (:209-212)     */
-  LGK_F_INIT_DONE         = 1u << 9      /* self.init_done (curriculum skipped before)     */
+  LGK_F_INIT_DONE         = 1u << 9,     /* self.init_done (curriculum skipped before)     */
+  LGK_F_EP_INCREMENTED    = 1u << 10     /* episode_length_buf already counts this step
+                                            (lgk_pre_reward_state ran): do not add 1 again */
 };
 
 typedef struct LgkRewardEntry {
@@ -299,6 +301,15 @@ int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_
 
 /* Everything post_physics_step() does for every env (legged_robot.py:109-141) in one launch. */
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream);
+
+/* For reward terms evaluated OUTSIDE the library (a subclass's python _reward_<name>, bound as
+ * LGK_REW_EXTERNAL): brings the buffers such a term may read to the state the reference has when
+ * compute_reward() runs (legged_robot.py:118-131) -- episode_length_buf += 1, base_lin_vel, base_ang_vel,
+ * projected_gravity, commands after the callback's resample / heading update, measured_heights when
+ * materialised, reset_buf and time_out_buf.  The caller then fills ext_rewards and calls
+ * lgk_post_physics_step with LGK_F_EP_INCREMENTED set; that call recomputes all of the above identically
+ * (the random draws are keyed by step, env and site).  Not needed when every term is built in. */
+int lgk_pre_reward_state(const LgkConsts* c, const LgkBuffers* b, void* stream);
 
 /* reset_idx(env_ids) (legged_robot.py:150-193) for an ascending int64 id list on the device
  * (env_ids == NULL means arange(n)); n == 0 returns at once like the reference (:160).

@@ -45,6 +45,7 @@ F_CUSTOM_ORIGINS = 1 << 6
 F_ONLY_POSITIVE = 1 << 7
 F_HAS_TERMINATION = 1 << 8
 F_INIT_DONE = 1 << 9
+F_EP_INCREMENTED = 1 << 10
 
 STATUS = {0: "LGK_OK", -1: "LGK_ERR_NULL", -2: "LGK_ERR_DIM", -3: "LGK_ERR_CONTROL_TYPE", -4: "LGK_ERR_REWARD",
           -5: "LGK_ERR_ALIGN", -6: "LGK_ERR_VERSION", -7: "LGK_ERR_TERRAIN"}
@@ -162,6 +163,7 @@ def load():
         "lgk_lstm_actuator_advance": (C.c_int, [cp, C.POINTER(LgkLstmWeights), fp, fp, fp, fp, fp, fp, fp]),
         "lgk_lstm_reset_hidden": (C.c_int, [C.c_int32, C.c_int32, fp, fp, C.c_int32, fp, fp, fp]),
         "lgk_post_physics_step": (C.c_int, [cp, bp, fp]),
+        "lgk_pre_reward_state": (C.c_int, [cp, bp, fp]),
         "lgk_reset_idx": (C.c_int, [cp, bp, fp, C.c_int32, fp]),
         "lgk_reset_all": (C.c_int, [cp, bp, fp]),
         "lgk_set_step_counter": (C.c_int, [fp, C.c_int64, fp]),
@@ -184,7 +186,7 @@ def load():
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
     "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
-    "lgk_lstm_actuator_advance", "lgk_lstm_reset_hidden", "lgk_post_physics_step", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
+    "lgk_lstm_actuator_advance", "lgk_lstm_reset_hidden", "lgk_post_physics_step", "lgk_pre_reward_state", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]
 
 

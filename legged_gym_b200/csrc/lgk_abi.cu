@@ -6,6 +6,7 @@
 extern "C" {
 int lgk_post_physics_step_impl(const LgkConsts*, const LgkBuffers*, cudaStream_t);
 int lgk_reset_idx_impl(const LgkConsts*, const LgkBuffers*, const long long*, int, cudaStream_t);
+int lgk_pre_reward_state_impl(const LgkConsts*, const LgkBuffers*, cudaStream_t);
 int lgk_build_height_min3_impl(const int16_t*, int, int, int16_t*, int, cudaStream_t);
 int lgk_clip_actions_impl(const float*, float*, long long, float, cudaStream_t);
 int lgk_compute_poses_impl(const LgkConsts*, const float*, float*, cudaStream_t);
@@ -186,6 +187,14 @@ int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream)
   if (rc) return rc;
   g_launches += 2;   // tile kernel + epilogue
   return lgk_post_physics_step_impl(c, b, (cudaStream_t)stream);
+}
+
+int lgk_pre_reward_state(const LgkConsts* c, const LgkBuffers* b, void* stream) {
+  int rc = check_step(c, b);
+  if (rc) return rc;
+  if (c->flags & LGK_F_EP_INCREMENTED) return LGK_ERR_DIM;   // would count the step twice
+  g_launches += 1;
+  return lgk_pre_reward_state_impl(c, b, (cudaStream_t)stream);
 }
 
 int lgk_reset_idx(const LgkConsts* c, const LgkBuffers* b, const int64_t* env_ids, int32_t n, void* stream) {

@@ -521,11 +521,12 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     float* head_row = sm + L.head + lane * HS;
     const float* cf_row = sm + L.cf + lane * B3;
     const long long ep_in = reinterpret_cast<const long long*>(sm + L.ep)[lane];
+    const long long ep_inc = (flags & LGK_F_EP_INCREMENTED) ? 0 : 1;   // lgk_pre_reward_state already counted this step
 
     // the reset decision (:143-148) is cheap: every stage-1 warp forms it for its own lane
     bool time_out = false, reset = false;
     if (active) {
-      time_out = (ep_in + 1) > c.max_episode_length;
+      time_out = (ep_in + ep_inc) > c.max_episode_length;
       reset = term_contact(c, s_idx, cf_row, a.thr_term) || time_out;
     }
 
@@ -545,7 +546,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         const float* rp = sm + L.root + lane * 13;
 #pragma unroll
         for (int i = 0; i < 13; ++i) root[i] = rp[i];
-        long long ep = ep_in + 1;                                   // (:118)
+        long long ep = ep_in + ep_inc;                              // (:118)
         const float q[4] = {root[3], root[4], root[5], root[6]};
         quat_rotate_inverse(q, root[7], root[8], root[9], blv);     // (:123-125)
         quat_rotate_inverse(q, root[10], root[11], root[12], bav);
@@ -1104,6 +1105,115 @@ static float sqrt_le_threshold(float c) {
 }
 static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// ---------------------------------------------------------------------------------------------
+// State the reference has when compute_reward() runs (:118-131), for reward terms that live in Python
+// (a subclass's own _reward_<name>, LGK_REW_EXTERNAL): episode counter, body-frame velocities and gravity,
+// commands after the callback's resample + heading update, measured heights (when materialised) and the
+// termination flags.  One thread per env, plain global loads: this is the cold path of user-defined terms,
+// not the tuned one.  Everything it writes is either a pure output of the step kernel or idempotent -- the
+// step kernel that follows redraws the same random numbers (counter-based: same step, env, site) and
+// recomputes the same values -- except episode_length_buf, which the step kernel is told not to count
+// again (LGK_F_EP_INCREMENTED).  The push (:351) is left to the step kernel: body-frame velocities must be
+// formed from the un-pushed state (:123-124).
+template <bool TAPS>
+__global__ void lgk_pre_reward_kernel(const __grid_constant__ StepArgs a, int mul_rcp) {
+  const LgkConsts& c = a.c;
+  const LgkBuffers& b = a.b;
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= c.num_envs) return;
+  const unsigned flags = c.flags;
+  const bool heading_mode = flags & LGK_F_HEADING_COMMAND;
+  const LgkWorkspace* ws = reinterpret_cast<const LgkWorkspace*>(b.workspace);
+  const unsigned long long csc = ws->step_counter + 1ull;
+  const unsigned env_global = (unsigned)(c.env_id_offset + env);
+  float root[13];
+#pragma unroll
+  for (int i = 0; i < 13; ++i) root[i] = b.root_states[(size_t)env * 13 + i];
+  const long long ep = b.episode_length_buf[env] + 1;            // (:118)
+  b.episode_length_buf[env] = ep;
+  const float q[4] = {root[3], root[4], root[5], root[6]};
+  float v[3];
+  quat_rotate_inverse(q, root[7], root[8], root[9], v);
+  b.base_lin_vel[(size_t)env * 3] = v[0]; b.base_lin_vel[(size_t)env * 3 + 1] = v[1]; b.base_lin_vel[(size_t)env * 3 + 2] = v[2];
+  quat_rotate_inverse(q, root[10], root[11], root[12], v);
+  b.base_ang_vel[(size_t)env * 3] = v[0]; b.base_ang_vel[(size_t)env * 3 + 1] = v[1]; b.base_ang_vel[(size_t)env * 3 + 2] = v[2];
+  quat_rotate_inverse(q, 0.f, 0.f, -1.f, v);
+  b.projected_gravity[(size_t)env * 3] = v[0]; b.projected_gravity[(size_t)env * 3 + 1] = v[1]; b.projected_gravity[(size_t)env * 3 + 2] = v[2];
+  // _post_physics_step_callback (:337-349)
+  float4 cmd = *reinterpret_cast<const float4*>(b.commands + (size_t)env * 4);
+  if ((ep % c.resample_interval) == 0) {
+    float u0, u1, u2;
+    if (TAPS) { const float* t = b.tap_cmd_callback + (size_t)env * 3; u0 = t[0]; u1 = t[1]; u2 = t[2]; }
+    else { const uint4 r = philox_cold(a, csc, env_global, LGK_SITE_CMD_CB); u0 = u01(r.x); u1 = u01(r.y); u2 = u01(r.z); }
+    resample_command(cmd, b.command_ranges, heading_mode, u0, u1, u2);
+  }
+  if (heading_mode) {
+    float fwd[3];
+    quat_apply(q, 1.f, 0.f, 0.f, fwd);
+    cmd.z = clampf(0.5f * wrap_to_pi_fast(cmd.w - atan2f(fwd[1], fwd[0])), -1.f, 1.f);
+  }
+  *reinterpret_cast<float4*>(b.commands + (size_t)env * 4) = cmd;
+  // _get_heights (:818-854), scalar op-for-op chain (the step kernel's packed chain rounds identically)
+  const int H = c.num_height_points;
+  if (b.measured_heights != nullptr && H > 0) {
+    float* mrow = b.measured_heights + (size_t)env * H;
+    if (flags & LGK_F_TERRAIN_PLANE) {
+      for (int h = 0; h < H; ++h) mrow[h] = 0.f;
+    } else {
+      const float n = fmaxf(sqrtf(add_rn(mul_rn(q[2], q[2]), mul_rn(q[3], q[3]))), 1e-9f);
+      const float yz = __fdiv_rn(q[2], n), yw = __fdiv_rn(q[3], n);
+      const float yz2 = mul_rn(yz, 2.0f), inv_hs = 1.0f / c.horizontal_scale;
+      for (int h = 0; h < H; ++h) {
+        const float px = b.height_points_xy[2 * h], py = b.height_points_xy[2 * h + 1];
+        const float tx = mul_rn(-yz2, py), ty = mul_rn(yz2, px);
+        float wx = add_rn(add_rn(px, mul_rn(yw, tx)), mul_rn(-yz, ty));
+        float wy = add_rn(add_rn(py, mul_rn(yw, ty)), mul_rn(yz, tx));
+        wx = add_rn(add_rn(wx, root[0]), c.border_size);
+        wy = add_rn(add_rn(wy, root[1]), c.border_size);
+        const float sx = mul_rcp ? mul_rn(wx, inv_hs) : __fdiv_rn(wx, c.horizontal_scale);
+        const float sy = mul_rcp ? mul_rn(wy, inv_hs) : __fdiv_rn(wy, c.horizontal_scale);
+        // .long() truncates toward zero; clamp in floating point first so that the conversion cannot overflow
+        int ix = (int)fminf(fmaxf(sx, -1.0f), 1.0e7f), iy = (int)fminf(fmaxf(sy, -1.0f), 1.0e7f);
+        ix = min(max(ix, 0), c.terrain_rows - 2);
+        iy = min(max(iy, 0), c.terrain_cols - 2);
+        mrow[h] = mul_rn(s16_to_float(b.height_min3[(size_t)ix * c.terrain_pitch + iy]), c.vertical_scale);
+      }
+    }
+  }
+  // check_termination (:143-148)
+  bool term = false;
+  const float* cf = b.contact_forces + (size_t)env * c.num_bodies * 3;
+  for (int k = 0; k < c.num_term; ++k) {
+    const float* f = cf + 3 * c.term_idx[k];
+    term |= sumsq3(f[0], f[1], f[2]) > a.thr_term;
+  }
+  const bool time_out = ep > c.max_episode_length;
+  b.time_out_buf[env] = time_out ? 1 : 0;
+  b.reset_buf[env] = (term || time_out) ? 1 : 0;
+}
+
+static void fill_rng_and_thresholds(StepArgs& args, const LgkConsts* c) {
+  for (int r = 0; r < 10; ++r) {
+    args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
+    args.pk[2 * r + 1] = (unsigned)(c->seed >> 32) + (unsigned)r * 0xBB67AE85u;
+  }
+  args.thr_term = sqrt_le_threshold(1.0f);
+  args.thr_pen = sqrt_le_threshold(0.1f);
+  args.thr_ffp = sqrt_le_threshold(c->max_contact_force);
+}
+
+extern "C" int lgk_pre_reward_state_impl(const LgkConsts* c, const LgkBuffers* b, cudaStream_t stream) {
+  StepArgs args = {};
+  args.c = *c;
+  args.b = *b;
+  fill_rng_and_thresholds(args, c);
+  const int grid = (c->num_envs + 127) / 128;
+  const int mul = c->index_math == LGK_INDEX_MUL_RCP;
+  if (c->rng_mode == LGK_RNG_TAPS) lgk_pre_reward_kernel<true><<<grid, 128, 0, stream>>>(args, mul);
+  else lgk_pre_reward_kernel<false><<<grid, 128, 0, stream>>>(args, mul);
+  return (int)cudaGetLastError();
+}
+
 template <int DT, bool TAPS, bool MUL_RCP, int NP>
 static int launch_step(const StepArgs& args, int grid, size_t smem, cudaStream_t stream) {
   auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP, NP>;
@@ -1125,15 +1235,9 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   const int OH = 12 + 3 * D;
   args.num_rows = c->num_rewards + ((c->flags & LGK_F_HAS_TERMINATION) ? 1 : 0);
   args.head_stride = OH | 1;
-  for (int r = 0; r < 10; ++r) {
-    args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
-    args.pk[2 * r + 1] = (unsigned)(c->seed >> 32) + (unsigned)r * 0xBB67AE85u;
-  }
+  fill_rng_and_thresholds(args, c);
   args.hip_mask = 0u;
   for (int h = 0; h < c->num_hip; ++h) args.hip_mask |= 1u << c->hip_idx[h];
-  args.thr_term = sqrt_le_threshold(1.0f);
-  args.thr_pen = sqrt_le_threshold(0.1f);
-  args.thr_ffp = sqrt_le_threshold(c->max_contact_force);
   args.air_active = 0;
   args.bh_active = 0;
   for (int i = 0; i < c->num_rewards; ++i) {

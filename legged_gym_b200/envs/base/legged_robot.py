@@ -103,10 +103,31 @@ class LeggedRobot(BaseTask):
         self._ensure_dev_counter(self.common_step_counter - 1)
         if self.cfg.commands.curriculum and (self.common_step_counter % self.max_episode_length == 0):
             self._command_curriculum_prepass()
+        if self._external_terms:
+            self._evaluate_external_terms(lib)
         _lgk.check("lgk_post_physics_step", lib.lgk_post_physics_step(
             C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
+        self._consts.flags &= ~_lgk.F_EP_INCREMENTED
         self._dev_step_counter = self.common_step_counter
         self._after_step_sim_writes()
+
+    def _evaluate_external_terms(self, lib):
+        """Reward terms a subclass defines in Python (`_reward_<name>`, found like the reference does,
+        :588-593) that the kernel has no code for.  `lgk_pre_reward_state` first brings the buffers such a
+        term may read to the state the reference has inside compute_reward() -- episode_length_buf,
+        base_lin_vel / base_ang_vel / projected_gravity, commands after the callback, measured_heights,
+        reset_buf / time_out_buf -- then each term is evaluated and its values enter the fused kernel as an
+        LGK_REW_EXTERNAL row: scaled, summed in the term's alphabetical slot, accumulated in episode_sums.
+        Not reproduced for such terms: feet_air_time as advanced by a built-in term earlier in the order,
+        and the pushed root velocities on push steps (both are updated by the fused kernel afterwards)."""
+        _lgk.check("lgk_pre_reward_state", lib.lgk_pre_reward_state(
+            C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
+        self._consts.flags |= _lgk.F_EP_INCREMENTED
+        i = 0
+        for name, fn in zip(self.reward_names, self.reward_functions):
+            if fn is not None:
+                self._ext_rewards[i].copy_(fn().to(torch.float).reshape(self.num_envs))
+                i += 1
 
     # ------------------------------------------------------------------ control
     def _compute_poses(self, actions):
@@ -425,9 +446,6 @@ class LeggedRobot(BaseTask):
                 raise NotImplementedError(
                     f"{type(self).__name__} overrides {name}(), whose body runs inside the fused step kernel; "
                     f"overriding it is not supported")
-        if self._external_terms:
-            raise NotImplementedError(
-                f"python reward terms {self._external_terms} need the split pre/post launch, which is not wired up yet")
 
     # ------------------------------------------------------------------ terrain / envs
     def _create_ground_plane(self):

@@ -130,6 +130,9 @@ class OracleParams:
     feet_indices: torch.Tensor = None
     penalised_contact_indices: torch.Tensor = None
     termination_contact_indices: torch.Tensor = None
+    # reward terms a subclass adds as python methods (legged_robot.py:588-593 finds them by getattr): name ->
+    # callable(p, s) evaluated at the reference's point in compute_reward()
+    extra_reward_terms: Optional[dict] = None
 
     @staticmethod
     def from_env(env, device=None) -> "OracleParams":
@@ -495,6 +498,8 @@ def reward_terms(p: OracleParams, s: OracleState):
 def compute_reward(p, s):
     """envs/base/legged_robot.py:195-212"""
     terms = reward_terms(p, s)
+    for name, fn in (p.extra_reward_terms or {}).items():
+        terms[name] = (lambda f=fn: f(p, s))
     s.rew_buf[:] = 0.
     for name in p.reward_names:
         rew = terms[name]() * p.reward_scales[name]

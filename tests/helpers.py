@@ -16,7 +16,7 @@ from legged_gym_b200.utils.task_registry import task_registry
 RTOL, ATOL = 1e-5, 1e-6
 
 
-def make_env(scenario: str, num_envs: int, device: str = "cpu", seed: int = 0, extra=None):
+def make_env(scenario: str, num_envs: int, device: str = "cpu", seed: int = 0, extra=None, task_class=None):
     task, mutate = scenarios.SCENARIOS[scenario]
     cfg = copy.deepcopy(task_registry.env_cfgs[task])
     cfg.env.num_envs = num_envs
@@ -31,8 +31,8 @@ def make_env(scenario: str, num_envs: int, device: str = "cpu", seed: int = 0, e
     sp.use_gpu_pipeline = device.startswith("cuda")
     np.random.seed(seed)
     torch.manual_seed(seed)
-    return task_registry.get_task_class(task)(cfg=cfg, sim_params=sp, physics_engine=gymapi.SIM_PHYSX,
-                                              sim_device=device, headless=True)
+    cls = task_class or task_registry.get_task_class(task)
+    return cls(cfg=cfg, sim_params=sp, physics_engine=gymapi.SIM_PHYSX, sim_device=device, headless=True)
 
 
 def randomise_env_state(env, seed: int):
@@ -101,15 +101,17 @@ def compare_env_to_oracle(env, s, tag=""):
                 assert_close(f"{tag}extras[{k}]", env.extras["episode"][k].reshape(1), torch.as_tensor(v).reshape(1).float())
 
 
-def run_parity(scenario, num_envs, steps, oracle_device="cpu", index_math=None, seed=0, materialize=True, extra=None):
+def run_parity(scenario, num_envs, steps, oracle_device="cpu", index_math=None, seed=0, materialize=True, extra=None,
+               task_class=None, oracle_extra_terms=None):
     """Steps this repo's env (CUDA kernels, taps) and the oracle on the same frames; compares every step."""
     from legged_gym_b200 import _lgk
     from oracle import legged_oracle as lo
-    env = make_env(scenario, num_envs, device="cuda:0", seed=seed, extra=extra)
+    env = make_env(scenario, num_envs, device="cuda:0", seed=seed, extra=extra, task_class=task_class)
     randomise_env_state(env, seed)
     frames = synthetic.make_frames(env, 4, seed=1234 + seed)
     synthetic.load_frame(env, frames[0])
     p = lo.OracleParams.from_env(env, device=oracle_device)
+    p.extra_reward_terms = oracle_extra_terms
     s = lo.OracleState.from_env(env, p, device=oracle_device)
     if index_math is None:
         index_math = _lgk.INDEX_MATH_TORCH_CPU if oracle_device == "cpu" else _lgk.INDEX_MATH_TORCH_CUDA

@@ -213,6 +213,41 @@ def test_anymal_lstm_actuator_matches_oracle_free_running():
     assert float(env.sea_hidden_state.abs().sum()) > 0.0
 
 
+def test_python_reward_terms_of_a_subclass_enter_the_fused_kernel():
+    """The reference's way of adding a reward: define `_reward_<name>` on a subclass and give it a scale
+    (legged_robot.py:588-593).  Such terms run as Python here, on the state lgk_pre_reward_state prepares,
+    and are scaled / summed / accumulated by the kernel in their alphabetical slot; a python method named
+    like a built-in term replaces it."""
+    from legged_gym_b200.envs.go1.go1 import Go1
+
+    class Go1PythonTerms(Go1):
+        def _reward_alive_progress(self):      # episode counter, termination flags, commands, body-frame velocity
+            return (self.episode_length_buf.float() / self.max_episode_length) * (~self.reset_buf) * \
+                torch.exp(-torch.abs(self.commands[:, 0] - self.base_lin_vel[:, 0]))
+
+        def _reward_clearance(self):           # height scan and projected gravity
+            return torch.mean(torch.clip(self.root_states[:, 2:3] - 0.3 - self.measured_heights, 0., 1.), dim=1) * \
+                (1. + self.projected_gravity[:, 2])
+
+        def _reward_torques(self):             # overrides the built-in term of the same name
+            return torch.sum(torch.abs(self.torques), dim=1)
+
+    oracle_terms = {
+        "alive_progress": lambda p, s: (s.episode_length_buf.float() / p.max_episode_length) * (~s.reset_buf) *
+        torch.exp(-torch.abs(s.commands[:, 0] - s.base_lin_vel[:, 0])),
+        "clearance": lambda p, s: torch.mean(torch.clip(s.root_states[:, 2:3] - 0.3 - s.measured_heights, 0., 1.), dim=1) *
+        (1. + s.projected_gravity[:, 2]),
+        "torques": lambda p, s: torch.sum(torch.abs(s.torques), dim=1),
+    }
+
+    def scales(cfg):
+        cfg.rewards.scales.alive_progress = 0.7
+        cfg.rewards.scales.clearance = -0.3
+    n = helpers.run_parity("go1_rough_full", 777, 5, extra=scales, task_class=Go1PythonTerms,
+                           oracle_extra_terms=oracle_terms)
+    assert n > 0
+
+
 def test_outputs_written_straight_into_rollout_storage():
     """with the env's output pointers moved into [T,N,O] storage the kernel's stores are
     the only pass; the storage must equal what a plain env returns step by step (same seed, in-kernel RNG)."""
