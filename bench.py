@@ -40,6 +40,12 @@ METRIC = "env_steps_per_sec"
 UNIT = "env-steps/s"
 
 
+def workload_name(envs_per_gpu, decimation=4):
+    """The one workload both arms name (BASELINE.json: Go1 rough, 4096-65536 envs/GPU)."""
+    return (f"Go1 rough terrain, 187-point height scan, full reward set (20 terms + termination), terrain "
+            f"curriculum, {envs_per_gpu} envs/GPU, position control x{decimation} substeps + fused post_physics_step")
+
+
 def _peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(path):
@@ -256,10 +262,7 @@ def run_ours(args):
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 6), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"Go1 rough terrain, 187-point height scan, full reward set (20 terms + "
-                                   f"termination), terrain curriculum, {N} envs/GPU, position control x"
-                                   f"{env.cfg.control.decimation} substeps + fused post_physics_step",
-                       "envs_per_gpu": N, "envs_total": N * world, "num_obs": env.num_obs,
+            "config": {"workload": workload_name(N, env.cfg.control.decimation), "envs_per_gpu": N, "envs_total": N * world, "num_obs": env.num_obs,
                        "reward_terms": env._num_sum_rows, "rng": "in-kernel Philox4x32-10",
                        "l2": f"inputs cycle through {NUM_FRAMES} state frames resident in HBM "
                              f"({NUM_FRAMES * N * 448 / 1e6:.0f} MB) -- larger than L2 at the default size",
@@ -393,8 +396,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cpu["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"Go1 rough terrain, 187-point height scan, full reward set, {args.envs} envs/GPU "
-                                   f"(CPU sample of {n_sample} envs per step)", "envs_per_gpu": args.envs},
+            "config": {"workload": workload_name(args.envs), "envs_per_gpu": args.envs,
+                       "cpu_sample_envs_per_step": n_sample, "num_obs": 235, "reward_terms": 21},
             "cpu_baseline": cpu, "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
                                          "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": round(time.perf_counter() - t0, 1)}

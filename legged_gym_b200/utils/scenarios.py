@@ -53,6 +53,24 @@ def anymal_c_flat(cfg):
     """ANYmal C as shipped (plane, blind, 48 obs) with the LSTM actuator net."""
 
 
+def anymal_c_rough(cfg):
+    """ANYmal C rough as shipped: trimesh terrain, 187-point scan, terrain curriculum, LSTM actuator net."""
+
+
+def a1_variant(cfg):
+    """A1 with the switches the other scenarios leave at their defaults flipped: heightfield terrain without
+    curriculum (randomised sub-terrains, custom origins), yaw-rate instead of heading commands, no
+    observation noise, no pushes, negative total rewards kept."""
+    cfg.terrain.mesh_type = 'heightfield'
+    cfg.terrain.curriculum = False
+    cfg.terrain.measure_heights = True
+    cfg.env.num_observations = 235
+    cfg.commands.heading_command = False
+    cfg.noise.add_noise = False
+    cfg.domain_rand.push_robots = False
+    cfg.rewards.only_positive_rewards = False
+
+
 SCENARIOS = {
     "go1_flat": ("go1", go1_flat),
     "go1_rough_full": ("go1", go1_rough_full),
@@ -60,6 +78,8 @@ SCENARIOS = {
     "go1_rough_actuator": ("go1", go1_rough_actuator),
     "cassie_flat": ("cassie", cassie_flat),
     "anymal_c_flat": ("anymal_c_flat", anymal_c_flat),
+    "anymal_c_rough": ("anymal_c_rough", anymal_c_rough),
+    "a1_variant": ("a1", a1_variant),
 }
 
 
