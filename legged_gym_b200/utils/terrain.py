@@ -29,7 +29,10 @@ class Terrain:
         self.tot_cols = int(cfg.num_cols * self.width_per_env_pixels) + 2 * self.border
         self.tot_rows = int(cfg.num_rows * self.length_per_env_pixels) + 2 * self.border
         self.height_field_raw = np.zeros((self.tot_rows, self.tot_cols), dtype=np.int16)
-        if cfg.curriculum:
+        terrain_file = getattr(cfg, "terrain_file", None)
+        if terrain_file:
+            self._load(terrain_file)
+        elif cfg.curriculum:
             self.curiculum()
         elif cfg.selected:
             self.selected_terrain()
@@ -39,6 +42,34 @@ class Terrain:
         if self.type == "trimesh":
             self.vertices, self.triangles = terrain_utils.convert_heightfield_to_trimesh(
                 self.height_field_raw, cfg.horizontal_scale, cfg.vertical_scale, cfg.slope_treshold)
+
+    # ---- on-disk format: the hot path only needs the int16 field, the sub-terrain
+    # origins and the three scales, so a generated (or externally authored) terrain can be reused across runs
+    # and ranks instead of being regenerated from the numpy stream: one .npz, fields named as below
+    FILE_VERSION = 1
+
+    def save(self, path):
+        c = self.cfg
+        np.savez_compressed(path, version=np.array(self.FILE_VERSION), height_field_raw=self.height_field_raw,
+                            env_origins=self.env_origins, horizontal_scale=np.array(c.horizontal_scale),
+                            vertical_scale=np.array(c.vertical_scale), border_size=np.array(c.border_size),
+                            terrain_length=np.array(c.terrain_length), terrain_width=np.array(c.terrain_width),
+                            num_rows=np.array(c.num_rows), num_cols=np.array(c.num_cols))
+
+    def _load(self, path):
+        d = np.load(path)
+        c = self.cfg
+        if int(d["version"]) != self.FILE_VERSION:
+            raise ValueError(f"{path}: terrain file version {int(d['version'])} != {self.FILE_VERSION}")
+        for k in ("horizontal_scale", "vertical_scale", "border_size", "terrain_length", "terrain_width", "num_rows",
+                  "num_cols"):
+            if float(d[k]) != float(getattr(c, k)):
+                raise ValueError(f"{path}: {k}={float(d[k])} does not match cfg.terrain.{k}={getattr(c, k)}")
+        hf = d["height_field_raw"]
+        if hf.dtype != np.int16 or hf.shape != (self.tot_rows, self.tot_cols):
+            raise ValueError(f"{path}: height field {hf.dtype}{hf.shape}, expected int16{(self.tot_rows, self.tot_cols)}")
+        self.height_field_raw = hf.copy()
+        self.env_origins = d["env_origins"].astype(np.float64).copy()
 
     # difficulty grows with the row (level), the type changes with the column
     def curiculum(self):

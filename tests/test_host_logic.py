@@ -160,3 +160,22 @@ def test_env_state_checkpoint_roundtrip(scenario, tmp_path):
         assert torch.equal(got[n], want[n]), n
     with pytest.raises(ValueError, match="num_envs"):
         helpers.make_env(scenario, 8).load_state_dict(sd)
+
+
+def test_terrain_file_roundtrip(tmp_path):
+    """SURVEY 8(f) rank 3 (format half): a generated terrain saved to disk and loaded through
+    cfg.terrain.terrain_file gives the same height field, origins and env placement without touching numpy's RNG."""
+    a = helpers.make_env("go1_rough_full", 16, seed=3)
+    path = str(tmp_path / "terrain.npz")
+    a.terrain.save(path)
+
+    def from_file(cfg):
+        cfg.terrain.terrain_file = path
+    b = helpers.make_env("go1_rough_full", 16, seed=4, extra=from_file)   # another numpy stream: the field comes from the file
+    assert torch.equal(a.height_samples, b.height_samples) and torch.equal(a.terrain_origins, b.terrain_origins)
+
+    def wrong_scale(cfg):
+        cfg.terrain.terrain_file = path
+        cfg.terrain.vertical_scale = 0.01
+    with pytest.raises(ValueError, match="vertical_scale"):
+        helpers.make_env("go1_rough_full", 16, extra=wrong_scale)

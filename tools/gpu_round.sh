@@ -23,4 +23,11 @@ echo "ncu launches rc=$?"
 $CMD > $OUT/plain2_$TAG.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:lgk_step_kernel -s 12 -c 2 -o $OUT/prof_step_$TAG $CMD > $OUT/ncu_full_$TAG.log 2>&1
 echo "ncu full rc=$?"
+
+# ANYmal LSTM actuator kernel: timing + one full capture; the reference's op-by-op path on CUDA torch
+python tools/bench_lstm.py 4096 16384 65536 > $OUT/bench_lstm_$TAG.json 2> $OUT/bench_lstm_$TAG.err && \
+ncu --set full --clock-control none --import-source on -k regex:lgk_lstm_kernel -s 6 -c 1 -o $OUT/prof_lstm_$TAG python tools/bench_lstm.py 65536 > $OUT/ncu_lstm_$TAG.log 2>&1
+echo "ncu lstm rc=$?"
+python tests/bench_torch_cuda_reference.py 4096 65536 > $OUT/torch_cuda_reference_$TAG.json 2> $OUT/torch_cuda_reference_$TAG.err
+echo "torch cuda reference rc=$?"; cat $OUT/torch_cuda_reference_$TAG.json
 ls -la $OUT
