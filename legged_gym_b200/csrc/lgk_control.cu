@@ -320,6 +320,9 @@ lgk_act_mlp_kernel(int rows_total, const float* __restrict__ model_ins, const fl
   }
 }
 
+extern "C" int lgk_act_mlp_tc_impl(int rows, const float* model_ins, const float* weights, const float* norm,
+                                   float* dvel, cudaStream_t st);
+
 extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
                                          float* v_hist, float* model_ins, const float* weights, const float* norm,
                                          float* dvel, cudaStream_t st) {
@@ -327,6 +330,10 @@ extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const floa
   lgk_act_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int rows = N * ACT_LEGS;
+  // default: the 3xTF32 tensor-pipe kernel (lgk_mlp_tc.cu); LGK_MLP_FFMA=1 keeps the fp32 FFMA kernel below
+  const char* e = getenv("LGK_MLP_FFMA");      // read per call (cheap) so that a process can time / test both
+  const bool ffma = e && e[0] == '1';
+  if (!ffma) return lgk_act_mlp_tc_impl(rows, model_ins, weights, norm, dvel, st);
   const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);

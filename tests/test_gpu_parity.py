@@ -160,8 +160,12 @@ def test_clip_actions_and_poses(n):
     helpers.assert_close("target_poses", env._compute_poses(out), lo.compute_poses(p, out.cpu()))
 
 
-def test_actuator_net_matches_oracle_over_substeps():
+@pytest.mark.parametrize("kernel", ["tensor", "ffma"])
+def test_actuator_net_matches_oracle_over_substeps(kernel, monkeypatch):
+    """Both MLP kernels: 3xTF32 on the tensor pipe (default; floor of a few fp32 roundings of the output layer's
+    operands, helpers.actuator_dvel_atol) and fp32 FFMA (LGK_MLP_FFMA=1; plain 1e-5 + 1e-6)."""
     from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
+    monkeypatch.setenv("LGK_MLP_FFMA", "1" if kernel == "ffma" else "0")
     from oracle import legged_oracle as lo
     n = 1000
     env = helpers.make_env("go1_rough_actuator", n, device=DEV)
@@ -172,7 +176,10 @@ def test_actuator_net_matches_oracle_over_substeps():
         a = fr["actions"]
         got = env.actuator_advance(a)
         want = act.advance(a.cpu(), env.dof_pos.cpu(), env.dof_vel.cpu())
-        helpers.assert_close(f"dVel[{it}]", got, want)
+        if kernel == "ffma":
+            helpers.assert_close(f"dVel[{it}]", got, want)
+        else:
+            helpers.assert_close_abs(f"dVel[{it}]", got, want, helpers.actuator_dvel_atol(random_mlp_state_dict(0)))
         helpers.assert_close(f"model_ins[{it}]", env.model_ins, act.model_ins)
         assert torch.equal(env.pos_err_buffs.cpu().double(), torch.from_numpy(act.pos_err_buffs)) or \
             torch.allclose(env.pos_err_buffs.cpu().double(), torch.from_numpy(act.pos_err_buffs), rtol=1e-6, atol=1e-7)
