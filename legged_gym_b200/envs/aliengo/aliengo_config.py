@@ -1,6 +1,6 @@
 """Unitree Aliengo task config (values: reference ``envs/aliengo/aliengo_config.py``)."""
 from legged_gym_b200.envs.base.legged_robot_config import LeggedRobotCfg, LeggedRobotCfgPPO
-from legged_gym_b200.envs._unitree import joint_angles
+from legged_gym_b200.envs._unitree import joint_angles, ppo_cfg, unitree_asset
 
 
 class AliengoRoughCfg(LeggedRobotCfg):
@@ -24,13 +24,7 @@ class AliengoRoughCfg(LeggedRobotCfg):
         use_actuator_network = True
         actuator_net_file = "{LEGGED_GYM_ROOT_DIR}/resources/actuator_nets/go1_net.pt"
 
-    class asset(LeggedRobotCfg.asset):
-        file = '{LEGGED_GYM_ROOT_DIR}/resources/robots/aliengo/urdf/aliengo.urdf'
-        name = "aliengo"
-        foot_name = "foot"
-        penalize_contacts_on = ["thigh", "calf"]
-        terminate_after_contacts_on = ["base"]
-        self_collisions = 1
+    asset = unitree_asset(LeggedRobotCfg.asset, "aliengo")
 
     class domain_rand(LeggedRobotCfg.domain_rand):
         randomize_base_mass = True
@@ -47,10 +41,4 @@ class AliengoRoughCfg(LeggedRobotCfg):
             dof_pos_limits = -10.0
 
 
-class AliengoRoughCfgPPO(LeggedRobotCfgPPO):
-    class algorithm(LeggedRobotCfgPPO.algorithm):
-        entropy_coef = 0.01
-
-    class runner(LeggedRobotCfgPPO.runner):
-        run_name = ''
-        experiment_name = 'rough_aliengo'
+AliengoRoughCfgPPO = ppo_cfg(LeggedRobotCfgPPO, 'rough_aliengo')

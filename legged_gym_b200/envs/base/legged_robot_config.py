@@ -7,6 +7,13 @@ instance of this class at env construction.
 """
 from .base_config import BaseConfig
 
+
+
+def _ns(name, **attrs):
+    """A plain nested config class from a keyword table (subclassable like a hand-written one)."""
+    return type(name, (), attrs)
+
+
 _SCAN_X = [round(0.1 * i, 1) for i in range(-8, 9)]   # 17 samples, -0.8 .. 0.8 m
 _SCAN_Y = [round(0.1 * i, 1) for i in range(-5, 6)]   # 11 samples, -0.5 .. 0.5 m
 
@@ -150,64 +157,25 @@ class LeggedRobotCfg(BaseConfig):
             gravity = 0.05
             height_measurements = 0.1
 
-    class viewer:
-        ref_env = 0
-        pos = [10, 0, 6]
-        lookat = [11., 5, 3.]
-
-    class sim:
-        dt = 0.005
-        substeps = 1
-        gravity = [0., 0., -9.81]
-        up_axis = 1
-
-        class physx:
-            num_threads = 10
-            solver_type = 1
-            num_position_iterations = 4
-            num_velocity_iterations = 0
-            contact_offset = 0.01
-            rest_offset = 0.0
-            bounce_threshold_velocity = 0.5
-            max_depenetration_velocity = 1.0
-            max_gpu_contact_pairs = 2 ** 23
-            default_buffer_size_multiplier = 5
-            contact_collection = 2
+    # viewer / simulator parameters are handed through to the simulator untouched; built from keyword tables
+    viewer = _ns("viewer", ref_env=0, pos=[10, 0, 6], lookat=[11., 5, 3.])
+    sim = _ns("sim", dt=0.005, substeps=1, gravity=[0., 0., -9.81], up_axis=1,
+              physx=_ns("physx", num_threads=10, solver_type=1, num_position_iterations=4, num_velocity_iterations=0,
+                        contact_offset=0.01, rest_offset=0.0, bounce_threshold_velocity=0.5,
+                        max_depenetration_velocity=1.0, max_gpu_contact_pairs=2 ** 23,
+                        default_buffer_size_multiplier=5, contact_collection=2))
 
 
 class LeggedRobotCfgPPO(BaseConfig):
+    """rsl_rl's hyper-parameters: not read by anything on this path, kept because task registration
+    (``task_registry.register(name, task_class, env_cfg, train_cfg)``) carries them to the runner."""
     seed = 1
     runner_class_name = 'OnPolicyRunner'
-
-    class policy:
-        init_noise_std = 1.0
-        actor_hidden_dims = [512, 256, 128]
-        critic_hidden_dims = [512, 256, 128]
-        activation = 'elu'
-
-    class algorithm:
-        value_loss_coef = 1.0
-        use_clipped_value_loss = True
-        clip_param = 0.2
-        entropy_coef = 0.01
-        num_learning_epochs = 5
-        num_mini_batches = 4
-        learning_rate = 6.e-4
-        schedule = 'adaptive'
-        gamma = 0.99
-        lam = 0.95
-        desired_kl = 0.01
-        max_grad_norm = 1.
-
-    class runner:
-        policy_class_name = 'ActorCritic'
-        algorithm_class_name = 'PPO'
-        num_steps_per_env = 24
-        max_iterations = 800
-        save_interval = 50
-        experiment_name = 'test'
-        run_name = ''
-        resume = False
-        load_run = 'Dec21_16-36-59_'
-        checkpoint = -1
-        resume_path = None
+    policy = _ns("policy", init_noise_std=1.0, actor_hidden_dims=[512, 256, 128], critic_hidden_dims=[512, 256, 128],
+                 activation='elu')
+    algorithm = _ns("algorithm", value_loss_coef=1.0, use_clipped_value_loss=True, clip_param=0.2, entropy_coef=0.01,
+                    num_learning_epochs=5, num_mini_batches=4, learning_rate=6.e-4, schedule='adaptive', gamma=0.99,
+                    lam=0.95, desired_kl=0.01, max_grad_norm=1.)
+    runner = _ns("runner", policy_class_name='ActorCritic', algorithm_class_name='PPO', num_steps_per_env=24,
+                 max_iterations=800, save_interval=50, experiment_name='test', run_name='', resume=False,
+                 load_run='Dec21_16-36-59_', checkpoint=-1, resume_path=None)

@@ -4,7 +4,7 @@ As shipped the task is flat and blind (48 observations); rough terrain with the 
 is obtained by switching ``terrain.mesh_type`` / ``measure_heights`` (see utils/scenarios.py).
 """
 from legged_gym_b200.envs.base.legged_robot_config import LeggedRobotCfg, LeggedRobotCfgPPO
-from legged_gym_b200.envs._unitree import joint_angles
+from legged_gym_b200.envs._unitree import joint_angles, ppo_cfg, unitree_asset
 
 
 class Go1RoughCfg(LeggedRobotCfg):
@@ -28,13 +28,7 @@ class Go1RoughCfg(LeggedRobotCfg):
         use_actuator_network = True
         actuator_net_file = "{LEGGED_GYM_ROOT_DIR}/resources/actuator_nets/go1_net.pt"
 
-    class asset(LeggedRobotCfg.asset):
-        file = '{LEGGED_GYM_ROOT_DIR}/resources/robots/go1/urdf/go1.urdf'
-        name = "go1"
-        foot_name = "foot"
-        penalize_contacts_on = ["thigh", "calf"]
-        terminate_after_contacts_on = ["base"]
-        self_collisions = 1
+    asset = unitree_asset(LeggedRobotCfg.asset, "go1")
 
     class domain_rand(LeggedRobotCfg.domain_rand):
         randomize_base_mass = True
@@ -51,10 +45,4 @@ class Go1RoughCfg(LeggedRobotCfg):
             dof_pos_limits = -10.0
 
 
-class Go1RoughCfgPPO(LeggedRobotCfgPPO):
-    class algorithm(LeggedRobotCfgPPO.algorithm):
-        entropy_coef = 0.01
-
-    class runner(LeggedRobotCfgPPO.runner):
-        run_name = ''
-        experiment_name = 'rough_go1'
+Go1RoughCfgPPO = ppo_cfg(LeggedRobotCfgPPO, 'rough_go1')
