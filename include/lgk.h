@@ -220,7 +220,10 @@ typedef struct LgkBuffers {
   const float* height_points_xy;   /* [H,2] body-frame scan offsets (:802-816)             */
   const float* noise_scale_vec;    /* [O]                                                  */
   const float* terrain_origins;    /* [num_rows, num_cols, 3]                              */
-  float*       command_ranges;     /* [8] lin_vel_x lo/hi, lin_vel_y, ang_vel_yaw, heading */
+  float*       command_ranges;     /* [16] two sets of (lower, upper - lower) for lin_vel_x, lin_vel_y,
+                                      ang_vel_yaw, heading: [0,8) for the callback's resample (:342), [8,16)
+                                      for reset_idx's (:173).  They differ only on the step on which the
+                                      command curriculum widens the range inside reset_idx (:166-173) */
   /* random taps (rng_mode == LGK_RNG_TAPS), uniform [0,1), one row per env */
   const float* tap_cmd_callback;   /* [N,3]                                                */
   const float* tap_cmd_reset;      /* [N,3]                                                */

@@ -94,7 +94,7 @@ lgk_reset_kernel(const __grid_constant__ ResetArgs a) {
     float c0, c1, c2;
     if (taps) { const float* t = b.tap_cmd_reset + (size_t)env * 3; c0 = t[0]; c1 = t[1]; c2 = t[2]; }
     else { const uint4 r = lgk_philox(c.seed, csc, eg, SITE + LGK_SITE_CMD_RESET); c0 = u01(r.x); c1 = u01(r.y); c2 = u01(r.z); }
-    const float* cr = b.command_ranges;
+    const float* cr = b.command_ranges + 8;   // reset_idx's ranges
     cmd.x = rand_affine(cr[1], cr[0], c0);
     cmd.y = rand_affine(cr[3], cr[2], c1);
     if (flags & LGK_F_HEADING_COMMAND) cmd.w = rand_affine(cr[7], cr[6], c2);

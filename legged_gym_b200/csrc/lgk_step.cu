@@ -263,7 +263,7 @@ static __device__ __noinline__ void reset_root(const StepArgs& a, unsigned long 
   float c0, c1, c2;
   if (TAPS) { const float* t = b.tap_cmd_reset + (size_t)env * 3; c0 = t[0]; c1 = t[1]; c2 = t[2]; }
   else { const uint4 r = philox_cold(a, csc, env_global, LGK_SITE_CMD_RESET); c0 = u01(r.x); c1 = u01(r.y); c2 = u01(r.z); }
-  resample_command(o.cmd, b.command_ranges, flags & LGK_F_HEADING_COMMAND, c0, c1, c2);
+  resample_command(o.cmd, b.command_ranges + 8, flags & LGK_F_HEADING_COMMAND, c0, c1, c2);   // reset_idx's ranges
 }
 
 // generic (non-bulk) tile load / store for ragged or unaligned tiles

@@ -50,6 +50,8 @@ class LeggedRobot(BaseTask):
         self._prepare_reward_function()
         self._check_hooks()
         self._lib = None
+        self._ranges_cache = None
+        self._ranges_split = False
         self._consts = None
         self._bufs = None
         self.init_done = True
@@ -102,12 +104,14 @@ class LeggedRobot(BaseTask):
         self._sync_host_scalars()
         self._ensure_dev_counter(self.common_step_counter - 1)
         if self.cfg.commands.curriculum and (self.common_step_counter % self.max_episode_length == 0):
-            self._command_curriculum_prepass()
+            self._command_curriculum_prepass(lib)
         if self._external_terms:
             self._evaluate_external_terms(lib)
         _lgk.check("lgk_post_physics_step", lib.lgk_post_physics_step(
             C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
         self._consts.flags &= ~_lgk.F_EP_INCREMENTED
+        if self._ranges_split:
+            self._sync_host_scalars()          # both halves equal again from the next step on
         self._dev_step_counter = self.common_step_counter
         self._after_step_sim_writes()
 
@@ -120,9 +124,7 @@ class LeggedRobot(BaseTask):
         LGK_REW_EXTERNAL row: scaled, summed in the term's alphabetical slot, accumulated in episode_sums.
         Not reproduced for such terms: feet_air_time as advanced by a built-in term earlier in the order,
         and the pushed root velocities on push steps (both are updated by the fused kernel afterwards)."""
-        _lgk.check("lgk_pre_reward_state", lib.lgk_pre_reward_state(
-            C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
-        self._consts.flags |= _lgk.F_EP_INCREMENTED
+        self._ensure_pre_reward_state(lib)
         i = 0
         for name, fn in zip(self.reward_names, self.reward_functions):
             if fn is not None:
@@ -185,18 +187,39 @@ class LeggedRobot(BaseTask):
             r[0] = np.clip(r[0] - 0.5, -self.cfg.commands.max_curriculum, 0.)
             r[1] = np.clip(r[1] + 0.5, 0., self.cfg.commands.max_curriculum)
 
-    def _command_curriculum_prepass(self):
-        """The reference updates command_ranges inside reset_idx, *before* the reset envs resample
-        (:166-173); the fused kernel cannot stop mid-launch for a host decision, so on the one step in
-        max_episode_length where the gate is open the reset set is formed here first."""
-        cf = self.contact_forces[:, self.termination_contact_indices, :]
-        reset = torch.any(torch.norm(cf, dim=-1) > 1., dim=1) | (self.episode_length_buf + 1 > self.max_episode_length)
-        env_ids = reset.nonzero(as_tuple=False).flatten()
-        if len(env_ids) > 0:
-            # episode sums do not yet hold this step's reward; the reference's do. The gate is a
-            # threshold on a 1000-step mean, so one step's term moves it by <= 0.1 %.
-            self.update_command_curriculum(env_ids)
-            self._sync_host_scalars()
+    def _ensure_pre_reward_state(self, lib):
+        """Launch lgk_pre_reward_state once per step (python reward terms and the command curriculum's
+        gated step both need the compute_reward-time state before the fused launch)."""
+        if not (self._consts.flags & _lgk.F_EP_INCREMENTED):
+            _lgk.check("lgk_pre_reward_state", lib.lgk_pre_reward_state(
+                C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
+            self._consts.flags |= _lgk.F_EP_INCREMENTED
+
+    def _command_curriculum_prepass(self, lib):
+        """The reference updates command_ranges inside reset_idx -- after compute_reward, before the reset
+        envs resample (:166-173) -- from the episode sums that already include this step's reward.  The
+        fused kernel cannot stop mid-launch for a host decision, so on the one step in max_episode_length
+        where the gate is open the decision is formed here first, from the same quantities: the reset set
+        and the post-callback commands / body-frame velocity that lgk_pre_reward_state leaves, and this
+        step's tracking_lin_vel term added to the sums with the reference's own operations (:918-921, :207)."""
+        self._ensure_pre_reward_state(lib)
+        env_ids = self.reset_buf.nonzero(as_tuple=False).flatten()
+        if len(env_ids) == 0:
+            return
+        sums = self.episode_sums["tracking_lin_vel"]          # KeyError without the term, like the reference (:472)
+        row = self.reward_names.index("tracking_lin_vel")
+        fn = self.reward_functions[row]
+        if fn is not None:
+            rew = fn()
+        else:
+            lin_vel_error = torch.sum(torch.square(self.commands[:, :2] - self.base_lin_vel[:, :2]), dim=1)
+            rew = torch.exp(-lin_vel_error / self.cfg.rewards.tracking_sigma)
+        sums = sums + rew * self.reward_scales["tracking_lin_vel"]
+        if torch.mean(sums[env_ids]) / self.max_episode_length > 0.8 * self.reward_scales["tracking_lin_vel"]:
+            r = self.command_ranges["lin_vel_x"]
+            r[0] = np.clip(r[0] - 0.5, -self.cfg.commands.max_curriculum, 0.)
+            r[1] = np.clip(r[1] + 0.5, 0., self.cfg.commands.max_curriculum)
+            self._sync_host_scalars(reset_half_only=True)   # the callback's resample still sees the old range
 
     def _after_step_sim_writes(self):
         """Hand the state the kernel rewrote back to the simulator (:411,432,441)."""
@@ -629,6 +652,7 @@ class LeggedRobot(BaseTask):
         self._build_terrain_tables()
         self._bufs = self.build_buffers()
         self._ranges_cache = None
+        self._ranges_split = False
         self._sync_host_scalars()
         self._ensure_dev_counter(self.common_step_counter)
 
@@ -745,7 +769,7 @@ class LeggedRobot(BaseTask):
         if not hasattr(self, "_workspace"):
             nbytes = self._lib.lgk_workspace_bytes(N, self._num_sum_rows)
             self._workspace = torch.zeros((nbytes + 15) // 16 * 2, dtype=torch.int64, device=self.device)
-            self._command_ranges_dev = torch.zeros(8, dtype=torch.float, device=self.device)
+            self._command_ranges_dev = torch.zeros(16, dtype=torch.float, device=self.device)
         for name in ("root_states", "dof_state", "contact_forces", "torques", "actions", "last_actions",
                      "last_dof_vel", "last_root_vel", "commands", "feet_air_time", "env_origins", "obs_buf",
                      "rew_buf", "reset_buf", "time_out_buf", "base_lin_vel", "base_ang_vel", "projected_gravity",
@@ -893,16 +917,22 @@ class LeggedRobot(BaseTask):
                 _lgk.ptr(self._workspace), int(want), _lgk.current_stream(self.device)))
             self._dev_step_counter = want
 
-    def _sync_host_scalars(self):
+    def _sync_host_scalars(self, reset_half_only: bool = False):
         """Mirror host-side scalars the kernels read from device memory: command_ranges (a mutable
-        dict in the reference, :473-474) and common_step_counter."""
+        dict in the reference, :473-474) and common_step_counter.  The device copy holds the ranges twice:
+        for the callback's resample and for reset_idx's; `reset_half_only` updates the latter alone (the
+        command curriculum changes the dict between the two on its gated step)."""
         cr = self.command_ranges
         key = tuple(float(v) for k in ("lin_vel_x", "lin_vel_y", "ang_vel_yaw", "heading") for v in cr[k])
-        if key != self._ranges_cache:
+        if key != self._ranges_cache or (self._ranges_split and not reset_half_only):
             vals = []
             for lo, hi in zip(key[0::2], key[1::2]):
                 vals += [lo, hi - lo]         # (lower, upper - lower) as torch_rand_float forms them
-            self._command_ranges_dev.copy_(torch.tensor(vals, dtype=torch.float))
+            t = torch.tensor(vals, dtype=torch.float)
+            self._command_ranges_dev[8:].copy_(t)
+            if not reset_half_only:
+                self._command_ranges_dev[:8].copy_(t)
+            self._ranges_split = reset_half_only
             self._ranges_cache = key
         flag = _lgk.F_INIT_DONE if self.init_done else 0
         self._consts.flags = (self._consts.flags & ~_lgk.F_INIT_DONE) | flag

@@ -255,6 +255,47 @@ def test_python_reward_terms_of_a_subclass_enter_the_fused_kernel():
     assert n > 0
 
 
+@pytest.mark.parametrize("sums", [30.0, 15.9992, 15.99995, 3.0])
+def test_command_curriculum_widens_the_range_on_the_gated_step(sums):
+    """update_command_curriculum (:465-474): on the one step in max_episode_length where the gate is open, good
+    velocity tracking of the reset envs widens lin_vel_x by 0.5 BEFORE those envs resample their commands (and
+    after the callback's resample, which still uses the old range).  The gate compares the mean episode sum
+    INCLUDING this step's reward with 0.8 * scale * max_episode_length = 16: the values next to 16 make the
+    decision hinge on that last term."""
+    from oracle import legged_oracle as lo
+
+    def curriculum(cfg):
+        cfg.commands.curriculum = True
+        cfg.commands.max_curriculum = 2.0          # the shipped 1.0 equals the initial range: nothing could widen
+    env = helpers.make_env("go1_rough_full", 300, device=DEV, seed=6, extra=curriculum)
+    helpers.randomise_env_state(env, 6)
+    env.common_step_counter = int(env.max_episode_length) - 1          # this step: counter % max_episode_length == 0
+    env.episode_sums["tracking_lin_vel"][:] = sums                     # gate: mean / 1000 > 0.8 * scale (= 0.016)
+    env.episode_length_buf[:24] = int(env.max_episode_length)          # 24 time-outs
+    frames = synthetic.make_frames(env, 2, seed=41)
+    synthetic.load_frame(env, frames[0])
+    p = lo.OracleParams.from_env(env, device="cpu")
+    s = lo.OracleState.from_env(env, p, device="cpu")
+    assert p.command_ranges["lin_vel_x"] == [-1.0, 1.0]
+    for it, fr in enumerate(frames):
+        taps = synthetic.make_taps(env, seed=600 + it)
+        synthetic.load_frame(env, fr)
+        env.use_rng_taps(taps, index_math=_lgk.INDEX_MATH_TORCH_CPU)
+        env.step(fr["actions"].clone())
+        torch.cuda.synchronize()
+        s.root_states.copy_(fr["root_states"].cpu()); s.dof_state.copy_(fr["dof_state"].cpu())
+        s.contact_forces.copy_(fr["contact_forces"].cpu().view_as(s.contact_forces)); s.torques.copy_(fr["torques"].cpu())
+        lo.step(p, s, fr["actions"].cpu().clone(), {k: v.cpu() for k, v in taps.items()})
+        helpers.compare_env_to_oracle(env, s, tag=f"[command curriculum step {it}] ")
+        got = [float(v) for v in env.command_ranges["lin_vel_x"]]
+        assert got == [float(v) for v in p.command_ranges["lin_vel_x"]]
+        if sums >= 30.0:
+            assert got == [-1.5, 1.5]
+        if sums <= 3.0:
+            assert got == [-1.0, 1.0]
+        assert float(env.extras["episode"]["max_command_x"]) == got[1]
+
+
 def test_outputs_written_straight_into_rollout_storage():
     """with the env's output pointers moved into [T,N,O] storage the kernel's stores are
     the only pass; the storage must equal what a plain env returns step by step (same seed, in-kernel RNG)."""
