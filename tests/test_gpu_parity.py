@@ -37,6 +37,36 @@ def test_step_matches_oracle(name, oracle_device):
     assert n > 0
 
 
+def test_blind_flat_task_with_every_reward_term():
+    """Flat, blind Go1 (no height scan: measured_heights stays the python int 0, legged_robot.py:553) with all 20
+    terms + termination: base_height then reduces to (root_z - target)^2 (:869-872)."""
+    def full(cfg):
+        for k, v in scenarios.FULL_REWARD_EXTRA.items():
+            setattr(cfg.rewards.scales, k, v)
+    assert helpers.run_parity("go1_flat", 515, 5, extra=full) > 0
+    assert helpers.run_parity("go1_flat", 515, 3, extra=full, oracle_device="cuda:0") > 0
+
+
+def test_cassie_on_rough_terrain_scans_121_points():
+    """Cassie as shipped sits on a plane (121 zero heights); on a trimesh the 4-pass scan instantiation reads real
+    terrain, with two feet, the pelvis termination bodies and the terrain curriculum."""
+    def rough(cfg):
+        cfg.terrain.mesh_type = 'trimesh'
+        cfg.terrain.curriculum = True
+    assert helpers.run_parity("cassie_flat", 300, 4, extra=rough) > 0
+
+
+def test_generic_scan_width_256_points():
+    """A scan grid no shipped task uses (16 x 16 = 256 points, 304 observations): runs on the generic (not
+    specialised) instantiation of the step kernel with 8 passes."""
+    def wide(cfg):
+        scenarios.go1_rough_full(cfg)
+        cfg.terrain.measured_points_x = [round(-0.75 + 0.1 * i, 2) for i in range(16)]
+        cfg.terrain.measured_points_y = [round(-0.75 + 0.1 * i, 2) for i in range(16)]
+        cfg.env.num_observations = 48 + 256
+    assert helpers.run_parity("go1_flat", 200, 3, extra=wide) > 0
+
+
 @pytest.mark.parametrize("num_envs", [1, 3, 33, 127, 1800])
 def test_ragged_env_counts(num_envs):
     """env counts that are not multiples of the warp / CTA tile (config 1 uses 1800)."""
