@@ -107,8 +107,11 @@ enum {                                   /* LgkConsts.flags                     
   LGK_F_ONLY_POSITIVE     = 1u << 7,     /* cfg.rewards.only_positive_rewards              */
   LGK_F_HAS_TERMINATION   = 1u << 8,     /* 'termination' scale is non-zero (:209-212)     */
   LGK_F_INIT_DONE         = 1u << 9,     /* self.init_done (curriculum skipped before)     */
-  LGK_F_EP_INCREMENTED    = 1u << 10     /* episode_length_buf already counts this step
+  LGK_F_EP_INCREMENTED    = 1u << 10,    /* episode_length_buf already counts this step
                                             (lgk_pre_reward_state ran): do not add 1 again */
+  LGK_F_RESET_GIVEN       = 1u << 11     /* reset_buf / time_out_buf are INPUTS: a check_termination()
+                                            override (legged_robot.py:143-148) decided after
+                                            lgk_pre_reward_state; the step kernel acts on them as they are */
 };
 
 typedef struct LgkRewardEntry {

@@ -526,8 +526,13 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     // the reset decision (:143-148) is cheap: every stage-1 warp forms it for its own lane
     bool time_out = false, reset = false;
     if (active) {
-      time_out = (ep_in + ep_inc) > c.max_episode_length;
-      reset = term_contact(c, s_idx, cf_row, a.thr_term) || time_out;
+      if (flags & LGK_F_RESET_GIVEN) {   // a python check_termination() override has already decided (cold path)
+        time_out = b.time_out_buf[env] != 0;
+        reset = b.reset_buf[env] != 0;
+      } else {
+        time_out = (ep_in + ep_inc) > c.max_episode_length;
+        reset = term_contact(c, s_idx, cf_row, a.thr_term) || time_out;
+      }
     }
 
     // values W0 keeps in registers from stage 1 to stage 3

@@ -31,7 +31,7 @@ except ImportError:
 
 # hooks whose bodies live inside the fused kernel; a subclass overriding one of them would silently
 # be ignored, so construction fails instead
-_FUSED_HOOKS = ("check_termination", "compute_reward", "compute_observations", "_post_physics_step_callback",
+_FUSED_HOOKS = ("compute_reward", "_post_physics_step_callback",
                 "_resample_commands", "_get_heights", "_push_robots", "_reset_dofs", "_reset_root_states",
                 "_update_terrain_curriculum", "post_physics_step")
 
@@ -49,6 +49,7 @@ class LeggedRobot(BaseTask):
         self._init_buffers()
         self._prepare_reward_function()
         self._check_hooks()
+        self._init_observation_override()
         self._lib = None
         self._ranges_cache = None
         self._ranges_split = False
@@ -103,17 +104,32 @@ class LeggedRobot(BaseTask):
         self.common_step_counter += 1
         self._sync_host_scalars()
         self._ensure_dev_counter(self.common_step_counter - 1)
+        if self._termination_override:
+            # a subclass's check_termination(): the base decision (:143-148) is in reset_buf / time_out_buf after
+            # lgk_pre_reward_state, the override adds its own conditions, the kernel acts on the result
+            self._ensure_pre_reward_state(lib)
+            bound_reset, bound_time_out = self.reset_buf, self.time_out_buf
+            self.check_termination()
+            if self.reset_buf is not bound_reset:           # the override re-bound the attribute (as :146 does)
+                bound_reset.copy_(self.reset_buf.to(bound_reset.dtype).view_as(bound_reset))
+                self.reset_buf = bound_reset
+            if self.time_out_buf is not bound_time_out:
+                bound_time_out.copy_(self.time_out_buf.to(bound_time_out.dtype).view_as(bound_time_out))
+                self.time_out_buf = bound_time_out
+            self._consts.flags |= _lgk.F_RESET_GIVEN
         if self.cfg.commands.curriculum and (self.common_step_counter % self.max_episode_length == 0):
             self._command_curriculum_prepass(lib)
         if self._external_terms:
             self._evaluate_external_terms(lib)
         _lgk.check("lgk_post_physics_step", lib.lgk_post_physics_step(
             C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
-        self._consts.flags &= ~_lgk.F_EP_INCREMENTED
+        self._consts.flags &= ~(_lgk.F_EP_INCREMENTED | _lgk.F_RESET_GIVEN)
         if self._ranges_split:
             self._sync_host_scalars()          # both halves equal again from the next step on
         self._dev_step_counter = self.common_step_counter
         self._after_step_sim_writes()
+        if self._obs_override:
+            self._run_observation_override()
 
     def _evaluate_external_terms(self, lib):
         """Reward terms a subclass defines in Python (`_reward_<name>`, found like the reference does,
@@ -463,6 +479,44 @@ class LeggedRobot(BaseTask):
         else:
             self._ext_rewards = None
 
+    def _init_observation_override(self):
+        """A subclass may override compute_observations() to append its own columns (the usual way tasks
+        derived from the reference add observations: call super(), then torch.cat).  The fused kernel then
+        writes the base observation -- 12 + 3*num_dof (+ height scan) columns, noise and clip included --
+        into a buffer of its own, and the override runs right after the launch, where the reference calls
+        it too (after reset_idx, :133), with self.obs_buf bound to that base observation."""
+        self._obs_override = type(self).compute_observations is not LeggedRobot.compute_observations
+        self._termination_override = type(self).check_termination is not LeggedRobot.check_termination
+        H = self.num_height_points if self.cfg.terrain.measure_heights else 0
+        self._kernel_num_obs = 12 + 3 * self.num_dof + H
+        self._kernel_obs = None
+        if self._obs_override:
+            self._kernel_obs = torch.zeros(self.num_envs, self._kernel_num_obs, dtype=torch.float, device=self.device)
+        elif self._kernel_num_obs != self.num_obs:
+            raise ValueError(
+                f"cfg.env.num_observations={self.num_obs} but the observation of this config has "
+                f"{self._kernel_num_obs} columns (12 + 3*num_dof + height points); override compute_observations() "
+                f"to add columns")
+
+    def check_termination(self):
+        """reset_buf = any termination body in contact | time_out (:143-148) is formed on the device; when a
+        subclass overrides this method, its super().check_termination() finds both buffers already filled
+        (lgk_pre_reward_state) and may OR further conditions into self.reset_buf in place."""
+
+    def compute_observations(self):
+        """The observation (:214-231) -- body-frame velocities, gravity, commands, joint state, actions, the
+        height scan, noise -- is written by the fused step kernel; by the time a subclass override calls
+        super().compute_observations(), self.obs_buf already holds it.  Nothing to do here."""
+
+    def _run_observation_override(self):
+        self.obs_buf = self._kernel_obs
+        self.compute_observations()
+        if self.obs_buf.shape != (self.num_envs, self.num_obs):
+            raise ValueError(f"compute_observations() left obs_buf with shape {tuple(self.obs_buf.shape)}, "
+                             f"cfg.env.num_observations says {self.num_obs}")
+        clip_obs = self.cfg.normalization.clip_observations          # (:103-104)
+        self.obs_buf = torch.clip(self.obs_buf, -clip_obs, clip_obs)
+
     def _check_hooks(self):
         for name in _FUSED_HOOKS:
             if getattr(type(self), name, None) is not getattr(LeggedRobot, name, None):
@@ -668,7 +722,7 @@ class LeggedRobot(BaseTask):
         c.num_envs, c.num_dof, c.num_bodies = self.num_envs, D, self.num_bodies
         c.num_feet, c.num_pen, c.num_term = len(self.feet_indices), len(self.penalised_contact_indices), \
             len(self.termination_contact_indices)
-        c.num_height_points, c.num_obs = H, self.num_obs
+        c.num_height_points, c.num_obs = H, self._kernel_num_obs
         c.num_rewards = len(self.reward_names)
         c.num_commands = cfg.commands.num_commands
         c.env_id_offset = getattr(self, "env_id_offset", 0)
@@ -778,6 +832,8 @@ class LeggedRobot(BaseTask):
             if not t.is_contiguous():
                 raise ValueError(f"{name} must be contiguous")
             setattr(b, name, P(t))
+        if self._obs_override:
+            b.obs_buf = P(self._kernel_obs)
         b.episode_sums = P(self._episode_sums_buf)
         b.episode_length_buf = P(self._episode_length_buf)
         b.terrain_levels = P(getattr(self, "terrain_levels", None))
@@ -844,6 +900,8 @@ class LeggedRobot(BaseTask):
         self._kernels()
         N = self.num_envs
         if obs_buf is not None:
+            if self._obs_override:
+                raise ValueError("obs_buf is produced by this task's compute_observations() override, not by the kernel")
             if obs_buf.dtype != torch.float or obs_buf.numel() != N * self.num_obs or not obs_buf.is_contiguous():
                 raise ValueError(f"obs_buf must be contiguous float32 with {N}x{self.num_obs} elements")
             self.obs_buf = obs_buf.view(N, self.num_obs)

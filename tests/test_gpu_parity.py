@@ -326,6 +326,87 @@ def test_command_curriculum_widens_the_range_on_the_gated_step(sums):
         assert float(env.extras["episode"]["max_command_x"]) == got[1]
 
 
+def test_check_termination_override_adds_a_condition():
+    """A derived task that also terminates on a large tilt (a common customisation of :143-148).  The kernel
+    acts on the mask the override leaves -- resets, the termination reward, episode statistics -- which equals
+    the oracle run with the same extra condition."""
+    from oracle import legged_oracle as lo
+    from legged_gym_b200.envs.go1.go1 import Go1
+
+    class Go1TiltTermination(Go1):
+        def check_termination(self):
+            super().check_termination()
+            self.reset_buf = self.reset_buf | (self.projected_gravity[:, 2] > -0.985)      # re-binds, like :146
+
+    env = helpers.make_env("go1_rough_full", 640, device=DEV, seed=12, task_class=Go1TiltTermination)
+    helpers.randomise_env_state(env, 12)
+    frames = synthetic.make_frames(env, 3, seed=71)
+    synthetic.load_frame(env, frames[0])
+    p = lo.OracleParams.from_env(env, device="cpu")
+    s = lo.OracleState.from_env(env, p, device="cpu")
+    base_check = lo.check_termination
+
+    def tilted(pp, ss):
+        base_check(pp, ss)
+        ss.reset_buf = ss.reset_buf | (ss.projected_gravity[:, 2] > -0.985)
+    lo.check_termination = tilted
+    try:
+        extra_resets = 0
+        for it, fr in enumerate(frames):
+            taps = synthetic.make_taps(env, seed=900 + it)
+            synthetic.load_frame(env, fr)
+            env.use_rng_taps(taps, index_math=_lgk.INDEX_MATH_TORCH_CPU)
+            addr = env.reset_buf.data_ptr()
+            env.step(fr["actions"].clone())
+            torch.cuda.synchronize()
+            assert env.reset_buf.data_ptr() == addr
+            s.root_states.copy_(fr["root_states"].cpu()); s.dof_state.copy_(fr["dof_state"].cpu())
+            s.contact_forces.copy_(fr["contact_forces"].cpu().view_as(s.contact_forces)); s.torques.copy_(fr["torques"].cpu())
+            lo.step(p, s, fr["actions"].cpu().clone(), {k: v.cpu() for k, v in taps.items()})
+            helpers.compare_env_to_oracle(env, s, tag=f"[tilt termination step {it}] ")
+            extra_resets += int((s.reset_buf & ~s.time_out_buf).sum())
+        assert extra_resets > 20       # the tilt condition fires for a good share of the synthetic orientations
+    finally:
+        lo.check_termination = base_check
+
+
+def test_compute_observations_override_appends_columns():
+    """The usual way a derived task adds observations: override compute_observations(), call super(), torch.cat.
+    The override runs after the fused launch with self.obs_buf holding the kernel's (noisy, clipped) base
+    observation; the result is clipped like step() does (:103-104)."""
+    from legged_gym_b200.envs.go1.go1 import Go1
+
+    class Go1ExtraObs(Go1):
+        def compute_observations(self):
+            super().compute_observations()
+            contact = (self.contact_forces[:, self.feet_indices, 2] > 1.).float()
+            phase = (self.episode_length_buf.float() * 300.).unsqueeze(1)        # exceeds clip_observations
+            self.obs_buf = torch.cat((self.obs_buf, contact, phase), dim=-1)
+
+    def wider(cfg):
+        cfg.env.num_observations = 235 + 4 + 1
+    n = 257
+    plain = helpers.make_env("go1_rough_full", n, device=DEV, seed=8)
+    extra = helpers.make_env("go1_rough_full", n, device=DEV, seed=8, extra=wider, task_class=Go1ExtraObs)
+    assert extra.num_obs == 240 and extra.obs_buf.shape == (n, 240)
+    for e in (plain, extra):
+        helpers.randomise_env_state(e, 8)
+    frames = synthetic.make_frames(plain, 3, seed=55)
+    for fr in frames:
+        for e in (plain, extra):
+            synthetic.load_frame(e, fr)
+        o1 = plain.step(fr["actions"].clone())[0]
+        o2, _, r2, d2, _ = extra.step(fr["actions"].clone())
+        torch.cuda.synchronize()
+        assert o2.shape == (n, 240) and extra.get_observations() is o2
+        assert torch.equal(o2[:, :235], o1) and torch.equal(r2, plain.rew_buf) and torch.equal(d2, plain.reset_buf)
+        assert torch.equal(o2[:, 235:239], (extra.contact_forces[:, extra.feet_indices, 2] > 1.).float())
+        want_phase = (extra.episode_length_buf.float() * 300.).clip(max=extra.cfg.normalization.clip_observations)
+        assert torch.equal(o2[:, 239], want_phase) and float(o2[:, 239].max()) == 100.0
+    with pytest.raises(ValueError, match="num_observations"):
+        helpers.make_env("go1_rough_full", 8, device=DEV, extra=wider)      # wider obs without an override
+
+
 def test_outputs_written_straight_into_rollout_storage():
     """with the env's output pointers moved into [T,N,O] storage the kernel's stores are
     the only pass; the storage must equal what a plain env returns step by step (same seed, in-kernel RNG)."""

@@ -112,7 +112,7 @@ def test_there_is_no_cpu_step_path():
 
 def test_fused_hooks_cannot_be_overridden_silently():
     class Bad(LeggedRobot):
-        def check_termination(self):
+        def _resample_commands(self, env_ids):      # runs inside the fused kernel: an override would be ignored
             pass
     cfg = copy.deepcopy(task_registry.env_cfgs["a1"])
     cfg.env.num_envs = 4
@@ -120,7 +120,7 @@ def test_fused_hooks_cannot_be_overridden_silently():
     from legged_gym_b200.utils.helpers import class_to_dict
     sp = gymapi.SimParams()
     gymutil.parse_sim_config(class_to_dict(cfg.sim), sp)
-    with pytest.raises(NotImplementedError, match="check_termination"):
+    with pytest.raises(NotImplementedError, match="_resample_commands"):
         Bad(cfg=cfg, sim_params=sp, physics_engine=gymapi.SIM_PHYSX, sim_device="cpu", headless=True)
 
 
