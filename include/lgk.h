@@ -109,6 +109,9 @@ enum {                                   /* LgkConsts.flags                     
   LGK_F_INIT_DONE         = 1u << 9,     /* self.init_done (curriculum skipped before)     */
   LGK_F_EP_INCREMENTED    = 1u << 10,    /* episode_length_buf already counts this step
                                             (lgk_pre_reward_state ran): do not add 1 again */
+  LGK_F_CALLBACK_GIVEN    = 1u << 12,    /* commands are final: a _post_physics_step_callback() override
+                                            (legged_robot.py:337-352) ran after lgk_pre_reward_state did the
+                                            base resample / heading update; the step kernel does not redo them */
   LGK_F_RESET_GIVEN       = 1u << 11     /* reset_buf / time_out_buf are INPUTS: a check_termination()
                                             override (legged_robot.py:143-148) decided after
                                             lgk_pre_reward_state; the step kernel acts on them as they are */

@@ -47,6 +47,7 @@ F_HAS_TERMINATION = 1 << 8
 F_INIT_DONE = 1 << 9
 F_EP_INCREMENTED = 1 << 10
 F_RESET_GIVEN = 1 << 11
+F_CALLBACK_GIVEN = 1 << 12
 
 STATUS = {0: "LGK_OK", -1: "LGK_ERR_NULL", -2: "LGK_ERR_DIM", -3: "LGK_ERR_CONTROL_TYPE", -4: "LGK_ERR_REWARD",
           -5: "LGK_ERR_ALIGN", -6: "LGK_ERR_VERSION", -7: "LGK_ERR_TERRAIN"}

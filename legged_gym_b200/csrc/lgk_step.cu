@@ -561,7 +561,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         // ---- _post_physics_step_callback (:337-352) -------------------------------------------
         resample_cb = (unsigned long long)ep < 0x80000000ull ? ((int)ep % c.resample_interval) == 0
                                                              : (ep % c.resample_interval) == 0;
-        if (resample_cb) {
+        // LGK_F_CALLBACK_GIVEN: a python _post_physics_step_callback() override ran on the commands that
+        // lgk_pre_reward_state resampled; they are final (the id list still names the resampled envs)
+        const bool cb_given = flags & LGK_F_CALLBACK_GIVEN;
+        if (resample_cb && !cb_given) {
           float u0, u1, u2;
           if (TAPS) {
             const float* t = b.tap_cmd_callback + (size_t)env * 3;
@@ -572,7 +575,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           }
           resample_command(cmd, b.command_ranges, heading_mode, u0, u1, u2);
         }
-        if (heading_mode) {
+        if (heading_mode && !cb_given) {
           float fwd[3];
           quat_apply(q, 1.f, 0.f, 0.f, fwd);
           const float heading = atan2f(fwd[1], fwd[0]);

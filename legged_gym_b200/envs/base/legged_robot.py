@@ -31,7 +31,7 @@ except ImportError:
 
 # hooks whose bodies live inside the fused kernel; a subclass overriding one of them would silently
 # be ignored, so construction fails instead
-_FUSED_HOOKS = ("compute_reward", "_post_physics_step_callback",
+_FUSED_HOOKS = ("compute_reward",
                 "_resample_commands", "_get_heights", "_push_robots", "_reset_dofs", "_reset_root_states",
                 "_update_terrain_curriculum", "post_physics_step")
 
@@ -104,6 +104,17 @@ class LeggedRobot(BaseTask):
         self.common_step_counter += 1
         self._sync_host_scalars()
         self._ensure_dev_counter(self.common_step_counter - 1)
+        if self._callback_override:
+            # a subclass's _post_physics_step_callback(): the base part (:337-349: command resample, heading
+            # command, height scan) is done by lgk_pre_reward_state, the override then works on self.commands /
+            # self.measured_heights in place; the push (:351) stays with the step kernel
+            self._ensure_pre_reward_state(lib)
+            bound = self.commands
+            self._post_physics_step_callback()
+            if self.commands is not bound:
+                bound.copy_(self.commands.view_as(bound))
+                self.commands = bound
+            self._consts.flags |= _lgk.F_CALLBACK_GIVEN
         if self._termination_override:
             # a subclass's check_termination(): the base decision (:143-148) is in reset_buf / time_out_buf after
             # lgk_pre_reward_state, the override adds its own conditions, the kernel acts on the result
@@ -123,7 +134,7 @@ class LeggedRobot(BaseTask):
             self._evaluate_external_terms(lib)
         _lgk.check("lgk_post_physics_step", lib.lgk_post_physics_step(
             C.byref(self._consts), C.byref(self._bufs), _lgk.current_stream(self.device)))
-        self._consts.flags &= ~(_lgk.F_EP_INCREMENTED | _lgk.F_RESET_GIVEN)
+        self._consts.flags &= ~(_lgk.F_EP_INCREMENTED | _lgk.F_RESET_GIVEN | _lgk.F_CALLBACK_GIVEN)
         if self._ranges_split:
             self._sync_host_scalars()          # both halves equal again from the next step on
         self._dev_step_counter = self.common_step_counter
@@ -487,6 +498,8 @@ class LeggedRobot(BaseTask):
         it too (after reset_idx, :133), with self.obs_buf bound to that base observation."""
         self._obs_override = type(self).compute_observations is not LeggedRobot.compute_observations
         self._termination_override = type(self).check_termination is not LeggedRobot.check_termination
+        self._callback_override = (type(self)._post_physics_step_callback
+                                   is not LeggedRobot._post_physics_step_callback)
         H = self.num_height_points if self.cfg.terrain.measure_heights else 0
         self._kernel_num_obs = 12 + 3 * self.num_dof + H
         self._kernel_obs = None
@@ -497,6 +510,11 @@ class LeggedRobot(BaseTask):
                 f"cfg.env.num_observations={self.num_obs} but the observation of this config has "
                 f"{self._kernel_num_obs} columns (12 + 3*num_dof + height points); override compute_observations() "
                 f"to add columns")
+
+    def _post_physics_step_callback(self):
+        """Command resampling, the heading command, the height scan and the pushes (:337-352) happen on the
+        device; a subclass override's super()._post_physics_step_callback() finds commands and measured_heights
+        already updated for this step (lgk_pre_reward_state) and may go on from there."""
 
     def check_termination(self):
         """reset_buf = any termination body in contact | time_out (:143-148) is formed on the device; when a

@@ -326,6 +326,51 @@ def test_command_curriculum_widens_the_range_on_the_gated_step(sums):
         assert float(env.extras["episode"]["max_command_x"]) == got[1]
 
 
+def test_post_physics_step_callback_override_edits_the_commands():
+    """A derived task whose callback post-processes the commands (no turning while nearly standing) and keeps a
+    gait clock: the override sees this step's resampled commands, the kernel uses what it leaves."""
+    from oracle import legged_oracle as lo
+    from legged_gym_b200.envs.go1.go1 import Go1
+
+    class Go1Gait(Go1):
+        def _init_buffers(self):
+            super()._init_buffers()
+            self.gait_clock = torch.zeros(self.num_envs, device=self.device)
+
+        def _post_physics_step_callback(self):
+            super()._post_physics_step_callback()
+            self.commands[:, 2] *= (torch.norm(self.commands[:, :2], dim=1) > 0.5)
+            self.gait_clock = (self.gait_clock + self.dt * 2.0) % 1.0
+
+    env = helpers.make_env("go1_rough_full", 512, device=DEV, seed=13, task_class=Go1Gait)
+    helpers.randomise_env_state(env, 13)
+    frames = synthetic.make_frames(env, 3, seed=73)
+    synthetic.load_frame(env, frames[0])
+    p = lo.OracleParams.from_env(env, device="cpu")
+    s = lo.OracleState.from_env(env, p, device="cpu")
+    base_cb = lo.post_physics_step_callback
+
+    def edited(pp, ss, taps):
+        base_cb(pp, ss, taps)
+        ss.commands[:, 2] *= (torch.norm(ss.commands[:, :2], dim=1) > 0.5)
+    lo.post_physics_step_callback = edited
+    try:
+        for it, fr in enumerate(frames):
+            taps = synthetic.make_taps(env, seed=950 + it)
+            synthetic.load_frame(env, fr)
+            env.use_rng_taps(taps, index_math=_lgk.INDEX_MATH_TORCH_CPU)
+            env.step(fr["actions"].clone())
+            torch.cuda.synchronize()
+            s.root_states.copy_(fr["root_states"].cpu()); s.dof_state.copy_(fr["dof_state"].cpu())
+            s.contact_forces.copy_(fr["contact_forces"].cpu().view_as(s.contact_forces)); s.torques.copy_(fr["torques"].cpu())
+            lo.step(p, s, fr["actions"].cpu().clone(), {k: v.cpu() for k, v in taps.items()})
+            helpers.compare_env_to_oracle(env, s, tag=f"[callback override step {it}] ")
+        assert abs(float(env.gait_clock[0]) - (3 * env.dt * 2.0) % 1.0) < 1e-6
+        assert int((env.commands[:, 2] == 0).sum()) > 50
+    finally:
+        lo.post_physics_step_callback = base_cb
+
+
 def test_check_termination_override_adds_a_condition():
     """A derived task that also terminates on a large tilt (a common customisation of :143-148).  The kernel
     acts on the mask the override leaves -- resets, the termination reward, episode statistics -- which equals
