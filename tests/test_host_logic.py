@@ -179,3 +179,14 @@ def test_terrain_file_roundtrip(tmp_path):
         cfg.terrain.vertical_scale = 0.01
     with pytest.raises(ValueError, match="vertical_scale"):
         helpers.make_env("go1_rough_full", 16, extra=wrong_scale)
+
+
+def test_privileged_observations_buffer_like_the_reference():
+    """base_task.py:75-78: with cfg.env.num_privileged_obs set the buffer exists (zeros; no shipped task writes
+    it) and get_privileged_observations() returns it; None otherwise."""
+    def priv(cfg):
+        cfg.env.num_privileged_obs = 17
+    env = helpers.make_env("go1_flat", 6, extra=priv)
+    assert env.num_privileged_obs == 17 and env.get_privileged_observations() is env.privileged_obs_buf
+    assert env.privileged_obs_buf.shape == (6, 17) and float(env.privileged_obs_buf.abs().sum()) == 0.0
+    assert helpers.make_env("go1_flat", 6).get_privileged_observations() is None
