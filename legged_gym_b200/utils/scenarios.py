@@ -83,6 +83,16 @@ SCENARIOS = {
 }
 
 
+def _as_shipped(cfg):
+    """no change: the task exactly as registered"""
+
+
+# every registered task exactly as shipped (reference envs/__init__.py:52-59); parity-tested against the oracle
+# on the GPU, without golden fixtures of their own
+SHIPPED_TASKS = {name + "_shipped": (name, _as_shipped) for name in
+                 ("anymal_c_rough", "anymal_c_flat", "anymal_b", "a1", "cassie", "a1_src", "go1", "aliengo")}
+
+
 def algorithmic_bytes_per_env_step(D, B, F, R, O):
     """Compulsory HBM bytes of one post_physics_step per env: reads root 13 + dof_state 2D
     + contacts 3B + torques D + actions D + last_actions D + last_dof_vel D + commands 4 + feet_air_time F

@@ -17,7 +17,7 @@ RTOL, ATOL = 1e-5, 1e-6
 
 
 def make_env(scenario: str, num_envs: int, device: str = "cpu", seed: int = 0, extra=None, task_class=None):
-    task, mutate = scenarios.SCENARIOS[scenario]
+    task, mutate = scenarios.SCENARIOS[scenario] if scenario in scenarios.SCENARIOS else scenarios.SHIPPED_TASKS[scenario]
     cfg = copy.deepcopy(task_registry.env_cfgs[task])
     cfg.env.num_envs = num_envs
     cfg.seed = seed

@@ -37,6 +37,12 @@ def test_step_matches_oracle(name, oracle_device):
     assert n > 0
 
 
+@pytest.mark.parametrize("name", list(scenarios.SHIPPED_TASKS))
+def test_every_registered_task_as_shipped(name):
+    """The eight registrations of the reference (envs/__init__.py:52-59), configs untouched."""
+    assert helpers.run_parity(name, 200, 3) >= 0
+
+
 def test_blind_flat_task_with_every_reward_term():
     """Flat, blind Go1 (no height scan: measured_heights stays the python int 0, legged_robot.py:553) with all 20
     terms + termination: base_height then reduces to (root_z - target)^2 (:869-872)."""
