@@ -231,7 +231,8 @@ class LeggedRobot(BaseTask):
         step's tracking_lin_vel term added to the sums with the reference's own operations (:918-921, :207)."""
         self._ensure_pre_reward_state(lib)
         env_ids = self.reset_buf.nonzero(as_tuple=False).flatten()
-        if len(env_ids) == 0:
+        sharded = self._shard_world() > 1
+        if len(env_ids) == 0 and not sharded:
             return
         sums = self.episode_sums["tracking_lin_vel"]          # KeyError without the term, like the reference (:472)
         row = self.reward_names.index("tracking_lin_vel")
@@ -242,11 +243,28 @@ class LeggedRobot(BaseTask):
             lin_vel_error = torch.sum(torch.square(self.commands[:, :2] - self.base_lin_vel[:, :2]), dim=1)
             rew = torch.exp(-lin_vel_error / self.cfg.rewards.tracking_sigma)
         sums = sums + rew * self.reward_scales["tracking_lin_vel"]
-        if torch.mean(sums[env_ids]) / self.max_episode_length > 0.8 * self.reward_scales["tracking_lin_vel"]:
+        mean = self._mean_over_all_shards(sums[env_ids]) if sharded else torch.mean(sums[env_ids])
+        if mean is not None and mean / self.max_episode_length > 0.8 * self.reward_scales["tracking_lin_vel"]:
             r = self.command_ranges["lin_vel_x"]
             r[0] = np.clip(r[0] - 0.5, -self.cfg.commands.max_curriculum, 0.)
             r[1] = np.clip(r[1] + 0.5, 0., self.cfg.commands.max_curriculum)
             self._sync_host_scalars(reset_half_only=True)   # the callback's resample still sees the old range
+
+    def _shard_world(self) -> int:
+        import torch.distributed as dist
+        world = int(getattr(self.cfg.env, "shard_world", 1))
+        return world if (world > 1 and dist.is_available() and dist.is_initialized()) else 1
+
+    @staticmethod
+    def _mean_over_all_shards(values):
+        """Mean of `values` over the envs of every rank (one all-reduce of [sum, count]): the command
+        curriculum's gate (:472) then decides on every GPU what a single process holding all the envs would
+        decide, and command_ranges stay identical across ranks.  Returns None when no rank has a value (the
+        reference does not call update_command_curriculum on an empty reset set, :160)."""
+        import torch.distributed as dist
+        t = torch.stack([values.sum().float(), torch.tensor(float(values.numel()), device=values.device)])
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return None if float(t[1]) == 0.0 else t[0] / t[1]
 
     def _after_step_sim_writes(self):
         """Hand the state the kernel rewrote back to the simulator (:411,432,441)."""

@@ -50,6 +50,10 @@ def _worker(rank, world, port, out):
         ex = st.after_step(2)
         assert float(env.episode_stats[half:half + R + 1].abs().sum()) == 0.0   # accumulators cleared
         res = {k: float(v) for k, v in ex.items()}
+        # the command curriculum's gate: mean over the reset envs of ALL ranks (rank 0: 2 envs at 10, rank 1: 4 at 40)
+        vals = torch.full((2 + 2 * rank,), 10.0 + 30.0 * rank)
+        res["_gate_mean"] = float(env._mean_over_all_shards(vals))
+        assert env._mean_over_all_shards(torch.zeros(0)) is None and env._shard_world() == world
         res["_types"] = env.terrain_types.tolist()
         res["_levels"] = level_sum
         out[rank] = res
@@ -69,6 +73,7 @@ def test_sharded_stats_allreduce_world2():
         assert a[k] == b[k], f"ranks disagree on {k}"
     # global mean = (sum over ranks) / (resets over ranks) / max_episode_length_s(20)
     assert a["num_resets"] == 7.0
+    assert a["_gate_mean"] == b["_gate_mean"] == (2 * 10.0 + 4 * 40.0) / 6
     assert abs(a["rew_ang_vel_xy"] - (1 * 1 + 1 * 2) / 7.0 / 20.0) < 1e-6
     assert abs(a["terrain_level"] - (a["_levels"] + b["_levels"]) / 64.0) < 1e-6
     # terrain types partition the global index range: rank 0 owns the low types, rank 1 the high ones
