@@ -323,6 +323,9 @@ lgk_act_mlp_kernel(int rows_total, const float* __restrict__ model_ins, const fl
 extern "C" int lgk_act_mlp_tc_impl(int rows, const float* model_ins, const float* weights, const float* norm,
                                    float* dvel, cudaStream_t st);
 
+extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const float* norm,
+                                     float* dvel, cudaStream_t st);
+
 extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
                                          float* v_hist, float* model_ins, const float* weights, const float* norm,
                                          float* dvel, cudaStream_t st) {
@@ -330,9 +333,14 @@ extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const floa
   lgk_act_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int rows = N * ACT_LEGS;
-  // default: the 3xTF32 tensor-pipe kernel (lgk_mlp_tc.cu); LGK_MLP_FFMA=1 keeps the fp32 FFMA kernel below
-  const char* e = getenv("LGK_MLP_FFMA");      // read per call (cheap) so that a process can time / test both
-  const bool ffma = e && e[0] == '1';
+  // LGK_MLP_KERNEL picks the MLP kernel (read per call, cheap, so that one process can time / test them all):
+  //   "umma" tcgen05 3xTF32, activations + accumulator in tensor memory (lgk_mlp_umma.cu)
+  //   "mma"  warp-level 3xTF32 mma.sync (lgk_mlp_tc.cu; the default)      "ffma" the fp32 FFMA kernel below
+  // LGK_MLP_FFMA=1 is the older spelling of "ffma".
+  const char* e = getenv("LGK_MLP_FFMA");
+  const char* k = getenv("LGK_MLP_KERNEL");
+  const bool ffma = (e && e[0] == '1') || (k && k[0] == 'f');
+  if (!ffma && k && k[0] == 'u') return lgk_act_mlp_umma_impl(rows, model_ins, weights, norm, dvel, st);
   if (!ffma) return lgk_act_mlp_tc_impl(rows, model_ins, weights, norm, dvel, st);
   const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
   int dev = 0, sms = 148;

@@ -1,0 +1,353 @@
+// Go1 / Aliengo actuator net on the 5th-generation tensor cores (reference envs/go1/go1.py:22-35,102-105):
+// the per-leg MLP 30 -> 128 -> 128 -> 128 -> 3 (tanh) as 3xTF32 tcgen05.mma with the accumulator AND the
+// activations in tensor memory (sm_100a).
+//
+// fp32 parity (1e-5 relative) rules out single-pass TF32, so every product is split as in lgk_mlp_tc.cu:
+//   a*w ~= a_lo*w_hi + a_hi*w_hi + a_hi*w_lo   (hi = fp32 rounded to the 10-bit TF32 mantissa, lo = the
+//                                               remainder, itself rounded; the dropped lo*lo is 2^-22 relative)
+// Decomposition: one CTA per SM, 128 leg-rows per tile = the 128 lanes of tensor memory.
+//   * A operand (activations) lives in TMEM: columns [256,384) hold a_hi, [384,512) a_lo, one row per lane.
+//     The MMA reads them from there (tcgen05.mma [d], [a], b-desc) -- activations never touch shared memory.
+//   * D (fp32 accumulator, 128 x 128) lives in TMEM columns [0,128).
+//   * B operand (weights, [out][in] = K-major as torch stores them) sits in shared memory as ready-made
+//     no-swizzle UMMA images: 8x(16 B) core matrices, LBO 128 B along K, SBO (K/4)*128 B along N.  hi and lo
+//     images of the two 128x128 layers are 256 KB, more than an SM has, so W0 hi/lo, W1 hi and W2 hi are
+//     resident (224 KB) and one 64 KB slot is re-filled by the TMA engine with W1 lo, then W2 lo, every tile
+//     (cp.async.bulk from L2, hidden behind the epilogues; the lo pass of a layer is issued last).
+//   * epilogue: thread = row.  tcgen05.ld 32 columns -> + bias, tanh, split hi/lo -> tcgen05.st into the A
+//     columns of the next layer; the 128 -> 3 output layer is folded into the last epilogue on the FMA pipe.
+//     Biases and W3 are read from constant memory (the column index is uniform across the CTA).
+// A prep kernel builds the images and the constant block from the fp32 weight blob on every call (stream
+// ordered, ~3 us); the image buffer is a per-device workspace, so calls for different weight blobs must not
+// run concurrently on two streams of one device.
+#include "lgk_common.cuh"
+
+#define ACT_LEGS 4
+#define ACT_LEG_DOF 3
+#define ACT_DOF 12
+#define ACT_IN 30
+#define ACT_HID 128
+
+namespace {
+constexpr int UM_ROWS = 128;
+constexpr int UM_THREADS = 128;
+constexpr int UM_K0 = 32;                               // layer-0 reduction length, 30 padded to 4 k-steps
+constexpr uint32_t IMG0 = ACT_HID * UM_K0 * 4;          // 16 KB
+constexpr uint32_t IMG = ACT_HID * ACT_HID * 4;         // 64 KB
+// global image buffer: W0hi W0lo W1hi W1lo W2hi W2lo
+constexpr uint32_t G_W0HI = 0, G_W0LO = IMG0, G_W1HI = 2 * IMG0, G_W1LO = G_W1HI + IMG, G_W2HI = G_W1LO + IMG,
+                   G_W2LO = G_W2HI + IMG, G_TOTAL = G_W2LO + IMG;
+// shared memory: W0hi W0lo W1hi W2hi slot
+constexpr uint32_t S_W0HI = 0, S_W0LO = IMG0, S_W1HI = 2 * IMG0, S_W2HI = S_W1HI + IMG, S_SLOT = S_W2HI + IMG,
+                   S_BARS = S_SLOT + IMG, S_TOTAL = S_BARS + 64;
+// tensor-memory columns
+constexpr uint32_t T_D = 0, T_AHI = 256, T_ALO = 384, T_COLS = 512;
+// instruction descriptor: D fp32 (1<<4), A, B tf32 (2<<7, 2<<10), both K-major, N=128 (>>3 at 17), M=128 (>>4 at 24)
+constexpr uint32_t UM_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((ACT_HID >> 3) << 17) | ((UM_ROWS >> 4) << 24);
+}  // namespace
+
+// biases of the three hidden layers, W3 [3][128], b3 [3] (+1 pad) -- written by the prep kernel
+__constant__ float c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + 4];
+#define C_B(l, col) c_um[(l) * ACT_HID + (col)]
+#define C_W3(o, col) c_um[3 * ACT_HID + (o) * ACT_HID + (col)]
+#define C_B3(o) c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + (o)]
+
+__device__ __forceinline__ void um_split(float v, uint32_t& hi, uint32_t& lo) {
+  hi = (__float_as_uint(v) + 0x1000u) & 0xffffe000u;
+  lo = (__float_as_uint(v - __uint_as_float(hi)) + 0x1000u) & 0xffffe000u;
+}
+
+// element (n, k) of an [128][K] K-major operand inside its no-swizzle UMMA image, in floats
+__device__ __forceinline__ uint32_t um_img_index(int n, int k, int K) {
+  return (uint32_t)(((n >> 3) * (K >> 2) + (k >> 2)) * 32 + (n & 7) * 4 + (k & 3));
+}
+
+__global__ void lgk_umma_prep_kernel(const float* __restrict__ weights, float* __restrict__ img,
+                                     float* __restrict__ cblock) {
+  const float* W0 = weights;
+  const float* B0 = W0 + ACT_HID * ACT_IN;
+  const float* W1 = B0 + ACT_HID;
+  const float* B1 = W1 + ACT_HID * ACT_HID;
+  const float* W2 = B1 + ACT_HID;
+  const float* B2 = W2 + ACT_HID * ACT_HID;
+  const float* W3 = B2 + ACT_HID;
+  const float* B3 = W3 + ACT_LEG_DOF * ACT_HID;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t* out = reinterpret_cast<uint32_t*>(img);
+  if (i < ACT_HID * UM_K0) {
+    const int n = i / UM_K0, k = i % UM_K0;
+    uint32_t hi, lo;
+    um_split(k < ACT_IN ? W0[n * ACT_IN + k] : 0.f, hi, lo);
+    const uint32_t at = um_img_index(n, k, UM_K0);
+    out[G_W0HI / 4 + at] = hi;
+    out[G_W0LO / 4 + at] = lo;
+  }
+  if (i < ACT_HID * ACT_HID) {
+    const int n = i >> 7, k = i & 127;
+    const uint32_t at = um_img_index(n, k, ACT_HID);
+    uint32_t hi, lo;
+    um_split(W1[i], hi, lo);
+    out[G_W1HI / 4 + at] = hi;
+    out[G_W1LO / 4 + at] = lo;
+    um_split(W2[i], hi, lo);
+    out[G_W2HI / 4 + at] = hi;
+    out[G_W2LO / 4 + at] = lo;
+  }
+  if (i < ACT_HID) {
+    cblock[i] = B0[i];
+    cblock[ACT_HID + i] = B1[i];
+    cblock[2 * ACT_HID + i] = B2[i];
+  }
+  if (i < ACT_LEG_DOF * ACT_HID) cblock[3 * ACT_HID + i] = W3[i];
+  if (i < ACT_LEG_DOF) cblock[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + i] = B3[i];
+}
+
+// ---- tcgen05 / tensor-memory helpers ---------------------------------------------------------------------
+__device__ __forceinline__ void um_tmem_alloc(uint32_t* slot_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_smem)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void um_tmem_free(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void um_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void um_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void um_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void um_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// all MMAs issued so far by this thread -> one arrival on `bar` when they have completed
+__device__ __forceinline__ void um_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// D[128x128] (+)= A[128x8] (TMEM, one row per lane, k along the columns) * B[128x8]^T (shared-memory image)
+__device__ __forceinline__ void um_mma(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(UM_IDESC), "r"(accumulate)
+      : "memory");
+}
+// K-major, no swizzle: start address, LBO = 128 B (next core matrix along K), SBO = (K/4)*128 B (next 8 rows
+// of N), descriptor version 1 (bits 46-47), layout type 0
+__device__ __forceinline__ uint64_t um_desc(uint32_t smem_addr, uint32_t sbo_bytes) {
+  return (uint64_t)((smem_addr & 0x3ffffu) >> 4) | ((uint64_t)(128u >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+         (1ull << 46);
+}
+
+#define UM_R8(v, o) "=r"(v[o]), "=r"(v[o + 1]), "=r"(v[o + 2]), "=r"(v[o + 3]), "=r"(v[o + 4]), "=r"(v[o + 5]), "=r"(v[o + 6]), "=r"(v[o + 7])
+#define UM_W8(v, o) "r"(v[o]), "r"(v[o + 1]), "r"(v[o + 2]), "r"(v[o + 3]), "r"(v[o + 4]), "r"(v[o + 5]), "r"(v[o + 6]), "r"(v[o + 7])
+// this warp's 32 lanes x 32 consecutive columns: thread i <-> lane (addr.lane + i), register j <-> column + j
+__device__ __forceinline__ void um_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : UM_R8(v, 0), UM_R8(v, 8), UM_R8(v, 16), UM_R8(v, 24)
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void um_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), UM_W8(v, 0), UM_W8(v, 8), UM_W8(v, 16), UM_W8(v, 24)
+      : "memory");
+}
+// mbarrier wait that traps instead of hanging the device if the arrival never comes (~2 s)
+__device__ __forceinline__ void um_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok = 0;
+  const uint32_t addr = smem_u32(bar);
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (ok) break;
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+
+// the three passes of one layer: D = a_lo*w_hi + a_hi*w_hi over all k-steps, then (once the streamed image has
+// landed) += a_hi*w_lo.  One k-step = 8 tf32 = two 128 B core matrices = 256 B of the image, 8 TMEM columns.
+template <int K>
+__device__ __forceinline__ void um_issue_layer(uint32_t tmem, uint32_t w_hi_smem, uint32_t w_lo_smem,
+                                               uint64_t* lo_ready, uint32_t lo_parity) {
+  constexpr uint32_t SBO = (K / 4) * 128;
+#pragma unroll
+  for (int ks = 0; ks < K / 8; ++ks) {
+    const uint64_t bh = um_desc(w_hi_smem + ks * 256, SBO);
+    um_mma(tmem + T_D, tmem + T_ALO + ks * 8, bh, ks > 0);
+    um_mma(tmem + T_D, tmem + T_AHI + ks * 8, bh, 1);
+  }
+  if (lo_ready) um_wait(lo_ready, lo_parity);
+#pragma unroll
+  for (int ks = 0; ks < K / 8; ++ks)
+    um_mma(tmem + T_D, tmem + T_AHI + ks * 8, um_desc(w_lo_smem + ks * 256, SBO), 1);
+}
+
+// hidden-layer epilogue for this thread's row: D -> tanh(D + b) -> hi / lo into the A columns
+template <int L>
+__device__ __forceinline__ void um_epilogue_hidden(uint32_t trow) {
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[32], hi[32], lo[32];
+    um_ld32(trow + T_D + c * 32, v);
+    um_wait_ld();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) um_split(tanh_fast(__uint_as_float(v[j]) + C_B(L, c * 32 + j)), hi[j], lo[j]);
+    um_st32(trow + T_AHI + c * 32, hi);
+    um_st32(trow + T_ALO + c * 32, lo);
+  }
+  um_wait_st();
+}
+
+__global__ void __launch_bounds__(UM_THREADS, 1)
+lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, const unsigned char* __restrict__ wimg,
+                        const float* __restrict__ norm, float* __restrict__ dvel) {
+  extern __shared__ __align__(1024) unsigned char um_smem[];
+  uint64_t* bar_res = reinterpret_cast<uint64_t*>(um_smem + S_BARS);   // resident images landed
+  uint64_t* bar_lo = bar_res + 1;                                      // streamed lo image landed
+  uint64_t* bar_mma = bar_res + 2;                                     // a layer's MMAs completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_res + 4);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const uint32_t sbase = smem_u32(um_smem);
+
+  if (tid == 0) {
+    mbar_init(bar_res, 1);
+    mbar_init(bar_lo, 1);
+    mbar_init(bar_mma, 1);
+  }
+  if (warp == 0) um_tmem_alloc(tmem_slot, T_COLS);
+  um_fence_before();
+  __syncthreads();
+  um_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);          // this warp's lane quadrant
+  if (tid == 0) {
+    mbar_expect_tx(bar_res, 2 * IMG0 + 2 * IMG);
+    bulk_g2s(um_smem + S_W0HI, wimg + G_W0HI, 2 * IMG0, bar_res);      // W0 hi and lo are adjacent in both
+    bulk_g2s(um_smem + S_W1HI, wimg + G_W1HI, IMG, bar_res);
+    bulk_g2s(um_smem + S_W2HI, wimg + G_W2HI, IMG, bar_res);
+  }
+  uint32_t ph_mma = 0, ph_lo = 0;
+  bool resident = false;
+
+  const int num_tiles = (rows_total + UM_ROWS - 1) / UM_ROWS;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int row = tile * UM_ROWS + tid;
+    // the slot is free: every thread has seen the previous tile's last MMAs complete
+    if (tid == 0) {
+      mbar_expect_tx(bar_lo, IMG);
+      bulk_g2s(um_smem + S_SLOT, wimg + G_W1LO, IMG, bar_lo);
+    }
+    {  // layer-0 A operand: this row's 30 inputs (+2 zero columns), split, into A columns [0,32)
+      uint32_t hi[32], lo[32];
+      const float2* src = reinterpret_cast<const float2*>(model_ins + (size_t)row * ACT_IN);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        float2 x = make_float2(0.f, 0.f);
+        if (j < ACT_IN / 2 && row < rows_total) x = __ldg(src + j);
+        um_split(x.x, hi[2 * j], lo[2 * j]);
+        um_split(x.y, hi[2 * j + 1], lo[2 * j + 1]);
+      }
+      um_st32(trow + T_AHI, hi);
+      um_st32(trow + T_ALO, lo);
+      um_wait_st();
+    }
+    um_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      um_fence_after();
+      if (!resident) { um_wait(bar_res, 0); resident = true; }
+      um_issue_layer<UM_K0>(tmem, sbase + S_W0HI, sbase + S_W0LO, nullptr, 0);
+      um_commit(bar_mma);
+    }
+    __syncwarp();
+    um_wait(bar_mma, ph_mma); ph_mma ^= 1;
+    __syncwarp();
+    um_fence_after();
+    um_epilogue_hidden<0>(trow);
+    um_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      um_fence_after();
+      um_issue_layer<ACT_HID>(tmem, sbase + S_W1HI, sbase + S_SLOT, bar_lo, ph_lo);
+      ph_lo ^= 1;
+      um_commit(bar_mma);
+    }
+    __syncwarp();
+    um_wait(bar_mma, ph_mma); ph_mma ^= 1;
+    __syncwarp();
+    um_fence_after();
+    if (tid == 0) {   // layer 1 has finished reading the slot: fetch W2 lo behind this epilogue
+      mbar_expect_tx(bar_lo, IMG);
+      bulk_g2s(um_smem + S_SLOT, wimg + G_W2LO, IMG, bar_lo);
+    }
+    __syncwarp();
+    um_epilogue_hidden<1>(trow);
+    um_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      um_fence_after();
+      um_issue_layer<ACT_HID>(tmem, sbase + S_W2HI, sbase + S_SLOT, bar_lo, ph_lo);
+      ph_lo ^= 1;
+      um_commit(bar_mma);
+    }
+    __syncwarp();
+    um_wait(bar_mma, ph_mma); ph_mma ^= 1;
+    __syncwarp();
+    um_fence_after();
+    // last hidden epilogue with the 128 -> 3 output layer folded in (FMA pipe, W3 from the constant bank)
+    float p[ACT_LEG_DOF] = {0.f, 0.f, 0.f};
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t v[32];
+      um_ld32(trow + T_D + c * 32, v);
+      um_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float h = tanh_fast(__uint_as_float(v[j]) + C_B(2, c * 32 + j));
+#pragma unroll
+        for (int o = 0; o < ACT_LEG_DOF; ++o) p[o] = fmaf(h, C_W3(o, c * 32 + j), p[o]);
+      }
+    }
+    if (row < rows_total) {
+      // dVel = net(x) * vel_std   (go1.py:102-105); leg = row % 4
+#pragma unroll
+      for (int o = 0; o < ACT_LEG_DOF; ++o)
+        dvel[(size_t)row * ACT_LEG_DOF + o] = (p[o] + C_B3(o)) * norm[3 * ACT_DOF + (row % ACT_LEGS) * ACT_LEG_DOF + o];
+    }
+    // D is read out before the next tile's layer 0 overwrites it (the __syncthreads after the A stores)
+    um_fence_before();
+  }
+  if (tid == 0 && !resident) um_wait(bar_res, 0);    // never exit with a bulk copy in flight
+  um_fence_before();
+  __syncthreads();
+  if (warp == 0) um_tmem_free(tmem, T_COLS);
+}
+
+extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const float* norm,
+                                     float* dvel, cudaStream_t st) {
+  static unsigned char* images[64] = {nullptr};
+  static float* cblock[64] = {nullptr};
+  int dev = 0, sms = 148;
+  LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if (!images[dev]) {   // first call on this device (must not be inside a stream capture)
+    LGK_CUDA_RETURN_IF(cudaMalloc(&images[dev], G_TOTAL));
+    LGK_CUDA_RETURN_IF(cudaGetSymbolAddress(reinterpret_cast<void**>(&cblock[dev]), c_um));
+  }
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  lgk_umma_prep_kernel<<<ACT_HID * ACT_HID / 256, 256, 0, st>>>(weights, reinterpret_cast<float*>(images[dev]), cblock[dev]);
+  LGK_CUDA_RETURN_IF(cudaGetLastError());
+  const int tiles = (rows + UM_ROWS - 1) / UM_ROWS;
+  const int grid = tiles < sms ? tiles : sms;
+  LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S_TOTAL));
+  lgk_act_mlp_umma_kernel<<<grid, UM_THREADS, S_TOTAL, st>>>(rows, model_ins, images[dev], norm, dvel);
+  return (int)cudaGetLastError();
+}

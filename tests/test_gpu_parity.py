@@ -196,12 +196,14 @@ def test_clip_actions_and_poses(n):
     helpers.assert_close("target_poses", env._compute_poses(out), lo.compute_poses(p, out.cpu()))
 
 
-@pytest.mark.parametrize("kernel", ["tensor", "ffma"])
+@pytest.mark.parametrize("kernel", ["umma", "mma", "ffma"])
 def test_actuator_net_matches_oracle_over_substeps(kernel, monkeypatch):
-    """Both MLP kernels: 3xTF32 on the tensor pipe (default; floor of a few fp32 roundings of the output layer's
-    operands, helpers.actuator_dvel_atol) and fp32 FFMA (LGK_MLP_FFMA=1; plain 1e-5 + 1e-6)."""
+    """All three MLP kernels: 3xTF32 on tcgen05 with the activations in tensor memory and 3xTF32 on mma.sync (floor
+    of a few fp32 roundings of the output layer's operands, helpers.actuator_dvel_atol), and fp32 FFMA (plain
+    1e-5 + 1e-6)."""
     from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
-    monkeypatch.setenv("LGK_MLP_FFMA", "1" if kernel == "ffma" else "0")
+    monkeypatch.delenv("LGK_MLP_FFMA", raising=False)
+    monkeypatch.setenv("LGK_MLP_KERNEL", kernel)
     from oracle import legged_oracle as lo
     n = 1000
     env = helpers.make_env("go1_rough_actuator", n, device=DEV)
