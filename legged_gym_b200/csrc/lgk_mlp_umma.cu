@@ -8,19 +8,25 @@
 // Decomposition: one CTA per SM, 128 leg-rows per tile = the 128 lanes of tensor memory.
 //   * A operand (activations) lives in TMEM: columns [256,384) hold a_hi, [384,512) a_lo, one row per lane.
 //     The MMA reads them from there (tcgen05.mma [d], [a], b-desc) -- activations never touch shared memory.
-//   * D (fp32 accumulator, 128 x 128) lives in TMEM columns [0,128).
+//   * D (fp32 accumulators, 128 x 128 each) live in TMEM columns [0,128) and [128,256).
 //   * B operand (weights, [out][in] = K-major as torch stores them) sits in shared memory as ready-made
 //     no-swizzle UMMA images: 8x(16 B) core matrices, LBO 128 B along K, SBO (K/4)*128 B along N.  hi and lo
 //     images of the two 128x128 layers are 256 KB, more than an SM has, so W0 hi/lo, W1 hi and W2 hi are
 //     resident (224 KB) and one 64 KB slot is re-filled by the TMA engine with W1 lo, then W2 lo, every tile
 //     (cp.async.bulk from L2, hidden behind the epilogues; the lo pass of a layer is issued last).
-//   * epilogue: thread = row.  tcgen05.ld 32 columns -> + bias, tanh, split hi/lo -> tcgen05.st into the A
-//     columns of the next layer; the 128 -> 3 output layer is folded into the last epilogue on the FMA pipe.
-//     Biases and W3 are read from constant memory (the column index is uniform across the CTA).
+//   * epilogue: eight warps, thread = row (warps e and e+4 share a lane quadrant and split every 32-column
+//     group).  tcgen05.ld 16 columns -> + bias, tanh, split hi/lo -> tcgen05.st into the A columns of the next
+//     layer; after every group an mbarrier tells the control warp, which issues that group's k-steps of the next
+//     layer into the OTHER accumulator (D0 / D1 alternate), so the tensor core runs under the epilogue.  The
+//     128 -> 3 output layer is folded into the last epilogue on the FMA pipe.  Biases and W3 are immediate
+//     constant-bank operands (the column index is uniform across the CTA and known at compile time).
+//   * control warp: one thread issues the bulk copies and every tcgen05.mma / tcgen05.commit.
 // A prep kernel builds the images and the constant block from the fp32 weight blob on every call (stream
 // ordered, ~3 us); the image buffer is a per-device workspace, so calls for different weight blobs must not
 // run concurrently on two streams of one device.
 #include "lgk_common.cuh"
+#include <cstdio>
+#include <cstdlib>
 
 #define ACT_LEGS 4
 #define ACT_LEG_DOF 3
@@ -30,7 +36,8 @@
 
 namespace {
 constexpr int UM_ROWS = 128;
-constexpr int UM_THREADS = 128;
+constexpr int UM_EPI_WARPS = 8;                        // two per lane quadrant, each takes half of the columns
+constexpr int UM_THREADS = (UM_EPI_WARPS + 1) * 32;      // + the control warp (TMA and MMA issue)
 constexpr int UM_K0 = 32;                               // layer-0 reduction length, 30 padded to 4 k-steps
 constexpr uint32_t IMG0 = ACT_HID * UM_K0 * 4;          // 16 KB
 constexpr uint32_t IMG = ACT_HID * ACT_HID * 4;         // 64 KB
@@ -39,16 +46,17 @@ constexpr uint32_t G_W0HI = 0, G_W0LO = IMG0, G_W1HI = 2 * IMG0, G_W1LO = G_W1HI
                    G_W2LO = G_W2HI + IMG, G_TOTAL = G_W2LO + IMG;
 // shared memory: W0hi W0lo W1hi W2hi slot
 constexpr uint32_t S_W0HI = 0, S_W0LO = IMG0, S_W1HI = 2 * IMG0, S_W2HI = S_W1HI + IMG, S_SLOT = S_W2HI + IMG,
-                   S_BARS = S_SLOT + IMG, S_TOTAL = S_BARS + 64;
-// tensor-memory columns
-constexpr uint32_t T_D = 0, T_AHI = 256, T_ALO = 384, T_COLS = 512;
+                   S_BARS = S_SLOT + IMG, S_TOTAL = S_BARS + 128 + UM_ROWS * 3 * 4;
+// tensor-memory columns (the two accumulators D0, D1 are [0,128) and [128,256))
+constexpr uint32_t T_AHI = 256, T_ALO = 384, T_COLS = 512;
 // instruction descriptor: D fp32 (1<<4), A, B tf32 (2<<7, 2<<10), both K-major, N=128 (>>3 at 17), M=128 (>>4 at 24)
 constexpr uint32_t UM_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((ACT_HID >> 3) << 17) | ((UM_ROWS >> 4) << 24);
 }  // namespace
 
-// biases of the three hidden layers, W3 [3][128], b3 [3] (+1 pad) -- written by the prep kernel
+// biases of the three hidden layers times 2*log2(e) (the epilogue's tanh takes its argument in that scale),
+// W3 [3][128], b3 [3] (+1 pad) -- written by the prep kernel
 __constant__ float c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + 4];
-#define C_B(l, col) c_um[(l) * ACT_HID + (col)]
+#define C_BS(l, col) c_um[(l) * ACT_HID + (col)]
 #define C_W3(o, col) c_um[3 * ACT_HID + (o) * ACT_HID + (col)]
 #define C_B3(o) c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + (o)]
 
@@ -94,9 +102,9 @@ __global__ void lgk_umma_prep_kernel(const float* __restrict__ weights, float* _
     out[G_W2LO / 4 + at] = lo;
   }
   if (i < ACT_HID) {
-    cblock[i] = B0[i];
-    cblock[ACT_HID + i] = B1[i];
-    cblock[2 * ACT_HID + i] = B2[i];
+    cblock[i] = B0[i] * 2.885390081777927f;
+    cblock[ACT_HID + i] = B1[i] * 2.885390081777927f;
+    cblock[2 * ACT_HID + i] = B2[i] * 2.885390081777927f;
   }
   if (i < ACT_LEG_DOF * ACT_HID) cblock[3 * ACT_HID + i] = W3[i];
   if (i < ACT_LEG_DOF) cblock[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + i] = B3[i];
@@ -154,11 +162,24 @@ __device__ __forceinline__ void um_st32(uint32_t taddr, const uint32_t (&v)[32])
       ::"r"(taddr), UM_W8(v, 0), UM_W8(v, 8), UM_W8(v, 16), UM_W8(v, 24)
       : "memory");
 }
-// mbarrier wait that traps instead of hanging the device if the arrival never comes (~2 s)
+__device__ __forceinline__ void um_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : UM_R8(v, 0), UM_R8(v, 8)
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void um_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), UM_W8(v, 0), UM_W8(v, 8)
+      : "memory");
+}
+// mbarrier wait that traps instead of hanging the device if the arrival never comes
 __device__ __forceinline__ void um_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok = 0;
   const uint32_t addr = smem_u32(bar);
-  const long long t0 = clock64();
+  uint32_t spins = 0;
   while (true) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -168,41 +189,97 @@ __device__ __forceinline__ void um_wait(uint64_t* bar, uint32_t parity) {
         : "r"(addr), "r"(parity)
         : "memory");
     if (ok) break;
-    if (clock64() - t0 > 4000000000ll) __trap();
+    if (++spins > (1u << 28)) __trap();
   }
 }
 
-// the three passes of one layer: D = a_lo*w_hi + a_hi*w_hi over all k-steps, then (once the streamed image has
-// landed) += a_hi*w_lo.  One k-step = 8 tf32 = two 128 B core matrices = 256 B of the image, 8 TMEM columns.
+#ifdef UM_PROFILE
+__device__ long long um_prof[64];
+#define UM_STAMP(cond, i) do { if (cond) um_prof[i] = clock64(); } while (0)
+#else
+#define UM_STAMP(cond, i) do { } while (0)
+#endif
+__device__ __forceinline__ void um_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// tanh(x) for x*2*log2(e) given: 1 - 2 / (1 + 2^t) on two bare MUFU ops; absolute error ~1e-7 (it cancels for
+// small |x|), which is the rounding of the O(1) sums the activations feed; saturates exactly (ex2 -> inf / 0)
+__device__ __forceinline__ float um_tanh_scaled(float t) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return fmaf(-2.0f, r, 1.0f);
+}
+#define UM_2LOG2E 2.885390081777927f
+
+// k-steps [ks0, ks0+n) of the two w_hi passes of a layer: D (+)= a_lo*w_hi + a_hi*w_hi.  One k-step = 8 tf32 =
+// two 128 B core matrices = 256 B of the image = 8 TMEM columns.
 template <int K>
-__device__ __forceinline__ void um_issue_layer(uint32_t tmem, uint32_t w_hi_smem, uint32_t w_lo_smem,
-                                               uint64_t* lo_ready, uint32_t lo_parity) {
+__device__ __forceinline__ void um_issue_hi(uint32_t d, uint32_t tmem, uint32_t w_hi_smem, int ks0, int n, bool& first) {
   constexpr uint32_t SBO = (K / 4) * 128;
 #pragma unroll
-  for (int ks = 0; ks < K / 8; ++ks) {
+  for (int i = 0; i < n; ++i) {
+    const int ks = ks0 + i;
     const uint64_t bh = um_desc(w_hi_smem + ks * 256, SBO);
-    um_mma(tmem + T_D, tmem + T_ALO + ks * 8, bh, ks > 0);
-    um_mma(tmem + T_D, tmem + T_AHI + ks * 8, bh, 1);
+    um_mma(d, tmem + T_ALO + ks * 8, bh, first ? 0u : 1u);
+    first = false;
+    um_mma(d, tmem + T_AHI + ks * 8, bh, 1u);
   }
-  if (lo_ready) um_wait(lo_ready, lo_parity);
+}
+// the w_lo pass: D += a_hi*w_lo over all k-steps
+template <int K>
+__device__ __forceinline__ void um_issue_lo(uint32_t d, uint32_t tmem, uint32_t w_lo_smem) {
+  constexpr uint32_t SBO = (K / 4) * 128;
 #pragma unroll
-  for (int ks = 0; ks < K / 8; ++ks)
-    um_mma(tmem + T_D, tmem + T_AHI + ks * 8, um_desc(w_lo_smem + ks * 256, SBO), 1);
+  for (int ks = 0; ks < K / 8; ++ks) um_mma(d, tmem + T_AHI + ks * 8, um_desc(w_lo_smem + ks * 256, SBO), 1u);
 }
 
-// hidden-layer epilogue for this thread's row: D -> tanh(D + b) -> hi / lo into the A columns
-template <int L>
-__device__ __forceinline__ void um_epilogue_hidden(uint32_t trow) {
-#pragma unroll 1
-  for (int c = 0; c < 4; ++c) {
-    uint32_t v[32], hi[32], lo[32];
-    um_ld32(trow + T_D + c * 32, v);
-    um_wait_ld();
+// hidden-layer epilogue for this thread's row, 16 columns at col0 = 32G + 16*HALF: D -> tanh(D + b) -> hi / lo
+// into the A columns.  L, HALF and G are compile-time so that the biases are immediate constant-bank operands.
+template <int L, int HALF, int G>
+__device__ __forceinline__ void um_epilogue_group(uint32_t trow, uint32_t d_col) {
+  constexpr int col0 = G * 32 + HALF * 16;
+  uint32_t v[16], hi[16], lo[16];
+  um_ld16(trow + d_col + col0, v);
+  um_wait_ld();
 #pragma unroll
-    for (int j = 0; j < 32; ++j) um_split(tanh_fast(__uint_as_float(v[j]) + C_B(L, c * 32 + j)), hi[j], lo[j]);
-    um_st32(trow + T_AHI + c * 32, hi);
-    um_st32(trow + T_ALO + c * 32, lo);
+  for (int j = 0; j < 16; ++j)
+    um_split(um_tanh_scaled(fmaf(__uint_as_float(v[j]), UM_2LOG2E, C_BS(L, col0 + j))), hi[j], lo[j]);
+  um_st16(trow + T_AHI + col0, hi);
+  um_st16(trow + T_ALO + col0, lo);
+  um_wait_st();
+}
+// last hidden layer: tanh, then this thread's share of the 128 -> 3 output layer (FMA pipe, W3 from the constant bank)
+template <int HALF, int G>
+__device__ __forceinline__ void um_final_group(uint32_t trow, uint32_t d_col, float (&p)[ACT_LEG_DOF]) {
+  constexpr int col0 = G * 32 + HALF * 16;
+  uint32_t v[16];
+  um_ld16(trow + d_col + col0, v);
+  um_wait_ld();
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float h = um_tanh_scaled(fmaf(__uint_as_float(v[j]), UM_2LOG2E, C_BS(2, col0 + j)));
+#pragma unroll
+    for (int o = 0; o < ACT_LEG_DOF; ++o) p[o] = fmaf(h, C_W3(o, col0 + j), p[o]);
   }
+}
+
+// a row's 30 inputs: fetched early (registers), split and stored into A columns [0,32) (+2 zero columns) later
+__device__ __forceinline__ void um_fetch_inputs(float2 (&x)[ACT_IN / 2], const float* __restrict__ model_ins, int row, int rows_total) {
+  const float2* src = reinterpret_cast<const float2*>(model_ins + (size_t)row * ACT_IN);
+#pragma unroll
+  for (int j = 0; j < ACT_IN / 2; ++j) x[j] = row < rows_total ? __ldg(src + j) : make_float2(0.f, 0.f);
+}
+__device__ __forceinline__ void um_stage_inputs(uint32_t trow, const float2 (&x)[ACT_IN / 2]) {
+  uint32_t hi[32], lo[32];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float2 v = j < ACT_IN / 2 ? x[j < ACT_IN / 2 ? j : 0] : make_float2(0.f, 0.f);
+    um_split(v.x, hi[2 * j], lo[2 * j]);
+    um_split(v.y, hi[2 * j + 1], lo[2 * j + 1]);
+  }
+  um_st32(trow + T_AHI, hi);
+  um_st32(trow + T_ALO, lo);
   um_wait_st();
 }
 
@@ -210,125 +287,188 @@ __global__ void __launch_bounds__(UM_THREADS, 1)
 lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, const unsigned char* __restrict__ wimg,
                         const float* __restrict__ norm, float* __restrict__ dvel) {
   extern __shared__ __align__(1024) unsigned char um_smem[];
-  uint64_t* bar_res = reinterpret_cast<uint64_t*>(um_smem + S_BARS);   // resident images landed
-  uint64_t* bar_lo = bar_res + 1;                                      // streamed lo image landed
-  uint64_t* bar_mma = bar_res + 2;                                     // a layer's MMAs completed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_res + 4);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(um_smem + S_BARS);
+  uint64_t* bar_res = bars + 0;    // resident weight images landed (TMA)
+  uint64_t* bar_lo = bars + 1;     // streamed lo image landed (TMA)
+  uint64_t* bar_mma = bars + 2;    // a layer's MMAs completed: D readable, A writable (tcgen05.commit)
+  uint64_t* bar_free = bars + 3;   // same event, for the control thread: the slot may be re-filled
+  uint64_t* bar_in = bars + 4;     // next tile's inputs staged in A columns [0,32)      (4 warps)
+  uint64_t* bar_fin = bars + 5;    // last epilogue of a tile has read D                  (8 warps)
+  uint64_t* bar_a = bars + 6;      // [4] A columns [32g, 32g+32) of the next layer written (8 warps each)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  float* scratch = reinterpret_cast<float*>(um_smem + S_BARS + 128);   // [128][3] partial outputs of the upper half
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t sbase = smem_u32(um_smem);
 
   if (tid == 0) {
     mbar_init(bar_res, 1);
     mbar_init(bar_lo, 1);
     mbar_init(bar_mma, 1);
+    mbar_init(bar_free, 1);
+    mbar_init(bar_in, 4);
+    mbar_init(bar_fin, UM_EPI_WARPS);
+    for (int c = 0; c < 4; ++c) mbar_init(bar_a + c, UM_EPI_WARPS);
   }
-  if (warp == 0) um_tmem_alloc(tmem_slot, T_COLS);
+  if (warp == UM_EPI_WARPS) um_tmem_alloc(tmem_slot, T_COLS);
   um_fence_before();
   __syncthreads();
   um_fence_after();
   const uint32_t tmem = *tmem_slot;
-  const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);          // this warp's lane quadrant
-  if (tid == 0) {
-    mbar_expect_tx(bar_res, 2 * IMG0 + 2 * IMG);
-    bulk_g2s(um_smem + S_W0HI, wimg + G_W0HI, 2 * IMG0, bar_res);      // W0 hi and lo are adjacent in both
-    bulk_g2s(um_smem + S_W1HI, wimg + G_W1HI, IMG, bar_res);
-    bulk_g2s(um_smem + S_W2HI, wimg + G_W2HI, IMG, bar_res);
-  }
-  uint32_t ph_mma = 0, ph_lo = 0;
-  bool resident = false;
-
   const int num_tiles = (rows_total + UM_ROWS - 1) / UM_ROWS;
-  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-    const int row = tile * UM_ROWS + tid;
-    // the slot is free: every thread has seen the previous tile's last MMAs complete
-    if (tid == 0) {
-      mbar_expect_tx(bar_lo, IMG);
-      bulk_g2s(um_smem + S_SLOT, wimg + G_W1LO, IMG, bar_lo);
-    }
-    {  // layer-0 A operand: this row's 30 inputs (+2 zero columns), split, into A columns [0,32)
-      uint32_t hi[32], lo[32];
-      const float2* src = reinterpret_cast<const float2*>(model_ins + (size_t)row * ACT_IN);
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        float2 x = make_float2(0.f, 0.f);
-        if (j < ACT_IN / 2 && row < rows_total) x = __ldg(src + j);
-        um_split(x.x, hi[2 * j], lo[2 * j]);
-        um_split(x.y, hi[2 * j + 1], lo[2 * j + 1]);
-      }
-      um_st32(trow + T_AHI, hi);
-      um_st32(trow + T_ALO, lo);
-      um_wait_st();
-    }
-    um_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      um_fence_after();
-      if (!resident) { um_wait(bar_res, 0); resident = true; }
-      um_issue_layer<UM_K0>(tmem, sbase + S_W0HI, sbase + S_W0LO, nullptr, 0);
-      um_commit(bar_mma);
-    }
-    __syncwarp();
-    um_wait(bar_mma, ph_mma); ph_mma ^= 1;
-    __syncwarp();
-    um_fence_after();
-    um_epilogue_hidden<0>(trow);
-    um_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      um_fence_after();
-      um_issue_layer<ACT_HID>(tmem, sbase + S_W1HI, sbase + S_SLOT, bar_lo, ph_lo);
-      ph_lo ^= 1;
-      um_commit(bar_mma);
-    }
-    __syncwarp();
-    um_wait(bar_mma, ph_mma); ph_mma ^= 1;
-    __syncwarp();
-    um_fence_after();
-    if (tid == 0) {   // layer 1 has finished reading the slot: fetch W2 lo behind this epilogue
-      mbar_expect_tx(bar_lo, IMG);
-      bulk_g2s(um_smem + S_SLOT, wimg + G_W2LO, IMG, bar_lo);
-    }
-    __syncwarp();
-    um_epilogue_hidden<1>(trow);
-    um_fence_before();
-    __syncthreads();
-    if (tid == 0) {
-      um_fence_after();
-      um_issue_layer<ACT_HID>(tmem, sbase + S_W2HI, sbase + S_SLOT, bar_lo, ph_lo);
-      ph_lo ^= 1;
-      um_commit(bar_mma);
-    }
-    __syncwarp();
-    um_wait(bar_mma, ph_mma); ph_mma ^= 1;
-    __syncwarp();
-    um_fence_after();
-    // last hidden epilogue with the 128 -> 3 output layer folded in (FMA pipe, W3 from the constant bank)
-    float p[ACT_LEG_DOF] = {0.f, 0.f, 0.f};
+
+  if (warp == UM_EPI_WARPS) {
+    // ---------------- control warp: one thread feeds the TMA engine and the tensor core ----------------
+    if (lane == 0) {
+      mbar_expect_tx(bar_res, 2 * IMG0 + 2 * IMG);
+      bulk_g2s(um_smem + S_W0HI, wimg + G_W0HI, 2 * IMG0, bar_res);    // W0 hi and lo are adjacent in both
+      bulk_g2s(um_smem + S_W1HI, wimg + G_W1HI, IMG, bar_res);
+      bulk_g2s(um_smem + S_W2HI, wimg + G_W2HI, IMG, bar_res);
+      uint32_t ph_in = 0, ph_lo = 0, ph_free = 0, ph_fin = 0, ph_a = 0, dsel = 0;
+      um_wait(bar_res, 0);
+      for (int tile = blockIdx.x, it = 0; tile < num_tiles; tile += gridDim.x, ++it) {
+        const bool pr = blockIdx.x == 0 && it == 3;
+        (void)pr;
+        UM_STAMP(pr, 0);
+        mbar_expect_tx(bar_lo, IMG);                                   // the slot is free (bar_free below)
+        bulk_g2s(um_smem + S_SLOT, wimg + G_W1LO, IMG, bar_lo);
+        // layer 0: all three passes from resident images
+        um_wait(bar_in, ph_in); ph_in ^= 1;
+        um_fence_after();
+        UM_STAMP(pr, 1);
+        bool first = true;
+        um_issue_hi<UM_K0>(tmem + dsel * ACT_HID, tmem, sbase + S_W0HI, 0, UM_K0 / 8, first);
+        um_issue_lo<UM_K0>(tmem + dsel * ACT_HID, tmem, sbase + S_W0LO);
+        um_commit(bar_mma);
+        dsel ^= 1;
 #pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-      uint32_t v[32];
-      um_ld32(trow + T_D + c * 32, v);
-      um_wait_ld();
+        for (int l = 1; l <= 2; ++l) {
+          // this layer's accumulator is the buffer the previous tile's last epilogue read: let it finish
+          if (l == 1 && it > 0) { um_wait(bar_fin, ph_fin); ph_fin ^= 1; }
+          const uint32_t d = tmem + dsel * ACT_HID;
+          const uint32_t w_hi = sbase + (l == 1 ? S_W1HI : S_W2HI);
+          first = true;
+          // the w_hi passes follow the epilogue of the layer before, 32 columns (4 k-steps) at a time
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float h = tanh_fast(__uint_as_float(v[j]) + C_B(2, c * 32 + j));
-#pragma unroll
-        for (int o = 0; o < ACT_LEG_DOF; ++o) p[o] = fmaf(h, C_W3(o, c * 32 + j), p[o]);
+          for (int g = 0; g < 4; ++g) {
+            um_wait(bar_a + g, ph_a);
+            um_fence_after();
+            UM_STAMP(pr, l * 8 + g);
+            um_issue_hi<ACT_HID>(d, tmem, w_hi, g * 4, 4, first);
+          }
+          ph_a ^= 1;
+          UM_STAMP(pr, l * 8 + 4);
+          um_wait(bar_lo, ph_lo); ph_lo ^= 1;
+          UM_STAMP(pr, l * 8 + 5);
+          um_issue_lo<ACT_HID>(d, tmem, sbase + S_SLOT);
+          um_commit(bar_mma);
+          um_commit(bar_free);
+          dsel ^= 1;
+          UM_STAMP(pr, l * 8 + 6);
+          um_wait(bar_free, ph_free); ph_free ^= 1;                    // the MMAs have read the slot
+          UM_STAMP(pr, l * 8 + 7);
+          if (l == 1) {
+            mbar_expect_tx(bar_lo, IMG);
+            bulk_g2s(um_smem + S_SLOT, wimg + G_W2LO, IMG, bar_lo);
+          }
+        }
       }
     }
-    if (row < rows_total) {
-      // dVel = net(x) * vel_std   (go1.py:102-105); leg = row % 4
-#pragma unroll
-      for (int o = 0; o < ACT_LEG_DOF; ++o)
-        dvel[(size_t)row * ACT_LEG_DOF + o] = (p[o] + C_B3(o)) * norm[3 * ACT_DOF + (row % ACT_LEGS) * ACT_LEG_DOF + o];
+    __syncwarp();
+  } else {
+    // ---------------- epilogue warps: thread = row; warps e and e+4 share a lane quadrant ----------------
+    // and split every 32-column group between them (16 columns each), so that a group is ready for the
+    // tensor core after one eighth of the layer's epilogue work
+    const int q = warp & 3, half = warp >> 2;
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    uint32_t ph_mma = 0, dsel = 0;
+    float2 xin[ACT_IN / 2];
+    if (half == 0 && (int)blockIdx.x < num_tiles) {
+      um_fetch_inputs(xin, model_ins, blockIdx.x * UM_ROWS + q * 32 + lane, rows_total);
+      um_stage_inputs(trow, xin);
+      um_fence_before();
+      __syncwarp();
+      if (lane == 0) um_arrive(bar_in);
     }
-    // D is read out before the next tile's layer 0 overwrites it (the __syncthreads after the A stores)
-    um_fence_before();
+#define UM_GROUP_DONE(g)                   \
+  do {                                     \
+    um_fence_before();                     \
+    __syncwarp();                          \
+    if (lane == 0) um_arrive(bar_a + (g)); \
+    UM_STAMP(pr, pb + l * 5 + 1 + (g));    \
+  } while (0)
+#define UM_HIDDEN_LAYER(L, H)                                           \
+  do {                                                                  \
+    um_epilogue_group<L, H, 0>(trow, dsel * ACT_HID); UM_GROUP_DONE(0); \
+    um_epilogue_group<L, H, 1>(trow, dsel * ACT_HID); UM_GROUP_DONE(1); \
+    um_epilogue_group<L, H, 2>(trow, dsel * ACT_HID); UM_GROUP_DONE(2); \
+    um_epilogue_group<L, H, 3>(trow, dsel * ACT_HID); UM_GROUP_DONE(3); \
+  } while (0)
+    for (int tile = blockIdx.x, it = 0; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int row = tile * UM_ROWS + q * 32 + lane;
+      const int next = tile + gridDim.x;
+      const bool pr = blockIdx.x == 0 && it == 3 && lane == 0 && q == 0;
+      const int pb = 32 + half * 16;
+      (void)pr; (void)pb;
+      // the next tile's inputs travel while this tile's epilogues run
+      if (half == 0 && next < num_tiles) um_fetch_inputs(xin, model_ins, next * UM_ROWS + q * 32 + lane, rows_total);
+#pragma unroll 1
+      for (int l = 0; l < 2; ++l) {
+        um_wait(bar_mma, ph_mma); ph_mma ^= 1;
+        __syncwarp();
+        um_fence_after();
+        UM_STAMP(pr, pb + l * 5);
+        if (half == 0) {
+          if (l == 0) UM_HIDDEN_LAYER(0, 0); else UM_HIDDEN_LAYER(1, 0);
+        } else {
+          if (l == 0) UM_HIDDEN_LAYER(0, 1); else UM_HIDDEN_LAYER(1, 1);
+        }
+        dsel ^= 1;
+      }
+      um_wait(bar_mma, ph_mma); ph_mma ^= 1;
+      __syncwarp();
+      um_fence_after();
+      UM_STAMP(pr, pb + 10);
+      // A is free again: the lower half stages the next tile's inputs so that its layer 0 runs under this epilogue
+      if (half == 0 && next < num_tiles) {
+        um_stage_inputs(trow, xin);
+        um_fence_before();
+        __syncwarp();
+        if (lane == 0) um_arrive(bar_in);
+      }
+      UM_STAMP(pr, pb + 11);
+      float p[ACT_LEG_DOF] = {0.f, 0.f, 0.f};
+      if (half == 0) {
+        um_final_group<0, 0>(trow, dsel * ACT_HID, p); um_final_group<0, 1>(trow, dsel * ACT_HID, p);
+        um_final_group<0, 2>(trow, dsel * ACT_HID, p); um_final_group<0, 3>(trow, dsel * ACT_HID, p);
+      } else {
+        um_final_group<1, 0>(trow, dsel * ACT_HID, p); um_final_group<1, 1>(trow, dsel * ACT_HID, p);
+        um_final_group<1, 2>(trow, dsel * ACT_HID, p); um_final_group<1, 3>(trow, dsel * ACT_HID, p);
+      }
+      UM_STAMP(pr, pb + 12);
+      um_fence_before();
+      __syncwarp();
+      if (lane == 0) um_arrive(bar_fin);
+      dsel ^= 1;
+      // the two column halves of a row meet through shared memory
+      if (half == 1) {
+#pragma unroll
+        for (int o = 0; o < ACT_LEG_DOF; ++o) scratch[(q * 32 + lane) * ACT_LEG_DOF + o] = p[o];
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(UM_EPI_WARPS * 32) : "memory");
+      if (half == 0 && row < rows_total) {
+        // dVel = net(x) * vel_std   (go1.py:102-105); leg = row % 4
+#pragma unroll
+        for (int o = 0; o < ACT_LEG_DOF; ++o)
+          dvel[(size_t)row * ACT_LEG_DOF + o] = (p[o] + scratch[(q * 32 + lane) * ACT_LEG_DOF + o] + C_B3(o)) *
+                                                norm[3 * ACT_DOF + (row % ACT_LEGS) * ACT_LEG_DOF + o];
+      }
+    }
+#undef UM_HIDDEN_LAYER
+#undef UM_GROUP_DONE
   }
-  if (tid == 0 && !resident) um_wait(bar_res, 0);    // never exit with a bulk copy in flight
   um_fence_before();
   __syncthreads();
-  if (warp == 0) um_tmem_free(tmem, T_COLS);
+  if (warp == UM_EPI_WARPS) um_tmem_free(tmem, T_COLS);
 }
 
 extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const float* norm,
@@ -349,5 +489,19 @@ extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const flo
   const int grid = tiles < sms ? tiles : sms;
   LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S_TOTAL));
   lgk_act_mlp_umma_kernel<<<grid, UM_THREADS, S_TOTAL, st>>>(rows, model_ins, images[dev], norm, dvel);
+#ifdef UM_PROFILE
+  if (getenv("LGK_UMMA_PROFILE")) {
+    long long h[64];
+    cudaStreamSynchronize(st);
+    cudaMemcpyFromSymbol(h, um_prof, sizeof(h));
+    fprintf(stderr, "umma profile, cycles from tile start\n ctl  (in | L1: a0 a1 a2 a3 hi-issued lo-landed committed done | L2 ...):");
+    for (int i = 1; i < 24; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
+    fprintf(stderr, "\n epi half0 (mma0 g0 g1 g2 g3 | mma1 g0 g1 g2 g3 | mma2 staged fin):");
+    for (int i = 32; i < 45; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
+    fprintf(stderr, "\n epi half1:");
+    for (int i = 48; i < 61; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
+    fprintf(stderr, "\n");
+  }
+#endif
   return (int)cudaGetLastError();
 }
