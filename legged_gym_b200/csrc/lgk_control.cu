@@ -184,29 +184,57 @@ extern "C" int lgk_compute_torques_impl(const LgkConsts* c, const float* actions
 #define ACT_IN (2 * ACT_LEG_DOF * ACT_HIST)   // 30
 #define ACT_HID 128
 
-// history shift + pack: one thread per (env, joint)
-__global__ void lgk_act_hist_kernel(int N, const float* __restrict__ actions, const float* __restrict__ dof_state,
-                                    float* __restrict__ pe_hist, float* __restrict__ v_hist,
-                                    float* __restrict__ model_ins, const float* __restrict__ norm) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N * ACT_DOF) return;
-  const int j = i % ACT_DOF;
-  const float2 s = __ldg(reinterpret_cast<const float2*>(dof_state) + i);
-  // pos_err uses the RAW action, not the scaled one (go1.py:81)
-  const float pe = __fdiv_rn(sub_rn(sub_rn(__ldg(actions + i), s.x), norm[j]), norm[ACT_DOF + j]);
-  const float vs = __fdiv_rn(sub_rn(s.y, norm[2 * ACT_DOF + j]), norm[3 * ACT_DOF + j]);
-  float* ph = pe_hist + (size_t)i * ACT_HIST;
-  float* vh = v_hist + (size_t)i * ACT_HIST;
-  float* mi = model_ins + (size_t)(i / ACT_DOF) * (ACT_DOF * 2 * ACT_HIST) + j * 2 * ACT_HIST;
-#pragma unroll
-  for (int k = 0; k < ACT_HIST; ++k) {
-    const float a = (k < ACT_HIST - 1) ? ph[k + 1] : pe;   // drop the oldest, append the newest
-    const float b = (k < ACT_HIST - 1) ? vh[k + 1] : vs;
-    ph[k] = a;
-    vh[k] = b;
-    mi[k] = a;
-    mi[ACT_HIST + k] = b;
+// history shift + pack: one thread per (env, joint).  A thread owns 5 + 5 history floats and 10 floats of
+// model_ins, 20 / 40 B apart from its neighbour's: the CTA's slices of the three arrays are contiguous, so they
+// move between HBM and shared memory as float4 and the threads do their stride-5 / stride-10 work there.
+#define HIST_THREADS 256
+__global__ void __launch_bounds__(HIST_THREADS)
+lgk_act_hist_kernel(int N, const float* __restrict__ actions, const float* __restrict__ dof_state,
+                    float* __restrict__ pe_hist, float* __restrict__ v_hist, float* __restrict__ model_ins,
+                    const float* __restrict__ norm) {
+  __shared__ __align__(16) float s_pe[HIST_THREADS * ACT_HIST];
+  __shared__ __align__(16) float s_v[HIST_THREADS * ACT_HIST];
+  __shared__ __align__(16) float s_mi[HIST_THREADS * 2 * ACT_HIST];
+  const int total = N * ACT_DOF;                       // a multiple of 4, and so is every CTA's first index
+  const int i0 = blockIdx.x * HIST_THREADS, tid = threadIdx.x;
+  const int cnt = min(HIST_THREADS, total - i0);
+  const int nv4 = cnt * ACT_HIST / 4;                  // float4s of this CTA's history slices
+  const float4* pe4 = reinterpret_cast<const float4*>(pe_hist + (size_t)i0 * ACT_HIST);
+  const float4* v4 = reinterpret_cast<const float4*>(v_hist + (size_t)i0 * ACT_HIST);
+  for (int t = tid; t < nv4; t += HIST_THREADS) {
+    reinterpret_cast<float4*>(s_pe)[t] = pe4[t];
+    reinterpret_cast<float4*>(s_v)[t] = v4[t];
   }
+  __syncthreads();
+  const int i = i0 + tid;
+  if (tid < cnt) {
+    const int j = i % ACT_DOF;
+    const float2 s = __ldg(reinterpret_cast<const float2*>(dof_state) + i);
+    // pos_err uses the RAW action, not the scaled one (go1.py:81)
+    const float pe = __fdiv_rn(sub_rn(sub_rn(__ldg(actions + i), s.x), norm[j]), norm[ACT_DOF + j]);
+    const float vs = __fdiv_rn(sub_rn(s.y, norm[2 * ACT_DOF + j]), norm[3 * ACT_DOF + j]);
+    float* ph = s_pe + tid * ACT_HIST;
+    float* vh = s_v + tid * ACT_HIST;
+    float* mi = s_mi + tid * 2 * ACT_HIST;             // model_ins[env][j][0..4] = pos_err window, [5..9] = velocity window
+#pragma unroll
+    for (int k = 0; k < ACT_HIST; ++k) {
+      const float a = (k < ACT_HIST - 1) ? ph[k + 1] : pe;   // drop the oldest, append the newest
+      const float b = (k < ACT_HIST - 1) ? vh[k + 1] : vs;
+      ph[k] = a;
+      vh[k] = b;
+      mi[k] = a;
+      mi[ACT_HIST + k] = b;
+    }
+  }
+  __syncthreads();
+  float4* pe4o = reinterpret_cast<float4*>(pe_hist + (size_t)i0 * ACT_HIST);
+  float4* v4o = reinterpret_cast<float4*>(v_hist + (size_t)i0 * ACT_HIST);
+  float4* mi4o = reinterpret_cast<float4*>(model_ins + (size_t)i0 * 2 * ACT_HIST);
+  for (int t = tid; t < nv4; t += HIST_THREADS) {
+    pe4o[t] = reinterpret_cast<const float4*>(s_pe)[t];
+    v4o[t] = reinterpret_cast<const float4*>(s_v)[t];
+  }
+  for (int t = tid; t < 2 * nv4; t += HIST_THREADS) mi4o[t] = reinterpret_cast<const float4*>(s_mi)[t];
 }
 
 // MLP 30 -> 128 -> 128 -> 128 -> 3 (tanh), fp32 SIMT; weights resident in shared memory,
@@ -330,7 +358,7 @@ extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const floa
                                          float* v_hist, float* model_ins, const float* weights, const float* norm,
                                          float* dvel, cudaStream_t st) {
   const int n = N * ACT_DOF;
-  lgk_act_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
+  lgk_act_hist_kernel<<<(n + HIST_THREADS - 1) / HIST_THREADS, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int rows = N * ACT_LEGS;
   // LGK_MLP_KERNEL picks the MLP kernel (read per call, cheap, so that one process can time / test them all):

@@ -195,6 +195,7 @@ __device__ __forceinline__ void um_wait(uint64_t* bar, uint32_t parity) {
 
 #ifdef UM_PROFILE
 __device__ long long um_prof[64];
+__device__ long long um_prof_cta[160][4];   // per CTA: start, resident images landed, end (ctl thread), tiles
 #define UM_STAMP(cond, i) do { if (cond) um_prof[i] = clock64(); } while (0)
 #else
 #define UM_STAMP(cond, i) do { } while (0)
@@ -226,12 +227,15 @@ __device__ __forceinline__ void um_issue_hi(uint32_t d, uint32_t tmem, uint32_t 
     um_mma(d, tmem + T_AHI + ks * 8, bh, 1u);
   }
 }
-// the w_lo pass: D += a_hi*w_lo over all k-steps
+// the w_lo pass: D += a_hi*w_lo over k-steps [ks0, ks0+n)
 template <int K>
-__device__ __forceinline__ void um_issue_lo(uint32_t d, uint32_t tmem, uint32_t w_lo_smem) {
+__device__ __forceinline__ void um_issue_lo(uint32_t d, uint32_t tmem, uint32_t w_lo_smem, int ks0, int n) {
   constexpr uint32_t SBO = (K / 4) * 128;
 #pragma unroll
-  for (int ks = 0; ks < K / 8; ++ks) um_mma(d, tmem + T_AHI + ks * 8, um_desc(w_lo_smem + ks * 256, SBO), 1u);
+  for (int i = 0; i < n; ++i) {
+    const int ks = ks0 + i;
+    um_mma(d, tmem + T_AHI + ks * 8, um_desc(w_lo_smem + ks * 256, SBO), 1u);
+  }
 }
 
 // hidden-layer epilogue for this thread's row, 16 columns at col0 = 32G + 16*HALF: D -> tanh(D + b) -> hi / lo
@@ -324,7 +328,13 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
       bulk_g2s(um_smem + S_W1HI, wimg + G_W1HI, IMG, bar_res);
       bulk_g2s(um_smem + S_W2HI, wimg + G_W2HI, IMG, bar_res);
       uint32_t ph_in = 0, ph_lo = 0, ph_free = 0, ph_fin = 0, ph_a = 0, dsel = 0;
+#ifdef UM_PROFILE
+      um_prof_cta[blockIdx.x][0] = clock64();
+#endif
       um_wait(bar_res, 0);
+#ifdef UM_PROFILE
+      um_prof_cta[blockIdx.x][1] = clock64();
+#endif
       for (int tile = blockIdx.x, it = 0; tile < num_tiles; tile += gridDim.x, ++it) {
         const bool pr = blockIdx.x == 0 && it == 3;
         (void)pr;
@@ -337,7 +347,7 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
         UM_STAMP(pr, 1);
         bool first = true;
         um_issue_hi<UM_K0>(tmem + dsel * ACT_HID, tmem, sbase + S_W0HI, 0, UM_K0 / 8, first);
-        um_issue_lo<UM_K0>(tmem + dsel * ACT_HID, tmem, sbase + S_W0LO);
+        um_issue_lo<UM_K0>(tmem + dsel * ACT_HID, tmem, sbase + S_W0LO, 0, UM_K0 / 8);
         um_commit(bar_mma);
         dsel ^= 1;
 #pragma unroll 1
@@ -347,19 +357,25 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
           const uint32_t d = tmem + dsel * ACT_HID;
           const uint32_t w_hi = sbase + (l == 1 ? S_W1HI : S_W2HI);
           first = true;
-          // the w_hi passes follow the epilogue of the layer before, 32 columns (4 k-steps) at a time
+          // all three passes follow the epilogue of the layer before, 32 columns (4 k-steps) at a time; the w_lo
+          // pass joins from the second group on (the streamed image has had a group's time more to land), so
+          // only 12 MMAs remain to be run after the last group arrives
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             um_wait(bar_a + g, ph_a);
             um_fence_after();
             UM_STAMP(pr, l * 8 + g);
             um_issue_hi<ACT_HID>(d, tmem, w_hi, g * 4, 4, first);
+            if (g == 1) {
+              um_wait(bar_lo, ph_lo); ph_lo ^= 1;
+              UM_STAMP(pr, l * 8 + 5);
+              um_issue_lo<ACT_HID>(d, tmem, sbase + S_SLOT, 0, 8);
+            } else if (g > 1) {
+              um_issue_lo<ACT_HID>(d, tmem, sbase + S_SLOT, g * 4, 4);
+            }
           }
           ph_a ^= 1;
           UM_STAMP(pr, l * 8 + 4);
-          um_wait(bar_lo, ph_lo); ph_lo ^= 1;
-          UM_STAMP(pr, l * 8 + 5);
-          um_issue_lo<ACT_HID>(d, tmem, sbase + S_SLOT);
           um_commit(bar_mma);
           um_commit(bar_free);
           dsel ^= 1;
@@ -371,6 +387,10 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
             bulk_g2s(um_smem + S_SLOT, wimg + G_W2LO, IMG, bar_lo);
           }
         }
+#ifdef UM_PROFILE
+        um_prof_cta[blockIdx.x][2] = clock64();
+        um_prof_cta[blockIdx.x][3] = it + 1;
+#endif
       }
     }
     __syncwarp();
@@ -500,7 +520,16 @@ extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const flo
     for (int i = 32; i < 45; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
     fprintf(stderr, "\n epi half1:");
     for (int i = 48; i < 61; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
-    fprintf(stderr, "\n");
+    long long c[160][4];
+    cudaMemcpyFromSymbol(c, um_prof_cta, sizeof(c));
+    long long tmax = 0, tsum = 0, rmax = 0, per_tile_max = 0, per_tile_min = 1ll << 60;
+    for (int b = 0; b < grid; ++b) {
+      const long long t = c[b][2] - c[b][0], r = c[b][1] - c[b][0], pt = (c[b][2] - c[b][1]) / (c[b][3] ? c[b][3] : 1);
+      tmax = t > tmax ? t : tmax; tsum += t; rmax = r > rmax ? r : rmax;
+      per_tile_max = pt > per_tile_max ? pt : per_tile_max; per_tile_min = pt < per_tile_min ? pt : per_tile_min;
+    }
+    fprintf(stderr, "\n per CTA: cycles start->end max %lld avg %lld; resident images landed after max %lld; cycles per tile min %lld max %lld\n",
+            tmax, tsum / grid, rmax, per_tile_min, per_tile_max);
   }
 #endif
   return (int)cudaGetLastError();
