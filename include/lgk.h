@@ -273,7 +273,9 @@ int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* d
 /* Go1 / Aliengo actuator net (go1.py:79-107): shifts the 5-deep joint-error / velocity
  * histories, packs model_ins [N,120] and evaluates the 30-128-128-128-3 tanh MLP per leg.
  * weights: fp32 blob W0[128,30] b0[128] W1[128,128] b1 W2[128,128] b2 W3[3,128] b3[3].
- * norm: pos_err_mean[12] pos_err_std[12] vel_mean[12] vel_std[12]. */
+ * norm: pos_err_mean[12] pos_err_std[12] vel_mean[12] vel_std[12].
+ * num_envs == 0 is the set-up call: it launches nothing and allocates the MLP kernel's per-device workspace, so
+ * that later calls may be made inside a CUDA-graph capture (the first call with envs does the same otherwise). */
 int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state,
                          float* pos_err_hist, float* vel_hist, float* model_ins,
                          const float* weights, const float* norm, float* dvel_out, void* stream);

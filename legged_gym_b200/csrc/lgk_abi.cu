@@ -147,11 +147,11 @@ int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* d
 int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state, float* pos_err_hist,
                          float* vel_hist, float* model_ins, const float* weights, const float* norm, float* dvel_out,
                          void* stream) {
-  if (num_envs <= 0) return LGK_ERR_DIM;
+  if (num_envs < 0) return LGK_ERR_DIM;
   if (!actions || !dof_state || !pos_err_hist || !vel_hist || !model_ins || !weights || !norm || !dvel_out)
     return LGK_ERR_NULL;
   if ((reinterpret_cast<uintptr_t>(dof_state) & 7u) != 0) return LGK_ERR_ALIGN;
-  g_launches += 2;
+  if (num_envs > 0) g_launches += 2;   /* zero envs: set-up only, nothing is launched */
   return lgk_actuator_advance_impl(num_envs, actions, dof_state, pos_err_hist, vel_hist, model_ins, weights, norm,
                                    dvel_out, (cudaStream_t)stream);
 }

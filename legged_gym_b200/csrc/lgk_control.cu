@@ -357,19 +357,22 @@ extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const flo
 extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
                                          float* v_hist, float* model_ins, const float* weights, const float* norm,
                                          float* dvel, cudaStream_t st) {
-  const int n = N * ACT_DOF;
-  lgk_act_hist_kernel<<<(n + HIST_THREADS - 1) / HIST_THREADS, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
-  LGK_CUDA_RETURN_IF(cudaGetLastError());
-  const int rows = N * ACT_LEGS;
   // LGK_MLP_KERNEL picks the MLP kernel (read per call, cheap, so that one process can time / test them all):
-  //   "umma" tcgen05 3xTF32, activations + accumulator in tensor memory (lgk_mlp_umma.cu)
-  //   "mma"  warp-level 3xTF32 mma.sync (lgk_mlp_tc.cu; the default)      "ffma" the fp32 FFMA kernel below
+  //   "umma" tcgen05 3xTF32, activations + accumulator in tensor memory (lgk_mlp_umma.cu; the default)
+  //   "mma"  warp-level 3xTF32 mma.sync (lgk_mlp_tc.cu)      "ffma" the fp32 FFMA kernel below
   // LGK_MLP_FFMA=1 is the older spelling of "ffma".
   const char* e = getenv("LGK_MLP_FFMA");
   const char* k = getenv("LGK_MLP_KERNEL");
   const bool ffma = (e && e[0] == '1') || (k && k[0] == 'f');
-  if (!ffma && k && k[0] == 'u') return lgk_act_mlp_umma_impl(rows, model_ins, weights, norm, dvel, st);
-  if (!ffma) return lgk_act_mlp_tc_impl(rows, model_ins, weights, norm, dvel, st);
+  const bool mma = !ffma && k && k[0] == 'm';
+  // zero envs: set-up only (the tcgen05 kernel's per-device workspace must exist before a stream capture)
+  if (N <= 0) return (ffma || mma) ? 0 : lgk_act_mlp_umma_impl(0, model_ins, weights, norm, dvel, st);
+  const int n = N * ACT_DOF;
+  lgk_act_hist_kernel<<<(n + HIST_THREADS - 1) / HIST_THREADS, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
+  LGK_CUDA_RETURN_IF(cudaGetLastError());
+  const int rows = N * ACT_LEGS;
+  if (mma) return lgk_act_mlp_tc_impl(rows, model_ins, weights, norm, dvel, st);
+  if (!ffma) return lgk_act_mlp_umma_impl(rows, model_ins, weights, norm, dvel, st);
   const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);

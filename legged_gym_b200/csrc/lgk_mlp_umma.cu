@@ -498,16 +498,21 @@ extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const flo
   int dev = 0, sms = 148;
   LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
-  if (!images[dev]) {   // first call on this device (must not be inside a stream capture)
+  if (!images[dev]) {   // first call on this device: allocate the image workspace (not allowed inside a stream capture;
+                        // lgk_actuator_advance with zero envs does just this, the Go1 env calls it when it is built)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    LGK_CUDA_RETURN_IF(cudaStreamIsCapturing(st, &cap));
+    if (cap != cudaStreamCaptureStatusNone) return (int)cudaErrorStreamCaptureUnsupported;
     LGK_CUDA_RETURN_IF(cudaMalloc(&images[dev], G_TOTAL));
     LGK_CUDA_RETURN_IF(cudaGetSymbolAddress(reinterpret_cast<void**>(&cblock[dev]), c_um));
+    LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S_TOTAL));
   }
+  if (rows <= 0) return 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   lgk_umma_prep_kernel<<<ACT_HID * ACT_HID / 256, 256, 0, st>>>(weights, reinterpret_cast<float*>(images[dev]), cblock[dev]);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int tiles = (rows + UM_ROWS - 1) / UM_ROWS;
   const int grid = tiles < sms ? tiles : sms;
-  LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S_TOTAL));
   lgk_act_mlp_umma_kernel<<<grid, UM_THREADS, S_TOTAL, st>>>(rows, model_ins, images[dev], norm, dvel);
 #ifdef UM_PROFILE
   if (getenv("LGK_UMMA_PROFILE")) {

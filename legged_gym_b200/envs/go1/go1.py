@@ -55,6 +55,13 @@ class Go1(LeggedRobot):
         self._act_norm = torch.cat([self.pos_err_mean, self.pos_err_std, self.vel_mean, self.vel_std]).contiguous()
         if getattr(self.cfg.control, "use_actuator_network", False):
             self.actuator_weights = self._load_actuator_weights().to(self.device)
+            if self.device.startswith("cuda") if isinstance(self.device, str) else self.device.type == "cuda":
+                # zero envs = set-up only: the tcgen05 MLP kernel allocates its per-device weight-image workspace
+                # here, so that the first real call may already sit inside a CUDA-graph capture
+                P = _lgk.ptr
+                _lgk.check("lgk_actuator_advance", self._kernels().lgk_actuator_advance(
+                    0, P(self.dVel), P(self.dof_state), P(self.pos_err_buffs), P(self.vel_buffs), P(self.model_ins),
+                    P(self.actuator_weights), P(self._act_norm), P(self.dVel), _lgk.current_stream(self.device)))
 
     def _load_actuator_weights(self) -> torch.Tensor:
         seed = getattr(self.cfg.control, "actuator_net_random_seed", None)

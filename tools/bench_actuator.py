@@ -25,6 +25,8 @@ flop = 2 * (30 * 128 + 128 * 128 + 128 * 128 + 128 * 3) * 4 * N
 p = torch.cuda.get_device_properties(0)
 peak = p.multi_processor_count * 128 * 2 * 1.965e9
 import os as _os
-print("kernel:", "fp32 FFMA" if _os.environ.get("LGK_MLP_FFMA") == "1" else "3xTF32 tensor pipe (mma.sync m16n8k8)")
+_k = "ffma" if _os.environ.get("LGK_MLP_FFMA") == "1" else _os.environ.get("LGK_MLP_KERNEL", "umma")
+print("kernel:", {"f": "fp32 FFMA", "m": "3xTF32 tensor pipe (mma.sync m16n8k8)",
+                  "u": "3xTF32 tcgen05.mma kind::tf32, activations + accumulator in tensor memory"}[_k[0]])
 print(f"actuator substep, {N} envs: {ms * 1e3:.1f} us  {flop / ms / 1e9:.2f} TFLOP/s fp32 = {100 * flop / (ms * 1e-3) / peak:.1f}% of the FFMA peak "
       f"({peak / 1e12:.1f} TFLOP/s at 1965 MHz)  -> {N / ms * 1e3:.3e} env-substeps/s")
