@@ -42,6 +42,9 @@ UNIT = "env-steps/s"
 
 def workload_name(envs_per_gpu, decimation=4):
     """The one workload both arms name (BASELINE.json: Go1 rough, 4096-65536 envs/GPU)."""
+    if SCENARIO != "go1_rough_full":      # --scenario: another BASELINE.json config, e.g. configs[2] (actuator net)
+        return (f"scenario {SCENARIO} (legged_gym_b200/utils/scenarios.py), {envs_per_gpu} envs/GPU, "
+                f"x{decimation} control substeps + fused post_physics_step")
     return (f"Go1 rough terrain, 187-point height scan, full reward set (20 terms + termination), terrain "
             f"curriculum, {envs_per_gpu} envs/GPU, position control x{decimation} substeps + fused post_physics_step")
 
@@ -405,6 +408,7 @@ def run_reference(args):
 
 
 def main():
+    global SCENARIO
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=400)
@@ -413,7 +417,11 @@ def main():
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
+    ap.add_argument("--scenario", default=SCENARIO,
+                    help="parity-test scenario to time instead of the headline one, e.g. go1_rough_actuator "
+                         "(BASELINE.json configs[2], with --envs 16384)")
     args = ap.parse_args()
+    SCENARIO = args.scenario
     if args.impl == "reference":
         run_reference(args)
     else:
