@@ -183,6 +183,7 @@ extern "C" int lgk_compute_torques_impl(const LgkConsts* c, const float* actions
 #define ACT_DOF (ACT_LEGS * ACT_LEG_DOF)
 #define ACT_IN (2 * ACT_LEG_DOF * ACT_HIST)   // 30
 #define ACT_HID 128
+#include "lgk_umma_prep.cuh"   // after the ACT_* constants above (it only defines what is missing)
 
 // history shift + pack: one thread per (env, joint).  A thread owns 5 + 5 history floats and 10 floats of
 // model_ins, 20 / 40 B apart from its neighbour's: the CTA's slices of the three arrays are contiguous, so they
@@ -191,7 +192,13 @@ extern "C" int lgk_compute_torques_impl(const LgkConsts* c, const float* actions
 __global__ void __launch_bounds__(HIST_THREADS)
 lgk_act_hist_kernel(int N, const float* __restrict__ actions, const float* __restrict__ dof_state,
                     float* __restrict__ pe_hist, float* __restrict__ v_hist, float* __restrict__ model_ins,
-                    const float* __restrict__ norm) {
+                    const float* __restrict__ norm, int hist_ctas, const float* __restrict__ weights,
+                    float* __restrict__ img, float* __restrict__ cblock) {
+  if ((int)blockIdx.x >= hist_ctas) {
+    // CTAs past the history work build the tcgen05 MLP's weight images (lgk_umma_prep.cuh) under it
+    lgk_umma_prep_element(((int)blockIdx.x - hist_ctas) * HIST_THREADS + (int)threadIdx.x, weights, img, cblock);
+    return;
+  }
   __shared__ __align__(16) float s_pe[HIST_THREADS * ACT_HIST];
   __shared__ __align__(16) float s_v[HIST_THREADS * ACT_HIST];
   __shared__ __align__(16) float s_mi[HIST_THREADS * 2 * ACT_HIST];
@@ -351,8 +358,8 @@ lgk_act_mlp_kernel(int rows_total, const float* __restrict__ model_ins, const fl
 extern "C" int lgk_act_mlp_tc_impl(int rows, const float* model_ins, const float* weights, const float* norm,
                                    float* dvel, cudaStream_t st);
 
-extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const float* norm,
-                                     float* dvel, cudaStream_t st);
+extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* norm, float* dvel, cudaStream_t st);
+extern "C" int lgk_umma_workspace(cudaStream_t st, float** img, float** cblock);
 
 extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
                                          float* v_hist, float* model_ins, const float* weights, const float* norm,
@@ -365,14 +372,23 @@ extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const floa
   const char* k = getenv("LGK_MLP_KERNEL");
   const bool ffma = (e && e[0] == '1') || (k && k[0] == 'f');
   const bool mma = !ffma && k && k[0] == 'm';
+  const bool umma = !ffma && !mma;
+  float *img = nullptr, *cblock = nullptr;
+  if (umma) {
+    const int rc = lgk_umma_workspace(st, &img, &cblock);
+    if (rc) return rc;
+  }
   // zero envs: set-up only (the tcgen05 kernel's per-device workspace must exist before a stream capture)
-  if (N <= 0) return (ffma || mma) ? 0 : lgk_act_mlp_umma_impl(0, model_ins, weights, norm, dvel, st);
+  if (N <= 0) return 0;
   const int n = N * ACT_DOF;
-  lgk_act_hist_kernel<<<(n + HIST_THREADS - 1) / HIST_THREADS, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm);
+  const int hist_ctas = (n + HIST_THREADS - 1) / HIST_THREADS;
+  const int prep_ctas = umma ? um::PREP_ELEMENTS / HIST_THREADS : 0;
+  lgk_act_hist_kernel<<<hist_ctas + prep_ctas, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm,
+                                                                     hist_ctas, weights, img, cblock);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int rows = N * ACT_LEGS;
   if (mma) return lgk_act_mlp_tc_impl(rows, model_ins, weights, norm, dvel, st);
-  if (!ffma) return lgk_act_mlp_umma_impl(rows, model_ins, weights, norm, dvel, st);
+  if (umma) return lgk_act_mlp_umma_impl(rows, model_ins, norm, dvel, st);
   const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);

@@ -28,22 +28,14 @@
 #include <cstdio>
 #include <cstdlib>
 
-#define ACT_LEGS 4
-#define ACT_LEG_DOF 3
-#define ACT_DOF 12
-#define ACT_IN 30
-#define ACT_HID 128
+#include "lgk_umma_prep.cuh"
 
 namespace {
+using namespace um;
 constexpr int UM_ROWS = 128;
 constexpr int UM_EPI_WARPS = 8;                        // two per lane quadrant, each takes half of the columns
 constexpr int UM_THREADS = (UM_EPI_WARPS + 1) * 32;      // + the control warp (TMA and MMA issue)
-constexpr int UM_K0 = 32;                               // layer-0 reduction length, 30 padded to 4 k-steps
-constexpr uint32_t IMG0 = ACT_HID * UM_K0 * 4;          // 16 KB
-constexpr uint32_t IMG = ACT_HID * ACT_HID * 4;         // 64 KB
-// global image buffer: W0hi W0lo W1hi W1lo W2hi W2lo
-constexpr uint32_t G_W0HI = 0, G_W0LO = IMG0, G_W1HI = 2 * IMG0, G_W1LO = G_W1HI + IMG, G_W2HI = G_W1LO + IMG,
-                   G_W2LO = G_W2HI + IMG, G_TOTAL = G_W2LO + IMG;
+constexpr int UM_K0 = K0;
 // shared memory: W0hi W0lo W1hi W2hi slot
 constexpr uint32_t S_W0HI = 0, S_W0LO = IMG0, S_W1HI = 2 * IMG0, S_W2HI = S_W1HI + IMG, S_SLOT = S_W2HI + IMG,
                    S_BARS = S_SLOT + IMG, S_TOTAL = S_BARS + 128 + UM_ROWS * 3 * 4;
@@ -55,60 +47,10 @@ constexpr uint32_t UM_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((ACT_HID >> 
 
 // biases of the three hidden layers times 2*log2(e) (the epilogue's tanh takes its argument in that scale),
 // W3 [3][128], b3 [3] (+1 pad) -- written by the prep kernel
-__constant__ float c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + 4];
+__constant__ float c_um[um::CBLOCK_FLOATS];
 #define C_BS(l, col) c_um[(l) * ACT_HID + (col)]
 #define C_W3(o, col) c_um[3 * ACT_HID + (o) * ACT_HID + (col)]
 #define C_B3(o) c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + (o)]
-
-__device__ __forceinline__ void um_split(float v, uint32_t& hi, uint32_t& lo) {
-  hi = (__float_as_uint(v) + 0x1000u) & 0xffffe000u;
-  lo = (__float_as_uint(v - __uint_as_float(hi)) + 0x1000u) & 0xffffe000u;
-}
-
-// element (n, k) of an [128][K] K-major operand inside its no-swizzle UMMA image, in floats
-__device__ __forceinline__ uint32_t um_img_index(int n, int k, int K) {
-  return (uint32_t)(((n >> 3) * (K >> 2) + (k >> 2)) * 32 + (n & 7) * 4 + (k & 3));
-}
-
-__global__ void lgk_umma_prep_kernel(const float* __restrict__ weights, float* __restrict__ img,
-                                     float* __restrict__ cblock) {
-  const float* W0 = weights;
-  const float* B0 = W0 + ACT_HID * ACT_IN;
-  const float* W1 = B0 + ACT_HID;
-  const float* B1 = W1 + ACT_HID * ACT_HID;
-  const float* W2 = B1 + ACT_HID;
-  const float* B2 = W2 + ACT_HID * ACT_HID;
-  const float* W3 = B2 + ACT_HID;
-  const float* B3 = W3 + ACT_LEG_DOF * ACT_HID;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t* out = reinterpret_cast<uint32_t*>(img);
-  if (i < ACT_HID * UM_K0) {
-    const int n = i / UM_K0, k = i % UM_K0;
-    uint32_t hi, lo;
-    um_split(k < ACT_IN ? W0[n * ACT_IN + k] : 0.f, hi, lo);
-    const uint32_t at = um_img_index(n, k, UM_K0);
-    out[G_W0HI / 4 + at] = hi;
-    out[G_W0LO / 4 + at] = lo;
-  }
-  if (i < ACT_HID * ACT_HID) {
-    const int n = i >> 7, k = i & 127;
-    const uint32_t at = um_img_index(n, k, ACT_HID);
-    uint32_t hi, lo;
-    um_split(W1[i], hi, lo);
-    out[G_W1HI / 4 + at] = hi;
-    out[G_W1LO / 4 + at] = lo;
-    um_split(W2[i], hi, lo);
-    out[G_W2HI / 4 + at] = hi;
-    out[G_W2LO / 4 + at] = lo;
-  }
-  if (i < ACT_HID) {
-    cblock[i] = B0[i] * 2.885390081777927f;
-    cblock[ACT_HID + i] = B1[i] * 2.885390081777927f;
-    cblock[2 * ACT_HID + i] = B2[i] * 2.885390081777927f;
-  }
-  if (i < ACT_LEG_DOF * ACT_HID) cblock[3 * ACT_HID + i] = W3[i];
-  if (i < ACT_LEG_DOF) cblock[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + i] = B3[i];
-}
 
 // ---- tcgen05 / tensor-memory helpers ---------------------------------------------------------------------
 __device__ __forceinline__ void um_tmem_alloc(uint32_t* slot_smem, uint32_t cols) {
@@ -491,29 +433,39 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
   if (warp == UM_EPI_WARPS) um_tmem_free(tmem, T_COLS);
 }
 
-extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const float* norm,
-                                     float* dvel, cudaStream_t st) {
-  static unsigned char* images[64] = {nullptr};
-  static float* cblock[64] = {nullptr};
-  int dev = 0, sms = 148;
+// The per-device workspace: the weight images (global memory, TMA source) and the address of the constant block.
+// First call on a device allocates; that is not allowed inside a stream capture (lgk_actuator_advance with zero
+// envs does just this, the Go1 env calls it when it is built).
+static unsigned char* g_images[64] = {nullptr};
+static float* g_cblock[64] = {nullptr};
+
+extern "C" int lgk_umma_workspace(cudaStream_t st, float** img, float** cblock) {
+  int dev = 0;
   LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
-  if (!images[dev]) {   // first call on this device: allocate the image workspace (not allowed inside a stream capture;
-                        // lgk_actuator_advance with zero envs does just this, the Go1 env calls it when it is built)
+  if (!g_images[dev]) {
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     LGK_CUDA_RETURN_IF(cudaStreamIsCapturing(st, &cap));
     if (cap != cudaStreamCaptureStatusNone) return (int)cudaErrorStreamCaptureUnsupported;
-    LGK_CUDA_RETURN_IF(cudaMalloc(&images[dev], G_TOTAL));
-    LGK_CUDA_RETURN_IF(cudaGetSymbolAddress(reinterpret_cast<void**>(&cblock[dev]), c_um));
+    LGK_CUDA_RETURN_IF(cudaMalloc(&g_images[dev], G_TOTAL));
+    LGK_CUDA_RETURN_IF(cudaGetSymbolAddress(reinterpret_cast<void**>(&g_cblock[dev]), c_um));
     LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S_TOTAL));
   }
+  *img = reinterpret_cast<float*>(g_images[dev]);
+  *cblock = g_cblock[dev];
+  return 0;
+}
+
+// the MLP on images that are already built for these weights (the history kernel's extra CTAs build them)
+extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* norm, float* dvel, cudaStream_t st) {
+  int dev = 0, sms = 148;
+  LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !g_images[dev]) return (int)cudaErrorInvalidValue;
   if (rows <= 0) return 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  lgk_umma_prep_kernel<<<ACT_HID * ACT_HID / 256, 256, 0, st>>>(weights, reinterpret_cast<float*>(images[dev]), cblock[dev]);
-  LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int tiles = (rows + UM_ROWS - 1) / UM_ROWS;
   const int grid = tiles < sms ? tiles : sms;
-  lgk_act_mlp_umma_kernel<<<grid, UM_THREADS, S_TOTAL, st>>>(rows, model_ins, images[dev], norm, dvel);
+  lgk_act_mlp_umma_kernel<<<grid, UM_THREADS, S_TOTAL, st>>>(rows, model_ins, g_images[dev], norm, dvel);
 #ifdef UM_PROFILE
   if (getenv("LGK_UMMA_PROFILE")) {
     long long h[64];
