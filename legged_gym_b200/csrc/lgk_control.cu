@@ -194,6 +194,7 @@ lgk_act_hist_kernel(int N, const float* __restrict__ actions, const float* __res
                     float* __restrict__ pe_hist, float* __restrict__ v_hist, float* __restrict__ model_ins,
                     const float* __restrict__ norm, int hist_ctas, const float* __restrict__ weights,
                     float* __restrict__ img, float* __restrict__ cblock) {
+  pdl_launch_dependents();   // the MLP kernel behind this one may set itself up on free SMs (it waits before reading)
   if ((int)blockIdx.x >= hist_ctas) {
     // CTAs past the history work build the tcgen05 MLP's weight images (lgk_umma_prep.cuh) under it
     lgk_umma_prep_element(((int)blockIdx.x - hist_ctas) * HIST_THREADS + (int)threadIdx.x, weights, img, cblock);

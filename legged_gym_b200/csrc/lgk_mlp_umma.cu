@@ -261,6 +261,9 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
   um_fence_after();
   const uint32_t tmem = *tmem_slot;
   const int num_tiles = (rows_total + UM_ROWS - 1) / UM_ROWS;
+  // launched behind the history kernel with programmatic serialisation: the set-up above ran under its tail; its
+  // writes (model_ins, the weight images, the constant block) are visible from here
+  pdl_wait();
 
   if (warp == UM_EPI_WARPS) {
     // ---------------- control warp: one thread feeds the TMA engine and the tensor core ----------------
@@ -465,7 +468,8 @@ extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const flo
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int tiles = (rows + UM_ROWS - 1) / UM_ROWS;
   const int grid = tiles < sms ? tiles : sms;
-  lgk_act_mlp_umma_kernel<<<grid, UM_THREADS, S_TOTAL, st>>>(rows, model_ins, g_images[dev], norm, dvel);
+  LGK_CUDA_RETURN_IF(lgk_launch_pdl(lgk_act_mlp_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)S_TOTAL, st, rows, model_ins,
+                                    (const unsigned char*)g_images[dev], norm, dvel));
 #ifdef UM_PROFILE
   if (getenv("LGK_UMMA_PROFILE")) {
     long long h[64];
