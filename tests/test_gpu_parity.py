@@ -670,3 +670,29 @@ def test_step_is_graph_capturable_and_sync_free():
         st.synchronize()
     keep = env.episode_length_buf > 4
     assert keep.any() and torch.equal(env.episode_length_buf[keep], ep0[keep] + 5)
+
+
+def test_actuator_net_is_graph_capturable():
+    """The tcgen05 MLP's per-device workspace is allocated by the env's set-up call (lgk_actuator_advance with zero
+    envs), so the very first substep may already sit inside a CUDA-graph capture; replays equal eager calls bit
+    for bit (history shift included)."""
+    n = 777
+    eager = helpers.make_env("go1_rough_actuator", n, device=DEV)
+    graphed = helpers.make_env("go1_rough_actuator", n, device=DEV)
+    fr = synthetic.make_frames(eager, 1, seed=5)[0]
+    synthetic.load_frame(eager, fr)
+    synthetic.load_frame(graphed, fr)
+    a = fr["actions"].clone()
+    stream = torch.cuda.Stream(DEV)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(stream):
+        with torch.cuda.graph(g, stream=stream):
+            graphed.actuator_advance(a)          # first call with envs on this env: inside the capture
+    torch.cuda.synchronize()
+    assert float(graphed.dVel.abs().sum()) == 0.0   # capture records, it does not run
+    for it in range(3):
+        want = eager.actuator_advance(a).clone()
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(graphed.dVel, want), it
+        assert torch.equal(graphed.pos_err_buffs, eager.pos_err_buffs)
