@@ -30,3 +30,19 @@ print("kernel:", {"f": "fp32 FFMA", "m": "3xTF32 tensor pipe (mma.sync m16n8k8)"
                   "u": "3xTF32 tcgen05.mma kind::tf32, activations + accumulator in tensor memory"}[_k[0]])
 print(f"actuator substep, {N} envs: {ms * 1e3:.1f} us  {flop / ms / 1e9:.2f} TFLOP/s fp32 = {100 * flop / (ms * 1e-3) / peak:.1f}% of the FFMA peak "
       f"({peak / 1e12:.1f} TFLOP/s at 1965 MHz)  -> {N / ms * 1e3:.3e} env-substeps/s")
+
+# roofline of the MLP kernel on the tensor pipe: every product runs as three TF32 passes (layer 0's K = 30 padded to 32);
+# the peak is half the measured dense bf16 rate of MEASURED_PEAKS.json (TF32 runs at half the bf16 rate; the in-kernel
+# micro-benchmark of DESIGN.md section 4 -- 64 cycles per 128x128x8 MMA -- is the same figure at the boost clock)
+import json as _json
+_tf32 = 3 * 2 * (32 * 128 + 128 * 128 + 128 * 128) * 4 * N
+try:
+    _pk = _json.load(open(_os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    _peak, _src = _pk["bf16_tflops_sustained"] / 2, "MEASURED_PEAKS.json bf16_tflops_sustained / 2"
+except Exception:   # noqa: BLE001
+    _peak, _src = 4096 * p.multi_processor_count * 1.965e9 / 1e12, "64 cycles per 128x128x8 TF32 MMA x SMs x 1965 MHz"
+_ach = _tf32 / (ms * 1e-3) / 1e12
+print(_json.dumps({"kernel": _k, "envs": N, "us_per_substep": round(ms * 1e3, 1), "timed": "history kernel + MLP kernel, back to back",
+                   "roofline": {"bound": "tensor", "achieved": round(_ach, 1), "peak": round(_peak, 1), "unit": "TFLOP/s",
+                                "frac": round(_ach / _peak, 3), "peak_source": _src,
+                                "flops": "3 TF32 passes x 2 x (32x128 + 2 x 128x128) per leg-row; the 128->3 layer is on the FMA pipe"}}))
