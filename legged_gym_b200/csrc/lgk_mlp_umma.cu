@@ -145,6 +145,13 @@ __device__ long long um_prof_cta[160][4];   // per CTA: start, resident images l
 __device__ __forceinline__ void um_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// Activation split on three instructions: hi = v truncated to the TF32 mantissa (one LOP3; the remainder v - hi is
+// exact either way), lo = the remainder plus half an ulp of ITS TF32 mantissa (the tensor core truncates, so this
+// rounds it to nearest and keeps the error zero-mean).  The weights are split with hi rounded (um_split).
+__device__ __forceinline__ void um_split_act(float v, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(v) & 0xffffe000u;
+  lo = __float_as_uint(v - __uint_as_float(hi)) + 0x1000u;
+}
 // tanh(x) for x*2*log2(e) given: 1 - 2 / (1 + 2^t) on two bare MUFU ops; absolute error ~1e-7 (it cancels for
 // small |x|), which is the rounding of the O(1) sums the activations feed; saturates exactly (ex2 -> inf / 0)
 __device__ __forceinline__ float um_tanh_scaled(float t) {
@@ -190,7 +197,7 @@ __device__ __forceinline__ void um_epilogue_group(uint32_t trow, uint32_t d_col)
   um_wait_ld();
 #pragma unroll
   for (int j = 0; j < 16; ++j)
-    um_split(um_tanh_scaled(fmaf(__uint_as_float(v[j]), UM_2LOG2E, C_BS(L, col0 + j))), hi[j], lo[j]);
+    um_split_act(um_tanh_scaled(fmaf(__uint_as_float(v[j]), UM_2LOG2E, C_BS(L, col0 + j))), hi[j], lo[j]);
   um_st16(trow + T_AHI + col0, hi);
   um_st16(trow + T_ALO + col0, lo);
   um_wait_st();
