@@ -21,9 +21,10 @@
 //     128 -> 3 output layer is folded into the last epilogue on the FMA pipe.  Biases and W3 are immediate
 //     constant-bank operands (the column index is uniform across the CTA and known at compile time).
 //   * control warp: one thread issues the bulk copies and every tcgen05.mma / tcgen05.commit.
-// A prep kernel builds the images and the constant block from the fp32 weight blob on every call (stream
-// ordered, ~3 us); the image buffer is a per-device workspace, so calls for different weight blobs must not
-// run concurrently on two streams of one device.
+// The images and the constant block are built from the fp32 weight blob on every call by 64 extra CTAs of the
+// history kernel (lgk_umma_prep.cuh, lgk_control.cu), which this kernel is launched behind with programmatic
+// serialisation; the image buffer is a per-device workspace, so calls for different weight blobs must not run
+// concurrently on two streams of one device.
 #include "lgk_common.cuh"
 #include <cstdio>
 #include <cstdlib>
