@@ -30,4 +30,9 @@ ncu --set full --clock-control none --import-source on -k regex:lgk_lstm_kernel 
 echo "ncu lstm rc=$?"
 python tests/bench_torch_cuda_reference.py 4096 65536 > $OUT/torch_cuda_reference_$TAG.json 2> $OUT/torch_cuda_reference_$TAG.err
 echo "torch cuda reference rc=$?"; cat $OUT/torch_cuda_reference_$TAG.json
+# Go1 actuator MLP: the three kernels, config 3 as a whole step, one full capture of the tcgen05 kernel
+for k in umma mma ffma; do for n in 4096 16384 65536; do LGK_MLP_KERNEL=$k python tools/bench_actuator.py $n | tail -3; done; done > $OUT/bench_actuator_$TAG.txt 2>&1
+python bench.py --scenario go1_rough_actuator --envs 16384 --no-cpu-baseline 2>/dev/null | tail -1 > $OUT/bench_config3_$TAG.json
+ncu --set full --clock-control none --import-source on -k regex:lgk_act_mlp_umma -s 6 -c 1 -o $OUT/prof_umma_$TAG python tools/bench_actuator.py 65536 > $OUT/ncu_umma_$TAG.log 2>&1
+echo "ncu umma rc=$?"
 ls -la $OUT
