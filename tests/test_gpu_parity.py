@@ -696,3 +696,29 @@ def test_actuator_net_is_graph_capturable():
         torch.cuda.synchronize()
         assert torch.equal(graphed.dVel, want), it
         assert torch.equal(graphed.pos_err_buffs, eager.pos_err_buffs)
+
+
+def test_actuator_two_weight_sets_alternate():
+    """Two envs with different actuator-net weights take turns on one stream: the weight images and the constant
+    block (biases, output layer) of the tcgen05 kernel are rebuilt on every call, behind a programmatic launch
+    dependency, and must never be stale."""
+    from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
+    from oracle import legged_oracle as lo
+    n = 640
+
+    def with_seed(seed):
+        def edit(cfg):
+            cfg.control.actuator_net_random_seed = seed
+        return edit
+    envs = [helpers.make_env("go1_rough_actuator", n, device=DEV, extra=with_seed(s)) for s in (0, 7)]
+    oracles = [lo.ActuatorOracle(n, random_mlp_state_dict(s)) for s in (0, 7)]
+    atols = [helpers.actuator_dvel_atol(random_mlp_state_dict(s)) for s in (0, 7)]
+    assert not torch.equal(envs[0].actuator_weights, envs[1].actuator_weights)
+    frames = synthetic.make_frames(envs[0], 4, seed=12)
+    for it, fr in enumerate(frames):
+        for env in envs:
+            synthetic.load_frame(env, fr)
+        got = [env.actuator_advance(fr["actions"]) for env in envs]      # back to back, no sync in between
+        for env, act, atol, g in zip(envs, oracles, atols, got):
+            want = act.advance(fr["actions"].cpu(), env.dof_pos.cpu(), env.dof_vel.cpu())
+            helpers.assert_close_abs(f"dVel[{it}]", g, want, atol)
