@@ -1,7 +1,7 @@
 // extern "C" entry points of liblgk.so (declared in include/lgk.h): argument validation,
 // then one or two kernel launches on the caller's stream.  No allocation, no host sync.
 #include <atomic>
-#include "lgk_common.cuh"
+#include "lgk_step.cuh"
 
 extern "C" {
 int lgk_post_physics_step_impl(const LgkConsts*, const LgkBuffers*, cudaStream_t);
@@ -38,7 +38,7 @@ static int check_step(const LgkConsts* c, const LgkBuffers* b) {
   if (!b) return LGK_ERR_NULL;
   if (c->num_bodies <= 0 || c->num_feet < 0 || c->num_feet > LGK_MAX_FEET || c->num_pen < 0 ||
       c->num_pen > LGK_MAX_PEN || c->num_term < 0 || c->num_term > LGK_MAX_TERM || c->num_hip < 0 ||
-      c->num_hip > LGK_MAX_HIP || c->num_commands != 4 || c->num_height_points < 0 || c->num_height_points > 256)
+      c->num_hip > LGK_MAX_HIP || c->num_commands != 4 || c->num_height_points < 0)
     return LGK_ERR_DIM;
   const int has_term = (c->flags & LGK_F_HAS_TERMINATION) ? 1 : 0;
   if (c->num_rewards < 0 || c->num_rewards + has_term > LGK_MAX_REWARDS) return LGK_ERR_DIM;
@@ -98,7 +98,8 @@ int64_t lgk_launch_count(void) { return g_launches.load(); }
 
 int64_t lgk_workspace_bytes(int32_t num_envs, int32_t num_sum_rows) {
   (void)num_sum_rows;
-  return (int64_t)LGK_WS_HEADER_BYTES + 2ll * (int64_t)lgk_max_warps(num_envs) * (int64_t)sizeof(unsigned);
+  // header, the two per-tile bitmask arrays, then one float per env: the scan kernel's height sums
+  return (int64_t)lgk_ws_hsum_offset(num_envs) + 4ll * (int64_t)num_envs;
 }
 
 int lgk_build_height_min3(const int16_t* height_samples, int32_t rows, int32_t cols, int16_t* out, int32_t pitch,
@@ -185,7 +186,7 @@ int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream) {
   int rc = check_step(c, b);
   if (rc) return rc;
-  g_launches += 2;   // tile kernel + epilogue
+  g_launches += 2 + (c->num_height_points > 0 ? 1 : 0);   // (scan kernel,) step kernel, epilogue
   return lgk_post_physics_step_impl(c, b, (cudaStream_t)stream);
 }
 
@@ -224,8 +225,11 @@ int lgk_set_step_counter(void* workspace, int64_t value, void* stream) {
   static_assert(offsetof(LgkWorkspace, step_counter) == 0, "step_counter must lead the workspace");
   // value travels through the launch parameters of a 1-thread memset-like copy: use cudaMemcpyAsync
   // from a pageable stack variable only when not capturing; callers inside a capture must not call this
-  unsigned long long v = (unsigned long long)value;
-  return (int)cudaMemcpyAsync(workspace, &v, sizeof(v), cudaMemcpyHostToDevice, (cudaStream_t)stream);
+  // The whole header goes with it: the step epilogue zeroes only the accumulators of the OTHER step parity, so a
+  // counter set by hand (load_state_dict into an env that has stepped) must not leave this parity's sums behind.
+  LgkWorkspace hdr = {};
+  hdr.step_counter = (unsigned long long)value;
+  return (int)cudaMemcpyAsync(workspace, &hdr, sizeof(hdr), cudaMemcpyHostToDevice, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,64 +1,52 @@
-// Fused post_physics_step kernel (sm_100a): one CTA of four warps per tile of 32 envs.
+// Step kernel of post_physics_step (sm_100a): one CTA of four warps per tile of 32 envs, lanes = envs.
 //
-// One launch replaces everything LeggedRobot.post_physics_step() does per env
-// (reference legged_robot.py:109-141): episode counters, body-frame velocities / projected
-// gravity, command resampling + heading command, the yaw-rotated terrain height scan, pushes,
-// terminations, every active _reward_* term with in-place episode sums, resets (terrain
-// curriculum, dof / root state, commands), the noisy scaled observation row, last_* copies,
-// ascending compacted reset / resample id lists and the episode statistics behind extras.
+// Together with the height-scan kernel launched ahead of it (lgk_scan.cu) and the one-CTA epilogue behind it,
+// this replaces everything LeggedRobot.post_physics_step() does per env (reference legged_robot.py:109-141):
+// episode counters, body-frame velocities / projected gravity, command resampling + heading command, pushes,
+// terminations, every active _reward_* term with in-place episode sums, resets (terrain curriculum, dof / root
+// state, commands), the noisy scaled head of the observation row, last_* copies, the per-tile reset / resample
+// bitmasks behind the ascending id lists, and the episode statistics behind extras.
 //
 // Work decomposition
-//   grid    CTA c owns the contiguous env range [c*per, (c+1)*per) and walks it in sub-tiles of
-//           <= 32 envs.  per = 32 by default (six CTAs resident per SM, the hardware scheduler
-//           backfills); LgkConsts.envs_per_cta selects longer, persistent ranges.
-//   load    every per-env input row of a sub-tile is contiguous in HBM ([N,13], [N,D,2], [N,B,3], ...):
-//           the lanes of warp 0 issue 1-D bulk async copies (cp.async.bulk -> SASS UBLKCP, the TMA
-//           engine) into shared memory, completion counted on an mbarrier.  No register staging,
-//           full coalescing, ~22 KB in flight per CTA.  The [R,N] episode-sum rows (128 B per row
-//           and tile) come in through 4-byte cp.async (LDGSTS) issued by W3.
-//   stage 1 the four warps run four different per-env jobs with lane = env (no divergence inside a
-//           warp): W0 base state / commands / termination / reset of the root, W1 + W2 the joints,
-//           W3 contacts + feet air time.  The reset flag is cheap and is recomputed by each warp.
-//   stage 2 the envs of the sub-tile are dealt to the warps; lanes cover the observation columns of
-//           one env at a time: noise on the head, then the H scan points in passes of 32 (index
-//           chain on packed f32x2 ops, one int16 gather per point from the precomputed
-//           min-of-three-neighbours table, all gathers of an env in flight together).
-//   stage 3 W0 alone, while W1..W3 already wait for the next sub-tile's loads: term values by env,
-//           then lane = episode-sum row (scale, accumulate, statistics: independent lanes), then
-//           lane = env again for the ordered reward sum and the coalesced stores.
-//   store   observation rows and episode sums are written straight from registers (128-byte
-//           coalesced); last_actions and last_dof_vel leave through bulk async stores.
-//   The CTA that publishes the last reset / resample masks compacts them into ascending id lists;
-//   the last W0 to finish finalises the episode statistics.
+//   grid    CTA c owns the contiguous env range [c*per, (c+1)*per) and walks it in sub-tiles of <= 32 envs.
+//           per = 32 by default (the hardware scheduler backfills); LgkConsts.envs_per_cta selects longer ranges.
+//   load    every per-env input row of a sub-tile is contiguous in HBM ([N,13], [N,D,2], [N,B,3], ...), and so is
+//           the tile's slice of each [R,N] episode-sum row: the lanes of W0 issue 1-D bulk async copies
+//           (cp.async.bulk -> SASS UBLKCP, the TMA engine) into shared memory, completion counted on one mbarrier.
+//   stage 1 four roles, lane = env (no divergence inside a warp):
+//             W0  episode counter, commands (resample, heading command), push, root reset with the terrain
+//                 curriculum, the per-tile bitmasks;  W1, W2  half of the joints each;  W3  body-frame
+//                 velocities / gravity, contacts, feet air time.
+//           Each role writes its columns of the observation head -- scaled, with noise, clipped -- into a staging
+//           row per env; the noise fields come from Philox blocks dealt to the roles (lane = env: every lane of a
+//           block computation is used).  The reset flag is cheap and is recomputed by each warp.
+//   -- the only CTA barrier of a sub-tile --
+//   store   W0..W2 write the staged heads to the observation rows, 128 B per warp store; last_actions and
+//           last_dof_vel leave through bulk async stores.
+//   stage 3 W3 alone, lane = env: waits for the scan kernel (griddepcontrol.wait -- the only place this kernel
+//           needs it), rewrites the scan columns of the envs reset in this tile (new root z, :227), then walks
+//           the episode-sum rows in the reference's order (:195-212): r = value * scale, sum += r, reward += r,
+//           statistics of the reset envs by red.global.add -- 8 instructions per row for 32 envs, all coalesced.
 //
-// Code size matters here (the four roles + two stages exceed the instruction cache when everything
-// is inlined): paths that run once per launch or only for ragged / unaligned tiles are __noinline__.
+// Code size matters (four roles live in different regions of the code at once): paths that run for ~1 % of the
+// envs, once per launch, or only for ragged / unaligned tiles are __noinline__.
 #include <cmath>
 #include <limits>
 #include <type_traits>
-#include "lgk_common.cuh"
+#include "lgk_step.cuh"
 
-#define TILE 32
-#define HP_OFF (((RS * (LGK_REW_COUNT + 1)) + 3) & ~3)   // base-height partial sums, after the reward table
-#define RS (TILE + 1)   // row stride of the [row][env] reward tables: conflict-free by row and by env
-#ifndef LGK_STAGE2_ENVS
-#define LGK_STAGE2_ENVS 1   // envs a warp keeps in flight in stage 2 (2 measured slower: stage 2 is issue-bound at full residency)
-#endif
 #ifndef LGK_MIN_CTAS
-#define LGK_MIN_CTAS 6   // register cap 85: six 128-thread CTAs per SM
+#define LGK_MIN_CTAS 6
 #endif
 
 #ifdef LGK_PROFILE
-// development build only: per-CTA phase timestamps (clock64) of the first sub-tile, [cta][warp][8]
+// development build only: per-CTA phase timestamps (clock64) of the first sub-tile, [cta][warp][16]
 __device__ long long lgk_prof[4096 * 4 * 16];
-#ifndef LGK_PROF_SUB
-#define LGK_PROF_SUB 0
-#endif
-#define LGK_STAMP(k) do { if (sub == LGK_PROF_SUB && lane == 0 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 4 + wic) * 16 + (k)] = clock64(); } while (0)
+#define LGK_STAMP(k) do { if (sub == 0 && lane == 0 && blockIdx.x < 4096) lgk_prof[(blockIdx.x * 4 + wic) * 16 + (k)] = clock64(); } while (0)
 extern "C" int lgk_debug_read_prof(long long* out, int n) {
   return (int)cudaMemcpyFromSymbol(out, lgk_prof, sizeof(long long) * n);
 }
-// CTA timeline: [cta][globaltimer at start, globaltimer when W0 leaves, SM id, 0]
+// CTA timeline: [cta][globaltimer at start, globaltimer when W0 leaves, SM id, globaltimer when W3 leaves]
 __device__ long long lgk_prof_cta[4096 * 4];
 static __device__ __forceinline__ long long lgk_gtime() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 static __device__ __forceinline__ int lgk_smid() { int r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
@@ -71,43 +59,12 @@ extern "C" int lgk_debug_read_prof_cta(long long* out, int n) {
 #define LGK_CTA_STAMP(k) do {} while (0)
 #endif
 
-struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
-  int root, dof, act, ldv, cmd, fat, ep, lvl, sums, head, scr, cf, tq, lact, total;
-};
-
-#define LGK_LD_ARRAYS 11
-struct StepArgs {
-  LgkConsts c;
-  LgkBuffers b;
-  TileLayout L;
-  int per;           // envs per CTA (multiple of 4) of the first n_big CTAs, walked in sub-tiles of <= 32
-  int n_big;         // CTAs past n_big own per_small envs each: the launch's last, partial wave runs on
-  int per_small;     //   smaller tiles so that it is shorter than a full wave (per_small <= 32)
-  int max_sub;       // sub-tiles per CTA = ceil(per / 32)
-  int head_stride;   // odd row stride of the staged observation head
-  int air_active;    // feet_air_time term active (:945-948 only run then)
-  int bh_active;     // base_height term active
-  int tma_ok;        // every tiled array 16-byte aligned and N % 4 == 0
-  int num_rows;      // episode_sums rows: num_rewards (+1 with termination)
-  unsigned pk[20];   // Philox4x32-10 round keys of c.seed
-  // bulk-load table: lane i of W0 copies input array i of a sub-tile (source base, offset into shared
-  // memory in floats, bytes per env); src == nullptr: nothing to copy
-  const char* ld_src[LGK_LD_ARRAYS];
-  unsigned ld_off[LGK_LD_ARRAYS], ld_bpe[LGK_LD_ARRAYS];
-  unsigned ld_bytes_per_env;   // sum of ld_bpe
-  // norm > c without the square root: sqrt is monotone and correctly rounded, so sqrtf(s) > c is the same
-  // predicate as s > thr(c), thr(c) = the largest float whose square root rounds to <= c (found on the host)
-  float thr_term, thr_pen, thr_ffp;   // c = 1 (:146), 0.1 (:897), max_contact_force (:962)
-  unsigned hip_mask;                  // bit d set: joint d is a hip joint (_reward_hip_motion)
-};
-
-// scratch fields (SoA, [field][TILE]) exchanged between the stages
-enum { SC_ES = 0,            // 12 floats per env (AoS), the scan's per-env operands as ready-made f32x2 pairs:
-                             //   (-2qz, 2qz) (2qz, -2qz) | (qw, qw) (-qz, qz) | (rx, ry) rz zo      (yaw-only unit quaternion)
-       ES_W = 12,
-       SC_J1 = 12, SC_J2 = 22,  // joint partial sums of W1 / W2 (10 each)
-       SC_COLL = 32, SC_FFP, SC_RAIR, SC_STUMBLE, SC_NOFLY, SC_FIELDS };
-
+// scratch fields (SoA, [field][TILE]) exchanged between the roles
+enum { SC_J1 = 0, SC_J2 = 10,    // joint partial sums of W1 / W2 (10 each)
+       SC_CMDX = 20, SC_CMDY, SC_CMDZ,   // command after the callback, before any reset (what the rewards see)
+       SC_ZPRE,                  // root z before any reset (_reward_base_height)
+       SC_FIELDS,
+       SC_ES = SC_FIELDS };      // then 8 floats per env (AoS): scan operands of the envs reset in this tile
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float norm3(float x, float y, float z) {
   return sqrtf(fmaf(z, z, fmaf(y, y, x * x)));
@@ -149,10 +106,11 @@ struct DofAcc {   // per-env sums over joints feeding the reward terms (:874-916
 };
 enum { A_TQ2 = 0, A_ENERGY, A_QD2, A_ACC2, A_ARATE, A_POSLIM, A_VELLIM, A_TQLIM, A_STAND, A_HIP };
 
-// one joint: reward partial sums on the pre-reset state, reset values, observation head columns
-__device__ __forceinline__ void joint_update(const LgkConsts& c, int d, int D, unsigned hip_mask, bool reset,
-                                             float inv_dt, float av, float lav, float tqv, float ldvv, float& p,
-                                             float& v, float u, DofAcc& acc, float* __restrict__ head_row) {
+// one joint: reward partial sums on the pre-reset state, reset values; the three observation-head values of the
+// joint (:221-223) come back unscaled-by-noise in hv[]
+__device__ __forceinline__ void joint_update(const LgkConsts& c, int d, unsigned hip_mask, bool reset, float inv_dt,
+                                             float av, float lav, float tqv, float ldvv, float& p, float& v, float u,
+                                             DofAcc& acc, float (&hv)[3]) {
   acc.v[A_TQ2] = fmaf(tqv, tqv, acc.v[A_TQ2]);
   const float pw = tqv * v;
   acc.v[A_ENERGY] = fmaf(pw, pw, acc.v[A_ENERGY]);
@@ -171,9 +129,31 @@ __device__ __forceinline__ void joint_update(const LgkConsts& c, int d, int D, u
     p = mul_rn(c.default_dof_pos[d], rand_affine(1.0f, 0.5f, u));
     v = 0.f;
   }
-  head_row[12 + d] = (p - c.default_dof_pos[d]) * c.obs_scale_dof_pos;
-  head_row[12 + D + d] = v * c.obs_scale_dof_vel;
-  head_row[12 + 2 * D + d] = av;
+  hv[0] = (p - c.default_dof_pos[d]) * c.obs_scale_dof_pos;
+  hv[1] = v * c.obs_scale_dof_vel;
+  hv[2] = av;
+}
+
+// 16-bit field k (0..7) of a Philox block
+__device__ __forceinline__ unsigned philox_word(const uint4& r, int w) {
+  return w == 0 ? r.x : w == 1 ? r.y : w == 2 ? r.z : r.w;
+}
+// one column of the observation head: obs = clip(v + (2*rand - 1) * noise_scale_vec[col], +-clip_observations)
+// (:231, :104).  Philox mode: field k of `blk` as the float 2^23 + r16 (one PRMT, no I2F on the quarter-rate
+// conversion unit), (2^23 + r16) * 2^-15 - 257 = r16 / 2^15 - 1 exactly: uniform on [-1, 1) in steps of 2^-15.
+// s_ns holds the head's noise scales (zeros without noise); trow: the env's tap row in tap mode with noise.
+template <bool TAPS>
+__device__ __forceinline__ float head_obs(float v, int col, const uint4& blk, int k, const float* __restrict__ s_ns,
+                                          const float* __restrict__ trow, float clip_obs) {
+  const float ns = s_ns[col];
+  if (TAPS) {
+    if (trow != nullptr) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
+  } else {
+    const unsigned rw = philox_word(blk, k >> 1);
+    const unsigned m = (k & 1) ? __byte_perm(rw, 0x4b000000u, 0x7632) : __byte_perm(rw, 0x4b000000u, 0x7610);
+    v = fmaf(fmaf(__uint_as_float(m), 3.0517578125e-05f, -257.0f), ns, v);
+  }
+  return clampf(v, -clip_obs, clip_obs);
 }
 
 // ---- cold paths (kept out of line: they run for ~1 % of the envs, or once per launch) ---------------
@@ -202,7 +182,7 @@ __device__ __forceinline__ float wrap_to_pi_fast(float x) {
 struct ResetOut {
   float4 cmd;      // in: command after the callback; out: command of the new episode
   float rvel[6];   // new root velocities (-> last_root_vel)
-  float z;         // new root z (-> height observation offset)
+  float z;         // new root z (-> height observation offset, :227)
   int level;       // terrain level after the curriculum update
 };
 template <bool TAPS>
@@ -272,7 +252,7 @@ static __device__ __noinline__ void tile_load_fallback(const StepArgs& a, float*
   const LgkBuffers& b = a.b;
   const TileLayout& L = a.L;
   const int D = c.num_dof, B3 = c.num_bodies * 3, F = c.num_feet, N = c.num_envs;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x;   // (physical thread index: every thread takes part, whatever its role)
   auto ld = [&](int off, const void* g, int words_per_env) {
     const unsigned* src = reinterpret_cast<const unsigned*>(g);
     unsigned* dst = reinterpret_cast<unsigned*>(sm + off);
@@ -290,6 +270,9 @@ static __device__ __noinline__ void tile_load_fallback(const StepArgs& a, float*
   ld(L.ldv, b.last_dof_vel + (size_t)env0 * D, D);
   ld(L.fat, b.feet_air_time + (size_t)env0 * F, F);
   if (b.terrain_levels != nullptr) ld(L.lvl, b.terrain_levels + env0, 2);
+#pragma unroll 1
+  for (int r = 0; r < a.num_rows; ++r)
+    for (int i = tid; i < ne; i += LGK_CTA_THREADS) sm[L.sums + r * TILE + i] = b.episode_sums[(size_t)r * N + env0 + i];
 }
 static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const float* sm, int env0, int ne, int tid) {
   const int D = a.c.num_dof;
@@ -299,7 +282,6 @@ static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const
 #pragma unroll 1
   for (int i = t; i < ne * D; i += nt) { la[i] = sm[a.L.act + i]; lv[i] = sm[a.L.ldv + i]; }
 }
-
 // ---------------------------------------------------------------------------------------------
 // Step epilogue: the two once-per-step serial jobs, as a second small launch behind the tile kernel
 // (one CTA of 1024 threads).  Being a separate launch, the kernel boundary orders it after every tile's
@@ -406,11 +388,14 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
   }
 }
 
-template <int DT, bool TAPS, bool MUL_RCP, int NP>
+template <int DT, bool TAPS, bool MUL_RCP>
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_MIN_CTAS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
   pdl_launch_dependents();   // the epilogue may be scheduled as soon as the last tile CTA has started
-  pdl_wait();                // launched behind clip_actions_poses: its writes (actions) are visible from here
+  // Behind the scan kernel this launch needs no wait on entry: that kernel waits for ITS predecessor before it lets
+  // its dependents go, so every input here (simulator tensors, clipped actions, the previous step's state) is
+  // complete when the first CTA starts; only W3 waits, before stage 3.  Without a scan kernel: wait now.
+  if (!a.scan_first) pdl_wait();
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
   const TileLayout& L = a.L;
@@ -419,19 +404,21 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int N = c.num_envs;
   const int B3 = c.num_bodies * 3;
   const int F = c.num_feet;
-  const int H = c.num_height_points;
   const int O = c.num_obs;
   const int OH = 12 + 3 * D;               // width of the observation head (:217-224)
   const int HS = a.head_stride;
   const unsigned flags = c.flags;
   const bool heading_mode = flags & LGK_F_HEADING_COMMAND;
+  const bool add_noise = flags & LGK_F_ADD_NOISE;
   const int num_rows = a.num_rows;
 
   extern __shared__ __align__(16) float sm[];
   __shared__ __align__(8) uint64_t s_bar;
+  __shared__ int s_idx[32];
+  __shared__ float s_ns[64];   // noise scales of the head columns (zeros without noise)
 
-  // roles go by the logical warp index wic: rotated per CTA so that the W0s of the CTAs resident on an
-  // SM (the longest role, and the only one running in stage 3) do not all sit on the same scheduler
+  // roles go by the logical warp index wic: rotated per CTA so that the same role of the CTAs resident on an SM
+  // does not always sit on the same scheduler
   const int lane = threadIdx.x & 31;
   const int wic = ((int)(threadIdx.x >> 5) + (int)((blockIdx.x * 2654435761u) >> 30)) & (LGK_WARPS_PER_CTA - 1);
   const int tid = wic * 32 + lane;
@@ -441,40 +428,30 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const int nsub = (cta_ne + TILE - 1) / TILE;
   const bool has_levels = b.terrain_levels != nullptr;
 
-  // ---- first thing: W0 sets the mbarrier up and gets the bulk loads of the first sub-tile going; the
-  // rest of the prologue runs under their latency.  Lane i copies input array i.
+  // ---- first thing: W0 sets the mbarrier up and gets the bulk loads of the first sub-tile going; the rest of the
+  // prologue runs under their latency.  Lane i copies input array i, then the lanes share the episode-sum rows.
   const char* ld_src = nullptr;
   unsigned ld_off = 0, ld_bpe = 0;
+  if (wic == 0 && lane < LGK_LD_ARRAYS) { ld_src = a.ld_src[lane]; ld_off = a.ld_off[lane]; ld_bpe = a.ld_bpe[lane]; }
+  auto issue_loads = [&](int env0, int ne) {   // W0, converged
+    if (lane == 0) mbar_expect_tx(&s_bar, (unsigned)ne * (a.ld_bytes_per_env + 4u * (unsigned)num_rows));
+    __syncwarp();
+    if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)env0 * ld_bpe, (unsigned)ne * ld_bpe, &s_bar);
+    for (int r = lane; r < num_rows; r += 32)
+      bulk_g2s(sm + L.sums + r * TILE, b.episode_sums + (size_t)r * N + env0, (unsigned)ne * 4u, &s_bar);
+  };
   if (wic == 0) {
-    if (lane < LGK_LD_ARRAYS) { ld_src = a.ld_src[lane]; ld_off = a.ld_off[lane]; ld_bpe = a.ld_bpe[lane]; }
     if (lane == 0) mbar_init(&s_bar, 1);
     __syncwarp();
     const int ne0 = min(TILE, cta_ne);
-    if (a.tma_ok && (ne0 & 3) == 0) {
-      if (lane == 0) mbar_expect_tx(&s_bar, (unsigned)ne0 * a.ld_bytes_per_env);
-      __syncwarp();
-      if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)cta_env0 * ld_bpe, (unsigned)ne0 * ld_bpe, &s_bar);
-    }
-  }
-  // stage 3, pass B: lane l of W0 owns episode-sum row l (term, scale, index among the external terms)
-  __shared__ int s_row_term[32], s_row_ext[32], s_idx[32];
-  __shared__ float s_row_scale[32];
-  if (wic == 0) {
-    const bool in = lane < c.num_rewards;
-    const int term = in ? c.rewards[lane].term : LGK_REW_COUNT;   // LGK_REW_COUNT: the termination row
-    const unsigned xm = __ballot_sync(LGK_FULL_MASK, in && term == LGK_REW_EXTERNAL);
+    if (a.tma_ok && (ne0 & 3) == 0) issue_loads(cta_env0, ne0);
+  } else if (wic == 1) {
     s_idx[lane] = 3 * (lane < IDX_PEN ? c.feet_idx[lane] : lane < IDX_TERM ? c.pen_idx[lane - IDX_PEN] : c.term_idx[lane - IDX_TERM]);
-    s_row_term[lane] = term;
-    s_row_ext[lane] = __popc(xm & ((1u << lane) - 1u));
-    s_row_scale[lane] = in ? c.rewards[lane].scale : c.termination_scale;
+  } else if (wic == 2) {
+    s_ns[lane] = (add_noise && lane < OH) ? __ldg(b.noise_scale_vec + lane) : 0.f;
+    s_ns[lane + 32] = (add_noise && lane + 32 < OH) ? __ldg(b.noise_scale_vec + lane + 32) : 0.f;
   }
   if (tid == 0) LGK_CTA_STAMP(0);
-#ifdef LGK_STAGGER_NS   // experiment: de-phase the CTAs that start together on an SM
-  if (blockIdx.x < 888) {
-    const unsigned k = min(blockIdx.x / 148u, 5u);
-    for (unsigned i = 0; i < k; ++i) __nanosleep(LGK_STAGGER_NS);
-  }
-#endif
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
   const int parity = (int)(csc & 1ull);
@@ -482,33 +459,29 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   if (wic == 0 && (flags & LGK_F_PUSH_ROBOTS))
     push_step = (csc >> 32) == 0ull ? ((unsigned)csc % (unsigned)c.push_interval == 0u)
                                     : (csc % (unsigned long long)c.push_interval == 0ull);
+  const float clip_obs = c.clip_obs;
 
-  __syncthreads();          // barrier initialised before anyone polls it, row table written
+  __syncthreads();          // barrier initialised before anyone polls it, tables written
 
   for (int sub = 0; sub < nsub; ++sub) {
     const int env0 = cta_env0 + sub * TILE;
     const int ne = min(TILE, cta_ne - sub * TILE);
     const bool full = a.tma_ok && ((ne & 3) == 0);   // bulk copies need 16-byte multiples: 4 envs x 4 B
     const int slot = blockIdx.x * a.max_sub + sub;   // where this sub-tile's reset / resample masks go
-    const bool last_sub = sub == nsub - 1;
 
     LGK_STAMP(0);
     // ---- load the sub-tile --------------------------------------------------------------------
     if (full) {
       if (sub > 0) {            // (the first sub-tile's loads were issued at the top of the kernel)
-        __syncthreads();        // every warp is through stage 3 of the previous sub-tile
+        __syncthreads();        // every warp is through the previous sub-tile
         if (wic == 0) {
-          if (lane == 0) {
-            fence_proxy_async_smem();   // generic reads of the previous sub-tile before the async writes
-            mbar_expect_tx(&s_bar, (unsigned)ne * a.ld_bytes_per_env);
-          }
-          __syncwarp();
-          if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)env0 * ld_bpe, (unsigned)ne * ld_bpe, &s_bar);
+          if (lane == 0) fence_proxy_async_smem();   // generic reads of the previous sub-tile before the async writes
+          issue_loads(env0, ne);
         }
       }
       mbar_wait(&s_bar, sub & 1);
     } else {
-      __syncthreads();          // every warp is through stage 3 of the previous sub-tile
+      __syncthreads();          // every warp is through the previous sub-tile
       tile_load_fallback(a, sm, env0, ne);
       __syncthreads();
     }
@@ -520,10 +493,11 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     float* scr = sm + L.scr;
     float* head_row = sm + L.head + lane * HS;
     const float* cf_row = sm + L.cf + lane * B3;
+    const float* trow = (TAPS && add_noise) ? b.tap_noise + (size_t)env * O : nullptr;
     const long long ep_in = reinterpret_cast<const long long*>(sm + L.ep)[lane];
     const long long ep_inc = (flags & LGK_F_EP_INCREMENTED) ? 0 : 1;   // lgk_pre_reward_state already counted this step
 
-    // the reset decision (:143-148) is cheap: every stage-1 warp forms it for its own lane
+    // the reset decision (:143-148) is cheap: every warp forms it for its own lane
     bool time_out = false, reset = false;
     if (active) {
       if (flags & LGK_F_RESET_GIVEN) {   // a python check_termination() override has already decided (cold path)
@@ -534,32 +508,25 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         reset = term_contact(c, s_idx, cf_row, a.thr_term) || time_out;
       }
     }
-
-    // values W0 keeps in registers from stage 1 to stage 3
-    float blv[3] = {0, 0, 0}, bav[3] = {0, 0, 0}, grav[3] = {0, 0, 0};
-    float4 cmd_rew = make_float4(0, 0, 0, 0);
     const unsigned reset_mask = __ballot_sync(LGK_FULL_MASK, active && reset);
 
-    LGK_STAMP(12);
+    // values W3 keeps in registers from stage 1 to stage 3
+    float blv[3] = {0, 0, 0}, bav[3] = {0, 0, 0}, grav[3] = {0, 0, 0};
+    float collisions = 0.f, ffp = 0.f, r_air = 0.f, stumble_f = 0.f, nofly_f = 0.f;
+
     // =========================================== stage 1 =========================================
     if (wic == 0) {
-      // ---- W0: base state, commands, termination, root reset, per-env outputs --------------------
+      // ---- W0: episode counter, commands, push, root reset, bitmasks ------------------------------
       bool resample_cb = false;
       int level_contrib = 0;
       if (active) {
-        float root[13];
         const float* rp = sm + L.root + lane * 13;
-#pragma unroll
-        for (int i = 0; i < 13; ++i) root[i] = rp[i];
         long long ep = ep_in + ep_inc;                              // (:118)
-        const float q[4] = {root[3], root[4], root[5], root[6]};
-        quat_rotate_inverse(q, root[7], root[8], root[9], blv);     // (:123-125)
-        quat_rotate_inverse(q, root[10], root[11], root[12], bav);
-        quat_rotate_inverse(q, 0.f, 0.f, -1.f, grav);
+        const float q[4] = {rp[3], rp[4], rp[5], rp[6]};
         float4 cmd = *reinterpret_cast<const float4*>(sm + L.cmd + lane * 4);
 
         // ---- _post_physics_step_callback (:337-352) -------------------------------------------
-        resample_cb = (unsigned long long)ep < 0x80000000ull ? ((int)ep % c.resample_interval) == 0
+        resample_cb = (unsigned long long)ep < 0x80000000ull ? ((int)ep % (int)c.resample_interval) == 0
                                                              : (ep % c.resample_interval) == 0;
         // LGK_F_CALLBACK_GIVEN: a python _post_physics_step_callback() override ran on the commands that
         // lgk_pre_reward_state resampled; they are final (the id list still names the resampled envs)
@@ -581,17 +548,12 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           const float heading = atan2f(fwd[1], fwd[0]);
           cmd.z = clampf(0.5f * wrap_to_pi_fast(cmd.w - heading), -1.f, 1.f);
         }
-        cmd_rew = cmd;
-        // yaw-only quaternion of quat_apply_yaw (utils/math.py:38-42): normalize([0,0,qz,qw]);
-        // x.norm(p=2): separately rounded squares, correctly rounded sqrt (same on torch CPU / CUDA)
-        float yaw_z, yaw_w;
-        {
-          const float n = fmaxf(sqrtf(add_rn(mul_rn(q[2], q[2]), mul_rn(q[3], q[3]))), 1e-9f);
-          yaw_z = __fdiv_rn(q[2], n);
-          yaw_w = __fdiv_rn(q[3], n);
-        }
-        float z_obs = root[2];
-        float rvel[6] = {root[7], root[8], root[9], root[10], root[11], root[12]};
+        // what the rewards see: the command after the callback, the root height before any reset
+        scr[SC_CMDX * TILE + lane] = cmd.x;
+        scr[SC_CMDY * TILE + lane] = cmd.y;
+        scr[SC_CMDZ * TILE + lane] = cmd.z;
+        scr[SC_ZPRE * TILE + lane] = rp[2];
+        float rvel[6] = {rp[7], rp[8], rp[9], rp[10], rp[11], rp[12]};
         if (push_step) {   // _push_robots (:436-441): every env, after the body-frame velocities
           float u0, u1;
           if (TAPS) { u0 = b.tap_push[(size_t)env * 2]; u1 = b.tap_push[(size_t)env * 2 + 1]; }
@@ -604,13 +566,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         if (reset) {   // reset_idx for this env (:150-193): curriculum, root state, command
           ResetOut ro;
           ro.cmd = cmd;
-          reset_root<TAPS>(a, csc, env, env_global, root[0], root[1], level, ro);
+          reset_root<TAPS>(a, csc, env, env_global, rp[0], rp[1], level, ro);
           cmd = ro.cmd;
 #pragma unroll
           for (int i = 0; i < 6; ++i) rvel[i] = ro.rvel[i];
-          z_obs = ro.z;
           level = ro.level;
           ep = 0;
+          if (a.scan_first) {   // W3 redoes this env's scan columns with the new root z (:227)
+            const ScanEnv e = scan_env_operands(rp[0], rp[1], ro.z, q[2], q[3]);
+            float4* d = reinterpret_cast<float4*>(scr + SC_ES * TILE + lane * 8);
+            d[0] = make_float4(e.k_t.x, e.k_t.y, e.k_c.x, e.k_c.y);
+            d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
+          }
         } else if (push_step) {
           float* rw = b.root_states + (size_t)env * 13;
           rw[7] = rvel[0];
@@ -624,23 +591,15 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         b.time_out_buf[env] = time_out ? 1 : 0;
         *reinterpret_cast<float4*>(b.commands + (size_t)env * 4) = cmd;
         {
-          float* p = b.base_lin_vel + (size_t)env * 3; p[0] = blv[0]; p[1] = blv[1]; p[2] = blv[2];
-          p = b.base_ang_vel + (size_t)env * 3;        p[0] = bav[0]; p[1] = bav[1]; p[2] = bav[2];
-          p = b.projected_gravity + (size_t)env * 3;   p[0] = grav[0]; p[1] = grav[1]; p[2] = grav[2];
           float2* lr = reinterpret_cast<float2*>(b.last_root_vel + (size_t)env * 6);   // (:138)
           lr[0] = make_float2(rvel[0], rvel[1]); lr[1] = make_float2(rvel[2], rvel[3]); lr[2] = make_float2(rvel[4], rvel[5]);
         }
-        // obs head columns 0..11 (:217-220), post-reset commands
-        head_row[0] = blv[0] * c.obs_scale_lin_vel; head_row[1] = blv[1] * c.obs_scale_lin_vel; head_row[2] = blv[2] * c.obs_scale_lin_vel;
-        head_row[3] = bav[0] * c.obs_scale_ang_vel; head_row[4] = bav[1] * c.obs_scale_ang_vel; head_row[5] = bav[2] * c.obs_scale_ang_vel;
-        head_row[6] = grav[0]; head_row[7] = grav[1]; head_row[8] = grav[2];
-        head_row[9] = cmd.x * c.commands_scale[0]; head_row[10] = cmd.y * c.commands_scale[1]; head_row[11] = cmd.z * c.commands_scale[2];
-        // scalars of the height scan: pre-reset position / yaw, post-reset z for the observation (:227)
-        float4* es = reinterpret_cast<float4*>(scr + SC_ES * TILE + lane * ES_W);
-        const float yz2 = mul_rn(yaw_z, 2.0f);
-        es[0] = make_float4(-yz2, yz2, yz2, -yz2);
-        es[1] = make_float4(yaw_w, yaw_w, -yaw_z, yaw_z);
-        es[2] = make_float4(root[0], root[1], root[2], sub_rn(z_obs, 0.5f));
+        // obs head columns 9..11 (:220): the commands after any reset
+        uint4 nb = make_uint4(0, 0, 0, 0);
+        if (!TAPS && add_noise) nb = philox_keyed(a.pk, csc, env_global, LGK_SITE_NOISE_HEAD + 2);
+        head_row[9] = head_obs<TAPS>(cmd.x * c.commands_scale[0], 9, nb, 0, s_ns, trow, clip_obs);
+        head_row[10] = head_obs<TAPS>(cmd.y * c.commands_scale[1], 10, nb, 1, s_ns, trow, clip_obs);
+        head_row[11] = head_obs<TAPS>(cmd.z * c.commands_scale[2], 11, nb, 2, s_ns, trow, clip_obs);
       }
       // ---- sub-tile bookkeeping: bitmasks for the ordered compaction, level sum --------------------
       const unsigned resample_mask = __ballot_sync(LGK_FULL_MASK, active && resample_cb);
@@ -657,7 +616,7 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       }
     }
     else if (wic == 1 || wic == 2) {
-      // ---- W1 / W2: joints (:874-916, :956-966 sums; :399-408 reset; obs head; last_dof_vel) -----
+      // ---- W1 / W2: joints (:874-916, :956-966 sums; :399-408 reset; obs head 12..; last_dof_vel) --
       DofAcc acc;
 #pragma unroll
       for (int i = 0; i < 10; ++i) acc.v[i] = 0.f;
@@ -671,36 +630,41 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         const float* dof_p = sm + L.dof + lane * 2 * D;
         float* dof_g = b.dof_state + (size_t)env * D * 2;
         if constexpr (VEC) {
-          constexpr int NC = DT / 4, NC1 = (NC + 1) / 2;
-          const int cb = (wic == 1) ? 0 : NC1, ce = (wic == 1) ? NC1 : NC;
+          // two joints per trip (one 16-byte dof_state quad); W1 takes the first half of the pairs.  The six head
+          // columns of a pair take fields 0..5 of Philox block LGK_SITE_NOISE_HEAD + 3 + pair
+          constexpr int NPAIR = DT / 2, NP1 = (NPAIR + 1) / 2;
+          const int pb = (wic == 1) ? 0 : NP1, pe = (wic == 1) ? NP1 : NPAIR;
 #pragma unroll 1
-          for (int ch = cb; ch < ce; ++ch) {
-            const int d0 = ch * 4;
-            const float4 a4 = *reinterpret_cast<const float4*>(act_p + d0);
-            const float4 la4 = *reinterpret_cast<const float4*>(lact_p + d0);
-            const float4 tq4 = *reinterpret_cast<const float4*>(tq_p + d0);
-            const float4 ldv4 = *reinterpret_cast<const float4*>(ldv_p + d0);
+          for (int pc = pb; pc < pe; ++pc) {
+            const int d0 = pc * 2;
+            const float2 a2 = *reinterpret_cast<const float2*>(act_p + d0);
+            const float2 la2 = *reinterpret_cast<const float2*>(lact_p + d0);
+            const float2 tq2 = *reinterpret_cast<const float2*>(tq_p + d0);
+            const float2 ldv2 = *reinterpret_cast<const float2*>(ldv_p + d0);
             float4 s0 = *reinterpret_cast<const float4*>(dof_p + 2 * d0);       // p0 v0 p1 v1
-            float4 s1 = *reinterpret_cast<const float4*>(dof_p + 2 * d0 + 4);   // p2 v2 p3 v3
-            float u[4] = {0, 0, 0, 0};
+            float u[2] = {0, 0};
             if (reset) {
               if (TAPS) {
                 const float* t = b.tap_dof + (size_t)env * D + d0;
-                u[0] = t[0]; u[1] = t[1]; u[2] = t[2]; u[3] = t[3];
+                u[0] = t[0]; u[1] = t[1];
               } else {
-                const uint4 r = philox_cold(a, csc, env_global, LGK_SITE_DOF + ch);
-                u[0] = u01(r.x); u[1] = u01(r.y); u[2] = u01(r.z); u[3] = u01(r.w);
+                const uint4 r = philox_cold(a, csc, env_global, LGK_SITE_DOF + (d0 >> 2));
+                u[0] = u01((d0 & 2) ? r.z : r.x); u[1] = u01((d0 & 2) ? r.w : r.y);
               }
             }
-            joint_update(c, d0 + 0, D, hip_mask, reset, inv_dt, a4.x, la4.x, tq4.x, ldv4.x, s0.x, s0.y, u[0], acc, head_row);
-            joint_update(c, d0 + 1, D, hip_mask, reset, inv_dt, a4.y, la4.y, tq4.y, ldv4.y, s0.z, s0.w, u[1], acc, head_row);
-            joint_update(c, d0 + 2, D, hip_mask, reset, inv_dt, a4.z, la4.z, tq4.z, ldv4.z, s1.x, s1.y, u[2], acc, head_row);
-            joint_update(c, d0 + 3, D, hip_mask, reset, inv_dt, a4.w, la4.w, tq4.w, ldv4.w, s1.z, s1.w, u[3], acc, head_row);
-            *reinterpret_cast<float4*>(ldv_p + d0) = make_float4(s0.y, s0.w, s1.y, s1.w);   // last_dof_vel = dof_vel (:137)
-            if (reset) {
-              *reinterpret_cast<float4*>(dof_g + 2 * d0) = s0;
-              *reinterpret_cast<float4*>(dof_g + 2 * d0 + 4) = s1;
-            }
+            uint4 nb = make_uint4(0, 0, 0, 0);
+            if (!TAPS && add_noise) nb = philox_keyed(a.pk, csc, env_global, LGK_SITE_NOISE_HEAD + 3 + pc);
+            float hv[3];
+            joint_update(c, d0 + 0, hip_mask, reset, inv_dt, a2.x, la2.x, tq2.x, ldv2.x, s0.x, s0.y, u[0], acc, hv);
+            head_row[12 + d0] = head_obs<TAPS>(hv[0], 12 + d0, nb, 0, s_ns, trow, clip_obs);
+            head_row[12 + D + d0] = head_obs<TAPS>(hv[1], 12 + D + d0, nb, 1, s_ns, trow, clip_obs);
+            head_row[12 + 2 * D + d0] = head_obs<TAPS>(hv[2], 12 + 2 * D + d0, nb, 2, s_ns, trow, clip_obs);
+            joint_update(c, d0 + 1, hip_mask, reset, inv_dt, a2.y, la2.y, tq2.y, ldv2.y, s0.z, s0.w, u[1], acc, hv);
+            head_row[13 + d0] = head_obs<TAPS>(hv[0], 13 + d0, nb, 3, s_ns, trow, clip_obs);
+            head_row[13 + D + d0] = head_obs<TAPS>(hv[1], 13 + D + d0, nb, 4, s_ns, trow, clip_obs);
+            head_row[13 + 2 * D + d0] = head_obs<TAPS>(hv[2], 13 + 2 * D + d0, nb, 5, s_ns, trow, clip_obs);
+            *reinterpret_cast<float2*>(ldv_p + d0) = make_float2(s0.y, s0.w);   // last_dof_vel = dof_vel (:137)
+            if (reset) *reinterpret_cast<float4*>(dof_g + 2 * d0) = s0;
           }
         } else {
           const int half = (D + 1) / 2;
@@ -714,11 +678,18 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
               if (TAPS) u = b.tap_dof[(size_t)env * D + d];
               else {
                 const uint4 r = philox_cold(a, csc, env_global, LGK_SITE_DOF + (d >> 2));
-                const unsigned rr[4] = {r.x, r.y, r.z, r.w};
-                u = u01(rr[d & 3]);
+                u = u01(philox_word(r, d & 3));
               }
             }
-            joint_update(c, d, D, hip_mask, reset, inv_dt, av, lav, tqv, ldvv, p, v, u, acc, head_row);
+            uint4 nb = make_uint4(0, 0, 0, 0);
+            if (!TAPS && add_noise) nb = philox_cold(a, csc, env_global, LGK_SITE_NOISE_HEAD + 3 + (d >> 1));
+            // fields 3 * (d & 1) .. + 2 of the pair's block, rotated down to fields 0..2
+            if (d & 1) nb = make_uint4((nb.y >> 16) | (nb.z << 16), nb.z >> 16, 0, 0);
+            float hv[3];
+            joint_update(c, d, hip_mask, reset, inv_dt, av, lav, tqv, ldvv, p, v, u, acc, hv);
+            head_row[12 + d] = head_obs<TAPS>(hv[0], 12 + d, nb, 0, s_ns, trow, clip_obs);
+            head_row[12 + D + d] = head_obs<TAPS>(hv[1], 12 + D + d, nb, 1, s_ns, trow, clip_obs);
+            head_row[12 + 2 * D + d] = head_obs<TAPS>(hv[2], 12 + 2 * D + d, nb, 2, s_ns, trow, clip_obs);
             ldv_p[d] = v;
             if (reset) { dof_g[2 * d] = p; dof_g[2 * d + 1] = v; }
           }
@@ -728,13 +699,35 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 #pragma unroll
       for (int i = 0; i < 10; ++i) jp[i * TILE] = acc.v[i];
     } else {
-      // ---- W3: contacts (:895-897, :951-962, cassie.py:43-46) and feet air time (:941-949) -------
-      float collisions = 0.f, ffp = 0.f, r_air = 0.f;
-      bool stumble = false;
-      int nofly = 0;
+      // ---- W3: body-frame velocities and gravity (:123-125), contacts (:895-897, :951-962, cassie.py:43-46),
+      //      feet air time (:941-949) ---------------------------------------------------------------------
       if (active) {
-        // four bodies per trip: the index loads (constant bank, dynamic offset), the row reads and the
-        // square roots of a trip are independent, so their latencies overlap instead of adding up
+        {
+          const float* rp = sm + L.root + lane * 13;
+          const float q[4] = {rp[3], rp[4], rp[5], rp[6]};
+          quat_rotate_inverse(q, rp[7], rp[8], rp[9], blv);
+          quat_rotate_inverse(q, rp[10], rp[11], rp[12], bav);
+          quat_rotate_inverse(q, 0.f, 0.f, -1.f, grav);
+          float* p = b.base_lin_vel + (size_t)env * 3; p[0] = blv[0]; p[1] = blv[1]; p[2] = blv[2];
+          p = b.base_ang_vel + (size_t)env * 3;        p[0] = bav[0]; p[1] = bav[1]; p[2] = bav[2];
+          p = b.projected_gravity + (size_t)env * 3;   p[0] = grav[0]; p[1] = grav[1]; p[2] = grav[2];
+          // obs head columns 0..8 (:217-219): fields 0..7 of one block, field 0 of the next
+          uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
+          if (!TAPS && add_noise) {
+            n0 = philox_keyed(a.pk, csc, env_global, LGK_SITE_NOISE_HEAD + 0);
+            n1 = philox_keyed(a.pk, csc, env_global, LGK_SITE_NOISE_HEAD + 1);
+          }
+          head_row[0] = head_obs<TAPS>(blv[0] * c.obs_scale_lin_vel, 0, n0, 0, s_ns, trow, clip_obs);
+          head_row[1] = head_obs<TAPS>(blv[1] * c.obs_scale_lin_vel, 1, n0, 1, s_ns, trow, clip_obs);
+          head_row[2] = head_obs<TAPS>(blv[2] * c.obs_scale_lin_vel, 2, n0, 2, s_ns, trow, clip_obs);
+          head_row[3] = head_obs<TAPS>(bav[0] * c.obs_scale_ang_vel, 3, n0, 3, s_ns, trow, clip_obs);
+          head_row[4] = head_obs<TAPS>(bav[1] * c.obs_scale_ang_vel, 4, n0, 4, s_ns, trow, clip_obs);
+          head_row[5] = head_obs<TAPS>(bav[2] * c.obs_scale_ang_vel, 5, n0, 5, s_ns, trow, clip_obs);
+          head_row[6] = head_obs<TAPS>(grav[0], 6, n0, 6, s_ns, trow, clip_obs);
+          head_row[7] = head_obs<TAPS>(grav[1], 7, n0, 7, s_ns, trow, clip_obs);
+          head_row[8] = head_obs<TAPS>(grav[2], 8, n1, 0, s_ns, trow, clip_obs);
+        }
+        // four bodies per trip: the row reads of a trip are independent, so their latencies overlap
 #pragma unroll 1
         for (int p0 = 0; p0 < c.num_pen; p0 += 4) {
           float n[4];
@@ -746,9 +739,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) collisions += (p0 + j < c.num_pen && n[j] > a.thr_pen) ? 1.f : 0.f;   // norm > 0.1
         }
-        LGK_STAMP(10);
         const float* fa_in = sm + L.fat + lane * F;
         float* fa_out = b.feet_air_time + (size_t)env * F;
+        bool stumble = false;
+        int nofly = 0;
 #pragma unroll 2
         for (int k = 0; k < F; ++k) {
           const float* f = cf_row + s_idx[IDX_FEET + k];
@@ -773,20 +767,16 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           }
           if (a.air_active || reset) fa_out[k] = reset ? 0.f : t;   // zeroed on reset (:178)
         }
+        stumble_f = stumble ? 1.f : 0.f;
+        nofly_f = (nofly == 1) ? 1.f : 0.f;
       }
-      LGK_STAMP(11);
-      scr[SC_COLL * TILE + lane] = collisions;
-      scr[SC_FFP * TILE + lane] = ffp;
-      scr[SC_RAIR * TILE + lane] = r_air;       // masked by |cmd_xy| > 0.1 in stage 3
-      scr[SC_STUMBLE * TILE + lane] = stumble ? 1.f : 0.f;
-      scr[SC_NOFLY * TILE + lane] = (nofly == 1) ? 1.f : 0.f;
     }
     LGK_STAMP(2);
     fence_proxy_async_smem();   // last_dof_vel rows (W1 / W2) -> visible to the bulk store
     __syncthreads();
     LGK_STAMP(3);
 
-    // ---- outputs that are complete after stage 1; id-list compaction by the last mask publisher ---
+    // ---- outputs that are complete after stage 1 ------------------------------------------------------
     if (full) {
       if (tid == 32) {
         bulk_s2g(b.last_actions + (size_t)env0 * D, sm + L.act, ne * 4 * D);   // last_actions = actions (:136)
@@ -796,309 +786,111 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
     } else if (wic > 0) {
       tile_store_fallback(a, sm, env0, ne, tid);
     }
-    if (wic == 3 && lane < ne) {
-      // episode-sum rows ([R, N], 128 B per row and tile): 4-byte cp.async (LDGSTS) per lane and row into
-      // rows the joints no longer need; in flight during stage 2, awaited before the stage-3 barrier
-      const float* src = b.episode_sums + env0 + lane;
-      const unsigned dst = smem_u32(sm + L.sums + lane);
-#pragma unroll 1
-      for (int r = 0; r < num_rows; ++r)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + (unsigned)r * (RS * 4)),
-                     "l"(src + (size_t)r * N) : "memory");
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-
-  // =========================================== stage 2 ===========================================
-  // one env at a time per warp, lanes over observation columns: noise on the head, then the H scan
-  // points in NP passes of 32.  All gathers of an env are issued before any is consumed.  The index
-  // chain runs on packed f32x2 instructions (x and y of a point share every operation; each packed
-  // op rounds its halves like the scalar op, so the result is bit-identical to the op-by-op chain).
-  {
-    constexpr int NPA = NP > 0 ? NP : 1;
-    const bool add_noise = flags & LGK_F_ADD_NOISE;
-    const bool plane = flags & LGK_F_TERRAIN_PLANE;
-    const float inv_hs = 1.0f / c.horizontal_scale;
-    const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
-    const float clip_obs = c.clip_obs;
-    // this lane's scan offsets and noise amplitudes (same for every env); lanes past H repeat point 0
-    float2 pxy_l[NPA];
-    float ns_h[NPA];
-#pragma unroll
-    for (int it = 0; it < NP; ++it) {
-      const int h = it * 32 + lane;
-      const bool ok = h < H;
-      pxy_l[it].x = ok ? __ldg(b.height_points_xy + 2 * h) : 0.f;
-      pxy_l[it].y = ok ? __ldg(b.height_points_xy + 2 * h + 1) : 0.f;
-      ns_h[it] = (ok && add_noise) ? __ldg(b.noise_scale_vec + OH + h) : 0.f;
-    }
-    const float ns_a = (add_noise && lane < OH) ? __ldg(b.noise_scale_vec + lane) : 0.f;
-    const float ns_b = (add_noise && lane + 32 < OH) ? __ldg(b.noise_scale_vec + lane + 32) : 0.f;
-    // obs = clip(v + (2*rand - 1) * noise_scale_vec, +-clip_observations)   (:231, :104)
-    auto noisy = [&](float v, const float* __restrict__ trow, int col, unsigned rw, int half, float ns, bool clip) {
-      if (TAPS) {
-        if (add_noise) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(trow + col)), 1.0f), ns));
-      } else {
-        // 2^23 + r16 as a float (one PRMT, no I2F on the quarter-rate conversion unit), then
-        // (2^23 + r16) * 2^-15 - 257 = r16 / 2^15 - 1, exact: uniform on [-1, 1) in steps of 2^-15; ns = 0 without noise
-        const unsigned m = half ? __byte_perm(rw, 0x4b000000u, 0x7632) : __byte_perm(rw, 0x4b000000u, 0x7610);
-        v = fmaf(fmaf(__uint_as_float(m), 3.0517578125e-05f, -257.0f), ns, v);
-      }
-      return clip ? clampf(v, -clip_obs, clip_obs) : v;
-    };
-    // the scan columns are bounded by obs_scale_height * 1 + noise: when that is inside clip_observations
-    // for every column (warp-uniform), their clip is the identity and is skipped
-    bool clip_h = false;
-#pragma unroll
-    for (int it = 0; it < NP; ++it) clip_h |= !(fabsf(c.obs_scale_height) + fabsf(ns_h[it]) <= clip_obs);
-    clip_h = __any_sync(LGK_FULL_MASK, clip_h);
-    float* hpart = sm + L.cf + HP_OFF;   // [env][RS]; torques / last_actions rows are dead after stage 1
-    const float2 border2 = make_float2(c.border_size, c.border_size);
-    const float2 inv2 = make_float2(inv_hs, inv_hs);
-    // U envs in flight per warp (e, e + 4, ...): a single env's instruction stream is a chain of
-    // dependent latencies (index chain -> gather -> scale / noise -> store), so the warp interleaves U of them
-    constexpr int U = LGK_STAGE2_ENVS;
-    for (int e0 = wic; e0 < ne; e0 += LGK_WARPS_PER_CTA * U) {
-      int eu[U];
-      bool live[U];
-      float zo[U];
-      int raw[U][NPA];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        eu[u] = e0 + u * LGK_WARPS_PER_CTA;
-        live[u] = eu[u] < ne;
-        if (!live[u]) eu[u] = e0;   // a dead slot recomputes the first env; its stores are predicated off
-      }
-      // ---- phase A: height-field indices of every pass, gathers in flight --------------------------
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const float4* es = reinterpret_cast<const float4*>(scr + SC_ES * TILE + eu[u] * ES_W);
-        const float4 esa = es[0], esb = es[1], esc = es[2];
-        zo[u] = esc.w;
-        if (NP > 0 && !plane) {
-          // quat_apply(normalize([0,0,qz,qw]), (px,py,0)) + root_pos, op for op (no contraction):
-          //   t = 2 * cross(xyz, p) = (-2qz*py, 2qz*px); r = p + w*t + cross(xyz, t) = p + qw*t + (-qz*ty, qz*tx)
-          const float2 k_t = make_float2(esa.x, esa.y), k_ts = make_float2(esa.z, esa.w);
-          const float2 qw2 = make_float2(esb.x, esb.y), k_c = make_float2(esb.z, esb.w), r2 = make_float2(esc.x, esc.y);
-#pragma unroll
-          for (int it = 0; it < NP; ++it) {
-            const float2 p = pxy_l[it], pyx = make_float2(p.y, p.x);
-            const float2 t = __fmul2_rn(k_t, pyx);     // (tx, ty)
-            const float2 ts = __fmul2_rn(k_ts, p);     // (ty, tx)
-            float2 w = __fadd2_rn(p, __fmul2_rn(qw2, t));
-            w = __fadd2_rn(w, __fmul2_rn(k_c, ts));
-            w = __fadd2_rn(__fadd2_rn(w, r2), border2);
-            // (points / horizontal_scale).long(): truncation toward zero (:842)
-            float2 sxy;
-            if (MUL_RCP) sxy = __fmul2_rn(w, inv2);
-            else sxy = make_float2(__fdiv_rn(w.x, c.horizontal_scale), __fdiv_rn(w.y, c.horizontal_scale));
-#ifdef LGK_F2I_ON_XU
-            int ix = __float2int_rz(sxy.x), iy = __float2int_rz(sxy.y);
-#else
-            // trunc toward zero without the quarter-rate conversion unit: 2^23 + s, rounded toward zero, holds
-            // trunc(s) in its mantissa for 0 <= s < 2^23; s < 0 lands below 2^23 (negative after the subtraction,
-            // clipped to 0 like trunc(s) would be), s >= 2^23 / NaN above the clip's upper bound
-            const float2 mg = __fadd2_rz(sxy, make_float2(8388608.0f, 8388608.0f));
-            int ix = __float_as_int(mg.x) - 0x4b000000, iy = __float_as_int(mg.y) - 0x4b000000;
-#endif
-            ix = __vimin_s32_relu(ix, max_px);   // clip(0, max): one VIMNMX.RELU
-            iy = __vimin_s32_relu(iy, max_py);
-            raw[u][it] = __ldg(b.height_min3 + (unsigned)(ix * c.terrain_pitch + iy));
-          }
-        } else {
-#pragma unroll
-          for (int it = 0; it < NPA; ++it) raw[u][it] = 0;
-        }
-      }
-      // ---- observation head (covers the gather latency) --------------------------------------------
-      // noise field j of this lane (head: j = 0, 1; scan pass it: j = 2 + it) = 16-bit half (j & 1) of
-      // word (j % 8) / 2 of Philox block LGK_SITE_NOISE + 3 * lane + j / 8: one block covers 6 passes
-      uint4 rnd[U];
-      float* orow[U];
-      const float* trow[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int env_e = env0 + eu[u];
-        orow[u] = b.obs_buf + (size_t)env_e * O;
-        trow[u] = TAPS ? b.tap_noise + (size_t)env_e * O : nullptr;
-        rnd[u] = make_uint4(0, 0, 0, 0);
-        if (!TAPS && add_noise) rnd[u] = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env_e), LGK_SITE_NOISE + 3 * lane);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const float* hrow = sm + L.head + eu[u] * HS;
-        const float o0 = noisy(hrow[lane], trow[u], lane, rnd[u].x, 0, ns_a, true);
-        if (live[u] && lane < OH) orow[u][lane] = o0;
-        if (lane + 32 < OH) {
-          const float o1 = noisy(hrow[lane + 32], trow[u], lane + 32, rnd[u].x, 1, ns_b, true);
-          if (live[u]) orow[u][lane + 32] = o1;
-        }
-      }
-      // ---- phase B: heights -> observation columns (two copies: with and without the final clip) ----
-      auto phase_b = [&](auto clip_tag) {
-        constexpr bool CLIP = decltype(clip_tag)::value;
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          float hsum = 0.f;
-#pragma unroll
-          for (int it = 0; it < NP; ++it) {
-            if (!TAPS && add_noise && it == 6)
-              rnd[u] = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env0 + eu[u]), LGK_SITE_NOISE + 3 * lane + 1);
-            const int w = ((it + 2) >> 1) & 3;
-            const unsigned rw = w == 0 ? rnd[u].x : w == 1 ? rnd[u].y : w == 2 ? rnd[u].z : rnd[u].w;
-            const int h = it * 32 + lane;
-            // the specialised instantiations run with ceil(H / 32) == NP: only the last pass holds lanes past H
-            const bool ok = (DT > 0 && it < NP - 1) ? true : h < H;
-            const float hgt = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
-            hsum += ok ? hgt : 0.f;
-            const float v = clampf(sub_rn(zo[u], hgt), -1.f, 1.f) * c.obs_scale_height;
-            const float o = noisy(v, trow[u], ok ? OH + h : 0, rw, it & 1, ns_h[it], CLIP);
-            if (ok && live[u]) orow[u][OH + h] = o;
-          }
-          if (b.measured_heights != nullptr && live[u]) {   // optional materialisation of measured_heights [N,H]
-            float* mrow = b.measured_heights + (size_t)(env0 + eu[u]) * H;
-#pragma unroll
-            for (int it = 0; it < NP; ++it)
-              if (it * 32 + lane < H) mrow[it * 32 + lane] = mul_rn(s16_to_float(raw[u][it]), c.vertical_scale);
-          }
-          // _reward_base_height (:871) needs mean_h(height): this lane's partial sum; added up in stage 3
-          if (a.bh_active && live[u]) hpart[eu[u] * RS + lane] = hsum;
-        }
-      };
-      if (clip_h) phase_b(std::true_type{});
-      else phase_b(std::false_type{});
-    }
-  }
-  LGK_STAMP(4);
-  // =========================================== stage 3 ===========================================
-  // reward terms in the reference's order (:195-212), episode sums, statistics; all four warps:
-  //   A (lane = env)  each warp puts its share of the term values into the table rv[term][env]
-  //   -- barrier --
-  //   then warp w alone for the envs [w * epw, (w + 1) * epw) of the sub-tile:
-  //   B (lane = row)  r = value * scale, episode sum += r, statistics over the reset envs; the lanes
-  //                   work on independent rows, so nothing here waits on a neighbour or on a constant
-  //   C (lane = (row group, env))  reward = ordered sum of the rows' r; the sums leave in 32-byte sectors
-  {
-    if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows before anything refills them
-    float* rv = sm + L.cf;     // [LGK_REW_COUNT + 1][RS]   (the contact rows are dead by now)
-    float* rr = sm + L.head;   // [num_rows][RS]            (written after the barrier: the heads have left)
-    float* sums = sm + L.sums; // [num_rows][RS]
-    {
-      auto J = [&](int k) { return scr[(SC_J1 + k) * TILE + lane] + scr[(SC_J2 + k) * TILE + lane]; };
-      auto put = [&](int term, float v) { rv[term * RS + lane] = v; };
-      if (wic == 0) {          // the terms on W0's registers
-        const float cn = sqrtf(fmaf(cmd_rew.y, cmd_rew.y, cmd_rew.x * cmd_rew.x));
-        put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
-        put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
-        put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
-        put(LGK_REW_FEET_AIR_TIME, scr[SC_RAIR * TILE + lane] * ((cn > 0.1f) ? 1.f : 0.f));
-        put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
-        const float e = cmd_rew.z - bav[2];
-        put(LGK_REW_TRACKING_ANG_VEL, expf(-(e * e) / c.tracking_sigma));
-        const float ex = cmd_rew.x - blv[0], ey = cmd_rew.y - blv[1];
-        put(LGK_REW_TRACKING_LIN_VEL, expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma));
-      } else if (wic == 1) {
-        put(LGK_REW_ACTION_RATE, J(A_ARATE));
-        put(LGK_REW_DOF_ACC, J(A_ACC2));
-        put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
-        put(LGK_REW_DOF_VEL, J(A_QD2));
-        put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
-      } else if (wic == 2) {
-        put(LGK_REW_ENERGY, J(A_ENERGY));
-        put(LGK_REW_HIP_MOTION, J(A_HIP));
-        put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
-        put(LGK_REW_TORQUES, J(A_TQ2));
-      } else {
-        put(LGK_REW_COLLISION, scr[SC_COLL * TILE + lane]);
-        put(LGK_REW_FEET_CONTACT_FORCES, scr[SC_FFP * TILE + lane]);
-        put(LGK_REW_NO_FLY, scr[SC_NOFLY * TILE + lane]);
-        put(LGK_REW_STUMBLE, scr[SC_STUMBLE * TILE + lane]);
-        put(LGK_REW_COUNT, (reset && !time_out) ? 1.f : 0.f);   // the termination row's value (:210-212)
-      }
-    }
-    if (wic == 3) asm volatile("cp.async.wait_group 0;" ::: "memory");   // this lane's episode-sum words have landed
-    __syncthreads();   // table and base-height partial sums complete, observation heads consumed
-    LGK_STAMP(5);
-    const int epw = (ne + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA;   // envs per warp (<= 8)
-    const int e_lo = wic * epw, e_hi = min(e_lo + epw, ne);
-    const int el = lane & 7, q = lane >> 3;
-    {   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height);
-        // lane (q, el) adds a quarter of the partial sums of env e_lo + el
-      const int e = min(e_lo + el, TILE - 1);
-      float bh = scr[SC_ES * TILE + e * ES_W + 10];   // root z before the reset
-      if (a.bh_active && H > 0) {
-        const float* hp = sm + L.cf + HP_OFF + e * RS + q * 8;
-        float hs = 0.f;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) hs += hp[k];
-        hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 8);
-        hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 16);
-        bh -= hs / (float)H;
-      }
-      const float d = bh - c.base_height_target;
-      if (q == 0 && e_lo + el < e_hi) rv[LGK_REW_BASE_HEIGHT * RS + e] = d * d;
-    }
-    __syncwarp();
-    LGK_STAMP(8);
-    const unsigned my_resets = reset_mask & (e_hi > e_lo ? ((0xffffffffu >> (32 - (e_hi - e_lo))) << e_lo) : 0u);
-    if (lane < num_rows) {
-      const int row_term = s_row_term[lane];
-      const float row_scale = s_row_scale[lane];
-      float* srow = sums + lane * RS;
-      float* rrow = rr + lane * RS;
-      float stat = 0.f;
-      if (row_term != LGK_REW_EXTERNAL) {
-        const float* vrow = rv + row_term * RS;
-#pragma unroll 4
-        for (int e = e_lo; e < e_hi; ++e) {
-          const float r = mul_rn(vrow[e], row_scale);
-          const float total = add_rn(srow[e], r);
-          const bool rs = (reset_mask >> e) & 1u;
-          rrow[e] = r;
-          srow[e] = rs ? 0.f : total;   // zeroed for reset envs after the statistics read it (:184-185)
-          stat += rs ? total : 0.f;
-        }
-      } else {
-        const float* xrow = b.ext_rewards != nullptr ? b.ext_rewards + (size_t)s_row_ext[lane] * N + env0 : nullptr;
-#pragma unroll 1
-        for (int e = e_lo; e < e_hi; ++e) {
-          const float r = mul_rn(xrow != nullptr ? xrow[e] : 0.f, row_scale);
-          const float total = add_rn(srow[e], r);
-          const bool rs = (reset_mask >> e) & 1u;
-          rrow[e] = r;
-          srow[e] = rs ? 0.f : total;
-          stat += rs ? total : 0.f;
-        }
-      }
-      if (my_resets != 0u) atomicAdd(&ws->stats[parity][lane], stat);
-    }
-    LGK_STAMP(9);
-    __syncwarp();
-    LGK_STAMP(7);
-    const int e_mine = e_lo + el;
-    if (e_mine < e_hi) {
-      if (q == 0) {
-        float rew = 0.f;
-        const int nrew = c.num_rewards;
-#pragma unroll 4
-        for (int i = 0; i < nrew; ++i) rew = add_rn(rew, rr[i * RS + e_mine]);
-        if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
-        // termination term is added after the positive clip (:206-212)
-        if (flags & LGK_F_HAS_TERMINATION) rew = add_rn(rew, rr[nrew * RS + e_mine]);
-        b.rew_buf[env0 + e_mine] = rew;
-      }
-      float* grow = b.episode_sums + env0 + e_mine;
+    if (wic < 3) {
+      // ---- W0..W2: the staged heads -> observation rows, lanes = columns, 128 B per warp store -------------
 #pragma unroll 2
-      for (int i = q; i < num_rows; i += 4) grow[(size_t)i * N] = sums[i * RS + e_mine];
+      for (int e = wic; e < ne; e += 3) {
+        const float* hrow = sm + L.head + e * HS;
+        float* orow = b.obs_buf + (size_t)(env0 + e) * O;
+        const float o0 = hrow[lane];
+        if (lane + 32 < OH) orow[lane + 32] = hrow[lane + 32];
+        if (lane < OH) orow[lane] = o0;
+      }
+      if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows before the next loads
+      LGK_STAMP(4);
+    } else {
+      // =========================================== stage 3 ===========================================
+      // W3, lane = env: every term's value into the table rv[term][env] (the contact rows are dead by now), then
+      // the episode-sum rows in the reference's order (:195-212)
+      float* rv = sm + L.rv;
+      const float* sums = sm + L.sums;
+      auto put = [&](int term, float v) { rv[term * TILE + lane] = v; };
+      auto J = [&](int k) { return scr[(SC_J1 + k) * TILE + lane] + scr[(SC_J2 + k) * TILE + lane]; };
+      const float cx = scr[SC_CMDX * TILE + lane], cy = scr[SC_CMDY * TILE + lane], cz = scr[SC_CMDZ * TILE + lane];
+      const float cn = sqrtf(fmaf(cy, cy, cx * cx));
+      put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
+      put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
+      put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
+      put(LGK_REW_FEET_AIR_TIME, r_air * ((cn > 0.1f) ? 1.f : 0.f));
+      put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
+      {
+        const float e = cz - bav[2];
+        put(LGK_REW_TRACKING_ANG_VEL, expf(-(e * e) / c.tracking_sigma));
+        const float ex = cx - blv[0], ey = cy - blv[1];
+        put(LGK_REW_TRACKING_LIN_VEL, expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma));
+      }
+      put(LGK_REW_ACTION_RATE, J(A_ARATE));
+      put(LGK_REW_DOF_ACC, J(A_ACC2));
+      put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
+      put(LGK_REW_DOF_VEL, J(A_QD2));
+      put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
+      put(LGK_REW_ENERGY, J(A_ENERGY));
+      put(LGK_REW_HIP_MOTION, J(A_HIP));
+      put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
+      put(LGK_REW_TORQUES, J(A_TQ2));
+      put(LGK_REW_COLLISION, collisions);
+      put(LGK_REW_FEET_CONTACT_FORCES, ffp);
+      put(LGK_REW_NO_FLY, nofly_f);
+      put(LGK_REW_STUMBLE, stumble_f);
+      put(LGK_REW_EXTERNAL, 0.f);
+      put(LGK_REW_COUNT, (reset && !time_out) ? 1.f : 0.f);   // the termination row's value (:210-212)
+      float bh = scr[SC_ZPRE * TILE + lane];
+      if (a.scan_first) {
+        // from here on the scan kernel's writes are visible: the scan columns of every env, the height sums
+        pdl_wait();
+        LGK_STAMP(5);
+        unsigned m = reset_mask;
+        while (m) {   // warp-uniform; ~1 % of the envs
+          const int e = __ffs(m) - 1;
+          m &= m - 1;
+          lgk_scan_fixup_env<TAPS, MUL_RCP>(a, scr + SC_ES * TILE + e * 8, env0 + e, csc);
+        }
+        // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height)
+        if (a.bh_active && active) bh -= a.hsum[env] / (float)c.num_height_points;
+      }
+      {
+        const float d = bh - c.base_height_target;
+        put(LGK_REW_BASE_HEIGHT, d * d);
+      }
+      __syncwarp();
+      if (active) {
+        float rew = 0.f;
+        int xi = 0;   // index among the external rows
+        const int nrew = c.num_rewards;
+        float* gsum = b.episode_sums + env;
+        float* stat = ws->stats[parity];
+#pragma unroll 4
+        for (int r = 0; r < nrew; ++r) {
+          const int term = c.rewards[r].term;
+          float v = rv[term * TILE + lane];
+          if (term == LGK_REW_EXTERNAL) {   // a python _reward_<name> of a subclass, evaluated by the host
+            v = b.ext_rewards[(size_t)xi * N + env];
+            ++xi;
+          }
+          const float rr = mul_rn(v, c.rewards[r].scale);
+          const float total = add_rn(sums[r * TILE + lane], rr);
+          rew = add_rn(rew, rr);
+          gsum[(size_t)r * N] = reset ? 0.f : total;   // zeroed for reset envs after the statistics read it (:184-185)
+          if (reset) atomicAdd(stat + r, total);
+        }
+        if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
+        if (flags & LGK_F_HAS_TERMINATION) {   // added after the positive clip (:206-212)
+          const float rr = mul_rn(rv[LGK_REW_COUNT * TILE + lane], c.termination_scale);
+          const float total = add_rn(sums[nrew * TILE + lane], rr);
+          rew = add_rn(rew, rr);
+          gsum[(size_t)nrew * N] = reset ? 0.f : total;
+          if (reset) atomicAdd(stat + nrew, total);
+        }
+        b.rew_buf[env] = rew;
+      }
+      LGK_STAMP(6);
     }
-  }
-  LGK_STAMP(6);
   }   // sub-tiles
   if (wic == 0 && lane == 0) LGK_CTA_STAMP(1);
 #ifdef LGK_PROFILE
-  if (tid == 96 && blockIdx.x < 4096) lgk_prof_cta[blockIdx.x * 4 + 3] = lgk_gtime();   // W3 leaves
+  if (wic == 3 && lane == 0 && blockIdx.x < 4096) lgk_prof_cta[blockIdx.x * 4 + 3] = lgk_gtime();   // W3 leaves
 #endif
 }
-
 // ---------------------------------------------------------------------------------------------
 static inline int up4(int x) { return (x + 3) & ~3; }
 // the largest float x with sqrtf(x) <= c  (c >= 0; host sqrtf is correctly rounded like the device's sqrt.rn)
@@ -1222,14 +1014,36 @@ extern "C" int lgk_pre_reward_state_impl(const LgkConsts* c, const LgkBuffers* b
   return (int)cudaGetLastError();
 }
 
-template <int DT, bool TAPS, bool MUL_RCP, int NP>
-static int launch_step(const StepArgs& args, int grid, size_t smem, cudaStream_t stream) {
-  auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP, NP>;
-  static size_t configured = 0;   // per instantiation
-  if (smem > 48 * 1024 && smem > configured) {
-    LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+// per-device facts and per-(device, kernel) set-up, looked up from the stream's device on every call: the library
+// keeps no process-wide "current" state (two envs on two devices, or on two streams of one, never share any)
+#define LGK_MAX_DEVICES 64
+struct DeviceInfo { int num_sms; };
+static int device_of_stream(cudaStream_t st, int* dev) {
+  if (cudaStreamGetDevice(st, dev) == cudaSuccess) return 0;
+  (void)cudaGetLastError();
+  return (int)cudaGetDevice(dev);
+}
+static int device_info(int dev, DeviceInfo* out) {
+  static DeviceInfo info[LGK_MAX_DEVICES];
+  static bool known[LGK_MAX_DEVICES];   // idempotent: a race writes the same values twice
+  if (dev < 0 || dev >= LGK_MAX_DEVICES) return LGK_ERR_DIM;
+  if (!known[dev]) {
+    LGK_CUDA_RETURN_IF(cudaDeviceGetAttribute(&info[dev].num_sms, cudaDevAttrMultiProcessorCount, dev));
+    known[dev] = true;
   }
+  *out = info[dev];
+  return 0;
+}
+
+template <int DT, bool TAPS, bool MUL_RCP>
+static int launch_step(const StepArgs& args, int dev, int grid, size_t smem, cudaStream_t stream) {
+  auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP>;
+  static size_t configured[LGK_MAX_DEVICES];   // per instantiation and device; the attribute is per device
+  if (smem > 48 * 1024 && smem > configured[dev]) {
+    LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[dev] = smem;
+  }
+  if (args.scan_first) { const int rc = lgk_scan_launch(args, stream); if (rc) return rc; }
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(kern, dim3(grid), dim3(LGK_CTA_THREADS), smem, stream, args));
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(lgk_step_epilogue_kernel, dim3(1), dim3(EPI_THREADS), 0, stream, args, grid));
   return (int)cudaGetLastError();
@@ -1239,10 +1053,13 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   StepArgs args;
   args.c = *c;
   args.b = *b;
-  const int D = c->num_dof, B3 = c->num_bodies * 3, F = c->num_feet, O = c->num_obs;
+  const int D = c->num_dof, B3 = c->num_bodies * 3, F = c->num_feet;
   const int OH = 12 + 3 * D;
   args.num_rows = c->num_rewards + ((c->flags & LGK_F_HAS_TERMINATION) ? 1 : 0);
   args.head_stride = OH | 1;
+  args.one = 1.0f;
+  args.scan_first = c->num_height_points > 0 ? 1 : 0;
+  args.hsum = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_hsum_offset(c->num_envs));
   fill_rng_and_thresholds(args, c);
   args.hip_mask = 0u;
   for (int h = 0; h < c->num_hip; ++h) args.hip_mask |= 1u << c->hip_idx[h];
@@ -1263,19 +1080,16 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   L.fat = o;  o += up4(TILE * (F > 0 ? F : 1));
   L.ep = o;   o += TILE * 2;
   L.lvl = o;  o += TILE * 2;
-  L.head = o; o += (TILE * args.head_stride > RS * args.num_rows) ? up4(TILE * args.head_stride) : up4(RS * args.num_rows);   // later: reward rows
-  L.scr = o;  o += TILE * SC_FIELDS;
-  // contact rows; later the reward table [LGK_REW_COUNT + 1][RS] and, running on into the torque /
-  // last_actions rows, the base-height partial sums [TILE][RS]
+  // contact rows; after the barrier the table of term values [LGK_REW_COUNT + 1][TILE] of stage 3
   {
-    const int need = HP_OFF + TILE * RS - 2 * up4(TILE * D);
-    L.cf = o; o += up4(TILE * B3 > need ? TILE * B3 : need);
+    const int rv = (LGK_REW_COUNT + 1) * TILE;
+    L.cf = o; L.rv = o; o += up4(TILE * B3 > rv ? TILE * B3 : rv);
   }
   L.tq = o;   o += up4(TILE * D);
   L.lact = o; o += up4(TILE * D);
-  // episode-sum rows [num_rows][RS]: loaded after stage 1, over the dof_state rows when they fit
-  if (RS * args.num_rows <= up4(TILE * 2 * D)) L.sums = L.dof;
-  else { L.sums = o; o += up4(RS * args.num_rows); }
+  L.sums = o; o += TILE * (args.num_rows > 0 ? args.num_rows : 1);   // episode-sum rows [num_rows][TILE]
+  L.head = o; o += up4(TILE * args.head_stride);
+  L.scr = o;  o += TILE * (SC_FIELDS + 8);
   L.total = o;
   const size_t smem = (size_t)L.total * sizeof(float);
   if (smem > 200 * 1024) return LGK_ERR_DIM;
@@ -1298,18 +1112,14 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   args.tma_ok = (c->num_envs % 4 == 0) && al16(b->root_states) && al16(b->dof_state) && al16(b->contact_forces) &&
                 al16(b->torques) && al16(b->actions) && al16(b->last_actions) && al16(b->last_dof_vel) &&
                 al16(b->commands) && al16(b->feet_air_time) && al16(b->episode_length_buf) &&
-                al16(b->episode_sums) && al16(b->obs_buf) && (b->terrain_levels == nullptr || al16(b->terrain_levels));
-  // Grid: the tile is latency-bound, so what counts is how many tiles are resident.  More
-  // envs than one wave of 32-env tiles: one tile per CTA, the hardware scheduler backfills the slots
-  // (measured at 65536 envs: 0.087 ms; equal persistent ranges 0.105 ms; smaller tiles for the last
-  // wave 0.094 ms).  Fewer: the envs are dealt to all the resident slots in equal smaller tiles (4096
-  // envs: 8-env tiles, 0.024 ms instead of 0.040 ms).  envs_per_cta > 0 overrides both.
-  static int num_sms = 0;
-  if (num_sms == 0) {
-    int dev = 0;
-    LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
-    LGK_CUDA_RETURN_IF(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+                (args.num_rows == 0 || al16(b->episode_sums)) && (b->terrain_levels == nullptr || al16(b->terrain_levels));
+  // Grid.  More envs than one wave of 32-env tiles: one tile per CTA, the hardware scheduler backfills the slots.
+  // Fewer: the envs are dealt to all the resident slots in equal smaller tiles.  envs_per_cta > 0 overrides both.
+  int dev = 0;
+  { const int rc = device_of_stream(stream, &dev); if (rc) return rc; }
+  DeviceInfo di;
+  { const int rc = device_info(dev, &di); if (rc) return rc; }
+  const int num_sms = di.num_sms;
   int grid;
   if (c->envs_per_cta > 0) {
     args.per = (c->envs_per_cta + 3) & ~3;
@@ -1329,18 +1139,20 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     grid = args.n_big + (rest > 0 ? (rest + args.per_small - 1) / args.per_small : 0);
   }
   args.max_sub = (args.per + TILE - 1) / TILE;
+  // scan kernel: 32 envs per CTA when that fills the GPU several times over, fewer otherwise
+  {
+    int epc = TILE;
+    while (epc > 4 && (c->num_envs + epc - 1) / epc < num_sms * LGK_SCAN_CTAS_PER_SM) epc >>= 1;
+    args.scan_epc = epc;
+  }
   const bool taps = c->rng_mode == LGK_RNG_TAPS;
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
-  const int H = c->num_height_points;
-  const int np = (H + 31) / 32;   // scan passes of 32 points
-#define LGK_DISPATCH(DT, NP)                                                            \
-  (taps ? (mul ? launch_step<DT, true, true, NP>(args, grid, smem, stream)              \
-               : launch_step<DT, true, false, NP>(args, grid, smem, stream))            \
-        : (mul ? launch_step<DT, false, true, NP>(args, grid, smem, stream)             \
-               : launch_step<DT, false, false, NP>(args, grid, smem, stream)))
-  if (D == 12 && np == 6) return LGK_DISPATCH(12, 6);   // 187-point scan
-  if (D == 12 && np == 0) return LGK_DISPATCH(12, 0);   // blind
-  if (D == 12 && np == 4) return LGK_DISPATCH(12, 4);   // Cassie's 121 points
-  return LGK_DISPATCH(0, 8);
+#define LGK_DISPATCH(DT)                                                             \
+  (taps ? (mul ? launch_step<DT, true, true>(args, dev, grid, smem, stream)          \
+               : launch_step<DT, true, false>(args, dev, grid, smem, stream))        \
+        : (mul ? launch_step<DT, false, true>(args, dev, grid, smem, stream)         \
+               : launch_step<DT, false, false>(args, dev, grid, smem, stream)))
+  if (D == 12) return LGK_DISPATCH(12);
+  return LGK_DISPATCH(0);
 #undef LGK_DISPATCH
 }

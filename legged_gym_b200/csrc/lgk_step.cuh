@@ -1,0 +1,223 @@
+// Shared between the two kernels of post_physics_step (sm_100a):
+//   lgk_scan_kernel  (lgk_scan.cu)  _get_heights + the scan columns of the observation row, lanes = points
+//   lgk_step_kernel  (lgk_step.cu)  everything else, lanes = envs (four roles per 32-env tile)
+// The scan depends on nothing but the simulator's root states, so it runs first; the step kernel, launched
+// behind it with programmatic dependent launch, needs its result (the mean measured height of
+// _reward_base_height, legged_robot.py:871) only in its last phase.
+#pragma once
+#include "lgk_common.cuh"
+
+#define TILE 32
+#define LGK_SCAN_CTAS_PER_SM 8   // scan kernel: register cap 64, eight 128-thread CTAs per SM
+#define RS (TILE + 1)   // row stride of [row][env] tables: conflict-free by row and by env
+
+struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
+  int root, dof, act, ldv, cmd, fat, ep, lvl, cf, tq, lact, sums, head, scr, rv, total;
+};
+
+#define LGK_LD_ARRAYS 11
+struct StepArgs {
+  LgkConsts c;
+  LgkBuffers b;
+  TileLayout L;
+  int per;           // envs per CTA (multiple of 4) of the first n_big CTAs, walked in sub-tiles of <= 32
+  int n_big;         // CTAs past n_big own per_small envs each (single-wave launches deal smaller tiles)
+  int per_small;
+  int max_sub;       // sub-tiles per CTA = ceil(per / 32)
+  int head_stride;   // odd row stride of the staged observation head
+  int air_active;    // feet_air_time term active (:945-948 only run then)
+  int bh_active;     // base_height term active
+  int tma_ok;        // every tiled array 16-byte aligned and N % 4 == 0
+  int num_rows;      // episode_sums rows: num_rewards (+1 with termination)
+  int scan_first;    // lgk_scan_kernel was launched ahead of the step kernel (num_height_points > 0)
+  int scan_epc;      // envs per CTA of the scan kernel (multiple of 4, <= 32)
+  float one;         // 1.0f the compiler cannot see: blocks ptxas' contraction of mul.rn.f32x2 + add.rn.f32x2
+  float* hsum;       // [N] sum over the scan points of the measured heights (workspace), scan -> step kernel
+  unsigned pk[20];   // Philox4x32-10 round keys of c.seed
+  // bulk-load table: lane i of W0 copies input array i of a sub-tile (source base, offset into shared
+  // memory in floats, bytes per env); src == nullptr: nothing to copy
+  const char* ld_src[LGK_LD_ARRAYS];
+  unsigned ld_off[LGK_LD_ARRAYS], ld_bpe[LGK_LD_ARRAYS];
+  unsigned ld_bytes_per_env;   // sum of ld_bpe
+  // norm > c without the square root: sqrt is monotone and correctly rounded, so sqrtf(s) > c is the same
+  // predicate as s > thr(c), thr(c) = the largest float whose square root rounds to <= c (found on the host)
+  float thr_term, thr_pen, thr_ffp;   // c = 1 (:146), 0.1 (:897), max_contact_force (:962)
+  unsigned hip_mask;                  // bit d set: joint d is a hip joint (_reward_hip_motion)
+};
+
+// where the scan sums live in the caller's workspace: behind the header and the two bitmask arrays
+__host__ __device__ inline size_t lgk_ws_hsum_offset(int num_envs) {
+  return ((size_t)LGK_WS_HEADER_BYTES + 2u * (size_t)lgk_max_warps(num_envs) * sizeof(unsigned) + 15u) & ~(size_t)15u;
+}
+
+// ---- the height scan of one env, lanes = scan points (legged_robot.py:818-854) ----------------------------
+// Per-env operands of quat_apply_yaw (utils/math.py:38-42) for the unit yaw quaternion (0, 0, yz, yw):
+//   t = 2 * cross(xyz, p) = (-2yz*py, 2yz*px);  r = p + yw*t + cross(xyz, t) = p + yw*t + (-yz*ty, yz*tx)
+struct ScanEnv {
+  float2 k_t;    // (-2yz, 2yz)
+  float2 k_c;    // (-yz, yz)
+  float2 r2;     // root x, y (before any reset)
+  float yw;
+  float zo;      // root z - 0.5 (after a reset, :227)
+};
+// normalize([0, 0, qz, qw]) as torch computes it: x.norm(p=2) with separately rounded squares and a correctly
+// rounded square root (same on torch CPU / CUDA, tools/calibrate_norm.py), clamp(min=1e-9), true division
+__device__ __forceinline__ ScanEnv scan_env_operands(float x, float y, float z_obs, float qz, float qw) {
+  const float n = fmaxf(sqrtf(add_rn(mul_rn(qz, qz), mul_rn(qw, qw))), 1e-9f);
+  const float yz = __fdiv_rn(qz, n), yw = __fdiv_rn(qw, n);
+  const float yz2 = mul_rn(yz, 2.0f);
+  ScanEnv e;
+  e.k_t = make_float2(-yz2, yz2);
+  e.k_c = make_float2(-yz, yz);
+  e.r2 = make_float2(x, y);
+  e.yw = yw;
+  e.zo = sub_rn(z_obs, 0.5f);
+  return e;
+}
+
+// Height-field cell of scan point p for env e, op for op like torch (no contraction): the chain runs on packed
+// f32x2 instructions, x and y of the point sharing every operation; each half rounds like the scalar op.
+// ptxas 12.9 contracts mul.rn.f32x2 followed by add.rn.f32x2 into one FFMA2 (a single rounding -- it does so
+// even with --fmad=false; the scalar forms are left alone), which changes the truncated index in ~1e-7 of the
+// points.  The two additions that follow a multiplication are therefore written as fma(p, one, q) with `one`
+// a 1.0f from the kernel parameters: p * 1 + q rounds once, like p + q, and there is nothing left to contract.
+template <bool MUL_RCP>
+__device__ __forceinline__ int scan_cell(const ScanEnv& e, float2 p, float one, float border, float inv_hs,
+                                         float hscale, int max_px, int max_py, int pitch) {
+  const float2 one2 = make_float2(one, one);
+  const float2 t = __fmul2_rn(e.k_t, make_float2(p.y, p.x));              // (tx, ty)
+  float2 w = __ffma2_rn(p, one2, __fmul2_rn(make_float2(e.yw, e.yw), t));   // p + yw * t
+  w = __ffma2_rn(w, one2, __fmul2_rn(e.k_c, make_float2(t.y, t.x)));        //   + cross(xyz, t)
+  w = __fadd2_rn(__fadd2_rn(w, e.r2), make_float2(border, border));         // + root_pos, + border_size (:840-841)
+  float2 s;   // (points / horizontal_scale).long(): truncation toward zero (:842)
+  if (MUL_RCP) s = __fmul2_rn(w, make_float2(inv_hs, inv_hs));
+  else s = make_float2(__fdiv_rn(w.x, hscale), __fdiv_rn(w.y, hscale));
+  // trunc toward zero without the quarter-rate conversion unit: 2^23 + s, rounded toward zero, holds trunc(s) in
+  // its mantissa for 0 <= s < 2^23; s < 0 lands below 2^23 (negative after the subtraction, clipped to 0 like
+  // trunc(s) would be), s >= 2^23 / NaN above the clip's upper bound.  Subtract + clip(0, max): one VIADDMNMX.RELU
+  const float2 mg = __fadd2_rz(s, make_float2(8388608.0f, 8388608.0f));
+  const int ix = __vimin_s32_relu(__float_as_int(mg.x) - 0x4b000000, max_px);
+  const int iy = __vimin_s32_relu(__float_as_int(mg.y) - 0x4b000000, max_py);
+  return ix * pitch + iy;
+}
+
+// per-lane constants of one scan pass (the same for every env): body-frame offset of the lane's point and the
+// noise factors of its observation column.  Philox mode: ka = ns * 2^-15, kb = -257 * ns (the 16-bit field r16
+// enters as the float 2^23 + r16, so ns * ((2^23 + r16) * 2^-15 - 257) = ns * (r16 / 2^15 - 1)).  Tap mode: ka = ns.
+struct ScanLane {
+  float2 p;
+  float ka, kb;
+};
+template <bool TAPS>
+__device__ __forceinline__ ScanLane scan_lane_consts(const StepArgs& a, int h, int OH) {
+  const bool ok = h < a.c.num_height_points;
+  const bool add_noise = a.c.flags & LGK_F_ADD_NOISE;
+  ScanLane s;
+  s.p.x = ok ? __ldg(a.b.height_points_xy + 2 * h) : 0.f;   // lanes past H repeat point 0
+  s.p.y = ok ? __ldg(a.b.height_points_xy + 2 * h + 1) : 0.f;
+  const float ns = (ok && add_noise) ? __ldg(a.b.noise_scale_vec + OH + h) : 0.f;
+  s.ka = TAPS ? ns : ns * 3.0517578125e-05f;
+  s.kb = TAPS ? 0.f : ns * -257.0f;
+  return s;
+}
+
+// Philox blocks of the observation noise: scan pass `it` of lane l takes 16-bit field (it & 7) of block
+// LGK_SITE_NOISE_SCAN + 32 * (it / 8) + l; the head's blocks are dealt by the step kernel's roles
+#define LGK_SITE_NOISE_SCAN 1024u
+#define LGK_SITE_NOISE_HEAD 112u   // up to 16 blocks
+
+// observation column of a scan point: clip(root_z - 0.5 - height, -1, 1) * scale (:227) + noise (:231), then the
+// optional final clip (:104).  Philox mode folds scale and noise into two FFMAs; without noise (ka = kb = 0) they
+// round like the plain product.
+template <bool TAPS, bool CLIP>
+__device__ __forceinline__ float scan_obs(float zo, float hgt, float scale, float ka, float kb, unsigned rw, int half,
+                                          const float* __restrict__ tap, float clip_obs) {
+  const float d = clampf(sub_rn(zo, hgt), -1.f, 1.f);
+  float v;
+  if (TAPS) {
+    v = mul_rn(d, scale);
+    if (tap != nullptr) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(tap)), 1.0f), ka));
+  } else {
+    const unsigned m = half ? __byte_perm(rw, 0x4b000000u, 0x7632) : __byte_perm(rw, 0x4b000000u, 0x7610);
+    v = fmaf(__uint_as_float(m), ka, fmaf(d, scale, kb));
+  }
+  return CLIP ? clampf(v, -clip_obs, clip_obs) : v;
+}
+
+// NP passes of 32 points (pass it0 .. it0 + NP - 1) of one env: indices, gathers (all in flight before the first is
+// consumed), observation columns, optional measured_heights row.  Returns this lane's sum of heights.
+// rnd: the Philox block whose 16-bit fields 0..7 belong to passes it0..it0+7 of this lane.
+template <bool TAPS, bool MUL_RCP, int NP, bool CLIP>
+__device__ __forceinline__ float scan_passes(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP], int it0,
+                                             int lane, uint4 rnd, float* __restrict__ orow,
+                                             const float* __restrict__ trow, float* __restrict__ mrow, bool check_all) {
+  const LgkConsts& c = a.c;
+  const int H = c.num_height_points;
+  const bool plane = c.flags & LGK_F_TERRAIN_PLANE;
+  int raw[NP];
+  if (!plane) {
+    const float inv_hs = 1.0f / c.horizontal_scale;
+    const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
+#pragma unroll
+    for (int it = 0; it < NP; ++it) {
+      const int cell = scan_cell<MUL_RCP>(e, ln[it].p, a.one, c.border_size, inv_hs, c.horizontal_scale, max_px, max_py,
+                                          c.terrain_pitch);
+      raw[it] = __ldg(a.b.height_min3 + (unsigned)cell);
+    }
+  } else {
+#pragma unroll
+    for (int it = 0; it < NP; ++it) raw[it] = 0;
+  }
+  float hsum = 0.f;
+#pragma unroll
+  for (int it = 0; it < NP; ++it) {
+    const int h = (it0 + it) * 32 + lane;
+    // the specialised instantiations run with ceil(H / 32) == NP: only the last pass holds lanes past H
+    const bool ok = (!check_all && it < NP - 1) ? true : h < H;
+    const unsigned rw = (it >> 1) == 0 ? rnd.x : (it >> 1) == 1 ? rnd.y : (it >> 1) == 2 ? rnd.z : rnd.w;
+    const float hgt = mul_rn(s16_to_float(raw[it]), c.vertical_scale);
+    hsum += ok ? hgt : 0.f;
+    const float o = scan_obs<TAPS, CLIP>(e.zo, hgt, c.obs_scale_height, ln[it].ka, ln[it].kb, rw, it & 1,
+                                         (TAPS && trow != nullptr) ? trow + (ok ? h : 0) : nullptr, c.clip_obs);
+    if (ok) orow[h] = o;
+    if (mrow != nullptr && ok) mrow[h] = hgt;   // optional materialisation of measured_heights [N,H]
+  }
+  return hsum;
+}
+
+// launches lgk_scan_kernel for args.c.num_envs envs (lgk_scan.cu)
+int lgk_scan_launch(const StepArgs& args, cudaStream_t stream);
+
+// The scan columns of one env by one warp, rolled and out of line: the step kernel's fix-up for the envs it has
+// just reset (their observation uses the new root z, :227; everything else -- indices, heights, noise -- is what
+// the scan kernel computed).  sc: the env's 8 operands in shared memory (k_t, k_c, r2, yw, zo).
+template <bool TAPS, bool MUL_RCP>
+static __device__ __noinline__ void lgk_scan_fixup_env(const StepArgs& a, const float* sc, int env,
+                                                       unsigned long long csc) {
+  const LgkConsts& c = a.c;
+  const int lane = threadIdx.x & 31;
+  const int H = c.num_height_points, OH = 12 + 3 * c.num_dof;
+  ScanEnv e;
+  e.k_t = make_float2(sc[0], sc[1]);
+  e.k_c = make_float2(sc[2], sc[3]);
+  e.r2 = make_float2(sc[4], sc[5]);
+  e.yw = sc[6];
+  e.zo = sc[7];
+  float* orow = a.b.obs_buf + (size_t)env * c.num_obs + OH;
+  const bool noise = c.flags & LGK_F_ADD_NOISE;
+  const float* trow = (TAPS && noise) ? a.b.tap_noise + (size_t)env * c.num_obs + OH : nullptr;
+  const int np = (H + 31) / 32;
+  uint4 rnd = make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+  for (int it = 0; it < np; ++it) {
+    if (!TAPS && noise && (it & 7) == 0)
+      rnd = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env), LGK_SITE_NOISE_SCAN + 32u * (unsigned)(it >> 3) + lane);
+    ScanLane ln[1];
+    ln[0] = scan_lane_consts<TAPS>(a, it * 32 + lane, OH);
+    // field (it & 7) of the block: rotate it into the position pass 0 reads
+    const int f = it & 7;
+    const unsigned w = (f >> 1) == 0 ? rnd.x : (f >> 1) == 1 ? rnd.y : (f >> 1) == 2 ? rnd.z : rnd.w;
+    const uint4 r1 = make_uint4((f & 1) ? (w >> 16) : w, 0, 0, 0);
+    (void)scan_passes<TAPS, MUL_RCP, 1, true>(a, e, ln, it, lane, r1, orow, trow, nullptr, true);
+  }
+}
