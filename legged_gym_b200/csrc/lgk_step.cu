@@ -1018,11 +1018,10 @@ extern "C" int lgk_pre_reward_state_impl(const LgkConsts* c, const LgkBuffers* b
 // keeps no process-wide "current" state (two envs on two devices, or on two streams of one, never share any)
 #define LGK_MAX_DEVICES 64
 struct DeviceInfo { int num_sms; };
-static int device_of_stream(cudaStream_t st, int* dev) {
-  if (cudaStreamGetDevice(st, dev) == cudaSuccess) return 0;
-  (void)cudaGetLastError();
-  return (int)cudaGetDevice(dev);
-}
+// The device the launch goes to is the calling thread's current device: CUDA rejects a launch on a stream that
+// belongs to another device, so "current device" and "the stream's device" are the same thing for every call that
+// can succeed (cudaStreamGetDevice would say the same but is not allowed under stream capture).
+static int device_of_stream(cudaStream_t, int* dev) { return (int)cudaGetDevice(dev); }
 static int device_info(int dev, DeviceInfo* out) {
   static DeviceInfo info[LGK_MAX_DEVICES];
   static bool known[LGK_MAX_DEVICES];   // idempotent: a race writes the same values twice
