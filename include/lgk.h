@@ -43,7 +43,8 @@ typedef enum LgkStatus {
   LGK_ERR_REWARD = -4,        /* unknown reward term id (reference: AttributeError, :593)  */
   LGK_ERR_ALIGN = -5,         /* pointer not aligned as required                           */
   LGK_ERR_VERSION = -6,       /* struct_size / abi_version mismatch                        */
-  LGK_ERR_TERRAIN = -7        /* heights requested but no height field given (:833-834)    */
+  LGK_ERR_TERRAIN = -7,       /* heights requested but no height field given (:833-834)    */
+  LGK_ERR_CAPACITY = -8       /* size beyond the fixed capacity of an allocation-free entry point */
 } LgkStatus;
 
 /* control_type of LeggedRobotCfg.control (legged_robot.py:383-391) */
@@ -279,6 +280,21 @@ int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* d
 int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state,
                          float* pos_err_hist, float* vel_hist, float* model_ins,
                          const float* weights, const float* norm, float* dvel_out, void* stream);
+
+/* Allocation-free variant of lgk_actuator_advance.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and arithmetic as lgk_actuator_advance with the fp32 FFMA MLP kernel
+ * (LGK_MLP_KERNEL=ffma), but the [N,120] model_ins scratch is a file-scope device array inside the library
+ * (LGK_STATIC_MAX_ENVS * 480 B = 1 966 080 B held by every GPU that loads the library, until exit) and nothing is
+ * allocated or freed: no cudaMalloc / cudaFree, no weight-image workspace.  num_envs > LGK_STATIC_MAX_ENVS returns
+ * LGK_ERR_CAPACITY; num_envs == 0 is the set-up call (resolves the array's device address, launches nothing).
+ * Every call on a device shares the array: calls that overlap on the GPU (different streams) race; calls on one
+ * stream are ordered and safe.  The array keeps the last call's rows; nothing in it needs clearing (rows [0, 4N)
+ * are rewritten before they are read). */
+#define LGK_STATIC_MAX_ENVS 4096
+int lgk_actuator_advance_static(int32_t num_envs, const float* actions, const float* dof_state,
+                                float* pos_err_hist, float* vel_hist, const float* weights, const float* norm,
+                                float* dvel_out, void* stream);
 
 /* ANYmal series-elastic actuator net (envs/anymal_c/anymal.py:46-81, resources/actuator_nets/
  * anydrive_v3_lstm.pt): per joint a 2-layer torch.nn.LSTM(input 2, hidden 8, batch_first) followed by

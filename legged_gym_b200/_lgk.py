@@ -50,7 +50,8 @@ F_RESET_GIVEN = 1 << 11
 F_CALLBACK_GIVEN = 1 << 12
 
 STATUS = {0: "LGK_OK", -1: "LGK_ERR_NULL", -2: "LGK_ERR_DIM", -3: "LGK_ERR_CONTROL_TYPE", -4: "LGK_ERR_REWARD",
-          -5: "LGK_ERR_ALIGN", -6: "LGK_ERR_VERSION", -7: "LGK_ERR_TERRAIN"}
+          -5: "LGK_ERR_ALIGN", -6: "LGK_ERR_VERSION", -7: "LGK_ERR_TERRAIN",
+          -8: "LGK_ERR_CAPACITY"}
 
 
 class LgkRewardEntry(C.Structure):
@@ -110,6 +111,7 @@ class LgkBuffers(C.Structure):
 
 
 LGK_LSTM_HID = 8
+LGK_STATIC_MAX_ENVS = 4096   # lgk_actuator_advance_static: envs its in-library scratch array holds
 
 
 class LgkLstmWeights(C.Structure):
@@ -162,6 +164,7 @@ def load():
         "lgk_clip_actions_poses": (C.c_int, [cp, fp, fp, fp, fp]),
         "lgk_compute_torques": (C.c_int, [cp, fp, fp, fp, fp, fp]),
         "lgk_actuator_advance": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp, fp]),
+        "lgk_actuator_advance_static": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp]),
         "lgk_lstm_actuator_advance": (C.c_int, [cp, C.POINTER(LgkLstmWeights), fp, fp, fp, fp, fp, fp, fp]),
         "lgk_lstm_reset_hidden": (C.c_int, [C.c_int32, C.c_int32, fp, fp, C.c_int32, fp, fp, fp]),
         "lgk_post_physics_step": (C.c_int, [cp, bp, fp]),
@@ -188,6 +191,7 @@ def load():
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
     "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
+    "lgk_actuator_advance_static",
     "lgk_lstm_actuator_advance", "lgk_lstm_reset_hidden", "lgk_post_physics_step", "lgk_pre_reward_state", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]
 

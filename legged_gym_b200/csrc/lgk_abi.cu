@@ -15,6 +15,8 @@ int lgk_compute_torques_impl(const LgkConsts*, const float*, const float*, const
 int lgk_debug_yaw_quat_impl(const float*, int, int, float*, cudaStream_t);
 int lgk_actuator_advance_impl(int, const float*, const float*, float*, float*, float*, const float*, const float*,
                               float*, cudaStream_t);
+int lgk_actuator_advance_static_impl(int, const float*, const float*, float*, float*, const float*, const float*, float*,
+                                     cudaStream_t);
 int lgk_lstm_actuator_advance_impl(const LgkConsts*, const LgkLstmWeights*, const float*, const float*, float*, float*,
                                    float*, float*, cudaStream_t);
 int lgk_lstm_reset_hidden_impl(int, int, const int*, const int*, int, float*, float*, cudaStream_t);
@@ -155,6 +157,18 @@ int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* do
   if (num_envs > 0) g_launches += 2;   /* zero envs: set-up only, nothing is launched */
   return lgk_actuator_advance_impl(num_envs, actions, dof_state, pos_err_hist, vel_hist, model_ins, weights, norm,
                                    dvel_out, (cudaStream_t)stream);
+}
+
+int lgk_actuator_advance_static(int32_t num_envs, const float* actions, const float* dof_state, float* pos_err_hist,
+                                float* vel_hist, const float* weights, const float* norm, float* dvel_out,
+                                void* stream) {
+  if (num_envs < 0) return LGK_ERR_DIM;
+  if (num_envs > LGK_STATIC_MAX_ENVS) return LGK_ERR_CAPACITY;   // the scratch array is fixed-size: no fallback
+  if (!actions || !dof_state || !pos_err_hist || !vel_hist || !weights || !norm || !dvel_out) return LGK_ERR_NULL;
+  if ((reinterpret_cast<uintptr_t>(dof_state) & 7u) != 0) return LGK_ERR_ALIGN;
+  if (num_envs > 0) g_launches += 2;
+  return lgk_actuator_advance_static_impl(num_envs, actions, dof_state, pos_err_hist, vel_hist, weights, norm, dvel_out,
+                                          (cudaStream_t)stream);
 }
 
 int lgk_lstm_actuator_advance(const LgkConsts* c, const LgkLstmWeights* weights_host, const float* actions,

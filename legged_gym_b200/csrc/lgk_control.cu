@@ -400,3 +400,54 @@ extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const floa
   lgk_act_mlp_kernel<<<grid, MLP_THREADS, smem, st>>>(rows, model_ins, weights, norm, dvel);
   return (int)cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free actuator substep (lgk_actuator_advance_static, include/lgk.h).  The [N,120] model_ins scratch
+// of the history kernel / MLP pair lives in this file-scope device array instead of a caller buffer, and the MLP
+// is the fp32 FFMA kernel above, which needs no weight images: the call makes no cudaMalloc / cudaFree and uses no
+// allocating routine.  Every GPU that loads the library holds the array (1 966 080 B) until the process exits.
+// All calls on one device share it: calls that overlap on the GPU (two streams) race.  Nothing in it has to start
+// at zero -- the history kernel rewrites rows [0, 4N) before the MLP reads exactly those rows.
+static __device__ __align__(256) float g_static_model_ins[(size_t)LGK_STATIC_MAX_ENVS * ACT_DOF * 2 * ACT_HIST];
+
+// In host code the array's name is only a handle: the device address comes from cudaGetSymbolAddress, asked once
+// per device with that device current.
+#define LGK_STATIC_MAX_DEVICES 64
+static int static_model_ins_ptr(float** out) {
+  static float* ptr[LGK_STATIC_MAX_DEVICES];   // idempotent: a race stores the same address twice
+  int dev = 0;
+  LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= LGK_STATIC_MAX_DEVICES) return (int)cudaErrorInvalidDevice;
+  if (!ptr[dev]) {
+    float* p = nullptr;
+    LGK_CUDA_RETURN_IF(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_model_ins));
+    if (!p) return (int)cudaErrorInvalidSymbol;
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+extern "C" int lgk_actuator_advance_static_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
+                                                float* v_hist, const float* weights, const float* norm, float* dvel,
+                                                cudaStream_t st) {
+  float* model_ins = nullptr;
+  const int rc = static_model_ins_ptr(&model_ins);
+  if (rc) return rc;
+  if (N <= 0) return 0;   // set-up call: the address is known from here on
+  const int n = N * ACT_DOF;
+  const int hist_ctas = (n + HIST_THREADS - 1) / HIST_THREADS;
+  lgk_act_hist_kernel<<<hist_ctas, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm,
+                                                          hist_ctas, weights, nullptr, nullptr);
+  LGK_CUDA_RETURN_IF(cudaGetLastError());
+  const int rows = N * ACT_LEGS;
+  const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
+  int dev = 0, sms = 148;
+  LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
+  LGK_CUDA_RETURN_IF(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = tiles < sms ? tiles : sms;
+  const int smem = (int)sizeof(MlpSmem);
+  LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  lgk_act_mlp_kernel<<<grid, MLP_THREADS, smem, st>>>(rows, model_ins, weights, norm, dvel);
+  return (int)cudaGetLastError();
+}
