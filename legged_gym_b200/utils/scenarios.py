@@ -45,6 +45,14 @@ def go1_rough_actuator(cfg):
     cfg.control.use_actuator_network = True
 
 
+def go1_flat_cmd_curriculum(cfg):
+    """config 1 with the command curriculum on (legged_robot.py:465-474): the fixture's step counter is set so
+    that the gated step (common_step_counter % max_episode_length == 0) falls on its third step."""
+    cfg.control.use_actuator_network = False
+    cfg.commands.curriculum = True
+    cfg.commands.max_curriculum = 2.0   # shipped: 1.0 = the shipped lin_vel_x range, i.e. a curriculum that cannot move
+
+
 def cassie_flat(cfg):
     """config 4: Cassie as shipped (plane, 121 zero heights, 169 obs, 10 terms + termination)."""
 
@@ -71,8 +79,27 @@ def a1_variant(cfg):
     cfg.rewards.only_positive_rewards = False
 
 
+def fixture_step_counter(env) -> int:
+    """common_step_counter a fixture / parity run starts from: a push (:350) on its third step and, with the command
+    curriculum on, the curriculum's gated step (:172) on that same step."""
+    import math
+    push = int(env.cfg.domain_rand.push_interval)
+    if getattr(env.cfg.commands, "curriculum", False):
+        return math.lcm(push, int(env.max_episode_length)) - 3
+    return push - 3
+
+
+def fixture_bias_tracking_sums(env, sums) -> None:
+    """With the command curriculum on, lift the tracking_lin_vel sums to the curriculum's threshold (:468: mean over
+    the reset envs / max_episode_length > 0.8 * scale) so that the decision hinges on the values, not on the sign."""
+    if getattr(env.cfg.commands, "curriculum", False) and "tracking_lin_vel" in sums:
+        thr = 0.8 * float(env.reward_scales["tracking_lin_vel"]) * float(env.max_episode_length)
+        sums["tracking_lin_vel"] += thr + 1.0
+
+
 SCENARIOS = {
     "go1_flat": ("go1", go1_flat),
+    "go1_flat_cmd_curriculum": ("go1", go1_flat_cmd_curriculum),
     "go1_rough_full": ("go1", go1_rough_full),
     "go1_rough_default": ("go1", go1_rough_default),
     "go1_rough_actuator": ("go1", go1_rough_actuator),

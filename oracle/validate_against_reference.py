@@ -39,6 +39,9 @@ def compare_step(env, s, p, tag):
         va, vb = torch.as_tensor(ea[k]), torch.as_tensor(eb[k])
         if not torch.equal(va.float(), vb.float()):
             bad.append("extras." + k)
+    for k, v in env.command_ranges.items():   # the command curriculum widens lin_vel_x in place (:465-474)
+        if [float(x) for x in v] != [float(x) for x in p.command_ranges[k]]:
+            bad.append("command_ranges." + k)
     if bad:
         raise AssertionError(f"{tag}: oracle != reference in {bad}")
 
@@ -52,13 +55,14 @@ def run_scenario(name, num_envs=256, steps=12, seed=0, verbose=True):
     g = torch.Generator().manual_seed(seed)
     env.episode_length_buf[:] = torch.randint(0, int(env.max_episode_length) + 2, (num_envs,), generator=g)
     env.episode_length_buf[: num_envs // 8] = 499          # callback resample on the first step
-    env.common_step_counter = int(env.cfg.domain_rand.push_interval) - 3   # a push on the third step
+    env.common_step_counter = scenarios.fixture_step_counter(env)   # a push (and the command-curriculum gate) on the third step
     env.commands[:] = torch.rand(num_envs, 4, generator=g) * 2 - 1
     env.feet_air_time[:] = torch.rand(num_envs, env.feet_air_time.shape[1], generator=g) * 0.6
     env.last_actions[:] = torch.randn(num_envs, env.num_actions, generator=g)
     env.last_dof_vel[:] = torch.randn(num_envs, env.num_dof, generator=g)
     for k in env.episode_sums:
         env.episode_sums[k][:] = torch.randn(num_envs, generator=g)
+    scenarios.fixture_bias_tracking_sums(env, env.episode_sums)
     synthetic.load_frame(env, frames[0])
     s = lo.OracleState.from_env(env, p)
     harness = TapHarness(env)
@@ -81,6 +85,39 @@ def run_scenario(name, num_envs=256, steps=12, seed=0, verbose=True):
         print(f"  {name}: {steps} steps x {num_envs} envs bit-identical ({n_resets} resets, "
               f"rewards {list(env.reward_names)} + {'termination' if 'termination' in env.reward_scales else '-'})")
     return n_resets
+
+
+def run_compute_torques(num_envs=96, seed=0, verbose=True):
+    """LeggedRobot._compute_torques (legged_robot.py:370-392) of the reference's base class for the three control
+    types against lo.compute_torques, bit-identical; an unknown type raises NameError in both."""
+    from legged_gym.envs.base.legged_robot import LeggedRobot
+    env = make_reference_env("go1", scenarios.go1_flat, num_envs=num_envs, seed=seed)
+    frames = synthetic.make_frames(env, 3, seed=4321 + seed)
+    g = torch.Generator().manual_seed(seed)
+    for it, ct in enumerate(("P", "V", "T")):
+        synthetic.load_frame(env, frames[it])
+        env.cfg.control.control_type = ct
+        env.last_dof_vel[:] = torch.randn(num_envs, env.num_dof, generator=g)
+        p = lo.OracleParams.from_env(env)
+        s = lo.OracleState.from_env(env, p)
+        assert p.control_type == ct
+        a = torch.randn(num_envs, env.num_actions, generator=g) * 3.0     # some torques hit the limits
+        want = LeggedRobot._compute_torques(env, a)                       # the base class's, not Go1's override
+        got = lo.compute_torques(p, s, a)
+        assert torch.equal(want, got), f"control_type {ct}: oracle != reference"
+        assert ct == "T" or bool((got.abs() == p.torque_limits).any())
+    env.cfg.control.control_type = "X"
+    p = lo.OracleParams.from_env(env)
+    for fn in (lambda: LeggedRobot._compute_torques(env, a), lambda: lo.compute_torques(p, lo.OracleState.from_env(env, p), a)):
+        try:
+            fn()
+        except NameError:
+            pass
+        else:
+            raise AssertionError("unknown control type must raise NameError (:391)")
+    if verbose:
+        print(f"  _compute_torques P / V / T: {num_envs} envs bit-identical, unknown type -> NameError")
+    return True
 
 
 def run_sea_lstm(num_envs=64, steps=20, seed=0, verbose=True):
@@ -132,6 +169,7 @@ def main(argv=None):
     a = ap.parse_args(argv)
     for name in scenarios.SCENARIOS:
         run_scenario(name, a.envs, a.steps)
+    run_compute_torques()
     run_sea_lstm()
     print("oracle == reference on every scenario")
 

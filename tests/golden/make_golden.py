@@ -17,6 +17,8 @@ Fixture layout (numpy arrays; S = steps, N = envs):
   out_reset_ids / out_resample_ids   [S, N] ascending ids padded with -1
   out_extras        [S, K+1] extras["episode"] values in episode_sums key order (+ terrain_level), NaN
                     where the reference did not rewrite them
+  out_command_ranges [S, 4, 2] command_ranges (lin_vel_x, lin_vel_y, ang_vel_yaw, heading) after step s: the command
+                    curriculum (legged_robot.py:465-474) widens lin_vel_x on its gated step
   out_dvel          [S, decimation, N, 12] Go1 actuator-net output per substep (actuator scenario only)
   in_sea_dof_state / out_sea_torques / out_sea_hidden / out_sea_cell / out_sea_input
                     ANYmal scenario only: after step s the reference's Anymal._compute_torques(actions) is
@@ -65,13 +67,14 @@ def randomise(env, seed):
     ep[N // 8: N // 8 + 3] = int(env.max_episode_length)            # time-outs on the first step
     ep[N // 8 + 3: N // 8 + 5] = int(env.max_episode_length) - 2    # ... and on the third
     env.episode_length_buf[:] = ep
-    env.common_step_counter = int(env.cfg.domain_rand.push_interval) - 3
+    env.common_step_counter = scenarios.fixture_step_counter(env)
     env.commands[:] = torch.rand(N, 4, generator=g) * 2 - 1
     env.feet_air_time[:] = torch.rand(N, env.feet_air_time.shape[1], generator=g) * 0.6
     env.last_actions[:] = torch.randn(N, env.num_actions, generator=g)
     env.last_dof_vel[:] = torch.randn(N, env.num_dof, generator=g)
     for k in env.episode_sums:
         env.episode_sums[k][:] = torch.randn(N, generator=g)
+    scenarios.fixture_bias_tracking_sums(env, env.episode_sums)
 
 
 def generate(name, num_envs, steps, seed=0):
@@ -136,7 +139,7 @@ def generate(name, num_envs, steps, seed=0):
     ins = {k: [] for k in IN_BUFFERS}
     taps_log = {}
     outs = {k: [] for k in OUT_BUFFERS + ("episode_sums", "terrain_levels", "measured_heights", "reset_ids",
-                                          "resample_ids", "extras")}
+                                          "resample_ids", "extras", "command_ranges")}
     interval = int(env.cfg.commands.resampling_time / env.dt)
     for it in range(steps):
         fr = frames[it]
@@ -176,6 +179,8 @@ def generate(name, num_envs, steps, seed=0):
         row = [float(ep["rew_" + k]) if ("rew_" + k) in ep else float("nan") for k in keys]
         row.append(float(ep["terrain_level"]) if "terrain_level" in ep else float("nan"))
         outs["extras"].append(np.array(row, np.float32))
+        outs["command_ranges"].append(np.array([env.command_ranges[k] for k in ("lin_vel_x", "lin_vel_y", "ang_vel_yaw", "heading")],
+                                               np.float64))
     for k, v in ins.items():
         d["in_" + k] = np.stack(v)
     for k, v in taps_log.items():

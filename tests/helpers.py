@@ -43,13 +43,14 @@ def randomise_env_state(env, seed: int):
     ep = torch.randint(0, int(env.max_episode_length) + 2, (N,), generator=g)
     ep[: max(N // 8, 1)] = int(env.cfg.commands.resampling_time / env.dt) - 1
     env.episode_length_buf = ep.to(dev)
-    env.common_step_counter = int(env.cfg.domain_rand.push_interval) - 3
+    env.common_step_counter = scenarios.fixture_step_counter(env)
     env.commands[:] = (torch.rand(N, 4, generator=g) * 2 - 1).to(dev)
     env.feet_air_time[:] = (torch.rand(N, env.feet_air_time.shape[1], generator=g) * 0.6).to(dev)
     env.last_actions[:] = torch.randn(N, env.num_actions, generator=g).to(dev)
     env.last_dof_vel[:] = torch.randn(N, env.num_dof, generator=g).to(dev)
     for k in env.episode_sums:
         env.episode_sums[k][:] = torch.randn(N, generator=g).to(dev)
+    scenarios.fixture_bias_tracking_sums(env, env.episode_sums)
 
 
 def assert_close(name, got, want, exact=False):
@@ -207,6 +208,10 @@ def compare_to_golden(get, g, it, keys, tag, float_names=GOLDEN_OUT):
     want = g["out_resample_ids"][it]
     want = want[want >= 0]
     assert_close(f"{tag}resample_ids", get("resample_ids").to(torch.int64).reshape(-1), T(want), exact=True)
+    if "out_command_ranges" in g:   # the command curriculum's widened range (legged_robot.py:465-474), exact
+        cr = get("command_ranges")
+        got_cr = np.array([cr[k] for k in ("lin_vel_x", "lin_vel_y", "ang_vel_yaw", "heading")], np.float64)
+        assert np.array_equal(got_cr, g["out_command_ranges"][it]), f"{tag}command_ranges {got_cr} != {g['out_command_ranges'][it]}"
     ex = get("extras")
     if ex is not None:
         row = g["out_extras"][it]
@@ -290,6 +295,8 @@ def replay_golden_oracle(name, device="cpu"):
                 return s.resample_env_ids
             if nm == "extras":
                 return s.extras.get("episode") if len(s.reset_env_ids) else None
+            if nm == "command_ranges":
+                return p.command_ranges
             return getattr(s, nm)
         compare_to_golden(get, g, it, keys, f"[oracle {name} step {it}] ")
         n += len(s.reset_env_ids)

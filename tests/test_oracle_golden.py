@@ -17,10 +17,27 @@ def test_oracle_matches_reference_golden(name):
 
 @pytest.mark.reference
 @pytest.mark.skipif(not reference_loader.reference_available(), reason="/root/reference only exists in the build container")
-@pytest.mark.parametrize("name", ["go1_rough_full", "cassie_flat"])
+@pytest.mark.parametrize("name", ["go1_rough_full", "cassie_flat", "go1_flat_cmd_curriculum"])
 def test_oracle_bit_identical_to_live_reference(name):
     from oracle import validate_against_reference as v
     assert v.run_scenario(name, num_envs=96, steps=6, seed=3, verbose=False) > 0
+
+
+@pytest.mark.reference
+@pytest.mark.skipif(not reference_loader.reference_available(), reason="/root/reference only exists in the build container")
+def test_oracle_compute_torques_bit_identical_to_live_reference():
+    """lo.compute_torques against LeggedRobot._compute_torques (legged_robot.py:370-392) for P / V / T."""
+    from oracle import validate_against_reference as v
+    assert v.run_compute_torques(num_envs=96, seed=1, verbose=False)
+
+
+def test_command_curriculum_fixture_widens_the_range_on_its_gated_step():
+    """update_command_curriculum (legged_robot.py:465-474) as the reference ran it: the recorded range steps
+    from the shipped [-1, 1] to [-1.5, 1.5] on the third step of the fixture and nowhere else."""
+    g = helpers.load_golden("go1_flat_cmd_curriculum")
+    cr = g["out_command_ranges"][:, 0]
+    assert (cr[:2] == cr[0]).all() and (cr[2:] == cr[2]).all()
+    assert cr[2][0] == cr[0][0] - 0.5 and cr[2][1] == cr[0][1] + 0.5
 
 
 @pytest.mark.reference
