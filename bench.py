@@ -49,6 +49,17 @@ def workload_name(envs_per_gpu, decimation=4):
             f"curriculum, {envs_per_gpu} envs/GPU, position control x{decimation} substeps + fused post_physics_step")
 
 
+def config_dict(envs_per_gpu, world, decimation=4, num_obs=235, reward_terms=21):
+    """`config` of the JSON line: the same dict from both arms (the driver compares them key by key)."""
+    return {"workload": workload_name(envs_per_gpu, decimation), "envs_per_gpu": envs_per_gpu,
+            "envs_total": envs_per_gpu * world, "num_obs": num_obs, "reward_terms": reward_terms,
+            "rng": "ours: in-kernel Philox4x32-10; reference: torch CPU generator",
+            "l2": f"inputs cycle through {NUM_FRAMES} state frames resident in HBM "
+                  f"({NUM_FRAMES * envs_per_gpu * 448 / 1e6:.0f} MB) -- larger than L2 at the default size",
+            "parallelism": f"env-sharded x{world}, terrain replica per GPU, NCCL all-reduce of episode statistics "
+                           f"inside the timed region"}
+
+
 def _peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(path):
@@ -159,7 +170,10 @@ def run_ours(args):
     env = _build_env(args.envs, device, rank, world)
     N = env.num_envs
     frames = synthetic.make_frames(env, NUM_FRAMES, seed=1234 + 1000 * 2 + rank, device=device)
-    stats = ShardedStats(env, interval=24) if world > 1 else None
+    # the statistics all-reduce (the path's only collective) must fire inside any timed region, however short
+    stats_interval = min(24, max(1, args.steps // 4))
+    stats = ShardedStats(env, interval=stats_interval) if world > 1 else None
+    n_collectives = [0]
     stream = torch.cuda.Stream(device)
     torch.cuda.synchronize()
 
@@ -189,8 +203,8 @@ def run_ours(args):
 
     def replay(i):
         graphs[i % NUM_FRAMES].replay()
-        if stats is not None:
-            stats.after_step(i)
+        if stats is not None and stats.after_step(i) is not None:
+            n_collectives[0] += 1
 
     with torch.cuda.stream(stream):
         for i in range(max(args.warmup, 3)):
@@ -203,10 +217,16 @@ def run_ours(args):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with ClockSampler(local) as clocks:
+            n_collectives[0] = 0
             e0.record(stream)
             for i in range(args.steps):
                 replay(i)
             e1.record(stream)
+            if stats is not None:
+                stats.wait()            # the side-stream all-reduces belong to the timed region
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record(stream)
+            collectives_timed = n_collectives[0]
             barrier()
         ms_total = e0.elapsed_time(e1)
     if world > 1:
@@ -247,13 +267,18 @@ def run_ours(args):
             traffic = json.load(open(tpath)).get(str(N))
         except Exception:   # noqa: BLE001
             traffic = None
-    roofline = {"kernel": "lgk_step_kernel", "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
+    roofline = {"kernel": "post_physics_step = lgk_scan_kernel + lgk_step_kernel + lgk_finish_kernel + epilogue "
+                          "(chained with programmatic dependent launch, overlapping; timed as one unit)",
+                "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                 "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
                 "algorithmic_bytes_per_env_step": bpe, "kernel_ms": round(k_ms, 5), "peak_source": peak_src,
-                "timing": "CUDA events around single launches, L2 flushed (256 MB memset) before each"}
+                "timing": "CUDA events around single lgk_post_physics_step calls, L2 flushed (256 MB memset) before each"}
+    if getattr(env.cfg.control, "use_actuator_network", False) and hasattr(env, "actuator_advance"):
+        # the dominant kernel of this scenario is the actuator MLP (decimation launches per step), tensor-bound
+        roofline = {"post_physics_step": roofline, **_actuator_roofline(env, frames, stream)}
 
     # ---- end to end through the public API with host buffers --------------------------------------
-    e2e = run_e2e(env, frames, args, world, device, stream)
+    e2e = None if args.no_e2e else run_e2e(env, frames, args, world, device, stream)
 
     # ---- CPU baseline (rank 0, single-GPU runs only) ------------------------------------------------
     cpu = None
@@ -265,12 +290,8 @@ def run_ours(args):
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 6), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(N, env.cfg.control.decimation), "envs_per_gpu": N, "envs_total": N * world, "num_obs": env.num_obs,
-                       "reward_terms": env._num_sum_rows, "rng": "in-kernel Philox4x32-10",
-                       "l2": f"inputs cycle through {NUM_FRAMES} state frames resident in HBM "
-                             f"({NUM_FRAMES * N * 448 / 1e6:.0f} MB) -- larger than L2 at the default size",
-                       "parallelism": f"env-sharded x{world}, terrain replica per GPU, "
-                                      f"NCCL all-reduce of episode statistics every 24 steps"},
+            "config": config_dict(N, world, env.cfg.control.decimation, env.num_obs, env._num_sum_rows),
+            "collectives_in_timed_region": collectives_timed, "stats_allreduce_interval": stats_interval if world > 1 else None,
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "launches_per_step": int(launches_per_step),
             "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(),
         }
@@ -279,6 +300,39 @@ def run_ours(args):
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
+
+
+def _actuator_roofline(env, frames, stream):
+    """Go1 actuator substep (history kernel + tcgen05 MLP kernel) timed alone, against the tensor pipe: every product
+    runs as three TF32 passes (layer 0's K = 30 padded to 32); TF32 peak = half the measured dense bf16 rate, the burst
+    figure because the kernel is timed in isolation."""
+    N = env.num_envs
+    act = frames[0]["actions"]
+    with torch.cuda.stream(stream):
+        for _ in range(5):
+            env.actuator_advance(act)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 50
+        e0.record(stream)
+        for _ in range(reps):
+            env.actuator_advance(act)
+        e1.record(stream)
+        stream.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    pipe = 3 * 2 * (32 * 128 + 2 * 128 * 128) * 4 * N
+    useful = 2 * (30 * 128 + 2 * 128 * 128 + 128 * 3) * 4 * N
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        peak, src = float(pk["bf16_tflops"]) / 2, "measured (MEASURED_PEAKS.json bf16_tflops / 2: TF32 runs at half the bf16 rate; burst figure)"
+    except Exception:   # noqa: BLE001
+        peak, src = 2250.0 / 2, "fallback (B200_PROFILING.md dense bf16 2.25 PFLOP/s / 2)"
+    ach = pipe / (ms * 1e-3) / 1e12
+    return {"kernel": "lgk_act_mlp_umma_kernel (+ lgk_act_hist_kernel ahead of it, timed together)", "bound": "tensor",
+            "achieved": round(ach, 1), "peak": round(peak, 1), "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None,
+            "kernel_ms": round(ms, 5), "peak_source": src,
+            "flops_per_launch": {"tensor_pipe_3xTF32": pipe, "useful_fp32_equivalent": useful,
+                                 "useful_tflops": round(useful / (ms * 1e-3) / 1e12, 1)},
+            "timing": "CUDA events over 50 back-to-back substeps (same inputs; weights and inputs L2-resident)"}
 
 
 def run_e2e(env, frames, args, world, device, stream):
@@ -351,20 +405,53 @@ def cpu_reference(envs, budget_s=20.0, steps=None, warmup=1):
     import helpers
     from legged_gym_b200.utils import synthetic
     from oracle import legged_oracle as lo
+    from oracle import reference_loader
     torch.set_num_threads(os.cpu_count() or 1)
+    # the reference's own code when it is here (oracle/_ref, staged by oracle/make_ref.sh; /root/reference in the
+    # build container), else the oracle port of it
+    use_ref = reference_loader.reference_available()
+    timer = (lambda n, k, w: _time_reference(n, k, w, synthetic, reference_loader)) if use_ref else \
+            (lambda n, k, w: _time_oracle(n, k, w, helpers, synthetic, lo))
     # size the sample from a short probe so the whole leg stays within the budget
     probe_n = min(envs, 4096)
-    t_probe = _time_oracle(probe_n, 2, 1, helpers, synthetic, lo)
+    t_probe = timer(probe_n, 2, 1)
     per_env = t_probe / probe_n
     n = envs
     if steps is None:
         steps = 5
     while n > 1024 and per_env * n * (steps + warmup) > budget_s:
         n //= 2
-    t = _time_oracle(n, steps, warmup, helpers, synthetic, lo)
-    return {"value": round(n / t, 1), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{steps} steps x {n} envs of the same workload after {warmup} warm-up (oracle/legged_oracle.py, "
+    t = timer(n, steps, warmup)
+    what = (f"the reference's own LeggedRobot.step() ({reference_loader.reference_kind()}, unmodified, over the "
+            f"tensor-only simulator stand-in)") if use_ref else "oracle/legged_oracle.py"
+    return {"value": round(n / t, 1), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "reference" if use_ref else "port",
+            "sample": f"{steps} steps x {n} envs of the same workload after {warmup} warm-up ({what}, "
                       f"torch {torch.__version__} CPU kernels)", "ms_per_step": round(t * 1e3, 3)}
+
+
+_CPU_META = {"decimation": 4, "num_obs": 235, "reward_terms": 21}
+
+
+def _time_reference(n, steps, warmup, synthetic, reference_loader):
+    """The reference's unmodified task class on CPU torch: env.step(actions) through its public API, stock random
+    draws, with a synthetic simulator frame written in place of gym.simulate()'s result before each step."""
+    from legged_gym_b200.utils import scenarios
+    task, mutate = scenarios.SCENARIOS[SCENARIO]
+    env = reference_loader.make_reference_env(task, mutate, num_envs=n, seed=1)
+    g = torch.Generator().manual_seed(99)
+    env.episode_length_buf[:] = torch.randint(0, int(env.max_episode_length), (n,), generator=g)
+    _CPU_META.update(decimation=int(env.cfg.control.decimation), num_obs=int(env.num_obs), reward_terms=len(env.episode_sums))
+    frames = synthetic.make_frames(env, 2, seed=3234)
+    ts = []
+    for i in range(steps + warmup):
+        fr = frames[i % 2]
+        synthetic.load_frame(env, fr)
+        a = fr["actions"].clone()
+        t0 = time.perf_counter()
+        env.step(a)
+        ts.append(time.perf_counter() - t0)
+    ts = sorted(ts[warmup:])
+    return ts[len(ts) // 2]
 
 
 def _time_oracle(n, steps, warmup, helpers, synthetic, lo):
@@ -373,6 +460,7 @@ def _time_oracle(n, steps, warmup, helpers, synthetic, lo):
     env.episode_length_buf = torch.randint(0, int(env.max_episode_length), (n,), generator=g)
     p = lo.OracleParams.from_env(env)
     s = lo.OracleState.from_env(env, p)
+    _CPU_META.update(decimation=int(env.cfg.control.decimation), num_obs=int(env.num_obs), reward_terms=int(env._num_sum_rows))
     frames = synthetic.make_frames(env, 2, seed=3234)
     taps = synthetic.make_taps(env, seed=5)
     ts = []
@@ -399,8 +487,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cpu["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.envs), "envs_per_gpu": args.envs,
-                       "cpu_sample_envs_per_step": n_sample, "num_obs": 235, "reward_terms": 21},
+            "config": config_dict(args.envs, max(1, args.gpus), _CPU_META["decimation"], _CPU_META["num_obs"], _CPU_META["reward_terms"]),
+            "cpu_sample_envs_per_step": n_sample,
             "cpu_baseline": cpu, "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
                                          "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": round(time.perf_counter() - t0, 1)}
@@ -416,6 +504,7 @@ def main():
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU (BASELINE.json: 4096-65536)")
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="development: skip the host-buffer leg (e2e: null)")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--scenario", default=SCENARIO,
                     help="parity-test scenario to time instead of the headline one, e.g. go1_rough_actuator "

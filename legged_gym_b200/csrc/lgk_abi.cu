@@ -20,6 +20,7 @@ int lgk_actuator_advance_static_impl(int, const float*, const float*, float*, fl
 int lgk_lstm_actuator_advance_impl(const LgkConsts*, const LgkLstmWeights*, const float*, const float*, float*, float*,
                                    float*, float*, cudaStream_t);
 int lgk_lstm_reset_hidden_impl(int, int, const int*, const int*, int, float*, float*, cudaStream_t);
+int lgk_set_step_counter_impl(void*, long long, cudaStream_t);
 }
 
 static std::atomic<long long> g_launches{0};
@@ -100,8 +101,8 @@ int64_t lgk_launch_count(void) { return g_launches.load(); }
 
 int64_t lgk_workspace_bytes(int32_t num_envs, int32_t num_sum_rows) {
   (void)num_sum_rows;
-  // header, the two per-tile bitmask arrays, then one float per env: the scan kernel's height sums
-  return (int64_t)lgk_ws_hsum_offset(num_envs) + 4ll * (int64_t)num_envs;
+  // header, the two per-tile bitmask arrays, one float per env (the scan kernel's height sums), one flag per scan tile
+  return (int64_t)lgk_ws_total_bytes(num_envs);
 }
 
 int lgk_build_height_min3(const int16_t* height_samples, int32_t rows, int32_t cols, int16_t* out, int32_t pitch,
@@ -200,7 +201,7 @@ int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream) {
   int rc = check_step(c, b);
   if (rc) return rc;
-  g_launches += 2 + (c->num_height_points > 0 ? 1 : 0);   // (scan kernel,) step kernel, epilogue
+  g_launches += 3 + (c->num_height_points > 0 ? 1 : 0);   // (scan kernel,) step kernel, finish kernel, epilogue
   return lgk_post_physics_step_impl(c, b, (cudaStream_t)stream);
 }
 
@@ -236,14 +237,11 @@ int lgk_debug_yaw_quat(const float* quat, int32_t n, int32_t norm_mode, float* o
 /* device-side common_step_counter (legged_robot.py:119,527) */
 int lgk_set_step_counter(void* workspace, int64_t value, void* stream) {
   if (!workspace) return LGK_ERR_NULL;
-  static_assert(offsetof(LgkWorkspace, step_counter) == 0, "step_counter must lead the workspace");
-  // value travels through the launch parameters of a 1-thread memset-like copy: use cudaMemcpyAsync
-  // from a pageable stack variable only when not capturing; callers inside a capture must not call this
-  // The whole header goes with it: the step epilogue zeroes only the accumulators of the OTHER step parity, so a
-  // counter set by hand (load_state_dict into an env that has stepped) must not leave this parity's sums behind.
-  LgkWorkspace hdr = {};
-  hdr.step_counter = (unsigned long long)value;
-  return (int)cudaMemcpyAsync(workspace, &hdr, sizeof(hdr), cudaMemcpyHostToDevice, (cudaStream_t)stream);
+  // The whole header goes with it, except the launch sequence number the scan flags are stamped with: the step
+  // epilogue zeroes only the accumulators of the OTHER step parity, so a counter set by hand (load_state_dict into an
+  // env that has stepped) must not leave this parity's sums behind.  One tiny launch; capturable.
+  g_launches += 1;
+  return lgk_set_step_counter_impl(workspace, value, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -12,7 +12,9 @@
 struct LgkWorkspace {
   unsigned long long step_counter;   // == reference common_step_counter (legged_robot.py:119)
   unsigned int done_ticket;          // CTAs finished in the current launch
-  unsigned int mask_ticket;          // CTAs that have published their reset / resample masks
+  unsigned int launch_seq;           // post_physics_step launches so far (the epilogue adds 1); value of the per-tile
+                                     // scan flags of the NEXT launch is launch_seq + 1.  lgk_set_step_counter keeps it
+  unsigned int scan_timeouts;        // step CTAs that gave up waiting for a scan tile (never, unless the launch order broke)
   int level_sum[2];                  // sum(terrain_levels) accumulators, indexed by step parity
   int reset_count[2];                // number of reset envs, indexed by step parity
   float stats[2][LGK_MAX_REWARDS + 4];   // per-parity: sum over reset ids of episode_sums[k]
@@ -33,6 +35,15 @@ __device__ __forceinline__ void ticket_relaxed(unsigned int* p) {
 }
 __device__ __forceinline__ void ticket_release(unsigned int* p) {
   asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+}
+// per-tile hand-over flags between two kernels that run side by side (scan kernel -> step kernel)
+__device__ __forceinline__ void flag_release(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int flag_acquire(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
 }
 #endif
 #ifdef __CUDACC__

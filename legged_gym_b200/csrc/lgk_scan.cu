@@ -7,20 +7,28 @@
 // (:871) -- only in its last phase.  Envs the step kernel resets get their scan columns rewritten there (the
 // observation uses the root z after the reset, :227); for everyone else what this kernel writes is final.
 //
+// The scan and the step kernel do not depend on each other (the step kernel neither reads heights nor writes the
+// root state: the new root row of a reset env waits in a side buffer until the finish kernel stores it).  This grid
+// is persistent and resident at once; every CTA waits for the launch's predecessor, then lets the step kernel go,
+// whose CTAs take SM slots as the warps here retire.  Hand-over to the finish kernel is per group of envs: when a
+// group's columns and sums are out, lane 0 stamps the group's flag in the workspace with this launch's sequence
+// number (st.release.gpu); the finish kernel polls the flags of its envs (ld.acquire.gpu).
+//
 // Work decomposition
-//   grid     one CTA of four warps per tile of `scan_epc` envs (32, or fewer when the launch would not fill the
-//            GPU otherwise).  No CTA is long-lived: ~2 us each, the hardware scheduler balances the tail.
-//   prologue W0, lane = env: root position and quaternion -> the env's eight scan operands (normalised yaw
-//            quaternion as ready-made f32x2 pairs) into shared memory.  One barrier, the only one.
-//   scan     each warp takes its envs one at a time, lanes over the H points in passes of 32: index chain on
-//            packed f32x2 instructions (bit-identical to torch's op-by-op chain), one int16 gather per point from
+//   grid     min(groups / 4, LGK_SCAN_CTAS_PER_SM x SMs) CTAs of four warps.  Warps are independent -- no CTA
+//            barrier anywhere: warp w of the grid walks groups w, w + W, ... of `scan_epc` envs (8, fewer when there
+//            are not enough envs to give every warp a group).
+//   prologue lane = env of the group: root position and quaternion -> the env's eight scan operands (normalised
+//            yaw quaternion as ready-made f32x2 pairs) into the warp's slice of shared memory.
+//   scan     the warp takes the group's envs one at a time, lanes over the H points in passes of 32: index chain
+//            on packed f32x2 instructions (bit-identical to torch's op-by-op chain), one int16 gather per point from
 //            the L2-resident min-of-three-neighbours table with all gathers of an env in flight together, then
 //            height -> clipped, scaled, noisy observation column, stored straight from registers (128 B per
-//            warp store).  The per-lane constants (point offsets, noise factors) stay in registers across envs.
-//   sums     per-lane partial sums of the heights go through shared memory; eight lanes per env add them up.
+//            warp store).  The per-lane constants (point offsets, noise factors) stay in registers across groups.
+//   sums     per-lane partial sums of the heights go through shared memory; four lanes per env add them up.
 #include "lgk_step.cuh"
 
-#define LGK_SCAN_MIN_CTAS LGK_SCAN_CTAS_PER_SM
+#define LGK_SCAN_MIN_CTAS LGK_SCAN_REG_CTAS
 
 template <bool TAPS, bool MUL_RCP, int NP>   // NP = 0: any H, passes in chunks of 8, constants re-read per env
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_SCAN_MIN_CTAS)
@@ -34,12 +42,12 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const bool add_noise = c.flags & LGK_F_ADD_NOISE;
 
-  __shared__ __align__(16) float s_es[TILE * 8];
-  __shared__ float s_hp[TILE * RS];
+  __shared__ __align__(16) float s_es_all[LGK_WARPS_PER_CTA][SCAN_GROUP * 8];
+  __shared__ float s_hp_all[LGK_WARPS_PER_CTA][SCAN_GROUP * RS];
+  float* s_es = s_es_all[wic];
+  float* s_hp = s_hp_all[wic];
 
-  const int epc = a.scan_epc;
-  const int env0 = blockIdx.x * epc;
-  const int ne = min(epc, N - env0);
+  const int epg = a.scan_epc;   // envs per group (= per flag): 8, fewer for small N
 
   // this lane's scan offsets and noise factors (same for every env), before the wait: they do not depend on
   // anything an earlier kernel wrote
@@ -58,68 +66,75 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
   }
 
   pdl_wait();   // root_states belong to the simulator: written by whatever ran before this launch
-  if (wic == 0 && lane < ne) {
-    const float* r = b.root_states + (size_t)(env0 + lane) * 13;
-    const ScanEnv e = scan_env_operands(r[0], r[1], r[2], r[5], r[6]);
-    float4* d = reinterpret_cast<float4*>(s_es + lane * 8);
-    d[0] = make_float4(e.k_t.x, e.k_t.y, e.k_c.x, e.k_c.y);
-    d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
-  }
-  __syncthreads();
-  // every read of root_states is done: the step kernel behind this launch (it rewrites the root state of the envs
-  // it resets) may start taking SM slots as they free up
+  // The whole grid is resident: the step kernel behind this launch may take SM slots as soon as warps here retire.
   pdl_launch_dependents();
 
   const LgkWorkspace* ws = reinterpret_cast<const LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
-  const int epw = epc >> 2;                                  // envs per warp
-  const int e_lo = wic * epw, e_hi = min(e_lo + epw, ne);
+  const unsigned stamp = ws->launch_seq + 1u;
   const int nchunks = GENERIC ? (H + 255) / 256 : 1;
+  const int gw = (int)blockIdx.x * LGK_WARPS_PER_CTA + wic, nw = (int)gridDim.x * LGK_WARPS_PER_CTA;
 
 #pragma unroll 1
-  for (int el = e_lo; el < e_hi; ++el) {
-    const int env = env0 + el;
-    const float4 ea = reinterpret_cast<const float4*>(s_es + el * 8)[0];
-    const float4 eb = reinterpret_cast<const float4*>(s_es + el * 8)[1];
-    ScanEnv e;
-    e.k_t = make_float2(ea.x, ea.y);
-    e.k_c = make_float2(ea.z, ea.w);
-    e.r2 = make_float2(eb.x, eb.y);
-    e.yw = eb.z;
-    e.zo = eb.w;
-    float* orow = b.obs_buf + (size_t)env * O + OH;
-    const float* trow = (TAPS && add_noise) ? b.tap_noise + (size_t)env * O + OH : nullptr;
-    float* mrow = b.measured_heights != nullptr ? b.measured_heights + (size_t)env * H : nullptr;
-    const unsigned eg = (unsigned)(c.env_id_offset + env);
-    float hsum = 0.f;
-#pragma unroll 1
-    for (int ch = 0; ch < nchunks; ++ch) {
-      uint4 rnd = make_uint4(0, 0, 0, 0);
-      if (!TAPS && add_noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE_SCAN + 32u * (unsigned)ch + lane);
-      if (GENERIC) {
-#pragma unroll
-        for (int it = 0; it < CH; ++it) ln[it] = scan_lane_consts<TAPS>(a, (ch * CH + it) * 32 + lane, OH);
-        hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, ch * CH, lane, rnd, orow, trow, mrow, true);
-      } else if (clip_h) {
-        hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
-      } else {
-        hsum += scan_passes<TAPS, MUL_RCP, CH, false>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
-      }
+  for (int grp = gw; grp < a.scan_tiles; grp += nw) {
+    const int env0 = grp * epg;
+    const int ne = min(epg, N - env0);
+    if (lane < ne) {
+      const float* r = b.root_states + (size_t)(env0 + lane) * 13;
+      const ScanEnv e = scan_env_operands(r[0], r[1], r[2], r[5], r[6]);
+      float4* d = reinterpret_cast<float4*>(s_es + lane * 8);
+      d[0] = make_float4(e.k_t.x, e.k_t.y, e.k_c.x, e.k_c.y);
+      d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
     }
-    s_hp[el * RS + lane] = hsum;
-  }
-  __syncwarp();
-  // sum over the points of each env's heights: lane (q, k) adds a quarter of the partial sums of env e_lo + k
-  {
-    const int k = lane & 7, q = lane >> 3;
-    const int el = min(e_lo + k, TILE - 1);
-    const float* hp = s_hp + el * RS + q * 8;
-    float hs = 0.f;
+    __syncwarp();
+
+#pragma unroll 1
+    for (int el = 0; el < ne; ++el) {
+      const int env = env0 + el;
+      const float4 ea = reinterpret_cast<const float4*>(s_es + el * 8)[0];
+      const float4 eb = reinterpret_cast<const float4*>(s_es + el * 8)[1];
+      ScanEnv e;
+      e.k_t = make_float2(ea.x, ea.y);
+      e.k_c = make_float2(ea.z, ea.w);
+      e.r2 = make_float2(eb.x, eb.y);
+      e.yw = eb.z;
+      e.zo = eb.w;
+      float* orow = b.obs_buf + (size_t)env * O + OH;
+      const float* trow = (TAPS && add_noise) ? b.tap_noise + (size_t)env * O + OH : nullptr;
+      float* mrow = b.measured_heights != nullptr ? b.measured_heights + (size_t)env * H : nullptr;
+      const unsigned eg = (unsigned)(c.env_id_offset + env);
+      float hsum = 0.f;
+#pragma unroll 1
+      for (int ch = 0; ch < nchunks; ++ch) {
+        uint4 rnd = make_uint4(0, 0, 0, 0);
+        if (!TAPS && add_noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE_SCAN + 32u * (unsigned)ch + lane);
+        if (GENERIC) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) hs += hp[i];
-    hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 8);
-    hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 16);
-    if (q == 0 && e_lo + k < e_hi) a.hsum[env0 + e_lo + k] = hs;
+          for (int it = 0; it < CH; ++it) ln[it] = scan_lane_consts<TAPS>(a, (ch * CH + it) * 32 + lane, OH);
+          hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, ch * CH, lane, rnd, orow, trow, mrow, true);
+        } else if (clip_h) {
+          hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
+        } else {
+          hsum += scan_passes<TAPS, MUL_RCP, CH, false>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
+        }
+      }
+      s_hp[el * RS + lane] = hsum;
+    }
+    __syncwarp();
+    // sum over the points of each env's heights: lane (q, k) adds a quarter of the partial sums of env k
+    {
+      const int k = lane & 7, q = lane >> 3;
+      const float* hp = s_hp + k * RS + q * 8;
+      float hs = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) hs += hp[i];
+      hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 8);
+      hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 16);
+      if (q == 0 && k < ne) a.hsum[env0 + k] = hs;
+    }
+    // the group's columns and sums are out (the warp barrier also frees s_es / s_hp for the next group): hand it over
+    __syncwarp();
+    if (lane == 0) flag_release(a.scan_flags + grp, stamp);
   }
 }
 
@@ -130,7 +145,7 @@ static int launch_scan(const StepArgs& args, int grid, cudaStream_t stream) {
 
 int lgk_scan_launch(const StepArgs& args, cudaStream_t stream) {
   const LgkConsts& c = args.c;
-  const int grid = (c.num_envs + args.scan_epc - 1) / args.scan_epc;
+  const int grid = args.scan_grid;
   const bool taps = c.rng_mode == LGK_RNG_TAPS;
   const bool mul = c.index_math == LGK_INDEX_MUL_RCP;
   const int np = (c.num_height_points + 31) / 32;

@@ -1,18 +1,26 @@
 // Step kernel of post_physics_step (sm_100a): one CTA of four warps per tile of 32 envs, lanes = envs.
 //
-// Together with the height-scan kernel launched ahead of it (lgk_scan.cu) and the one-CTA epilogue behind it,
-// this replaces everything LeggedRobot.post_physics_step() does per env (reference legged_robot.py:109-141):
-// episode counters, body-frame velocities / projected gravity, command resampling + heading command, pushes,
-// terminations, every active _reward_* term with in-place episode sums, resets (terrain curriculum, dof / root
-// state, commands), the noisy scaled head of the observation row, last_* copies, the per-tile reset / resample
-// bitmasks behind the ascending id lists, and the episode statistics behind extras.
+// post_physics_step() (reference legged_robot.py:109-141) is four launches chained with programmatic dependent launch:
+//   lgk_scan_kernel    (lgk_scan.cu)  _get_heights + the scan columns of the observation row, lanes = points
+//   lgk_step_kernel    (this file)    everything per env that needs no height: episode counters, body-frame
+//                                     velocities / projected gravity, command resampling + heading command, pushes,
+//                                     terminations, the VALUE of every _reward_* term, resets (terrain curriculum, dof
+//                                     state, commands), the noisy scaled head of the observation row, last_* copies,
+//                                     the per-tile reset / resample bitmasks behind the ascending id lists
+//   lgk_finish_kernel  (this file)    lanes = envs over the [R,N] episode-sum rows: scale, in-place sums, ordered
+//                                     reward sum, statistics of the reset envs; base_height from the scan's height
+//                                     sums; the root state and the scan columns of the envs reset this step
+//   lgk_step_epilogue_kernel          one CTA: ordered compaction of the bitmasks, extras, step counter
+// The scan and the step kernel do not depend on each other: the step kernel neither reads heights nor writes the
+// root state (the new root row of a reset env goes to a side buffer in the workspace; the finish kernel stores it),
+// so the step CTAs start as soon as the scan's persistent CTAs begin to retire, without waiting for anything.
 //
-// Work decomposition
+// Work decomposition of this kernel
 //   grid    CTA c owns the contiguous env range [c*per, (c+1)*per) and walks it in sub-tiles of <= 32 envs.
 //           per = 32 by default (the hardware scheduler backfills); LgkConsts.envs_per_cta selects longer ranges.
-//   load    every per-env input row of a sub-tile is contiguous in HBM ([N,13], [N,D,2], [N,B,3], ...), and so is
-//           the tile's slice of each [R,N] episode-sum row: the lanes of W0 issue 1-D bulk async copies
-//           (cp.async.bulk -> SASS UBLKCP, the TMA engine) into shared memory, completion counted on one mbarrier.
+//   load    every per-env input row of a sub-tile is contiguous in HBM ([N,13], [N,D,2], [N,B,3], ...): the lanes
+//           of W0 issue 1-D bulk async copies (cp.async.bulk -> SASS UBLKCP, the TMA engine) into shared memory,
+//           completion counted on one mbarrier.
 //   stage 1 four roles, lane = env (no divergence inside a warp):
 //             W0  episode counter, commands (resample, heading command), push, root reset with the terrain
 //                 curriculum, the per-tile bitmasks;  W1, W2  half of the joints each;  W3  body-frame
@@ -22,15 +30,13 @@
 //           block computation is used).  The reset flag is cheap and is recomputed by each warp.
 //   -- the only CTA barrier of a sub-tile --
 //   store   W0..W2 write the staged heads to the observation rows, 128 B per warp store; last_actions and
-//           last_dof_vel leave through bulk async stores.
-//   stage 3 W3 alone, lane = env: waits for the scan kernel (griddepcontrol.wait -- the only place this kernel
-//           needs it), rewrites the scan columns of the envs reset in this tile (new root z, :227), then walks
-//           the episode-sum rows in the reference's order (:195-212): r = value * scale, sum += r, reward += r,
-//           statistics of the reset envs by red.global.add -- 8 instructions per row for 32 envs, all coalesced.
+//           last_dof_vel leave through bulk async stores;  W3 writes the term values of its 32 envs into the
+//           [term][N] table of the workspace (one coalesced 128 B store per term) for the finish kernel.
 //
 // Code size matters (four roles live in different regions of the code at once): paths that run for ~1 % of the
 // envs, once per launch, or only for ragged / unaligned tiles are __noinline__.
 #include <cmath>
+#include <cstdio>
 #include <limits>
 #include <type_traits>
 #include "lgk_step.cuh"
@@ -63,8 +69,7 @@ extern "C" int lgk_debug_read_prof_cta(long long* out, int n) {
 enum { SC_J1 = 0, SC_J2 = 10,    // joint partial sums of W1 / W2 (10 each)
        SC_CMDX = 20, SC_CMDY, SC_CMDZ,   // command after the callback, before any reset (what the rewards see)
        SC_ZPRE,                  // root z before any reset (_reward_base_height)
-       SC_FIELDS,
-       SC_ES = SC_FIELDS };      // then 8 floats per env (AoS): scan operands of the envs reset in this tile
+       SC_FIELDS };
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float norm3(float x, float y, float z) {
   return sqrtf(fmaf(z, z, fmaf(y, y, x * x)));
@@ -187,7 +192,7 @@ struct ResetOut {
 };
 template <bool TAPS>
 static __device__ __noinline__ void reset_root(const StepArgs& a, unsigned long long csc, int env, unsigned env_global,
-                                               float rx, float ry, long long level, ResetOut& o) {
+                                               float rx, float ry, long long level, ResetOut& o, float* root_stage) {
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
   const unsigned flags = c.flags;
@@ -236,9 +241,10 @@ static __device__ __noinline__ void reset_root(const StepArgs& a, unsigned long 
   }
 #pragma unroll
   for (int i = 0; i < 6; ++i) { o.rvel[i] = rand_affine(1.0f, -0.5f, u[2 + i]); root[7 + i] = o.rvel[i]; }
-  float* rw = b.root_states + (size_t)env * 13;
+  // the new root state waits in the workspace's side buffer: the finish kernel stores it once the scan kernel, which
+  // runs side by side with this one and needs the pose from before the reset (:818-854 precede reset_idx), is done
 #pragma unroll
-  for (int i = 0; i < 13; ++i) rw[i] = root[i];
+  for (int i = 0; i < 13; ++i) root_stage[i] = root[i];
   o.z = root[2];
   float c0, c1, c2;
   if (TAPS) { const float* t = b.tap_cmd_reset + (size_t)env * 3; c0 = t[0]; c1 = t[1]; c2 = t[2]; }
@@ -251,7 +257,7 @@ static __device__ __noinline__ void tile_load_fallback(const StepArgs& a, float*
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
   const TileLayout& L = a.L;
-  const int D = c.num_dof, B3 = c.num_bodies * 3, F = c.num_feet, N = c.num_envs;
+  const int D = c.num_dof, B3 = c.num_bodies * 3, F = c.num_feet;
   const int tid = threadIdx.x;   // (physical thread index: every thread takes part, whatever its role)
   auto ld = [&](int off, const void* g, int words_per_env) {
     const unsigned* src = reinterpret_cast<const unsigned*>(g);
@@ -270,9 +276,6 @@ static __device__ __noinline__ void tile_load_fallback(const StepArgs& a, float*
   ld(L.ldv, b.last_dof_vel + (size_t)env0 * D, D);
   ld(L.fat, b.feet_air_time + (size_t)env0 * F, F);
   if (b.terrain_levels != nullptr) ld(L.lvl, b.terrain_levels + env0, 2);
-#pragma unroll 1
-  for (int r = 0; r < a.num_rows; ++r)
-    for (int i = tid; i < ne; i += LGK_CTA_THREADS) sm[L.sums + r * TILE + i] = b.episode_sums[(size_t)r * N + env0 + i];
 }
 static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const float* sm, int env0, int ne, int tid) {
   const int D = a.c.num_dof;
@@ -385,16 +388,17 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
     ws->level_sum[parity ^ 1] = 0;
     ws->reset_count[parity ^ 1] = 0;
     ws->step_counter = csc;
+    ws->launch_seq += 1u;
   }
 }
 
 template <int DT, bool TAPS, bool MUL_RCP>
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_MIN_CTAS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
-  pdl_launch_dependents();   // the epilogue may be scheduled as soon as the last tile CTA has started
+  pdl_launch_dependents();   // the finish kernel may be scheduled as soon as the last tile CTA has started
   // Behind the scan kernel this launch needs no wait on entry: that kernel waits for ITS predecessor before it lets
   // its dependents go, so every input here (simulator tensors, clipped actions, the previous step's state) is
-  // complete when the first CTA starts; only W3 waits, before stage 3.  Without a scan kernel: wait now.
+  // complete when the first CTA starts, and nothing here depends on the scan itself.  Without a scan kernel: wait now.
   if (!a.scan_first) pdl_wait();
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
@@ -410,7 +414,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   const unsigned flags = c.flags;
   const bool heading_mode = flags & LGK_F_HEADING_COMMAND;
   const bool add_noise = flags & LGK_F_ADD_NOISE;
-  const int num_rows = a.num_rows;
 
   extern __shared__ __align__(16) float sm[];
   __shared__ __align__(8) uint64_t s_bar;
@@ -434,11 +437,9 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
   unsigned ld_off = 0, ld_bpe = 0;
   if (wic == 0 && lane < LGK_LD_ARRAYS) { ld_src = a.ld_src[lane]; ld_off = a.ld_off[lane]; ld_bpe = a.ld_bpe[lane]; }
   auto issue_loads = [&](int env0, int ne) {   // W0, converged
-    if (lane == 0) mbar_expect_tx(&s_bar, (unsigned)ne * (a.ld_bytes_per_env + 4u * (unsigned)num_rows));
+    if (lane == 0) mbar_expect_tx(&s_bar, (unsigned)ne * a.ld_bytes_per_env);
     __syncwarp();
     if (ld_src != nullptr) bulk_g2s(sm + ld_off, ld_src + (size_t)env0 * ld_bpe, (unsigned)ne * ld_bpe, &s_bar);
-    for (int r = lane; r < num_rows; r += 32)
-      bulk_g2s(sm + L.sums + r * TILE, b.episode_sums + (size_t)r * N + env0, (unsigned)ne * 4u, &s_bar);
   };
   if (wic == 0) {
     if (lane == 0) mbar_init(&s_bar, 1);
@@ -566,15 +567,16 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         if (reset) {   // reset_idx for this env (:150-193): curriculum, root state, command
           ResetOut ro;
           ro.cmd = cmd;
-          reset_root<TAPS>(a, csc, env, env_global, rp[0], rp[1], level, ro);
+          float* side = a.side + (size_t)env * LGK_SIDE_FLOATS;
+          reset_root<TAPS>(a, csc, env, env_global, rp[0], rp[1], level, ro, side + 8);
           cmd = ro.cmd;
 #pragma unroll
           for (int i = 0; i < 6; ++i) rvel[i] = ro.rvel[i];
           level = ro.level;
           ep = 0;
-          if (a.scan_first) {   // W3 redoes this env's scan columns with the new root z (:227)
+          if (a.scan_first) {   // the finish kernel redoes this env's scan columns with the new root z (:227)
             const ScanEnv e = scan_env_operands(rp[0], rp[1], ro.z, q[2], q[3]);
-            float4* d = reinterpret_cast<float4*>(scr + SC_ES * TILE + lane * 8);
+            float4* d = reinterpret_cast<float4*>(side);
             d[0] = make_float4(e.k_t.x, e.k_t.y, e.k_c.x, e.k_c.y);
             d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
           }
@@ -611,8 +613,15 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
         unsigned* mask_base = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + LGK_WS_HEADER_BYTES);
         mask_base[slot] = reset_mask;
         mask_base[lgk_max_warps(N) + slot] = resample_mask;
+      }
+      {   // the envs reset in this sub-tile join the finish kernel's list (any order: the entries are independent)
         const int nr = __popc(reset_mask);
-        if (nr != 0) atomicAdd(&ws->reset_count[parity], nr);
+        if (nr != 0) {   // warp-uniform
+          int base = 0;
+          if (lane == 0) base = atomicAdd(&ws->reset_count[parity], nr);
+          base = __shfl_sync(LGK_FULL_MASK, base, 0);
+          if (active && reset) a.fix_list[base + __popc(reset_mask & ((1u << lane) - 1u))] = env;
+        }
       }
     }
     else if (wic == 1 || wic == 2) {
@@ -799,89 +808,43 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       if (full && tid == 32) bulk_wait_read_all();   // the bulk stores have read their rows before the next loads
       LGK_STAMP(4);
     } else {
-      // =========================================== stage 3 ===========================================
-      // W3, lane = env: every term's value into the table rv[term][env] (the contact rows are dead by now), then
-      // the episode-sum rows in the reference's order (:195-212)
-      float* rv = sm + L.rv;
-      const float* sums = sm + L.sums;
-      auto put = [&](int term, float v) { rv[term * TILE + lane] = v; };
-      auto J = [&](int k) { return scr[(SC_J1 + k) * TILE + lane] + scr[(SC_J2 + k) * TILE + lane]; };
-      const float cx = scr[SC_CMDX * TILE + lane], cy = scr[SC_CMDY * TILE + lane], cz = scr[SC_CMDZ * TILE + lane];
-      const float cn = sqrtf(fmaf(cy, cy, cx * cx));
-      put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
-      put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
-      put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
-      put(LGK_REW_FEET_AIR_TIME, r_air * ((cn > 0.1f) ? 1.f : 0.f));
-      put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
-      {
-        const float e = cz - bav[2];
-        put(LGK_REW_TRACKING_ANG_VEL, expf(-(e * e) / c.tracking_sigma));
-        const float ex = cx - blv[0], ey = cy - blv[1];
-        put(LGK_REW_TRACKING_LIN_VEL, expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma));
-      }
-      put(LGK_REW_ACTION_RATE, J(A_ARATE));
-      put(LGK_REW_DOF_ACC, J(A_ACC2));
-      put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
-      put(LGK_REW_DOF_VEL, J(A_QD2));
-      put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
-      put(LGK_REW_ENERGY, J(A_ENERGY));
-      put(LGK_REW_HIP_MOTION, J(A_HIP));
-      put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
-      put(LGK_REW_TORQUES, J(A_TQ2));
-      put(LGK_REW_COLLISION, collisions);
-      put(LGK_REW_FEET_CONTACT_FORCES, ffp);
-      put(LGK_REW_NO_FLY, nofly_f);
-      put(LGK_REW_STUMBLE, stumble_f);
-      put(LGK_REW_EXTERNAL, 0.f);
-      put(LGK_REW_COUNT, (reset && !time_out) ? 1.f : 0.f);   // the termination row's value (:210-212)
-      float bh = scr[SC_ZPRE * TILE + lane];
-      if (a.scan_first) {
-        // from here on the scan kernel's writes are visible: the scan columns of every env, the height sums
-        pdl_wait();
-        LGK_STAMP(5);
-        unsigned m = reset_mask;
-        while (m) {   // warp-uniform; ~1 % of the envs
-          const int e = __ffs(m) - 1;
-          m &= m - 1;
-          lgk_scan_fixup_env<TAPS, MUL_RCP>(a, scr + SC_ES * TILE + e * 8, env0 + e, csc);
-        }
-        // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height)
-        if (a.bh_active && active) bh -= a.hsum[env] / (float)c.num_height_points;
-      }
-      {
-        const float d = bh - c.base_height_target;
-        put(LGK_REW_BASE_HEIGHT, d * d);
-      }
-      __syncwarp();
+      // ---- W3: every term's value for its env into the [term][N] table of the workspace (one coalesced store
+      //      per term); the finish kernel scales, sums and accumulates them (:195-212).  Rows of terms that are not
+      //      active are never read.
       if (active) {
-        float rew = 0.f;
-        int xi = 0;   // index among the external rows
-        const int nrew = c.num_rewards;
-        float* gsum = b.episode_sums + env;
-        float* stat = ws->stats[parity];
-#pragma unroll 4
-        for (int r = 0; r < nrew; ++r) {
-          const int term = c.rewards[r].term;
-          float v = rv[term * TILE + lane];
-          if (term == LGK_REW_EXTERNAL) {   // a python _reward_<name> of a subclass, evaluated by the host
-            v = b.ext_rewards[(size_t)xi * N + env];
-            ++xi;
-          }
-          const float rr = mul_rn(v, c.rewards[r].scale);
-          const float total = add_rn(sums[r * TILE + lane], rr);
-          rew = add_rn(rew, rr);
-          gsum[(size_t)r * N] = reset ? 0.f : total;   // zeroed for reset envs after the statistics read it (:184-185)
-          if (reset) atomicAdd(stat + r, total);
+        float* rvg = a.rv + env;
+        const size_t NP = (size_t)a.rv_pitch;
+        auto put = [&](int term, float v) { rvg[(size_t)term * NP] = v; };
+        auto J = [&](int k) { return scr[(SC_J1 + k) * TILE + lane] + scr[(SC_J2 + k) * TILE + lane]; };
+        const float cx = scr[SC_CMDX * TILE + lane], cy = scr[SC_CMDY * TILE + lane], cz = scr[SC_CMDZ * TILE + lane];
+        const float cn = sqrtf(fmaf(cy, cy, cx * cx));
+        put(LGK_REW_ANG_VEL_XY, fmaf(bav[1], bav[1], bav[0] * bav[0]));
+        put(LGK_REW_LIN_VEL_Z, blv[2] * blv[2]);
+        put(LGK_REW_ORIENTATION, fmaf(grav[1], grav[1], grav[0] * grav[0]));
+        put(LGK_REW_FEET_AIR_TIME, r_air * ((cn > 0.1f) ? 1.f : 0.f));
+        put(LGK_REW_STAND_STILL, J(A_STAND) * ((cn < 0.1f) ? 1.f : 0.f));
+        {
+          const float e = cz - bav[2];
+          put(LGK_REW_TRACKING_ANG_VEL, expf(-(e * e) / c.tracking_sigma));
+          const float ex = cx - blv[0], ey = cy - blv[1];
+          put(LGK_REW_TRACKING_LIN_VEL, expf(-fmaf(ey, ey, ex * ex) / c.tracking_sigma));
         }
-        if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
-        if (flags & LGK_F_HAS_TERMINATION) {   // added after the positive clip (:206-212)
-          const float rr = mul_rn(rv[LGK_REW_COUNT * TILE + lane], c.termination_scale);
-          const float total = add_rn(sums[nrew * TILE + lane], rr);
-          rew = add_rn(rew, rr);
-          gsum[(size_t)nrew * N] = reset ? 0.f : total;
-          if (reset) atomicAdd(stat + nrew, total);
-        }
-        b.rew_buf[env] = rew;
+        put(LGK_REW_ACTION_RATE, J(A_ARATE));
+        put(LGK_REW_DOF_ACC, J(A_ACC2));
+        put(LGK_REW_DOF_POS_LIMITS, J(A_POSLIM));
+        put(LGK_REW_DOF_VEL, J(A_QD2));
+        put(LGK_REW_DOF_VEL_LIMITS, J(A_VELLIM));
+        put(LGK_REW_ENERGY, J(A_ENERGY));
+        put(LGK_REW_HIP_MOTION, J(A_HIP));
+        put(LGK_REW_TORQUE_LIMITS, J(A_TQLIM));
+        put(LGK_REW_TORQUES, J(A_TQ2));
+        put(LGK_REW_COLLISION, collisions);
+        put(LGK_REW_FEET_CONTACT_FORCES, ffp);
+        put(LGK_REW_NO_FLY, nofly_f);
+        put(LGK_REW_STUMBLE, stumble_f);
+        // _reward_base_height (:871) needs the measured heights: the root height before any reset goes into the
+        // term's row, the finish kernel subtracts the scan's mean height and squares the distance to the target
+        put(LGK_REW_BASE_HEIGHT, scr[SC_ZPRE * TILE + lane]);
       }
       LGK_STAMP(6);
     }
@@ -890,6 +853,134 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 #ifdef LGK_PROFILE
   if (wic == 3 && lane == 0 && blockIdx.x < 4096) lgk_prof_cta[blockIdx.x * 4 + 3] = lgk_gtime();   // W3 leaves
 #endif
+}
+// ---------------------------------------------------------------------------------------------
+// Finish kernel: compute_reward's sums (:195-212) and the tail of reset_idx for every env.
+// Launched behind the step kernel (griddepcontrol.wait: its value table, flags, fix list and side rows are complete);
+// the scan kernel's part -- height sums, scan columns, its last read of the root states -- is taken over group by
+// group through the flags it stamps with this launch's sequence number.
+//   every env (lanes = envs, one warp per 32 consecutive envs; every access to the [R,N] episode-sum rows and the
+//   [term][N] value table is a coalesced 128 B row segment, all of a lane's loads are issued before the first is
+//   used):  r = value * scale, sum += r, reward += r in the reference's order; only_positive clip; termination term;
+//   statistics of the reset envs by red.global.add
+//   reset envs (lanes = scan points; the step kernel listed them in the workspace, warp w takes entries w, w + W,
+//   ... so no warp meets more than one): the scan columns are rewritten with the root z after the reset (:227;
+//   indices, heights and noise are what the scan kernel computed) and the new root state (_reset_root_states,
+//   :414-434), held back in the side buffer while the scan kernel was reading poses, is stored
+#define FIN_THREADS 128
+__device__ __forceinline__ void wait_scan_flag(const StepArgs& a, LgkWorkspace* ws, const unsigned* f, unsigned stamp) {
+  // Bounded (~0.3 s): a hand-over that never comes -- it cannot, the scan grid was resident before the step kernel
+  // even started -- must fail the step's results, not hang the GPU; the header counts such give-ups
+  unsigned polls = 0;
+  while (flag_acquire(f) != stamp) {
+    if (++polls > (1u << 22)) { atomicAdd(&ws->scan_timeouts, 1u); break; }
+    __nanosleep(40);
+  }
+}
+template <bool TAPS, bool MUL_RCP, int NP>
+__global__ void __launch_bounds__(FIN_THREADS) lgk_finish_kernel(const __grid_constant__ StepArgs a) {
+  pdl_launch_dependents();   // the epilogue's CTA may take its slot; it waits for this grid to complete
+  const LgkConsts& c = a.c;
+  const LgkBuffers& b = a.b;
+  const int N = c.num_envs;
+  const int lane = threadIdx.x & 31;
+  const int env = blockIdx.x * FIN_THREADS + threadIdx.x;
+  const int wenv0 = env - lane;
+  const int ne = min(32, N - wenv0);   // <= 0: this warp only helps with the reset envs
+  const bool active = lane < ne;
+  const unsigned flags = c.flags;
+  const int nrew = c.num_rewards;
+  const bool has_term = flags & LGK_F_HAS_TERMINATION;
+  pdl_wait();
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  const unsigned long long csc = ws->step_counter + 1ull;
+  const unsigned stamp = ws->launch_seq + 1u;
+  const int parity = (int)(csc & 1ull);
+  const int n_reset = ws->reset_count[parity];
+#ifdef LGK_BOUNDS
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+    printf("[lgk bounds] finish: N %d nrew %d has_term %d n_reset %d epc %d tiles %d rv_pitch %d scan_first %d bh %d\n", N, nrew,
+           (int)has_term, n_reset, a.scan_epc, a.scan_tiles, a.rv_pitch, a.scan_first, a.bh_active);
+#endif
+
+  // ---- every load of this lane's env, issued together -------------------------------------------------------
+  float sv[LGK_MAX_REWARDS], vv[LGK_MAX_REWARDS];
+  bool reset = false, time_out = false;
+  float bh = 0.f;
+  const size_t NP_ = (size_t)a.rv_pitch;
+  if (active) {
+    reset = b.reset_buf[env] != 0;
+    time_out = b.time_out_buf[env] != 0;
+    const float* rvg = a.rv + env;
+    const float* gs = b.episode_sums + env;
+    int xi = 0;
+#pragma unroll
+    for (int r = 0; r < LGK_MAX_REWARDS; ++r) {
+      sv[r] = 0.f; vv[r] = 0.f;
+      if (r < nrew + (has_term ? 1 : 0)) sv[r] = gs[(size_t)r * N];
+      if (r < nrew) {
+        const int term = c.rewards[r].term;
+        if (term == LGK_REW_EXTERNAL) { vv[r] = b.ext_rewards[(size_t)xi * N + env]; ++xi; }   // a python _reward_<name>
+        else vv[r] = rvg[(size_t)term * NP_];        // (base_height: the root z before any reset)
+      }
+    }
+  }
+  if (a.scan_first && a.bh_active && ne > 0) {
+    // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height); the height sums of this
+    // warp's envs are out once every scan group overlapping them has been handed over (one lane per flag)
+    const int f0 = wenv0 / a.scan_epc, f1 = (wenv0 + ne - 1) / a.scan_epc;
+    if (f0 + lane <= f1) wait_scan_flag(a, ws, a.scan_flags + f0 + lane, stamp);
+    __syncwarp();
+    if (active) bh = a.hsum[env] / (float)c.num_height_points;
+  }
+  if (active) {
+    float rew = 0.f;
+    float* gsum = b.episode_sums + env;
+    float* stat = ws->stats[parity];
+#pragma unroll
+    for (int r = 0; r < LGK_MAX_REWARDS; ++r) {
+      if (r < nrew) {
+        float v = vv[r];
+        if (c.rewards[r].term == LGK_REW_BASE_HEIGHT) { const float d = (v - bh) - c.base_height_target; v = d * d; }
+        const float rr = mul_rn(v, c.rewards[r].scale);
+        const float total = add_rn(sv[r], rr);
+        rew = add_rn(rew, rr);
+        gsum[(size_t)r * N] = reset ? 0.f : total;   // zeroed for reset envs after the statistics read it (:184-185)
+        if (reset) atomicAdd(stat + r, total);
+      }
+    }
+    if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
+    if (has_term) {   // added after the positive clip (:206-212)
+      float total = 0.f;
+      const float rr = mul_rn((reset && !time_out) ? 1.f : 0.f, c.termination_scale);
+#pragma unroll
+      for (int r = 0; r < LGK_MAX_REWARDS; ++r) if (r == nrew) total = add_rn(sv[r], rr);
+      rew = add_rn(rew, rr);
+      gsum[(size_t)nrew * N] = reset ? 0.f : total;
+      if (reset) atomicAdd(stat + nrew, total);
+    }
+    b.rew_buf[env] = rew;
+  }
+
+  // ---- the envs reset this step, dealt over the warps of the grid ---------------------------------------------
+  const int gw = (int)(blockIdx.x * (FIN_THREADS / 32) + (threadIdx.x >> 5)), nw = (int)(gridDim.x * (FIN_THREADS / 32));
+#pragma unroll 1
+  for (int i = gw; i < n_reset; i += nw) {
+    const int e = a.fix_list[i];
+#ifdef LGK_BOUNDS
+    if (i < 0 || i >= N || e < 0 || e >= N) {
+      if (lane == 0) printf("[lgk bounds] finish: fix_list[%d] = %d, n_reset %d, N %d, parity %d\n", i, e, n_reset, N, parity);
+      return;
+    }
+#endif
+    const float* side = a.side + (size_t)e * LGK_SIDE_FLOATS;
+    if (a.scan_first) {
+      if (lane == 0) wait_scan_flag(a, ws, a.scan_flags + e / a.scan_epc, stamp);
+      __syncwarp();
+      lgk_scan_fixup_env<TAPS, MUL_RCP, NP>(a, side, e, csc);
+    }
+    if (lane < 13) b.root_states[(size_t)e * 13 + lane] = side[8 + lane];   // the row the step kernel held back
+  }
 }
 // ---------------------------------------------------------------------------------------------
 static inline int up4(int x) { return (x + 3) & ~3; }
@@ -992,6 +1083,21 @@ __global__ void lgk_pre_reward_kernel(const __grid_constant__ StepArgs a, int mu
   b.reset_buf[env] = (term || time_out) ? 1 : 0;
 }
 
+// lgk_set_step_counter: the header starts over (both parities' accumulators, tickets) with the given counter; the
+// launch sequence number stays -- scan flags stamped by earlier launches must never match a later one
+__global__ void lgk_set_counter_kernel(LgkWorkspace* ws, unsigned long long value) {
+  const unsigned seq = ws->launch_seq;
+  unsigned* w = reinterpret_cast<unsigned*>(ws);
+  __syncthreads();
+  for (int i = threadIdx.x; i < (int)(sizeof(LgkWorkspace) / 4); i += blockDim.x) w[i] = 0u;
+  __syncthreads();
+  if (threadIdx.x == 0) { ws->step_counter = value; ws->launch_seq = seq; }
+}
+extern "C" int lgk_set_step_counter_impl(void* workspace, long long value, cudaStream_t stream) {
+  lgk_set_counter_kernel<<<1, 128, 0, stream>>>(reinterpret_cast<LgkWorkspace*>(workspace), (unsigned long long)value);
+  return (int)cudaGetLastError();
+}
+
 static void fill_rng_and_thresholds(StepArgs& args, const LgkConsts* c) {
   for (int r = 0; r < 10; ++r) {
     args.pk[2 * r] = (unsigned)c->seed + (unsigned)r * 0x9E3779B9u;
@@ -1042,8 +1148,27 @@ static int launch_step(const StepArgs& args, int dev, int grid, size_t smem, cud
     LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured[dev] = smem;
   }
+  static const bool dbg = [] { const char* e = getenv("LGK_DEBUG_SYNC"); return e && e[0] == '1'; }();
+  auto dbg_sync = [&](const char* what) {   // development: name the launch a fault belongs to
+    if (!dbg) return;
+    const cudaError_t e = cudaStreamSynchronize(stream);
+    fprintf(stderr, "[lgk] %s: %s\n", what, cudaGetErrorString(e));
+  };
+  dbg_sync("before post_physics_step");
   if (args.scan_first) { const int rc = lgk_scan_launch(args, stream); if (rc) return rc; }
+  dbg_sync("scan kernel");
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(kern, dim3(grid), dim3(LGK_CTA_THREADS), smem, stream, args));
+  dbg_sync("step kernel");
+  {
+    const dim3 fgrid((args.c.num_envs + FIN_THREADS - 1) / FIN_THREADS);
+    const int np = (args.c.num_height_points + 31) / 32;
+    cudaError_t e;
+    if (np == 6) e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 6>, fgrid, dim3(FIN_THREADS), 0, stream, args);
+    else if (np == 4) e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 4>, fgrid, dim3(FIN_THREADS), 0, stream, args);
+    else e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 0>, fgrid, dim3(FIN_THREADS), 0, stream, args);
+    LGK_CUDA_RETURN_IF(e);
+  }
+  dbg_sync("finish kernel");
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(lgk_step_epilogue_kernel, dim3(1), dim3(EPI_THREADS), 0, stream, args, grid));
   return (int)cudaGetLastError();
 }
@@ -1059,6 +1184,11 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   args.one = 1.0f;
   args.scan_first = c->num_height_points > 0 ? 1 : 0;
   args.hsum = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_hsum_offset(c->num_envs));
+  args.scan_flags = reinterpret_cast<unsigned*>(static_cast<char*>(b->workspace) + lgk_ws_flags_offset(c->num_envs));
+  args.rv = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_rv_offset(c->num_envs));
+  args.rv_pitch = lgk_ws_rv_pitch(c->num_envs);
+  args.side = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_side_offset(c->num_envs));
+  args.fix_list = reinterpret_cast<int*>(static_cast<char*>(b->workspace) + lgk_ws_fix_offset(c->num_envs));
   fill_rng_and_thresholds(args, c);
   args.hip_mask = 0u;
   for (int h = 0; h < c->num_hip; ++h) args.hip_mask |= 1u << c->hip_idx[h];
@@ -1079,16 +1209,11 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   L.fat = o;  o += up4(TILE * (F > 0 ? F : 1));
   L.ep = o;   o += TILE * 2;
   L.lvl = o;  o += TILE * 2;
-  // contact rows; after the barrier the table of term values [LGK_REW_COUNT + 1][TILE] of stage 3
-  {
-    const int rv = (LGK_REW_COUNT + 1) * TILE;
-    L.cf = o; L.rv = o; o += up4(TILE * B3 > rv ? TILE * B3 : rv);
-  }
+  L.cf = o;   o += up4(TILE * B3);
   L.tq = o;   o += up4(TILE * D);
   L.lact = o; o += up4(TILE * D);
-  L.sums = o; o += TILE * (args.num_rows > 0 ? args.num_rows : 1);   // episode-sum rows [num_rows][TILE]
   L.head = o; o += up4(TILE * args.head_stride);
-  L.scr = o;  o += TILE * (SC_FIELDS + 8);
+  L.scr = o;  o += TILE * SC_FIELDS;
   L.total = o;
   const size_t smem = (size_t)L.total * sizeof(float);
   if (smem > 200 * 1024) return LGK_ERR_DIM;
@@ -1138,11 +1263,21 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     grid = args.n_big + (rest > 0 ? (rest + args.per_small - 1) / args.per_small : 0);
   }
   args.max_sub = (args.per + TILE - 1) / TILE;
-  // scan kernel: 32 envs per CTA when that fills the GPU several times over, fewer otherwise
+  // scan kernel: a persistent grid, resident at once; its warps walk groups of 8 envs (fewer when that would not
+  // give every warp a group)
   {
-    int epc = TILE;
-    while (epc > 4 && (c->num_envs + epc - 1) / epc < num_sms * LGK_SCAN_CTAS_PER_SM) epc >>= 1;
-    args.scan_epc = epc;
+    static const int scan_per_sm = [] {
+      const char* e = getenv("LGK_SCAN_CTAS");
+      const int v = e ? atoi(e) : 0;
+      return (v >= 1 && v <= LGK_SCAN_REG_CTAS) ? v : LGK_SCAN_CTAS_PER_SM;
+    }();
+    const int cap = num_sms * scan_per_sm;
+    int epg = SCAN_GROUP;
+    while (epg > 1 && (c->num_envs + epg - 1) / epg < cap * LGK_WARPS_PER_CTA) epg >>= 1;
+    args.scan_epc = epg;
+    args.scan_tiles = (c->num_envs + epg - 1) / epg;
+    const int ctas = (args.scan_tiles + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA;
+    args.scan_grid = ctas < cap ? ctas : cap;
   }
   const bool taps = c->rng_mode == LGK_RNG_TAPS;
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;

@@ -8,11 +8,14 @@
 #include "lgk_common.cuh"
 
 #define TILE 32
-#define LGK_SCAN_CTAS_PER_SM 8   // scan kernel: register cap 64, eight 128-thread CTAs per SM
+#define LGK_SCAN_REG_CTAS 8      // scan kernel: register cap 64 (eight 128-thread CTAs per SM would fit)
+#define LGK_SCAN_CTAS_PER_SM 8   // ... and that many are launched per SM (LGK_SCAN_CTAS in the environment: fewer, to
+                                 // leave room for step CTAs from the start -- measured slower)
 #define RS (TILE + 1)   // row stride of [row][env] tables: conflict-free by row and by env
+#define SCAN_GROUP 8    // envs a scan warp takes per group (one hand-over flag per group)
 
 struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
-  int root, dof, act, ldv, cmd, fat, ep, lvl, cf, tq, lact, sums, head, scr, rv, total;
+  int root, dof, act, ldv, cmd, fat, ep, lvl, cf, tq, lact, head, scr, total;
 };
 
 #define LGK_LD_ARRAYS 11
@@ -30,9 +33,17 @@ struct StepArgs {
   int tma_ok;        // every tiled array 16-byte aligned and N % 4 == 0
   int num_rows;      // episode_sums rows: num_rewards (+1 with termination)
   int scan_first;    // lgk_scan_kernel was launched ahead of the step kernel (num_height_points > 0)
-  int scan_epc;      // envs per CTA of the scan kernel (multiple of 4, <= 32)
+  int scan_epc;      // envs per group of the scan kernel (1, 2, 4 or 8)
   float one;         // 1.0f the compiler cannot see: blocks ptxas' contraction of mul.rn.f32x2 + add.rn.f32x2
   float* hsum;       // [N] sum over the scan points of the measured heights (workspace), scan -> step kernel
+  unsigned* scan_flags;   // [ceil(N / scan_epc)] (workspace): launch_seq + 1 once the scan group's columns and sums are out
+  int scan_tiles;    // scan groups of this launch = ceil(N / scan_epc); the scan grid's warps walk them persistently
+  int scan_grid;     // CTAs of the scan kernel: all resident at once
+  float* rv;         // [LGK_REW_COUNT][rv_pitch] (workspace): value of every reward term by env, step -> finish kernel
+  int rv_pitch;      // floats per row of rv (N rounded up to 32)
+  int* fix_list;     // [N] (workspace): the envs reset this step, in any order (reset_count of the step parity entries)
+  float* side;       // [N][LGK_SIDE_FLOATS] (workspace): rows of the envs reset this step -- 8 scan operands with the new
+                     // root z, then the 13 floats of the new root state -- step -> finish kernel
   unsigned pk[20];   // Philox4x32-10 round keys of c.seed
   // bulk-load table: lane i of W0 copies input array i of a sub-tile (source base, offset into shared
   // memory in floats, bytes per env); src == nullptr: nothing to copy
@@ -48,6 +59,26 @@ struct StepArgs {
 // where the scan sums live in the caller's workspace: behind the header and the two bitmask arrays
 __host__ __device__ inline size_t lgk_ws_hsum_offset(int num_envs) {
   return ((size_t)LGK_WS_HEADER_BYTES + 2u * (size_t)lgk_max_warps(num_envs) * sizeof(unsigned) + 15u) & ~(size_t)15u;
+}
+// ... and behind them one flag per scan group (groups of >= 1 env)
+__host__ __device__ inline size_t lgk_ws_flags_offset(int num_envs) {
+  return (lgk_ws_hsum_offset(num_envs) + 4u * (size_t)num_envs + 15u) & ~(size_t)15u;
+}
+// ... the [term][N] table of reward-term values and the side rows of reset envs (step kernel -> finish kernel)
+#define LGK_SIDE_FLOATS 24
+__host__ __device__ inline int lgk_ws_rv_pitch(int num_envs) { return (num_envs + 31) & ~31; }
+__host__ __device__ inline size_t lgk_ws_rv_offset(int num_envs) {
+  return (lgk_ws_flags_offset(num_envs) + 4u * (size_t)(num_envs + 4) + 127u) & ~(size_t)127u;
+}
+__host__ __device__ inline size_t lgk_ws_side_offset(int num_envs) {
+  return lgk_ws_rv_offset(num_envs) + 4u * (size_t)LGK_REW_COUNT * (size_t)lgk_ws_rv_pitch(num_envs);
+}
+// ... and the list of the envs reset this step (any order), filled by the step kernel for the finish kernel
+__host__ __device__ inline size_t lgk_ws_fix_offset(int num_envs) {
+  return lgk_ws_side_offset(num_envs) + 4u * (size_t)LGK_SIDE_FLOATS * (size_t)num_envs;
+}
+__host__ __device__ inline size_t lgk_ws_total_bytes(int num_envs) {
+  return lgk_ws_fix_offset(num_envs) + 4u * (size_t)num_envs;
 }
 
 // ---- the height scan of one env, lanes = scan points (legged_robot.py:818-854) ----------------------------
@@ -188,36 +219,50 @@ __device__ __forceinline__ float scan_passes(const StepArgs& a, const ScanEnv& e
 // launches lgk_scan_kernel for args.c.num_envs envs (lgk_scan.cu)
 int lgk_scan_launch(const StepArgs& args, cudaStream_t stream);
 
-// The scan columns of one env by one warp, rolled and out of line: the step kernel's fix-up for the envs it has
-// just reset (their observation uses the new root z, :227; everything else -- indices, heights, noise -- is what
-// the scan kernel computed).  sc: the env's 8 operands in shared memory (k_t, k_c, r2, yw, zo).
-template <bool TAPS, bool MUL_RCP>
-static __device__ __noinline__ void lgk_scan_fixup_env(const StepArgs& a, const float* sc, int env,
+// The scan columns of one env by one warp: the finish kernel's fix-up for the envs reset this step (their
+// observation uses the new root z, :227; everything else -- indices, heights, noise -- is what the scan kernel
+// computed).  sc: the env's 8 operands (k_t, k_c, r2, yw, zo).  NP = ceil(H / 32) for the specialised widths (every
+// gather of the env in flight together, like the scan kernel), 0 = any H, pass by pass.
+template <bool TAPS, bool MUL_RCP, int NP>
+static __device__ __forceinline__ void lgk_scan_fixup_env(const StepArgs& a, const float* sc, int env,
                                                        unsigned long long csc) {
   const LgkConsts& c = a.c;
   const int lane = threadIdx.x & 31;
   const int H = c.num_height_points, OH = 12 + 3 * c.num_dof;
   ScanEnv e;
-  e.k_t = make_float2(sc[0], sc[1]);
-  e.k_c = make_float2(sc[2], sc[3]);
-  e.r2 = make_float2(sc[4], sc[5]);
-  e.yw = sc[6];
-  e.zo = sc[7];
+  {
+    const float4 ea = reinterpret_cast<const float4*>(sc)[0], eb = reinterpret_cast<const float4*>(sc)[1];
+    e.k_t = make_float2(ea.x, ea.y);
+    e.k_c = make_float2(ea.z, ea.w);
+    e.r2 = make_float2(eb.x, eb.y);
+    e.yw = eb.z;
+    e.zo = eb.w;
+  }
   float* orow = a.b.obs_buf + (size_t)env * c.num_obs + OH;
   const bool noise = c.flags & LGK_F_ADD_NOISE;
   const float* trow = (TAPS && noise) ? a.b.tap_noise + (size_t)env * c.num_obs + OH : nullptr;
-  const int np = (H + 31) / 32;
-  uint4 rnd = make_uint4(0, 0, 0, 0);
+  const unsigned eg = (unsigned)(c.env_id_offset + env);
+  if constexpr (NP > 0) {
+    ScanLane ln[NP];
+#pragma unroll
+    for (int it = 0; it < NP; ++it) ln[it] = scan_lane_consts<TAPS>(a, it * 32 + lane, OH);
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+    if (!TAPS && noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE_SCAN + lane);
+    (void)scan_passes<TAPS, MUL_RCP, NP, true>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
+  } else {
+    const int np = (H + 31) / 32;
+    uint4 rnd = make_uint4(0, 0, 0, 0);
 #pragma unroll 1
-  for (int it = 0; it < np; ++it) {
-    if (!TAPS && noise && (it & 7) == 0)
-      rnd = philox_keyed(a.pk, csc, (unsigned)(c.env_id_offset + env), LGK_SITE_NOISE_SCAN + 32u * (unsigned)(it >> 3) + lane);
-    ScanLane ln[1];
-    ln[0] = scan_lane_consts<TAPS>(a, it * 32 + lane, OH);
-    // field (it & 7) of the block: rotate it into the position pass 0 reads
-    const int f = it & 7;
-    const unsigned w = (f >> 1) == 0 ? rnd.x : (f >> 1) == 1 ? rnd.y : (f >> 1) == 2 ? rnd.z : rnd.w;
-    const uint4 r1 = make_uint4((f & 1) ? (w >> 16) : w, 0, 0, 0);
-    (void)scan_passes<TAPS, MUL_RCP, 1, true>(a, e, ln, it, lane, r1, orow, trow, nullptr, true);
+    for (int it = 0; it < np; ++it) {
+      if (!TAPS && noise && (it & 7) == 0)
+        rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE_SCAN + 32u * (unsigned)(it >> 3) + lane);
+      ScanLane ln[1];
+      ln[0] = scan_lane_consts<TAPS>(a, it * 32 + lane, OH);
+      // field (it & 7) of the block: rotate it into the position pass 0 reads
+      const int f = it & 7;
+      const unsigned w = (f >> 1) == 0 ? rnd.x : (f >> 1) == 1 ? rnd.y : (f >> 1) == 2 ? rnd.z : rnd.w;
+      const uint4 r1 = make_uint4((f & 1) ? (w >> 16) : w, 0, 0, 0);
+      (void)scan_passes<TAPS, MUL_RCP, 1, true>(a, e, ln, it, lane, r1, orow, trow, nullptr, true);
+    }
   }
 }

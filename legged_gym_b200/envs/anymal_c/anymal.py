@@ -71,6 +71,9 @@ class Anymal(LeggedRobot):
             self._sea_weights = pack_lstm_weights(self.actuator_state_dict)
 
     def _load_actuator_state_dict(self):
+        sd = getattr(self.cfg.control, "actuator_net_state_dict", None)
+        if sd is not None:       # weights handed over in memory (e.g. the shipped checkpoint as fixture arrays)
+            return {k: torch.as_tensor(v) for k, v in sd.items()}
         seed = getattr(self.cfg.control, "actuator_net_random_seed", None)
         if seed is not None:
             return random_lstm_state_dict(int(seed))

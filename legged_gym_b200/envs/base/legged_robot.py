@@ -559,6 +559,16 @@ class LeggedRobot(BaseTask):
                 raise NotImplementedError(
                     f"{type(self).__name__} overrides {name}(), whose body runs inside the fused step kernel; "
                     f"overriding it is not supported")
+        # reset_idx() itself may be overridden (Anymal does, anymal.py:56-60), but step() never calls it: the
+        # per-step resets run inside the fused kernel.  The override's extra part must therefore also exist as
+        # _after_fused_resets(), which step() calls with the device-side id list in self.reset_ids /
+        # self.step_counts[0]; an override without it would silently miss every in-episode reset.
+        if (getattr(type(self), "reset_idx") is not LeggedRobot.reset_idx and
+                getattr(type(self), "_after_fused_resets") is LeggedRobot._after_fused_resets):
+            raise NotImplementedError(
+                f"{type(self).__name__} overrides reset_idx() without _after_fused_resets(): step() resets envs "
+                f"inside the fused kernel and never calls reset_idx(); put the override's extra per-env clean-up "
+                f"into _after_fused_resets() as well (ids: self.reset_ids[:self.step_counts[0]], on the device)")
 
     # ------------------------------------------------------------------ terrain / envs
     def _create_ground_plane(self):

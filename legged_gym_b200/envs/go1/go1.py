@@ -64,6 +64,9 @@ class Go1(LeggedRobot):
                     P(self.actuator_weights), P(self._act_norm), P(self.dVel), _lgk.current_stream(self.device)))
 
     def _load_actuator_weights(self) -> torch.Tensor:
+        sd = getattr(self.cfg.control, "actuator_net_state_dict", None)
+        if sd is not None:       # weights handed over in memory (e.g. the shipped checkpoint as fixture arrays)
+            return pack_mlp_weights({k: torch.as_tensor(v) for k, v in sd.items()})
         seed = getattr(self.cfg.control, "actuator_net_random_seed", None)
         if seed is not None:
             return pack_mlp_weights(random_mlp_state_dict(int(seed)))
@@ -78,9 +81,6 @@ class Go1(LeggedRobot):
                 f"cfg.control.actuator_net_random_seed for synthetic weights)")
         module = torch.jit.load(path, map_location="cpu")
         return pack_mlp_weights(module.state_dict())
-
-    def reset_idx(self, env_ids):
-        super().reset_idx(env_ids)
 
     def _init_buffers(self):
         super()._init_buffers()

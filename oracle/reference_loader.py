@@ -15,13 +15,37 @@ import sys
 
 import torch
 
-REFERENCE_ROOT = os.environ.get("LEGGED_GYM_REFERENCE", "/root/reference")
-_SHIM = os.path.join(os.path.dirname(os.path.abspath(__file__)), "refshim")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SHIM = os.path.join(_HERE, "refshim")
+STAGED_ROOT = os.path.join(_HERE, "_ref")      # oracle/make_ref.sh: unmodified copy that travels to the GPU box
 _loaded = None
 
 
+def _has_reference(root) -> bool:
+    return os.path.isfile(os.path.join(root, "legged_gym", "envs", "base", "legged_robot.py"))
+
+
+def _find_root() -> str:
+    """LEGGED_GYM_REFERENCE if set, else /root/reference (build container), else the staged copy oracle/_ref."""
+    env = os.environ.get("LEGGED_GYM_REFERENCE")
+    if env:
+        return env
+    for root in ("/root/reference", STAGED_ROOT):
+        if _has_reference(root):
+            return root
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
+
+
 def reference_available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "legged_gym", "envs", "base", "legged_robot.py"))
+    return _has_reference(REFERENCE_ROOT)
+
+
+def reference_kind() -> str:
+    """where the imported reference lives: 'source tree' (/root/reference) or 'staged copy' (oracle/_ref)"""
+    return "staged copy oracle/_ref" if os.path.abspath(REFERENCE_ROOT) == os.path.abspath(STAGED_ROOT) else REFERENCE_ROOT
 
 
 def load_reference():

@@ -233,6 +233,11 @@ def sea_setup(g, device):
     return sd, atol
 
 
+def sea_atol_of(sd):
+    """torque floor of an LSTM actuator net: 1e-6 of out_scale * (|b| + sum |w_k|) (see sea_setup)"""
+    return 0.1 * RTOL * float(sd["out_scale"].abs().max() * (sd["linear.bias"].abs().sum() + sd["linear.weight"].abs().sum()))
+
+
 def assert_close_abs(name, got, want, atol):
     """1e-5 relative plus an absolute floor `atol` (scalar, or a tensor broadcast over the last dimension)."""
     a, b = got.detach().cpu().double(), want.detach().cpu().double()

@@ -190,3 +190,21 @@ def test_privileged_observations_buffer_like_the_reference():
     assert env.num_privileged_obs == 17 and env.get_privileged_observations() is env.privileged_obs_buf
     assert env.privileged_obs_buf.shape == (6, 17) and float(env.privileged_obs_buf.abs().sum()) == 0.0
     assert helpers.make_env("go1_flat", 6).get_privileged_observations() is None
+
+
+def test_reset_idx_override_without_the_fused_hook_fails_at_construction():
+    """step() resets inside the fused kernel and never calls reset_idx(): an override that clears extra per-env
+    state must come with _after_fused_resets(), or construction fails."""
+    import helpers
+    from legged_gym_b200.envs.base.legged_robot import LeggedRobot
+
+    class Bad(LeggedRobot):
+        def reset_idx(self, env_ids):
+            super().reset_idx(env_ids)
+
+    class Good(Bad):
+        def _after_fused_resets(self):
+            pass
+    with pytest.raises(NotImplementedError, match="_after_fused_resets"):
+        helpers.make_env("go1_flat", 8, device="cpu", task_class=Bad)
+    helpers.make_env("go1_flat", 8, device="cpu", task_class=Good)

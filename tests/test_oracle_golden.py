@@ -60,3 +60,46 @@ def test_golden_fixtures_cover_the_edge_cases():
     # heights are int16 * 0.005f
     mh = g["out_measured_heights"][0]
     assert mh.shape == (64, 187) and (mh != 0).any()
+
+
+# ---- the actuator-net checkpoints the reference ships (as fixture arrays), and what the reference computes with them
+def _shipped():
+    import numpy as np
+    import os
+    d = np.load(os.path.join(helpers.GOLDEN_DIR, "shipped_actuator_nets.npz"))
+    return {k: d[k] for k in d.files}
+
+
+def test_go1_actuator_oracle_on_the_shipped_checkpoint():
+    """go1_net.pt (go1.py:45-47): ActuatorOracle with the shipped weights against the reference's own
+    Go1.actuator_advance outputs, bit for bit (same torch CPU kernels, same order)."""
+    from oracle import legged_oracle as lo
+    g = _shipped()
+    sd = {k[4:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("go1.")}
+    K, N = g["go1_in_actions"].shape[:2]
+    act = lo.ActuatorOracle(N, sd)
+    for k in range(K):
+        ds = torch.from_numpy(g["go1_in_dof_state"][k])
+        dv = act.advance(torch.from_numpy(g["go1_in_actions"][k]), ds[..., 0], ds[..., 1])
+        assert torch.equal(dv, torch.from_numpy(g["go1_out_dvel"][k])), f"substep {k}"
+    assert torch.equal(act.model_ins, torch.from_numpy(g["go1_out_model_ins"]))
+
+
+def test_anymal_lstm_oracle_on_the_shipped_checkpoint():
+    """anydrive_v3_lstm.pt (anymal.py:53-54): SeaLstmOracle's written-out cell, free-running, against the reference's
+    Anymal._compute_torques (aten::lstm orders the gate sums differently: a few ulp on the state, 1e-6 of the
+    output layer's operand magnitude on the torques)."""
+    from oracle import legged_oracle as lo
+    g = _shipped()
+    sd = {k[7:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("anymal.")}
+    K, N = g["sea_in_actions"].shape[:2]
+    sea = lo.SeaLstmOracle(N, 12, sd)
+    env = helpers.make_env("anymal_c_flat", N, device="cpu")
+    p = lo.OracleParams.from_env(env, device="cpu")
+    atol = helpers.sea_atol_of(sd)
+    for k in range(K):
+        ds = torch.from_numpy(g["sea_in_dof_state"][k])
+        tq = sea.compute_torques(torch.from_numpy(g["sea_in_actions"][k]), p.action_scale, p.default_dof_pos, ds[..., 0], ds[..., 1])
+        helpers.assert_close_abs(f"sea torques[{k}]", tq, torch.from_numpy(g["sea_out_torques"][k]), atol)
+        assert float((sea.sea_hidden_state - torch.from_numpy(g["sea_out_hidden"][k])).abs().max()) < 2e-6
+        assert float((sea.sea_cell_state - torch.from_numpy(g["sea_out_cell"][k])).abs().max()) < 2e-6
