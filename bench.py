@@ -282,8 +282,13 @@ def run_ours(args):
 
     # ---- CPU baseline (rank 0, single-GPU runs only) ------------------------------------------------
     cpu = None
+    torch_cuda = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_reference(args.envs, budget_s=args.cpu_budget)
+        try:
+            torch_cuda = torch_cuda_competitor(args.envs, device)
+        except Exception as exc:   # noqa: BLE001
+            torch_cuda = {"unavailable": f"{type(exc).__name__}: {exc}"[:200]}
 
     if rank == 0:
         line = {
@@ -293,7 +298,7 @@ def run_ours(args):
             "config": config_dict(N, world, env.cfg.control.decimation, env.num_obs, env._num_sum_rows),
             "collectives_in_timed_region": collectives_timed, "stats_allreduce_interval": stats_interval if world > 1 else None,
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "launches_per_step": int(launches_per_step),
-            "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(),
+            "roofline": roofline, "cpu_baseline": cpu, "torch_cuda": torch_cuda, "clocks": clocks.summary(),
         }
         print(json.dumps(line))
     if world > 1:
@@ -389,15 +394,106 @@ def run_e2e(env, frames, args, world, device, stream):
         e1.record(stream)
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
+    # where the time goes: each leg alone (events, 10 repetitions), this rank
+    def leg(fn):
+        with torch.cuda.stream(stream):
+            fn(); stream.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(stream)
+            for _ in range(10):
+                fn()
+            a1.record(stream)
+            stream.synchronize()
+        return a0.elapsed_time(a1) / 10
+
+    def leg_h2d():
+        for k in names:
+            dev[0][k].copy_(host[0][k], non_blocking=True)
+
+    def leg_d2h():
+        out_h["obs"].copy_(env.obs_buf, non_blocking=True)
+        out_h["rew"].copy_(env.rew_buf, non_blocking=True)
+        out_h["reset"].copy_(env.reset_buf, non_blocking=True)
+
+    def leg_step():
+        env.step(dev[0]["actions"])
+    t_h2d, t_d2h, t_step = leg(leg_h2d), leg(leg_d2h), leg(leg_step)
+    breakdown = {"h2d_ms": round(t_h2d, 4), "h2d_gbs": round(h2d / t_h2d / 1e6, 1), "step_kernels_ms": round(t_step, 4),
+                 "d2h_ms": round(t_d2h, 4), "d2h_gbs": round(d2h / t_d2h / 1e6, 1),
+                 "sync_and_launch_ms": round(max(ms / steps - t_step - t_d2h, 0.0), 4),
+                 "note": "per step the chain is actions H2D -> kernels -> D2H -> host sync; the simulator-state H2D of the "
+                         "next step runs on a second stream under this step's D2H.  The limiter is the D2H of the "
+                         "observation rows over PCIe"}
     if world > 1:
         import torch.distributed as dist
         t = torch.tensor([ms], device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     return {"value": round(N * world * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-            "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": round(ms / steps, 5),
+            "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": round(ms / steps, 5), "breakdown": breakdown,
             "path": "pinned host buffers -> LeggedRobot.step() -> pinned host buffers, stream-synchronised every step; "
                     "next step's simulator state is copied in (second stream) while this step's results are copied out"}
+
+
+def torch_cuda_competitor(envs, device):
+    """The "same box" competitor: the reference's own op-by-op torch
+    implementation of the path run on the GPU -- the unmodified reference over the simulator stand-in when it is here
+    (oracle/_ref), else the oracle port of it -- timed with CUDA events, median of a few steps."""
+    from legged_gym_b200.utils import scenarios, synthetic
+    from oracle import reference_loader
+    n, steps, warm = envs, 12, 4
+    out = {"envs": n, "torch": torch.__version__}
+    try:
+        if not reference_loader.reference_available():
+            raise RuntimeError("reference not staged (oracle/_ref)")
+        task, mutate = scenarios.SCENARIOS[SCENARIO]
+        env = reference_loader.make_reference_env(task, mutate, num_envs=n, device=device, seed=1)
+        g = torch.Generator().manual_seed(99)
+        env.episode_length_buf[:] = torch.randint(0, int(env.max_episode_length), (n,), generator=g).to(device)
+        frames = [{k: v.to(device) for k, v in fr.items()} for fr in synthetic.make_frames(env, 2, seed=3234)]
+
+        def one(i):
+            synthetic.load_frame(env, frames[i % 2])
+            a = frames[i % 2]["actions"].clone()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            env.step(a)
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1)
+        out["kind"] = f"the reference's own LeggedRobot.step() on CUDA torch ({reference_loader.reference_kind()})"
+    except Exception as exc:   # noqa: BLE001  (fall back to the port; say why)
+        import helpers
+        from oracle import legged_oracle as lo
+        out["reference_on_cuda_failed"] = f"{type(exc).__name__}: {exc}"[:200]
+        envc = helpers.make_env(SCENARIO, n, device="cpu", seed=1)
+        g = torch.Generator().manual_seed(99)
+        envc.episode_length_buf = torch.randint(0, int(envc.max_episode_length), (n,), generator=g)
+        p = lo.OracleParams.from_env(envc, device=device)
+        s = lo.OracleState.from_env(envc, p, device=device)
+        frames = [{k: v.to(device) for k, v in fr.items()} for fr in synthetic.make_frames(envc, 2, seed=3234)]
+        taps = {k: v.to(device) for k, v in synthetic.make_taps(envc, seed=5).items()}
+
+        def one(i):
+            fr = frames[i % 2]
+            s.root_states.copy_(fr["root_states"]); s.dof_state.copy_(fr["dof_state"])
+            s.contact_forces.copy_(fr["contact_forces"].view_as(s.contact_forces)); s.torques.copy_(fr["torques"])
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            taps["noise"] = torch.rand(n, envc.num_obs, device=device)
+            lo.step(p, s, fr["actions"], taps)
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1)
+        out["kind"] = "oracle port of the reference on CUDA torch"
+    ts = sorted([one(i) for i in range(steps + warm)][warm:])
+    ms = ts[len(ts) // 2]
+    out.update(ms_per_step=round(ms, 4), value=round(n / (ms * 1e-3), 1), unit=UNIT,
+               note="median of 12 steps, CUDA events; includes the reference's own host syncs (nonzero() on the reset / "
+                    "resample id lists)")
+    return out
 
 
 def cpu_reference(envs, budget_s=20.0, steps=None, warmup=1):

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define LGK_ABI_VERSION 5
+#define LGK_ABI_VERSION 6
 
 #define LGK_MAX_DOF     16   /* num_dof = num_actions (12 for every shipped robot)        */
 #define LGK_MAX_FEET     8
@@ -113,6 +113,10 @@ enum {                                   /* LgkConsts.flags                     
   LGK_F_CALLBACK_GIVEN    = 1u << 12,    /* commands are final: a _post_physics_step_callback() override
                                             (legged_robot.py:337-352) ran after lgk_pre_reward_state did the
                                             base resample / heading update; the step kernel does not redo them */
+  LGK_F_FILTERED_CONTACTS = 1u << 13,    /* cfg.rewards.filtered_feet_contact: _reward_feet_air_time in the variant the
+                                            reference keeps commented out (legged_robot.py:928-939) -- the foot counts
+                                            as in contact if it is now OR was at the previous step (PhysX contact
+                                            reporting is unreliable on meshes); needs LgkBuffers.last_contacts */
   LGK_F_RESET_GIVEN       = 1u << 11     /* reset_buf / time_out_buf are INPUTS: a check_termination()
                                             override (legged_robot.py:143-148) decided after
                                             lgk_pre_reward_state; the step kernel acts on them as they are */
@@ -240,7 +244,11 @@ typedef struct LgkBuffers {
   const float* tap_root_vel;       /* [N,6]                                                */
   const float* tap_noise;          /* [N,O]                                                */
   const int64_t* tap_level;        /* [N] ints in [0, max_terrain_level)                   */
-  /* scratch owned by the caller, sized by lgk_workspace_bytes(), zero-initialised once */
+  uint8_t*     last_contacts;      /* [N,F] torch.bool (legged_robot.py:547): foot contact flags of the previous step; read
+                                      and rewritten only with LGK_F_FILTERED_CONTACTS (else may be NULL)          */
+  /* scratch owned by the caller, sized by lgk_workspace_bytes() (about 330 B per env: header, per-tile bitmasks,
+     height sums, hand-over flags, the [term][N] table of reward-term values, the side rows / list / episode sums of the
+     envs reset in a step), zero-initialised once, never shared between two env instances */
   void*        workspace;
 } LgkBuffers;
 
@@ -346,8 +354,9 @@ int lgk_reset_idx(const LgkConsts* c, const LgkBuffers* b, const int64_t* env_id
 /* reset_idx(arange(N)) as issued by BaseTask.reset() (base_task.py:111-115). */
 int lgk_reset_all(const LgkConsts* c, const LgkBuffers* b, void* stream);
 
-/* Sets the device copy of common_step_counter (legged_robot.py:119,527) held in the workspace;
- * the step kernel increments it itself.  Not capturable in a CUDA graph. */
+/* Sets the device copy of common_step_counter (legged_robot.py:119,527) held in the workspace; the step
+ * epilogue increments it itself.  One tiny launch on the stream: the rest of the workspace header (both parities'
+ * statistics accumulators) starts over with it, the launch sequence number behind the scan hand-over flags stays. */
 int lgk_set_step_counter(void* workspace, int64_t value, void* stream);
 
 /* Calibration probe: out[i] = (qz, qw) / norm([0,0,qz,qw]) for quat [n,4], computed exactly as the

@@ -8,7 +8,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-LGK_ABI_VERSION = 5
+LGK_ABI_VERSION = 6
 LGK_MAX_DOF = 16
 LGK_MAX_FEET = 8
 LGK_MAX_PEN = 16
@@ -48,6 +48,7 @@ F_INIT_DONE = 1 << 9
 F_EP_INCREMENTED = 1 << 10
 F_RESET_GIVEN = 1 << 11
 F_CALLBACK_GIVEN = 1 << 12
+F_FILTERED_CONTACTS = 1 << 13
 
 STATUS = {0: "LGK_OK", -1: "LGK_ERR_NULL", -2: "LGK_ERR_DIM", -3: "LGK_ERR_CONTROL_TYPE", -4: "LGK_ERR_REWARD",
           -5: "LGK_ERR_ALIGN", -6: "LGK_ERR_VERSION", -7: "LGK_ERR_TERRAIN",
@@ -102,7 +103,7 @@ BUFFER_FIELDS = [
     "measured_heights", "reset_ids", "resample_ids", "counts", "episode_stats", "extras", "ext_rewards",
     "height_min3", "height_points_xy", "noise_scale_vec", "terrain_origins", "command_ranges",
     "tap_cmd_callback", "tap_cmd_reset", "tap_push", "tap_dof", "tap_root_xy", "tap_root_vel", "tap_noise",
-    "tap_level", "workspace",
+    "tap_level", "last_contacts", "workspace",
 ]
 
 

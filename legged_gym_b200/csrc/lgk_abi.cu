@@ -71,6 +71,7 @@ static int check_step(const LgkConsts* c, const LgkBuffers* b) {
     if (c->terrain_rows < 2 || c->terrain_cols < 2 || c->terrain_pitch < c->terrain_cols || !(c->horizontal_scale > 0.f))
       return LGK_ERR_TERRAIN;
   }
+  if ((c->flags & LGK_F_FILTERED_CONTACTS) && !b->last_contacts) return LGK_ERR_NULL;
   if ((c->flags & LGK_F_TERRAIN_CURRICULUM) && (!b->terrain_levels || !b->terrain_types || !b->terrain_origins))
     return LGK_ERR_NULL;
   if (c->rng_mode == LGK_RNG_TAPS) {
@@ -201,7 +202,7 @@ int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream) {
   int rc = check_step(c, b);
   if (rc) return rc;
-  g_launches += 3 + (c->num_height_points > 0 ? 1 : 0);   // (scan kernel,) step kernel, finish kernel, epilogue
+  g_launches += 2 + (c->num_height_points > 0 ? 1 : 0);   // (scan kernel,) step kernel, finish kernel
   return lgk_post_physics_step_impl(c, b, (cudaStream_t)stream);
 }
 

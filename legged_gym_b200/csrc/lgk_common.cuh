@@ -14,6 +14,7 @@ struct LgkWorkspace {
   unsigned int done_ticket;          // CTAs finished in the current launch
   unsigned int launch_seq;           // post_physics_step launches so far (the epilogue adds 1); value of the per-tile
                                      // scan flags of the NEXT launch is launch_seq + 1.  lgk_set_step_counter keeps it
+  unsigned int fin_ticket;           // CTAs of the finish kernel that are done (the last one publishes the statistics)
   unsigned int scan_timeouts;        // step CTAs that gave up waiting for a scan tile (never, unless the launch order broke)
   int level_sum[2];                  // sum(terrain_levels) accumulators, indexed by step parity
   int reset_count[2];                // number of reset envs, indexed by step parity

@@ -43,9 +43,9 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
   const bool add_noise = c.flags & LGK_F_ADD_NOISE;
 
   __shared__ __align__(16) float s_es_all[LGK_WARPS_PER_CTA][SCAN_GROUP * 8];
-  __shared__ float s_hp_all[LGK_WARPS_PER_CTA][SCAN_GROUP * RS];
+  __shared__ int s_hp_all[LGK_WARPS_PER_CTA][SCAN_GROUP * RS];
   float* s_es = s_es_all[wic];
-  float* s_hp = s_hp_all[wic];
+  int* s_hp = s_hp_all[wic];
 
   const int epg = a.scan_epc;   // envs per group (= per flag): 8, fewer for small N
 
@@ -64,6 +64,15 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
     }
     clip_h = __any_sync(LGK_FULL_MASK, clip_h);
   }
+#ifdef LGK_SCAN_SMEM_LN
+  // experiment: the lane constants live in shared memory (one copy per CTA), not in 24 registers per thread
+  __shared__ float4 s_ln[(GENERIC ? 1 : CH) * 32];
+  if (!GENERIC && wic == 0) {
+#pragma unroll
+    for (int it = 0; it < CH; ++it) s_ln[it * 32 + lane] = make_float4(ln[it].p.x, ln[it].p.y, ln[it].ka, ln[it].kb);
+  }
+  __syncthreads();
+#endif
 
   pdl_wait();   // root_states belong to the simulator: written by whatever ran before this launch
   // The whole grid is resident: the step kernel behind this launch may take SM slots as soon as warps here retire.
@@ -103,7 +112,7 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
       const float* trow = (TAPS && add_noise) ? b.tap_noise + (size_t)env * O + OH : nullptr;
       float* mrow = b.measured_heights != nullptr ? b.measured_heights + (size_t)env * H : nullptr;
       const unsigned eg = (unsigned)(c.env_id_offset + env);
-      float hsum = 0.f;
+      int hsum = 0;
 #pragma unroll 1
       for (int ch = 0; ch < nchunks; ++ch) {
         uint4 rnd = make_uint4(0, 0, 0, 0);
@@ -112,10 +121,18 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
 #pragma unroll
           for (int it = 0; it < CH; ++it) ln[it] = scan_lane_consts<TAPS>(a, (ch * CH + it) * 32 + lane, OH);
           hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, ch * CH, lane, rnd, orow, trow, mrow, true);
-        } else if (clip_h) {
+        } else if (clip_h || mrow != nullptr) {   // (warp-uniform)
+#ifdef LGK_SCAN_SMEM_LN
+          hsum += scan_passes<TAPS, MUL_RCP, CH, true, true, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false, s_ln);
+#else
           hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
-        } else {
-          hsum += scan_passes<TAPS, MUL_RCP, CH, false>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
+#endif
+        } else {          // the common case: no final clip needed, heights not materialised
+#ifdef LGK_SCAN_SMEM_LN
+          hsum += scan_passes<TAPS, MUL_RCP, CH, false, false, true>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false, s_ln);
+#else
+          hsum += scan_passes<TAPS, MUL_RCP, CH, false, false>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
+#endif
         }
       }
       s_hp[el * RS + lane] = hsum;
@@ -124,8 +141,8 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
     // sum over the points of each env's heights: lane (q, k) adds a quarter of the partial sums of env k
     {
       const int k = lane & 7, q = lane >> 3;
-      const float* hp = s_hp + k * RS + q * 8;
-      float hs = 0.f;
+      const int* hp = s_hp + k * RS + q * 8;
+      int hs = 0;
 #pragma unroll
       for (int i = 0; i < 8; ++i) hs += hp[i];
       hs += __shfl_xor_sync(LGK_FULL_MASK, hs, 8);

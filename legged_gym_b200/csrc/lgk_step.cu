@@ -1,6 +1,6 @@
 // Step kernel of post_physics_step (sm_100a): one CTA of four warps per tile of 32 envs, lanes = envs.
 //
-// post_physics_step() (reference legged_robot.py:109-141) is four launches chained with programmatic dependent launch:
+// post_physics_step() (reference legged_robot.py:109-141) is three launches chained with programmatic dependent launch:
 //   lgk_scan_kernel    (lgk_scan.cu)  _get_heights + the scan columns of the observation row, lanes = points
 //   lgk_step_kernel    (this file)    everything per env that needs no height: episode counters, body-frame
 //                                     velocities / projected gravity, command resampling + heading command, pushes,
@@ -9,8 +9,9 @@
 //                                     the per-tile reset / resample bitmasks behind the ascending id lists
 //   lgk_finish_kernel  (this file)    lanes = envs over the [R,N] episode-sum rows: scale, in-place sums, ordered
 //                                     reward sum, statistics of the reset envs; base_height from the scan's height
-//                                     sums; the root state and the scan columns of the envs reset this step
-//   lgk_step_epilogue_kernel          one CTA: ordered compaction of the bitmasks, extras, step counter
+//                                     sums; the root state and the scan columns of the envs reset this step; one CTA
+//                                     compacts the bitmasks into the id lists, the last CTA to finish publishes
+//                                     extras and advances the step counter
 // The scan and the step kernel do not depend on each other: the step kernel neither reads heights nor writes the
 // root state (the new root row of a reset env goes to a side buffer in the workspace; the finish kernel stores it),
 // so the step CTAs start as soon as the scan's persistent CTAs begin to retire, without waiting for anything.
@@ -286,24 +287,23 @@ static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const
   for (int i = t; i < ne * D; i += nt) { la[i] = sm[a.L.act + i]; lv[i] = sm[a.L.ldv + i]; }
 }
 // ---------------------------------------------------------------------------------------------
-// Step epilogue: the two once-per-step serial jobs, as a second small launch behind the tile kernel
-// (one CTA of 1024 threads).  Being a separate launch, the kernel boundary orders it after every tile's
-// masks and statistics: the tile CTAs need no tickets, fences or polling, and the job runs on an idle GPU
-// instead of on one SM that is busy with tiles (there it took 16-20 us, most of it instruction fetch).
-//   1. ordered compaction of the per-tile reset / resample bitmasks into ascending id lists (:150, :342)
-//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119)
-#define EPI_THREADS 1024
-__global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const __grid_constant__ StepArgs a, int n_ctas) {
-  __shared__ int s_scan[2][EPI_THREADS / 32 + 1];
-  const LgkConsts& c = a.c;
+// The two once-per-step serial jobs of post_physics_step.  Both run inside the finish kernel (below), each on one CTA:
+//   1. ordered compaction of the per-tile reset / resample bitmasks into ascending id lists (:150, :342) -- needs
+//      the step kernel's masks only, so a dedicated CTA of the finish grid does it next to the reward CTAs
+//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119) -- needs every reward CTA's
+//      sums, so the CTA that finishes last does it (ticket counter in the workspace header)
+// (earlier versions: a finisher CTA inside the fused tile kernel, 16-20 us on one busy SM; then an epilogue launch of
+// its own, 7-11 us at the end of the chain with the GPU otherwise idle)
+#define FIN_THREADS 128
+#define STAT_COPIES 64   // replicated accumulator rows of the reset statistics (see lgk_finish_kernel)
+template <int THREADS>
+__device__ __forceinline__ void compact_id_lists(const StepArgs& a, int n_ctas) {
+  constexpr int NW = THREADS / 32;
+  __shared__ int s_scan[2][NW + 1];
   const LgkBuffers& b = a.b;
-  const int N = c.num_envs;
+  const int N = a.c.num_envs;
   const int tid = threadIdx.x, lane = tid & 31, wic = tid >> 5;
-  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
-  pdl_wait();   // scheduled while the tile kernel drains; from here on every tile's writes are visible
-  const unsigned long long csc = ws->step_counter + 1ull;
-  const int parity = (int)(csc & 1ull);
-  // ---- id lists --------------------------------------------------------------------------------
+  const LgkWorkspace* ws = reinterpret_cast<const LgkWorkspace*>(b.workspace);
   const int nt = n_ctas * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
   const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
   const unsigned* rm = mask_base;
@@ -320,10 +320,10 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
     const int cta = t / a.max_sub, k = t - cta * a.max_sub;
     return k * TILE < min(a.per, N - cta * a.per);
   };
-  const int per = (nt + EPI_THREADS - 1) / EPI_THREADS;   // 2 at 65536 envs
+  const int per = (nt + THREADS - 1) / THREADS;   // 16 at 65536 envs
   const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
   int c0 = 0, c1 = 0;
-#pragma unroll 4
+#pragma unroll 8
   for (int t = t0; t < t1; ++t)
     if (slot_ok(t)) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
   // block-wide exclusive scan of (c0, c1): shuffles inside a warp, warp totals through shared memory
@@ -335,17 +335,16 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
   }
   if (lane == 31) { s_scan[0][wic] = i0; s_scan[1][wic] = i1; }
   __syncthreads();
-  if (wic == 0) {   // exclusive scan of the 32 warp totals
-    int w0 = s_scan[0][lane], w1 = s_scan[1][lane];
+  if (wic == 0) {   // exclusive scan of the warp totals
+    int w0 = lane < NW ? s_scan[0][lane] : 0, w1 = lane < NW ? s_scan[1][lane] : 0;
     const int t0w = w0, t1w = w1;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
+    for (int o = 1; o < NW; o <<= 1) {
       const int y0 = __shfl_up_sync(LGK_FULL_MASK, w0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, w1, o);
       if (lane >= o) { w0 += y0; w1 += y1; }
     }
-    s_scan[0][lane] = w0 - t0w;
-    s_scan[1][lane] = w1 - t1w;
-    if (lane == 31) { s_scan[0][32] = w0; s_scan[1][32] = w1; }
+    if (lane < NW) { s_scan[0][lane] = w0 - t0w; s_scan[1][lane] = w1 - t1w; }
+    if (lane == NW - 1) { s_scan[0][NW] = w0; s_scan[1][NW] = w1; }
   }
   __syncthreads();
   int o0 = s_scan[0][wic] + i0 - c0, o1 = s_scan[1][wic] + i1 - c1;
@@ -360,21 +359,50 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
     }
   }
   if (tid == 0) {
-    b.counts[0] = s_scan[0][32];
-    b.counts[1] = s_scan[1][32];
+    b.counts[0] = s_scan[0][NW];
+    b.counts[1] = s_scan[1][NW];
   }
-  if (wic != 1) return;
-  // ---- episode statistics (one warp) ------------------------------------------------------------
+}
+
+// episode statistics of the step (the last CTA of the finish kernel to get done, all of its threads) and the
+// counters of the next step
+__device__ __forceinline__ void publish_step_statistics(const StepArgs& a, unsigned long long csc) {
+  const LgkConsts& c = a.c;
+  const LgkBuffers& b = a.b;
+  const int N = c.num_envs;
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  constexpr int NW = FIN_THREADS / 32;
+  __shared__ float s_part[NW][33];
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  const int parity = (int)(csc & 1ull);
   const int num_rows = a.num_rows;
+  // the reset envs' episode sums were added into STAT_COPIES replicated rows (spread by env, see the finish kernel):
+  // thread (row = lane, quarter = warp) adds a quarter of the copies -- independent L2 loads, all in flight -- and
+  // zeroes them for the next step
+  {
+    float* cp = a.stat_copies + (size_t)wic * (STAT_COPIES / NW) * LGK_MAX_REWARDS + lane;
+    float v[STAT_COPIES / NW];
+#pragma unroll
+    for (int k = 0; k < STAT_COPIES / NW; ++k) v[k] = __ldcg(cp + k * LGK_MAX_REWARDS);
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < STAT_COPIES / NW; ++k) { acc += v[k]; cp[k * LGK_MAX_REWARDS] = 0.f; }
+    s_part[wic][lane] = acc;
+  }
+  __syncthreads();
+  if (wic != 0) return;
   const int n_reset = ws->reset_count[parity];
   const int level_sum = ws->level_sum[parity];
   if (lane < num_rows) {
-    const float s = ws->stats[parity][lane];
+    float s = ws->stats[parity][lane];   // (+ what lgk_reset_idx calls may have left: nothing today)
+#pragma unroll
+    for (int k = 0; k < NW; ++k) s += s_part[k][lane];
     b.episode_stats[lane] = s;
     b.episode_stats[num_rows + 4 + lane] += s;   // running sums since the host last cleared them
     if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
       b.extras[lane] = (s / (float)n_reset) / c.max_episode_length_s;
-    ws->stats[parity ^ 1][lane] = 0.f;   // next step's accumulators
+    ws->stats[parity][lane] = 0.f;
+    ws->stats[parity ^ 1][lane] = 0.f;
   }
   if (lane == 0) {
     b.episode_stats[num_rows] = (float)n_reset;
@@ -387,6 +415,7 @@ __global__ void __launch_bounds__(EPI_THREADS, 1) lgk_step_epilogue_kernel(const
       b.extras[num_rows] = (float)level_sum / (float)N;   // mean(terrain_levels.float()) (:188)
     ws->level_sum[parity ^ 1] = 0;
     ws->reset_count[parity ^ 1] = 0;
+    ws->fin_ticket = 0u;
     ws->step_counter = csc;
     ws->launch_seq += 1u;
   }
@@ -620,7 +649,10 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           int base = 0;
           if (lane == 0) base = atomicAdd(&ws->reset_count[parity], nr);
           base = __shfl_sync(LGK_FULL_MASK, base, 0);
-          if (active && reset) a.fix_list[base + __popc(reset_mask & ((1u << lane) - 1u))] = env;
+          if (active && reset) {
+            const int idx = base + __popc(reset_mask & ((1u << lane) - 1u));
+            a.fix_list[idx] = env;
+          }
         }
       }
     }
@@ -769,10 +801,16 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
           }
           float t = fa_in[k];
           if (a.air_active) {   // the state only advances inside _reward_feet_air_time
-            const bool first = (t > 0.f) && contact;
+            bool on = contact;
+            if (flags & LGK_F_FILTERED_CONTACTS) {   // contact now or at the previous step (:931-933, commented upstream)
+              uint8_t* lc = b.last_contacts + (size_t)env * F + k;
+              on = contact || (*lc != 0);
+              *lc = contact ? 1 : 0;
+            }
+            const bool first = (t > 0.f) && on;
             t = add_rn(t, c.dt);
             r_air += first ? (t - 0.5f) : 0.f;
-            if (contact) t = 0.f;
+            if (on) t = 0.f;
           }
           if (a.air_active || reset) fa_out[k] = reset ? 0.f : t;   // zeroed on reset (:178)
         }
@@ -855,19 +893,24 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 #endif
 }
 // ---------------------------------------------------------------------------------------------
-// Finish kernel: compute_reward's sums (:195-212) and the tail of reset_idx for every env.
-// Launched behind the step kernel (griddepcontrol.wait: its value table, flags, fix list and side rows are complete);
-// the scan kernel's part -- height sums, scan columns, its last read of the root states -- is taken over group by
-// group through the flags it stamps with this launch's sequence number.
-//   every env (lanes = envs, one warp per 32 consecutive envs; every access to the [R,N] episode-sum rows and the
-//   [term][N] value table is a coalesced 128 B row segment, all of a lane's loads are issued before the first is
-//   used):  r = value * scale, sum += r, reward += r in the reference's order; only_positive clip; termination term;
-//   statistics of the reset envs by red.global.add
-//   reset envs (lanes = scan points; the step kernel listed them in the workspace, warp w takes entries w, w + W,
-//   ... so no warp meets more than one): the scan columns are rewritten with the root z after the reset (:227;
-//   indices, heights and noise are what the scan kernel computed) and the new root state (_reset_root_states,
-//   :414-434), held back in the side buffer while the scan kernel was reading poses, is stored
-#define FIN_THREADS 128
+// Finish kernel: compute_reward's sums (:195-212), the tail of reset_idx, the id lists and the step's statistics.
+// Launched behind the step kernel (griddepcontrol.wait: its value table, flags, masks, reset list and side rows are
+// complete); the scan kernel's part -- height sums, scan columns, its last read of the root states -- is taken over
+// group by group through the flags it stamps with this launch's sequence number.  Three kinds of CTA, by blockIdx:
+//   CTA 0          the ascending reset / resample id lists from the step kernel's per-tile bitmasks
+//   fix CTAs       the envs reset this step (lanes = scan points; warp w takes list entries w, w + W, ...): the scan
+//                  columns are rewritten with the root z after the reset (:227; indices, heights and noise are what the
+//                  scan kernel computed) and the new root state (_reset_root_states, :414-434), held back in the side
+//                  buffer while the scan kernel was reading poses, is stored.  CTAs of their own, scheduled first: the
+//                  chain list -> side row -> flag -> gathers -> stores is as long as the reward chain and runs next
+//                  to it instead of behind it
+//   reward CTAs    lanes = envs, one warp per 32 consecutive envs; every access to the [R,N] episode-sum rows and the
+//                  [term][N] value table is a coalesced 128 B row segment: r = value * scale, sum += r, reward += r in
+//                  the reference's order; only_positive clip; termination term.  Sums of reset envs go by red.global.add
+//                  into one of STAT_COPIES replicated accumulator rows picked by the env's warp (all into ONE row cost
+//                  15 us: ~12 000 red.add on a single cache line at 65 536 envs)
+// and the CTA that finishes last adds the replicated rows up into extras["episode"] and advances the step counter.
+#define LGK_FIX_CTAS_MAX 296   // at most 2 x 148 CTAs of the finish kernel work on the reset envs
 __device__ __forceinline__ void wait_scan_flag(const StepArgs& a, LgkWorkspace* ws, const unsigned* f, unsigned stamp) {
   // Bounded (~0.3 s): a hand-over that never comes -- it cannot, the scan grid was resident before the step kernel
   // even started -- must fail the step's results, not hang the GPU; the header counts such give-ups
@@ -878,101 +921,17 @@ __device__ __forceinline__ void wait_scan_flag(const StepArgs& a, LgkWorkspace* 
   }
 }
 template <bool TAPS, bool MUL_RCP, int NP>
-__global__ void __launch_bounds__(FIN_THREADS) lgk_finish_kernel(const __grid_constant__ StepArgs a) {
-  pdl_launch_dependents();   // the epilogue's CTA may take its slot; it waits for this grid to complete
-  const LgkConsts& c = a.c;
+__device__ __forceinline__ void finish_fix_cta(const StepArgs& a, int fix_ctas) {
   const LgkBuffers& b = a.b;
-  const int N = c.num_envs;
   const int lane = threadIdx.x & 31;
-  const int env = blockIdx.x * FIN_THREADS + threadIdx.x;
-  const int wenv0 = env - lane;
-  const int ne = min(32, N - wenv0);   // <= 0: this warp only helps with the reset envs
-  const bool active = lane < ne;
-  const unsigned flags = c.flags;
-  const int nrew = c.num_rewards;
-  const bool has_term = flags & LGK_F_HAS_TERMINATION;
-  pdl_wait();
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const unsigned long long csc = ws->step_counter + 1ull;
   const unsigned stamp = ws->launch_seq + 1u;
-  const int parity = (int)(csc & 1ull);
-  const int n_reset = ws->reset_count[parity];
-#ifdef LGK_BOUNDS
-  if (threadIdx.x == 0 && blockIdx.x == 0)
-    printf("[lgk bounds] finish: N %d nrew %d has_term %d n_reset %d epc %d tiles %d rv_pitch %d scan_first %d bh %d\n", N, nrew,
-           (int)has_term, n_reset, a.scan_epc, a.scan_tiles, a.rv_pitch, a.scan_first, a.bh_active);
-#endif
-
-  // ---- every load of this lane's env, issued together -------------------------------------------------------
-  float sv[LGK_MAX_REWARDS], vv[LGK_MAX_REWARDS];
-  bool reset = false, time_out = false;
-  float bh = 0.f;
-  const size_t NP_ = (size_t)a.rv_pitch;
-  if (active) {
-    reset = b.reset_buf[env] != 0;
-    time_out = b.time_out_buf[env] != 0;
-    const float* rvg = a.rv + env;
-    const float* gs = b.episode_sums + env;
-    int xi = 0;
-#pragma unroll
-    for (int r = 0; r < LGK_MAX_REWARDS; ++r) {
-      sv[r] = 0.f; vv[r] = 0.f;
-      if (r < nrew + (has_term ? 1 : 0)) sv[r] = gs[(size_t)r * N];
-      if (r < nrew) {
-        const int term = c.rewards[r].term;
-        if (term == LGK_REW_EXTERNAL) { vv[r] = b.ext_rewards[(size_t)xi * N + env]; ++xi; }   // a python _reward_<name>
-        else vv[r] = rvg[(size_t)term * NP_];        // (base_height: the root z before any reset)
-      }
-    }
-  }
-  if (a.scan_first && a.bh_active && ne > 0) {
-    // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height); the height sums of this
-    // warp's envs are out once every scan group overlapping them has been handed over (one lane per flag)
-    const int f0 = wenv0 / a.scan_epc, f1 = (wenv0 + ne - 1) / a.scan_epc;
-    if (f0 + lane <= f1) wait_scan_flag(a, ws, a.scan_flags + f0 + lane, stamp);
-    __syncwarp();
-    if (active) bh = a.hsum[env] / (float)c.num_height_points;
-  }
-  if (active) {
-    float rew = 0.f;
-    float* gsum = b.episode_sums + env;
-    float* stat = ws->stats[parity];
-#pragma unroll
-    for (int r = 0; r < LGK_MAX_REWARDS; ++r) {
-      if (r < nrew) {
-        float v = vv[r];
-        if (c.rewards[r].term == LGK_REW_BASE_HEIGHT) { const float d = (v - bh) - c.base_height_target; v = d * d; }
-        const float rr = mul_rn(v, c.rewards[r].scale);
-        const float total = add_rn(sv[r], rr);
-        rew = add_rn(rew, rr);
-        gsum[(size_t)r * N] = reset ? 0.f : total;   // zeroed for reset envs after the statistics read it (:184-185)
-        if (reset) atomicAdd(stat + r, total);
-      }
-    }
-    if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
-    if (has_term) {   // added after the positive clip (:206-212)
-      float total = 0.f;
-      const float rr = mul_rn((reset && !time_out) ? 1.f : 0.f, c.termination_scale);
-#pragma unroll
-      for (int r = 0; r < LGK_MAX_REWARDS; ++r) if (r == nrew) total = add_rn(sv[r], rr);
-      rew = add_rn(rew, rr);
-      gsum[(size_t)nrew * N] = reset ? 0.f : total;
-      if (reset) atomicAdd(stat + nrew, total);
-    }
-    b.rew_buf[env] = rew;
-  }
-
-  // ---- the envs reset this step, dealt over the warps of the grid ---------------------------------------------
-  const int gw = (int)(blockIdx.x * (FIN_THREADS / 32) + (threadIdx.x >> 5)), nw = (int)(gridDim.x * (FIN_THREADS / 32));
+  const int n_reset = ws->reset_count[(int)(csc & 1ull)];
+  const int gw = ((int)blockIdx.x - 1) * (FIN_THREADS / 32) + (int)(threadIdx.x >> 5), nw = fix_ctas * (FIN_THREADS / 32);
 #pragma unroll 1
   for (int i = gw; i < n_reset; i += nw) {
     const int e = a.fix_list[i];
-#ifdef LGK_BOUNDS
-    if (i < 0 || i >= N || e < 0 || e >= N) {
-      if (lane == 0) printf("[lgk bounds] finish: fix_list[%d] = %d, n_reset %d, N %d, parity %d\n", i, e, n_reset, N, parity);
-      return;
-    }
-#endif
     const float* side = a.side + (size_t)e * LGK_SIDE_FLOATS;
     if (a.scan_first) {
       if (lane == 0) wait_scan_flag(a, ws, a.scan_flags + e / a.scan_epc, stamp);
@@ -981,6 +940,115 @@ __global__ void __launch_bounds__(FIN_THREADS) lgk_finish_kernel(const __grid_co
     }
     if (lane < 13) b.root_states[(size_t)e * 13 + lane] = side[8 + lane];   // the row the step kernel held back
   }
+}
+__device__ __forceinline__ void finish_reward_cta(const StepArgs& a, int first_cta) {
+  // the loads of a batch of FB rows are issued together, and the next batch's loads before this batch's stores (same
+  // array: the compiler may not move them there by itself).  Nothing is waited for before the first batch is out.
+  const LgkConsts& c = a.c;
+  const LgkBuffers& b = a.b;
+  const int N = c.num_envs;
+  const int lane = threadIdx.x & 31;
+  const unsigned flags = c.flags;
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  const int env = ((int)blockIdx.x - first_cta) * FIN_THREADS + threadIdx.x;
+  const int wenv0 = env - lane;
+  if (wenv0 >= N) return;
+  const int ne = min(32, N - wenv0);
+  const bool active = lane < ne;
+  const int nrew = c.num_rewards;
+  const bool has_term = flags & LGK_F_HAS_TERMINATION;
+  constexpr int FB = 8;
+  const size_t NP_ = (size_t)a.rv_pitch;
+  const int envc = active ? env : wenv0;        // inactive lanes shadow lane 0 (loads only)
+  const float* rvg = a.rv + envc;
+  float* gsum = b.episode_sums + envc;
+  const int nrows = nrew + (has_term ? 1 : 0);
+  float sv[2][FB], vv[2][FB];
+  int xi = 0;   // index among the external rows
+  auto load_batch = [&](int r0, float (&s8)[FB], float (&v8)[FB]) {
+#pragma unroll
+    for (int j = 0; j < FB; ++j) {
+      const int r = r0 + j;
+      s8[j] = 0.f; v8[j] = 0.f;
+      if (r < nrows) s8[j] = gsum[(size_t)r * N];
+      if (r < nrew) {
+        const int term = c.rewards[r].term;
+        if (term == LGK_REW_EXTERNAL) { v8[j] = b.ext_rewards[(size_t)xi * N + envc]; ++xi; }   // a python _reward_<name>
+        else v8[j] = rvg[(size_t)term * NP_];      // (base_height: the root z before any reset)
+      }
+    }
+  };
+  const bool reset = b.reset_buf[envc] != 0, time_out = b.time_out_buf[envc] != 0;
+  load_batch(0, sv[0], vv[0]);
+  float bh = 0.f;
+  if (a.scan_first && a.bh_active) {
+    // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height); the height sums of this
+    // warp's envs are out once every scan group overlapping them has been handed over (one lane per flag)
+    const unsigned stamp = ws->launch_seq + 1u;
+    const int f0 = wenv0 / a.scan_epc, f1 = (wenv0 + ne - 1) / a.scan_epc;
+    if (f0 + lane <= f1) wait_scan_flag(a, ws, a.scan_flags + f0 + lane, stamp);
+    __syncwarp();
+    bh = ((float)a.hsum[envc] * c.vertical_scale) / (float)c.num_height_points;
+  }
+  if (!active) return;
+  float* stat = a.stat_copies + (size_t)((wenv0 >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS;
+  float rew = 0.f;
+  auto finish_batch = [&](int r0, const float (&s8)[FB], const float (&v8)[FB]) {
+#pragma unroll
+    for (int j = 0; j < FB; ++j) {
+      const int r = r0 + j;
+      if (r < nrew) {
+        float v = v8[j];
+        if (c.rewards[r].term == LGK_REW_BASE_HEIGHT) { const float d = (v - bh) - c.base_height_target; v = d * d; }
+        const float rr = mul_rn(v, c.rewards[r].scale);
+        const float total = add_rn(s8[j], rr);
+        rew = add_rn(rew, rr);
+        gsum[(size_t)r * N] = reset ? 0.f : total;   // zeroed for reset envs after the statistics took it (:184-185)
+        if (reset) atomicAdd(stat + r, total);
+      } else if (r == nrew) {
+        if (flags & LGK_F_ONLY_POSITIVE) rew = fmaxf(rew, 0.f);
+        if (has_term) {   // added after the positive clip (:206-212)
+          const float rr = mul_rn((reset && !time_out) ? 1.f : 0.f, c.termination_scale);
+          const float total = add_rn(s8[j], rr);
+          rew = add_rn(rew, rr);
+          gsum[(size_t)r * N] = reset ? 0.f : total;
+          if (reset) atomicAdd(stat + r, total);
+        }
+      }
+    }
+  };
+#pragma unroll 1
+  for (int r0 = 0; r0 <= nrew; r0 += 2 * FB) {   // (<=: the batch holding row nrew does the clip / termination)
+    if (r0 + FB <= nrew) load_batch(r0 + FB, sv[1], vv[1]);
+    finish_batch(r0, sv[0], vv[0]);
+    if (r0 + FB <= nrew) {
+      if (r0 + 2 * FB <= nrew) load_batch(r0 + 2 * FB, sv[0], vv[0]);
+      finish_batch(r0 + FB, sv[1], vv[1]);
+    }
+  }
+  b.rew_buf[env] = rew;
+}
+template <bool TAPS, bool MUL_RCP, int NP>
+__global__ void __launch_bounds__(FIN_THREADS) lgk_finish_kernel(const __grid_constant__ StepArgs a, int fix_ctas,
+                                                                 int step_ctas) {
+  pdl_launch_dependents();   // whatever follows on the stream may take its slots; it waits for this grid to complete
+  __shared__ unsigned s_last;
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(a.b.workspace);
+  pdl_wait();
+  const unsigned long long csc = ws->step_counter + 1ull;
+  if (blockIdx.x == 0) compact_id_lists<FIN_THREADS>(a, step_ctas);
+  else if ((int)blockIdx.x <= fix_ctas) finish_fix_cta<TAPS, MUL_RCP, NP>(a, fix_ctas);
+  else finish_reward_cta(a, fix_ctas + 1);
+  // ---- the last CTA to get here publishes the step's statistics and advances the counters ------------------------
+  __syncthreads();   // (every thread of the CTA, whatever it returned from above)
+  if (threadIdx.x == 0) {
+    __threadfence();
+    s_last = (atomicAdd(&ws->fin_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (!s_last) return;   // (CTA-uniform)
+  __threadfence();
+  publish_step_statistics(a, csc);
 }
 // ---------------------------------------------------------------------------------------------
 static inline int up4(int x) { return (x + 3) & ~3; }
@@ -1160,16 +1228,19 @@ static int launch_step(const StepArgs& args, int dev, int grid, size_t smem, cud
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(kern, dim3(grid), dim3(LGK_CTA_THREADS), smem, stream, args));
   dbg_sync("step kernel");
   {
-    const dim3 fgrid((args.c.num_envs + FIN_THREADS - 1) / FIN_THREADS);
+    // CTA 0: id lists; then fix_ctas CTAs for the envs reset this step (about 1 % of them: one or two per warp); then
+    // one CTA per 128 envs
+    int fix_ctas = args.c.num_envs / 256;
+    fix_ctas = fix_ctas < 1 ? 1 : fix_ctas > LGK_FIX_CTAS_MAX ? LGK_FIX_CTAS_MAX : fix_ctas;
+    const dim3 fgrid(1 + fix_ctas + (args.c.num_envs + FIN_THREADS - 1) / FIN_THREADS);
     const int np = (args.c.num_height_points + 31) / 32;
     cudaError_t e;
-    if (np == 6) e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 6>, fgrid, dim3(FIN_THREADS), 0, stream, args);
-    else if (np == 4) e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 4>, fgrid, dim3(FIN_THREADS), 0, stream, args);
-    else e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 0>, fgrid, dim3(FIN_THREADS), 0, stream, args);
+    if (np == 6) e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 6>, fgrid, dim3(FIN_THREADS), 0, stream, args, fix_ctas, grid);
+    else if (np == 4) e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 4>, fgrid, dim3(FIN_THREADS), 0, stream, args, fix_ctas, grid);
+    else e = lgk_launch_pdl(lgk_finish_kernel<TAPS, MUL_RCP, 0>, fgrid, dim3(FIN_THREADS), 0, stream, args, fix_ctas, grid);
     LGK_CUDA_RETURN_IF(e);
   }
   dbg_sync("finish kernel");
-  LGK_CUDA_RETURN_IF(lgk_launch_pdl(lgk_step_epilogue_kernel, dim3(1), dim3(EPI_THREADS), 0, stream, args, grid));
   return (int)cudaGetLastError();
 }
 
@@ -1183,12 +1254,14 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   args.head_stride = OH | 1;
   args.one = 1.0f;
   args.scan_first = c->num_height_points > 0 ? 1 : 0;
-  args.hsum = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_hsum_offset(c->num_envs));
+  args.hsum = reinterpret_cast<int*>(static_cast<char*>(b->workspace) + lgk_ws_hsum_offset(c->num_envs));
+  args.expo23 = 0x4b000000u;
   args.scan_flags = reinterpret_cast<unsigned*>(static_cast<char*>(b->workspace) + lgk_ws_flags_offset(c->num_envs));
   args.rv = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_rv_offset(c->num_envs));
   args.rv_pitch = lgk_ws_rv_pitch(c->num_envs);
   args.side = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_side_offset(c->num_envs));
   args.fix_list = reinterpret_cast<int*>(static_cast<char*>(b->workspace) + lgk_ws_fix_offset(c->num_envs));
+  args.stat_copies = reinterpret_cast<float*>(static_cast<char*>(b->workspace) + lgk_ws_tot_offset(c->num_envs));
   fill_rng_and_thresholds(args, c);
   args.hip_mask = 0u;
   for (int h = 0; h < c->num_hip; ++h) args.hip_mask |= 1u << c->hip_idx[h];

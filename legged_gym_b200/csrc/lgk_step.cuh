@@ -8,8 +8,10 @@
 #include "lgk_common.cuh"
 
 #define TILE 32
+#ifndef LGK_SCAN_REG_CTAS
 #define LGK_SCAN_REG_CTAS 8      // scan kernel: register cap 64 (eight 128-thread CTAs per SM would fit)
-#define LGK_SCAN_CTAS_PER_SM 8   // ... and that many are launched per SM (LGK_SCAN_CTAS in the environment: fewer, to
+#endif
+#define LGK_SCAN_CTAS_PER_SM LGK_SCAN_REG_CTAS   // ... and that many are launched per SM (LGK_SCAN_CTAS in the environment: fewer, to
                                  // leave room for step CTAs from the start -- measured slower)
 #define RS (TILE + 1)   // row stride of [row][env] tables: conflict-free by row and by env
 #define SCAN_GROUP 8    // envs a scan warp takes per group (one hand-over flag per group)
@@ -35,15 +37,17 @@ struct StepArgs {
   int scan_first;    // lgk_scan_kernel was launched ahead of the step kernel (num_height_points > 0)
   int scan_epc;      // envs per group of the scan kernel (1, 2, 4 or 8)
   float one;         // 1.0f the compiler cannot see: blocks ptxas' contraction of mul.rn.f32x2 + add.rn.f32x2
-  float* hsum;       // [N] sum over the scan points of the measured heights (workspace), scan -> step kernel
+  unsigned expo23;   // 0x4b000000 (the float 2^23) the compiler cannot see: PRMT's register operand (field_as_float_bits)
+  int* hsum;         // [N] sum over the scan points of the raw int16 heights (workspace), scan -> finish kernel
   unsigned* scan_flags;   // [ceil(N / scan_epc)] (workspace): launch_seq + 1 once the scan group's columns and sums are out
   int scan_tiles;    // scan groups of this launch = ceil(N / scan_epc); the scan grid's warps walk them persistently
   int scan_grid;     // CTAs of the scan kernel: all resident at once
   float* rv;         // [LGK_REW_COUNT][rv_pitch] (workspace): value of every reward term by env, step -> finish kernel
   int rv_pitch;      // floats per row of rv (N rounded up to 32)
+  float* stat_copies;   // [64][LGK_MAX_REWARDS] (workspace): replicated accumulators of the reset envs' episode sums
   int* fix_list;     // [N] (workspace): the envs reset this step, in any order (reset_count of the step parity entries)
   float* side;       // [N][LGK_SIDE_FLOATS] (workspace): rows of the envs reset this step -- 8 scan operands with the new
-                     // root z, then the 13 floats of the new root state -- step -> finish kernel
+                     // root z, the 13 floats of the new root state -- step -> finish kernel
   unsigned pk[20];   // Philox4x32-10 round keys of c.seed
   // bulk-load table: lane i of W0 copies input array i of a sub-tile (source base, offset into shared
   // memory in floats, bytes per env); src == nullptr: nothing to copy
@@ -77,8 +81,13 @@ __host__ __device__ inline size_t lgk_ws_side_offset(int num_envs) {
 __host__ __device__ inline size_t lgk_ws_fix_offset(int num_envs) {
   return lgk_ws_side_offset(num_envs) + 4u * (size_t)LGK_SIDE_FLOATS * (size_t)num_envs;
 }
+// ... and 64 replicated accumulator rows of LGK_MAX_REWARDS floats for the episode sums of the reset envs
+// (extras["episode"], legged_robot.py:182-185); all zero between launches
+__host__ __device__ inline size_t lgk_ws_tot_offset(int num_envs) {
+  return (lgk_ws_fix_offset(num_envs) + 4u * (size_t)num_envs + 127u) & ~(size_t)127u;
+}
 __host__ __device__ inline size_t lgk_ws_total_bytes(int num_envs) {
-  return lgk_ws_fix_offset(num_envs) + 4u * (size_t)num_envs;
+  return lgk_ws_tot_offset(num_envs) + 4u * (size_t)LGK_MAX_REWARDS * 64u;
 }
 
 // ---- the height scan of one env, lanes = scan points (legged_robot.py:818-854) ----------------------------
@@ -160,28 +169,40 @@ __device__ __forceinline__ ScanLane scan_lane_consts(const StepArgs& a, int h, i
 // observation column of a scan point: clip(root_z - 0.5 - height, -1, 1) * scale (:227) + noise (:231), then the
 // optional final clip (:104).  Philox mode folds scale and noise into two FFMAs; without noise (ka = kb = 0) they
 // round like the plain product.
+// 16-bit field `half` of rw under the exponent of 2^23: the float 2^23 + r16.  The exponent word travels in a register
+// (from the kernel parameters, so that the compiler cannot fold it into the instruction): PRMT then takes the
+// byte selector as its immediate, one instruction per field instead of a selector move + PRMT
+__device__ __forceinline__ unsigned field_as_float_bits(unsigned rw, unsigned expo, int half) {
+  unsigned m;
+  if (half) asm("prmt.b32 %0, %1, %2, 0x7632;" : "=r"(m) : "r"(rw), "r"(expo));
+  else asm("prmt.b32 %0, %1, %2, 0x7610;" : "=r"(m) : "r"(rw), "r"(expo));
+  return m;
+}
 template <bool TAPS, bool CLIP>
 __device__ __forceinline__ float scan_obs(float zo, float hgt, float scale, float ka, float kb, unsigned rw, int half,
-                                          const float* __restrict__ tap, float clip_obs) {
+                                          const float* __restrict__ tap, float clip_obs, unsigned expo) {
   const float d = clampf(sub_rn(zo, hgt), -1.f, 1.f);
   float v;
   if (TAPS) {
     v = mul_rn(d, scale);
     if (tap != nullptr) v = add_rn(v, mul_rn(sub_rn(mul_rn(2.0f, __ldg(tap)), 1.0f), ka));
   } else {
-    const unsigned m = half ? __byte_perm(rw, 0x4b000000u, 0x7632) : __byte_perm(rw, 0x4b000000u, 0x7610);
-    v = fmaf(__uint_as_float(m), ka, fmaf(d, scale, kb));
+    v = fmaf(__uint_as_float(field_as_float_bits(rw, expo, half)), ka, fmaf(d, scale, kb));
   }
   return CLIP ? clampf(v, -clip_obs, clip_obs) : v;
 }
 
 // NP passes of 32 points (pass it0 .. it0 + NP - 1) of one env: indices, gathers (all in flight before the first is
-// consumed), observation columns, optional measured_heights row.  Returns this lane's sum of heights.
+// consumed), observation columns, measured_heights row when MAT.  Returns this lane's sum of the raw int16 heights
+// (exact; times vertical_scale it is the sum of the measured heights up to the rounding of each product).
 // rnd: the Philox block whose 16-bit fields 0..7 belong to passes it0..it0+7 of this lane.
-template <bool TAPS, bool MUL_RCP, int NP, bool CLIP>
-__device__ __forceinline__ float scan_passes(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP], int it0,
+// SLN: the per-lane constants are read from shared memory (sln[pass * 32 + lane] = {p.x, p.y, ka, kb}) where they are
+// used instead of living in registers across envs (24 registers the scan kernel trades for resident warps).
+template <bool TAPS, bool MUL_RCP, int NP, bool CLIP, bool MAT = true, bool SLN = false>
+__device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP], int it0,
                                              int lane, uint4 rnd, float* __restrict__ orow,
-                                             const float* __restrict__ trow, float* __restrict__ mrow, bool check_all) {
+                                             const float* __restrict__ trow, float* __restrict__ mrow, bool check_all,
+                                             const float4* sln = nullptr) {
   const LgkConsts& c = a.c;
   const int H = c.num_height_points;
   const bool plane = c.flags & LGK_F_TERRAIN_PLANE;
@@ -191,7 +212,8 @@ __device__ __forceinline__ float scan_passes(const StepArgs& a, const ScanEnv& e
     const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
 #pragma unroll
     for (int it = 0; it < NP; ++it) {
-      const int cell = scan_cell<MUL_RCP>(e, ln[it].p, a.one, c.border_size, inv_hs, c.horizontal_scale, max_px, max_py,
+      const float2 p = SLN ? reinterpret_cast<const float2*>(sln + it * 32 + lane)[0] : ln[it].p;
+      const int cell = scan_cell<MUL_RCP>(e, p, a.one, c.border_size, inv_hs, c.horizontal_scale, max_px, max_py,
                                           c.terrain_pitch);
       raw[it] = __ldg(a.b.height_min3 + (unsigned)cell);
     }
@@ -199,7 +221,7 @@ __device__ __forceinline__ float scan_passes(const StepArgs& a, const ScanEnv& e
 #pragma unroll
     for (int it = 0; it < NP; ++it) raw[it] = 0;
   }
-  float hsum = 0.f;
+  int hsum = 0;
 #pragma unroll
   for (int it = 0; it < NP; ++it) {
     const int h = (it0 + it) * 32 + lane;
@@ -207,11 +229,12 @@ __device__ __forceinline__ float scan_passes(const StepArgs& a, const ScanEnv& e
     const bool ok = (!check_all && it < NP - 1) ? true : h < H;
     const unsigned rw = (it >> 1) == 0 ? rnd.x : (it >> 1) == 1 ? rnd.y : (it >> 1) == 2 ? rnd.z : rnd.w;
     const float hgt = mul_rn(s16_to_float(raw[it]), c.vertical_scale);
-    hsum += ok ? hgt : 0.f;
-    const float o = scan_obs<TAPS, CLIP>(e.zo, hgt, c.obs_scale_height, ln[it].ka, ln[it].kb, rw, it & 1,
-                                         (TAPS && trow != nullptr) ? trow + (ok ? h : 0) : nullptr, c.clip_obs);
+    hsum += ok ? raw[it] : 0;
+    const float2 kk = SLN ? reinterpret_cast<const float2*>(sln + it * 32 + lane)[1] : make_float2(ln[it].ka, ln[it].kb);
+    const float o = scan_obs<TAPS, CLIP>(e.zo, hgt, c.obs_scale_height, kk.x, kk.y, rw, it & 1,
+                                         (TAPS && trow != nullptr) ? trow + (ok ? h : 0) : nullptr, c.clip_obs, a.expo23);
     if (ok) orow[h] = o;
-    if (mrow != nullptr && ok) mrow[h] = hgt;   // optional materialisation of measured_heights [N,H]
+    if (MAT && mrow != nullptr && ok) mrow[h] = hgt;   // optional materialisation of measured_heights [N,H]
   }
   return hsum;
 }
@@ -248,7 +271,7 @@ static __device__ __forceinline__ void lgk_scan_fixup_env(const StepArgs& a, con
     for (int it = 0; it < NP; ++it) ln[it] = scan_lane_consts<TAPS>(a, it * 32 + lane, OH);
     uint4 rnd = make_uint4(0, 0, 0, 0);
     if (!TAPS && noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE_SCAN + lane);
-    (void)scan_passes<TAPS, MUL_RCP, NP, true>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
+    (void)scan_passes<TAPS, MUL_RCP, NP, true, false>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
   } else {
     const int np = (H + 31) / 32;
     uint4 rnd = make_uint4(0, 0, 0, 0);
@@ -262,7 +285,7 @@ static __device__ __forceinline__ void lgk_scan_fixup_env(const StepArgs& a, con
       const int f = it & 7;
       const unsigned w = (f >> 1) == 0 ? rnd.x : (f >> 1) == 1 ? rnd.y : (f >> 1) == 2 ? rnd.z : rnd.w;
       const uint4 r1 = make_uint4((f & 1) ? (w >> 16) : w, 0, 0, 0);
-      (void)scan_passes<TAPS, MUL_RCP, 1, true>(a, e, ln, it, lane, r1, orow, trow, nullptr, true);
+      (void)scan_passes<TAPS, MUL_RCP, 1, true, false>(a, e, ln, it, lane, r1, orow, trow, nullptr, true);
     }
   }
 }

@@ -12,12 +12,8 @@ from __future__ import annotations
 
 import torch
 
-try:  # real simulator if present
-    from isaacgym import gymapi, gymutil  # type: ignore
-    HAVE_ISAACGYM = not hasattr(gymapi, "SyntheticGym")
-except ImportError:  # headless stand-in
-    from legged_gym_b200.sim import gymapi, gymutil
-    HAVE_ISAACGYM = False
+from legged_gym_b200.sim.backend import REAL_ISAACGYM as HAVE_ISAACGYM  # real simulator if present, else the stand-in
+from legged_gym_b200.sim.backend import gymapi, gymutil
 
 
 class BaseTask:

@@ -24,10 +24,7 @@ from legged_gym_b200.envs.base.base_task import BaseTask, HAVE_ISAACGYM, gymapi
 from legged_gym_b200.utils.helpers import class_to_dict
 from legged_gym_b200.utils.terrain import Terrain
 
-try:
-    from isaacgym import gymtorch  # type: ignore
-except ImportError:
-    from legged_gym_b200.sim import gymtorch
+from legged_gym_b200.sim.backend import gymtorch
 
 # hooks whose bodies live inside the fused kernel; a subclass overriding one of them would silently
 # be ignored, so construction fails instead
@@ -783,6 +780,7 @@ class LeggedRobot(BaseTask):
         flags |= _lgk.F_ONLY_POSITIVE if cfg.rewards.only_positive_rewards else 0
         flags |= _lgk.F_HAS_TERMINATION if "termination" in self.reward_scales else 0
         flags |= _lgk.F_INIT_DONE if self.init_done else 0
+        flags |= _lgk.F_FILTERED_CONTACTS if getattr(cfg.rewards, "filtered_feet_contact", False) else 0
         c.flags = flags
         if cfg.terrain.measure_heights and cfg.terrain.mesh_type == 'none':
             raise NameError("Can't measure height with terrain mesh type 'none'")   # (:833-834)
@@ -893,6 +891,7 @@ class LeggedRobot(BaseTask):
         b.height_points_xy = P(getattr(self, "_height_points_xy", None))
         b.terrain_origins = P(getattr(self, "terrain_origins", None))
         b.command_ranges = P(self._command_ranges_dev)
+        b.last_contacts = P(self.last_contacts)
         b.workspace = P(self._workspace)
         if taps:
             for k, t in taps.items():
@@ -971,7 +970,7 @@ class LeggedRobot(BaseTask):
     _STATE_TENSORS = ("root_states", "dof_state", "actions", "last_actions", "last_dof_vel", "last_root_vel",
                       "commands", "feet_air_time", "env_origins", "obs_buf", "rew_buf", "reset_buf", "time_out_buf",
                       "base_lin_vel", "base_ang_vel", "projected_gravity", "_episode_sums_buf", "episode_stats",
-                      "_extras_buf", "_episode_length_buf", "terrain_levels")
+                      "_extras_buf", "_episode_length_buf", "terrain_levels", "last_contacts")
 
     def _extra_state_tensors(self) -> Dict[str, torch.Tensor]:
         """Per-env state a subclass adds (actuator histories, LSTM state)."""

@@ -127,6 +127,9 @@ class LeggedRobotCfg(BaseConfig):
             action_rate = -0.01
 
         only_positive_rewards = True
+        # not in the reference's config: True selects the feet_air_time variant the reference keeps commented out
+        # (legged_robot.py:928-939: a foot counts as in contact if it is now or was at the previous step)
+        filtered_feet_contact = False
         tracking_sigma = 0.25
         soft_dof_pos_limit = 1.
         soft_dof_vel_limit = 1.

@@ -12,7 +12,7 @@ import random
 import numpy as np
 import torch
 
-from legged_gym_b200.sim import gymapi, gymutil
+from legged_gym_b200.sim.backend import gymapi, gymutil
 
 
 def class_to_dict(obj) -> dict:

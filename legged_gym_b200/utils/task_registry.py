@@ -10,7 +10,7 @@ import os
 from datetime import datetime
 
 from legged_gym_b200 import LEGGED_GYM_ROOT_DIR
-from legged_gym_b200.sim import gymapi
+from legged_gym_b200.sim.backend import gymapi
 from .helpers import class_to_dict, get_args, get_load_path, parse_sim_params, set_seed, update_cfg_from_args
 
 

@@ -105,6 +105,7 @@ class OracleParams:
     action_scale: float
     control_type: str
     only_positive_rewards: bool
+    filtered_feet_contact: bool
     tracking_sigma: float
     soft_dof_vel_limit: float
     soft_torque_limit: float
@@ -163,6 +164,7 @@ class OracleParams:
                         ("lin_vel", "ang_vel", "dof_pos", "dof_vel", "height_measurements")},
             action_scale=cfg.control.action_scale, control_type=cfg.control.control_type,
             only_positive_rewards=cfg.rewards.only_positive_rewards, tracking_sigma=cfg.rewards.tracking_sigma,
+            filtered_feet_contact=bool(getattr(cfg.rewards, "filtered_feet_contact", False)),
             soft_dof_vel_limit=cfg.rewards.soft_dof_vel_limit, soft_torque_limit=cfg.rewards.soft_torque_limit,
             base_height_target=cfg.rewards.base_height_target, max_contact_force=cfg.rewards.max_contact_force,
             send_timeouts=cfg.env.send_timeouts, reward_scales=dict(env.reward_scales),
@@ -212,6 +214,7 @@ class OracleState:
         self.last_root_vel = torch.zeros(N, 6, **f)
         self.commands = torch.zeros(N, 4, **f)
         self.feet_air_time = torch.zeros(N, len(p.feet_indices), **f)
+        self.last_contacts = torch.zeros(N, len(p.feet_indices), dtype=torch.bool, device=device)   # (:547)
         self.episode_length_buf = torch.zeros(N, dtype=torch.long, device=device)
         self.env_origins = torch.zeros(N, 3, **f)
         self.terrain_levels = torch.zeros(N, dtype=torch.long, device=device)
@@ -449,6 +452,13 @@ def reward_terms(p: OracleParams, s: OracleState):
     d = dict
     def feet_air_time():
         contact = cf[:, feet, 2] > 1.
+        if p.filtered_feet_contact:
+            # the variant the reference keeps commented out (:928-939): PhysX contact reporting is unreliable on
+            # meshes, so a foot counts as in contact if it is now or was at the previous step.  No executable
+            # reference exists for it: PARITY UNPINNED for this option (restated from the commented lines)
+            now = contact
+            contact = torch.logical_or(now, s.last_contacts)
+            s.last_contacts = now
         first_contact = (s.feet_air_time > 0.) * contact
         s.feet_air_time += p.dt
         rew = torch.sum((s.feet_air_time - 0.5) * first_contact, dim=1)

@@ -96,6 +96,8 @@ def compare_env_to_oracle(env, s, tag=""):
         assert_close(f"{tag}{name}", getattr(env, name).reshape(-1), getattr(s, name).reshape(-1))
     for k in env.episode_sums:
         assert_close(f"{tag}episode_sums[{k}]", env.episode_sums[k], s.episode_sums[k])
+    if getattr(env.cfg.rewards, "filtered_feet_contact", False):
+        assert_close(f"{tag}last_contacts", env.last_contacts, s.last_contacts, exact=True)
     if n > 0:
         for k, v in s.extras.get("episode", {}).items():
             if k in env.extras["episode"] and torch.is_tensor(env.extras["episode"][k]):

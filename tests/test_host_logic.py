@@ -208,3 +208,26 @@ def test_reset_idx_override_without_the_fused_hook_fails_at_construction():
     with pytest.raises(NotImplementedError, match="_after_fused_resets"):
         helpers.make_env("go1_flat", 8, device="cpu", task_class=Bad)
     helpers.make_env("go1_flat", 8, device="cpu", task_class=Good)
+
+
+def test_legged_gym_import_path_alias():
+    """User code written against the reference's module paths (envs/__init__.py:33-59) runs unchanged with
+    <repo>/compat on the path: legged_gym.<x> IS legged_gym_b200.<x>.  In a subprocess: this process may hold the
+    reference itself under that name (oracle)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("from legged_gym.envs.base.legged_robot import LeggedRobot\n"
+            "from legged_gym.envs.base.legged_robot_config import LeggedRobotCfg\n"
+            "from legged_gym.utils.task_registry import task_registry\n"
+            "from legged_gym.utils import helpers\n"
+            "from legged_gym import LEGGED_GYM_ROOT_DIR\n"
+            "import legged_gym.envs, legged_gym_b200.envs.base.legged_robot as real\n"
+            "assert LeggedRobot is real.LeggedRobot\n"
+            "assert 'go1' in task_registry.task_classes and 'anymal_c_rough' in task_registry.task_classes\n"
+            "class MyRobot(LeggedRobot):\n    def _reward_custom(self):\n        return self.base_lin_vel[:, 0]\n"
+            "print('ok')\n")
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([os.path.join(root, "compat"), root]))
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
