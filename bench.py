@@ -12,12 +12,14 @@ simulator state (legged_gym_b200/utils/synthetic.py).  Prints ONE JSON line (ran
             that live in HBM (8 x 29 MB of inputs at 65536 envs, larger than L2).
   e2e       the same step through the public API with HOST buffers: every step copies that step's
             simulator state + actions from pinned host memory and reads obs / rewards / resets back.
-  roofline  dominant kernel (lgk_step_kernel): algorithmic bytes per launch / CUDA-event time.
-  cpu_baseline  the oracle (CPU torch restatement of the reference, validated bit-identical to it)
-            timed on this box's host cores on a bounded sample of the same workload.
+  roofline  the three kernels of post_physics_step timed as one unit: algorithmic bytes per call / CUDA-event time
+            (for --scenario go1_rough_actuator: the tensor-bound actuator MLP kernel).
+  cpu_baseline  the reference's own, unmodified LeggedRobot.step() (staged into oracle/_ref by oracle/make_ref.sh,
+            imported over the tensor-only simulator stand-in) timed on this box's host cores on a bounded sample of
+            the same workload; the oracle port of it only where the staged copy is missing (kind says which).
+  torch_cuda    the same reference code on CUDA torch, the same-box competitor.
 
-`--impl reference` times that CPU implementation alone on the same config (the reference is pure
-Python/torch and cannot travel to the GPU box; its restatement in oracle/ is what runs).
+`--impl reference` times that CPU implementation alone on the same config.
 """
 from __future__ import annotations
 
@@ -267,7 +269,7 @@ def run_ours(args):
             traffic = json.load(open(tpath)).get(str(N))
         except Exception:   # noqa: BLE001
             traffic = None
-    roofline = {"kernel": "post_physics_step = lgk_scan_kernel + lgk_step_kernel + lgk_finish_kernel + epilogue "
+    roofline = {"kernel": "post_physics_step = lgk_scan_kernel + lgk_step_kernel + lgk_finish_kernel "
                           "(chained with programmatic dependent launch, overlapping; timed as one unit)",
                 "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                 "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,

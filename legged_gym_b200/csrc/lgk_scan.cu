@@ -64,15 +64,6 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
     }
     clip_h = __any_sync(LGK_FULL_MASK, clip_h);
   }
-#ifdef LGK_SCAN_SMEM_LN
-  // experiment: the lane constants live in shared memory (one copy per CTA), not in 24 registers per thread
-  __shared__ float4 s_ln[(GENERIC ? 1 : CH) * 32];
-  if (!GENERIC && wic == 0) {
-#pragma unroll
-    for (int it = 0; it < CH; ++it) s_ln[it * 32 + lane] = make_float4(ln[it].p.x, ln[it].p.y, ln[it].ka, ln[it].kb);
-  }
-  __syncthreads();
-#endif
 
   pdl_wait();   // root_states belong to the simulator: written by whatever ran before this launch
   // The whole grid is resident: the step kernel behind this launch may take SM slots as soon as warps here retire.
@@ -122,17 +113,9 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
           for (int it = 0; it < CH; ++it) ln[it] = scan_lane_consts<TAPS>(a, (ch * CH + it) * 32 + lane, OH);
           hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, ch * CH, lane, rnd, orow, trow, mrow, true);
         } else if (clip_h || mrow != nullptr) {   // (warp-uniform)
-#ifdef LGK_SCAN_SMEM_LN
-          hsum += scan_passes<TAPS, MUL_RCP, CH, true, true, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false, s_ln);
-#else
           hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
-#endif
         } else {          // the common case: no final clip needed, heights not materialised
-#ifdef LGK_SCAN_SMEM_LN
-          hsum += scan_passes<TAPS, MUL_RCP, CH, false, false, true>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false, s_ln);
-#else
           hsum += scan_passes<TAPS, MUL_RCP, CH, false, false>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
-#endif
         }
       }
       s_hp[el * RS + lane] = hsum;

@@ -198,16 +198,12 @@ __device__ __forceinline__ float scan_obs(float zo, float hgt, float scale, floa
 // rnd: the Philox block whose 16-bit fields 0..7 belong to passes it0..it0+7 of this lane.
 // SLN: the per-lane constants are read from shared memory (sln[pass * 32 + lane] = {p.x, p.y, ka, kb}) where they are
 // used instead of living in registers across envs (24 registers the scan kernel trades for resident warps).
-template <bool TAPS, bool MUL_RCP, int NP, bool CLIP, bool MAT = true, bool SLN = false>
-__device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP], int it0,
-                                             int lane, uint4 rnd, float* __restrict__ orow,
-                                             const float* __restrict__ trow, float* __restrict__ mrow, bool check_all,
-                                             const float4* sln = nullptr) {
+// first half: the height-field cells of the NP points of this lane and their gathers (FMA-pipe work + loads)
+template <bool MUL_RCP, int NP, bool SLN = false>
+__device__ __forceinline__ void scan_gather(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP], int lane,
+                                            int (&raw)[NP], const float4* sln = nullptr) {
   const LgkConsts& c = a.c;
-  const int H = c.num_height_points;
-  const bool plane = c.flags & LGK_F_TERRAIN_PLANE;
-  int raw[NP];
-  if (!plane) {
+  if (!(c.flags & LGK_F_TERRAIN_PLANE)) {
     const float inv_hs = 1.0f / c.horizontal_scale;
     const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
 #pragma unroll
@@ -221,6 +217,15 @@ __device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, 
 #pragma unroll
     for (int it = 0; it < NP; ++it) raw[it] = 0;
   }
+}
+// second half: heights -> observation columns (ALU-pipe work + stores); zo: root z - 0.5 of the env
+template <bool TAPS, int NP, bool CLIP, bool MAT = true, bool SLN = false>
+__device__ __forceinline__ int scan_emit(const StepArgs& a, float zo, const ScanLane (&ln)[NP], const int (&raw)[NP],
+                                         int it0, int lane, uint4 rnd, float* __restrict__ orow,
+                                         const float* __restrict__ trow, float* __restrict__ mrow, bool check_all,
+                                         const float4* sln = nullptr) {
+  const LgkConsts& c = a.c;
+  const int H = c.num_height_points;
   int hsum = 0;
 #pragma unroll
   for (int it = 0; it < NP; ++it) {
@@ -231,12 +236,21 @@ __device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, 
     const float hgt = mul_rn(s16_to_float(raw[it]), c.vertical_scale);
     hsum += ok ? raw[it] : 0;
     const float2 kk = SLN ? reinterpret_cast<const float2*>(sln + it * 32 + lane)[1] : make_float2(ln[it].ka, ln[it].kb);
-    const float o = scan_obs<TAPS, CLIP>(e.zo, hgt, c.obs_scale_height, kk.x, kk.y, rw, it & 1,
+    const float o = scan_obs<TAPS, CLIP>(zo, hgt, c.obs_scale_height, kk.x, kk.y, rw, it & 1,
                                          (TAPS && trow != nullptr) ? trow + (ok ? h : 0) : nullptr, c.clip_obs, a.expo23);
     if (ok) orow[h] = o;
     if (MAT && mrow != nullptr && ok) mrow[h] = hgt;   // optional materialisation of measured_heights [N,H]
   }
   return hsum;
+}
+template <bool TAPS, bool MUL_RCP, int NP, bool CLIP, bool MAT = true, bool SLN = false>
+__device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP], int it0,
+                                             int lane, uint4 rnd, float* __restrict__ orow,
+                                             const float* __restrict__ trow, float* __restrict__ mrow, bool check_all,
+                                             const float4* sln = nullptr) {
+  int raw[NP];
+  scan_gather<MUL_RCP, NP, SLN>(a, e, ln, lane, raw, sln);
+  return scan_emit<TAPS, NP, CLIP, MAT, SLN>(a, e.zo, ln, raw, it0, lane, rnd, orow, trow, mrow, check_all, sln);
 }
 
 // launches lgk_scan_kernel for args.c.num_envs envs (lgk_scan.cu)
