@@ -263,6 +263,41 @@ int32_t lgk_abi_version(void);
 int lgk_build_height_min3(const int16_t* height_samples, int32_t rows, int32_t cols,
                           int16_t* out, int32_t pitch, void* stream);
 
+/* Height-field generation on the device: the sub-terrain generators Terrain calls
+ * (utils/terrain.py:109-145 make_terrain, :166-187 gap / pit, and the isaacgym.terrain_utils generators behind them)
+ * plus add_terrain_to_map (:147-164).  The host draws the np.random stream in the reference's order and hands the
+ * resolved draws over; the kernel fills the int16 field and the env-origin heights.  p[] per type:
+ *   SLOPE        peak, clip lo, clip hi                       (pyramid_sloped_terrain)
+ *   SLOPE_NOISE  the same, then coarse nx, ny; draws: nx*ny levels (random_uniform_terrain)
+ *   STAIRS       step cells, step height, number of rings     (pyramid_stairs_terrain)
+ *   OBSTACLES    rectangles, platform x1, x2, y1, y2; draws: (i, j, w, l, height) per rectangle
+ *   STONES       stone cells, gap cells, depth, stones per row, platform x1, x2, y1, y2; draws: stone heights
+ *   GAP          outer half x, y, inner half x, y             PIT  depth, half size */
+typedef enum LgkTerrainType {
+  LGK_TER_FLAT = 0, LGK_TER_SLOPE, LGK_TER_SLOPE_NOISE, LGK_TER_STAIRS, LGK_TER_OBSTACLES, LGK_TER_STONES, LGK_TER_GAP,
+  LGK_TER_PIT
+} LgkTerrainType;
+typedef struct LgkSubTerrain {
+  int32_t type;        /* LgkTerrainType                                              */
+  int32_t row, col;    /* place in the grid (level, type column)                      */
+  int32_t p[10];
+  int32_t draws_off;   /* first entry of this sub-terrain in draws[]                  */
+} LgkSubTerrain;
+typedef struct LgkTerrainGrid {
+  int32_t num_rows, num_cols;   /* sub-terrains                                       */
+  int32_t sub_len, sub_wid;     /* cells per sub-terrain along x / y (length_per_env_pixels, width_per_env_pixels) */
+  int32_t gen_w, gen_l;         /* the generators' own frame (the reference builds width x width squares, :111-115) */
+  int32_t border;               /* cells                                              */
+  int32_t tot_rows, tot_cols;   /* height_samples.shape                               */
+  int32_t patch_x1, patch_x2, patch_y1, patch_y2;   /* env-origin patch (:158-161)    */
+  double  vertical_scale;
+} LgkTerrainGrid;
+/* g: HOST memory (read during the call); subs [n_sub], draws, lin (gen_w + gen_l float64: np.linspace of the noise
+ * up-sampling), field [tot_rows, tot_cols] int16 (fully written, border zero), origin_z [num_rows * num_cols] float64:
+ * device memory. */
+int lgk_generate_terrain(const LgkTerrainGrid* g, const LgkSubTerrain* subs, int32_t n_sub, const int32_t* draws,
+                         const double* lin, int16_t* field, double* origin_z, void* stream);
+
 /* actions = clip(actions_in, +-clip_actions)            (legged_robot.py:85-86) */
 int lgk_clip_actions(const float* actions_in, float* actions_out, int64_t count,
                      float clip_actions, void* stream);

@@ -123,6 +123,19 @@ class LgkLstmWeights(C.Structure):
                 ("b_hh1", _F * _G), ("lin_w", _F * LGK_LSTM_HID), ("lin_b", _F), ("in_scale", _F * 2), ("out_scale", _F)]
 
 
+class LgkSubTerrain(C.Structure):
+    _fields_ = [("type", _I), ("row", _I), ("col", _I), ("p", _I * 10), ("draws_off", _I)]
+
+
+class LgkTerrainGrid(C.Structure):
+    _fields_ = [("num_rows", _I), ("num_cols", _I), ("sub_len", _I), ("sub_wid", _I), ("gen_w", _I), ("gen_l", _I),
+                ("border", _I), ("tot_rows", _I), ("tot_cols", _I), ("patch_x1", _I), ("patch_x2", _I),
+                ("patch_y1", _I), ("patch_y2", _I), ("vertical_scale", C.c_double)]
+
+
+TER_FLAT, TER_SLOPE, TER_SLOPE_NOISE, TER_STAIRS, TER_OBSTACLES, TER_STONES, TER_GAP, TER_PIT = range(8)
+
+
 class LgkLibraryMissing(ImportError):
     pass
 
@@ -160,6 +173,7 @@ def load():
         "lgk_launch_count": (C.c_int64, []),
         "lgk_workspace_bytes": (C.c_int64, [C.c_int32, C.c_int32]),
         "lgk_build_height_min3": (C.c_int, [fp, C.c_int32, C.c_int32, fp, C.c_int32, fp]),
+        "lgk_generate_terrain": (C.c_int, [C.POINTER(LgkTerrainGrid), fp, C.c_int32, fp, fp, fp, fp, fp]),
         "lgk_clip_actions": (C.c_int, [fp, fp, C.c_int64, C.c_float, fp]),
         "lgk_compute_poses": (C.c_int, [cp, fp, fp, fp]),
         "lgk_clip_actions_poses": (C.c_int, [cp, fp, fp, fp, fp]),
@@ -191,7 +205,7 @@ def load():
 
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
-    "lgk_build_height_min3", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
+    "lgk_build_height_min3", "lgk_generate_terrain", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
     "lgk_actuator_advance_static",
     "lgk_lstm_actuator_advance", "lgk_lstm_reset_hidden", "lgk_post_physics_step", "lgk_pre_reward_state", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]

@@ -21,6 +21,8 @@ int lgk_lstm_actuator_advance_impl(const LgkConsts*, const LgkLstmWeights*, cons
                                    float*, float*, cudaStream_t);
 int lgk_lstm_reset_hidden_impl(int, int, const int*, const int*, int, float*, float*, cudaStream_t);
 int lgk_set_step_counter_impl(void*, long long, cudaStream_t);
+int lgk_generate_terrain_impl(const LgkTerrainGrid*, const LgkSubTerrain*, int, const int32_t*, const double*, int16_t*,
+                              double*, cudaStream_t);
 }
 
 static std::atomic<long long> g_launches{0};
@@ -112,6 +114,18 @@ int lgk_build_height_min3(const int16_t* height_samples, int32_t rows, int32_t c
   if (rows < 2 || cols < 2 || pitch < cols) return LGK_ERR_DIM;
   g_launches += 1;
   return lgk_build_height_min3_impl(height_samples, rows, cols, out, pitch, (cudaStream_t)stream);
+}
+
+int lgk_generate_terrain(const LgkTerrainGrid* g, const LgkSubTerrain* subs, int32_t n_sub, const int32_t* draws,
+                         const double* lin, int16_t* field, double* origin_z, void* stream) {
+  if (!g || !subs || !draws || !lin || !field || !origin_z) return LGK_ERR_NULL;
+  if (n_sub <= 0 || n_sub > g->num_rows * g->num_cols || g->sub_len <= 0 || g->sub_wid <= 0 || g->gen_w != g->sub_len ||
+      g->gen_l != g->sub_wid || g->border < 0 || g->tot_rows != g->num_rows * g->sub_len + 2 * g->border ||
+      g->tot_cols != g->num_cols * g->sub_wid + 2 * g->border || g->patch_x1 < 0 || g->patch_x2 > g->sub_len ||
+      g->patch_x1 >= g->patch_x2 || g->patch_y1 < 0 || g->patch_y2 > g->sub_wid || g->patch_y1 >= g->patch_y2)
+    return LGK_ERR_DIM;
+  g_launches += 2;
+  return lgk_generate_terrain_impl(g, subs, n_sub, draws, lin, field, origin_z, (cudaStream_t)stream);
 }
 
 int lgk_clip_actions(const float* in, float* out, int64_t count, float clip_actions, void* stream) {

@@ -311,7 +311,7 @@ class LeggedRobot(BaseTask):
         self.sim = self.gym.create_sim(self.sim_device_id, self.graphics_device_id, self.physics_engine, self.sim_params)
         mesh_type = self.cfg.terrain.mesh_type
         if mesh_type in ['heightfield', 'trimesh']:
-            self.terrain = Terrain(self.cfg.terrain, self.num_envs)
+            self.terrain = Terrain(self.cfg.terrain, self.num_envs, device=self.device)
         if mesh_type == 'plane':
             self._create_ground_plane()
         elif mesh_type == 'heightfield':
@@ -585,6 +585,9 @@ class LeggedRobot(BaseTask):
         p.restitution = self.cfg.terrain.restitution
 
     def _bind_height_samples(self):
+        if getattr(self.terrain, "height_field_dev", None) is not None:      # generated on the device: no upload
+            self.height_samples = self.terrain.height_field_dev.view(self.terrain.tot_rows, self.terrain.tot_cols)
+            return
         self.height_samples = torch.tensor(self.terrain.heightsamples).view(
             self.terrain.tot_rows, self.terrain.tot_cols).to(self.device)
 

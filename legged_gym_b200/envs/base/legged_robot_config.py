@@ -30,6 +30,7 @@ class LeggedRobotCfg(BaseConfig):
 
     class terrain:
         mesh_type = 'plane'            # none | plane | heightfield | trimesh
+        device_generation = False      # not in the reference: fill the int16 height field on the GPU (lgk_generate_terrain)
         horizontal_scale = 0.1         # [m] cell size
         vertical_scale = 0.005         # [m] per int16 unit
         border_size = 25               # [m]

@@ -61,6 +61,29 @@ def test_blind_flat_task_with_every_reward_term():
     assert helpers.run_parity("go1_flat", 515, 3, extra=full, oracle_device="cuda:0") > 0
 
 
+@pytest.mark.parametrize("scenario", ["go1_rough_full", "a1_variant"])
+def test_device_terrain_generation_matches_the_host_generator(scenario):
+    """cfg.terrain.device_generation: lgk_generate_terrain fills the int16 height field and
+    the env-origin heights from the host's recipes (same np.random stream) -- bit-identical to the host generators for
+    the curriculum grid (go1_rough_full: every sub-terrain type of make_terrain) and for randomised sub-terrains
+    (a1_variant), and therefore to the reference's field the golden fixtures were recorded on."""
+    def dev(cfg):
+        cfg.terrain.device_generation = True
+    host = helpers.make_env(scenario, 64, device=DEV, seed=0)
+    devi = helpers.make_env(scenario, 64, device=DEV, seed=0, extra=dev)
+    assert devi.terrain.height_field_dev is not None and devi.height_samples.is_cuda
+    assert devi.height_samples.data_ptr() == devi.terrain.height_field_dev.data_ptr()      # no host round trip
+    assert torch.equal(host.height_samples, devi.height_samples)
+    assert torch.equal(host.terrain_origins, devi.terrain_origins)
+    assert torch.equal(host.env_origins, devi.env_origins)
+    assert (host.terrain.height_field_raw == devi.terrain.height_field_raw).all()
+    g = helpers.load_golden(scenario)
+    assert helpers._crc(devi.height_samples) == int(g["meta_terrain_crc"])
+    assert helpers._crc(devi.terrain_origins) == int(g["meta_origins_crc"])
+    # and a step on it
+    assert helpers.run_parity(scenario, 256, 2, extra=dev) >= 0
+
+
 def test_filtered_feet_contact_variant_of_feet_air_time():
     """cfg.rewards.filtered_feet_contact: _reward_feet_air_time as the reference keeps it commented out
     (legged_robot.py:928-939) -- a foot is in contact if it is now or was at the previous step, last_contacts is real

@@ -231,3 +231,101 @@ def test_legged_gym_import_path_alias():
     env = dict(os.environ, PYTHONPATH=os.pathsep.join([os.path.join(root, "compat"), root]))
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
+
+
+def _emulate_terrain_recipes(ter, subs, draws, lin):
+    """numpy restatement of lgk_terrain.cu's per-cell formulas (so that the recipes and the formulas can be checked
+    against the host generators without a GPU)."""
+    import numpy as np
+    from legged_gym_b200 import _lgk
+    W = L = ter.width_per_env_pixels
+    field = np.zeros((ter.tot_rows, ter.tot_cols), np.int16)
+    X, Y = np.meshgrid(np.arange(W), np.arange(L), indexing="ij")
+    for t in subs:
+        p, d = list(t.p), np.array(draws[t.draws_off:] + [0], np.int64)
+        if t.type in (_lgk.TER_SLOPE, _lgk.TER_SLOPE_NOISE):
+            cx, cy = W // 2, L // 2
+            h = (p[0] * ((cx - np.abs(cx - X)) / cx) * ((cy - np.abs(cy - Y)) / cy)).astype(np.int16).astype(np.int64)
+            h = np.clip(h, p[1], p[2])
+            if t.type == _lgk.TER_SLOPE_NOISE:
+                nx, ny = p[3], p[4]
+                gx, gy = lin[:W][X], lin[W:][Y]
+                x0 = np.clip(np.floor(gx).astype(int), 0, nx - 2); y0 = np.clip(np.floor(gy).astype(int), 0, ny - 2)
+                fx, fy = gx - x0, gy - y0
+                x1, y1 = np.minimum(x0 + 1, nx - 1), np.minimum(y0 + 1, ny - 1)
+                c = d[:nx * ny].reshape(nx, ny).astype(np.float64)
+                f = c[x0, y0] * (1 - fx) * (1 - fy) + c[x1, y0] * fx * (1 - fy) + c[x0, y1] * (1 - fx) * fy + c[x1, y1] * fx * fy
+                h = h + np.rint(f).astype(np.int16)
+        elif t.type == _lgk.TER_STAIRS:
+            sw = p[0]
+            r = np.minimum(np.minimum(X // sw, (W - 1 - X) // sw), np.minimum(Y // sw, (L - 1 - Y) // sw))
+            h = p[1] * np.minimum(r, p[2])
+        elif t.type == _lgk.TER_OBSTACLES:
+            h = np.zeros((W, L), np.int64)
+            for k in range(p[0]):
+                i, j, w, l, hh = d[5 * k:5 * k + 5]
+                h[(X >= i) & (X < i + w) & (Y >= j) & (Y < j + l)] = hh
+            h[(X >= p[1]) & (X < p[2]) & (Y >= p[3]) & (Y < p[4])] = 0
+        elif t.type == _lgk.TER_STONES:
+            ss, pitch = p[0], p[0] + p[1]
+            sa, sb = X // pitch, Y // pitch
+            on = (X - sa * pitch < ss) & (Y - sb * pitch < ss)
+            h = np.where(on, d[np.minimum(sa * p[3] + sb, len(d) - 1)], p[2])
+            h[(X >= p[4]) & (X < p[5]) & (Y >= p[6]) & (Y < p[7])] = 0
+        elif t.type == _lgk.TER_GAP:
+            cx, cy = L // 2, W // 2
+            h = np.zeros((W, L), np.int64)
+            h[(X >= cx - p[0]) & (X < cx + p[0]) & (Y >= cy - p[1]) & (Y < cy + p[1])] = -1000
+            h[(X >= cx - p[2]) & (X < cx + p[2]) & (Y >= cy - p[3]) & (Y < cy + p[3])] = 0
+        elif t.type == _lgk.TER_PIT:
+            cx, cy = L // 2, W // 2
+            h = np.zeros((W, L), np.int64)
+            h[(X >= cx - p[1]) & (X < cx + p[1]) & (Y >= cy - p[1]) & (Y < cy + p[1])] = -p[0]
+        else:
+            h = np.zeros((W, L), np.int64)
+        x0 = ter.border + t.row * ter.length_per_env_pixels
+        y0 = ter.border + t.col * W
+        field[x0:x0 + W, y0:y0 + L] = h.astype(np.int16)
+    return field
+
+
+@pytest.mark.parametrize("curriculum", [True, False])
+def test_device_terrain_recipes_reproduce_the_host_generator(curriculum):
+    """The recipes lgk_generate_terrain consumes (Terrain._recipe: parameters + resolved np.random draws in the
+    generators' own order) describe exactly the field the host generators build, for every sub-terrain type
+    (slope, slope + noise, stairs up / down, obstacles, stepping stones, gap, pit) -- checked through a numpy
+    restatement of the kernel's per-cell formulas; the np.random stream ends in the same state."""
+    import copy
+    import numpy as np
+    from legged_gym_b200.envs.base.legged_robot_config import LeggedRobotCfg
+    from legged_gym_b200.utils.terrain import Terrain
+    cfg = type("TerrainCfg", (LeggedRobotCfg.terrain,), {})()      # an instance: the class attributes stay untouched
+    cfg.mesh_type, cfg.curriculum, cfg.selected = "heightfield", curriculum, False
+    cfg.num_rows, cfg.num_cols = 5, 14
+    cfg.terrain_proportions = [0.1, 0.1, 0.2, 0.2, 0.1, 0.1, 0.1]   # + pit: every branch of make_terrain
+    np.random.seed(7)
+    host = Terrain(copy.copy(cfg), 16)
+    end_state_host = np.random.get_state()[1].copy()
+    np.random.seed(7)
+    ter = copy.copy(host)          # geometry and proportions; the field itself is rebuilt from the recipes below
+    subs, draws = [], []
+    if curriculum:
+        for j in range(cfg.num_cols):
+            for i in range(cfg.num_rows):
+                subs.append(ter._recipe(j / cfg.num_cols + 0.001, i / cfg.num_rows, i, j, draws))
+    else:
+        for k in range(cfg.num_rows * cfg.num_cols):
+            i, j = np.unravel_index(k, (cfg.num_rows, cfg.num_cols))
+            choice = np.random.uniform(0, 1)
+            difficulty = np.random.choice([0.5, 0.75, 0.9])
+            subs.append(ter._recipe(choice, difficulty, int(i), int(j), draws))
+    assert (np.random.get_state()[1] == end_state_host).all(), "the recipes consume the np.random stream differently"
+    W = ter.width_per_env_pixels
+    nx = int(W * cfg.horizontal_scale / 0.2)
+    lin = np.concatenate([np.linspace(0, nx - 1, W), np.linspace(0, nx - 1, W)])
+    field = _emulate_terrain_recipes(ter, subs, draws, lin)
+    assert len({t.type for t in subs}) >= (7 if curriculum else 4)
+    assert field.shape == host.height_field_raw.shape
+    bad = np.argwhere(field != host.height_field_raw)
+    assert bad.size == 0, f"{len(bad)} cells differ, first at {bad[0]}"
+
