@@ -318,11 +318,19 @@ int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* d
  * histories, packs model_ins [N,120] and evaluates the 30-128-128-128-3 tanh MLP per leg.
  * weights: fp32 blob W0[128,30] b0[128] W1[128,128] b1 W2[128,128] b2 W3[3,128] b3[3].
  * norm: pos_err_mean[12] pos_err_std[12] vel_mean[12] vel_std[12].
- * num_envs == 0 is the set-up call: it launches nothing and allocates the MLP kernel's per-device workspace, so
- * that later calls may be made inside a CUDA-graph capture (the first call with envs does the same otherwise). */
+ * workspace: lgk_actuator_workspace_bytes() of caller-owned device memory, 128-byte aligned, one per weight set in
+ * use at a time (the tcgen05 kernel's weight images are rebuilt into it on every call); may be NULL when
+ * LGK_MLP_KERNEL selects the mma / ffma kernel.
+ * num_envs == 0 is the set-up call: it launches nothing and reads the biases and the output layer of `weights`
+ * back to the host (a synchronous copy -- they travel in the MLP kernel's parameter block), so that later calls may be
+ * made inside a CUDA-graph capture.  The first call with envs does the same if no set-up call was made for this
+ * weights pointer; after changing the weights IN PLACE make the set-up call again.  Apart from that table of host
+ * copies (read-only between set-up calls, keyed by device and weights pointer) the library keeps no state: envs with
+ * different nets may run on different streams of one device. */
+int64_t lgk_actuator_workspace_bytes(void);
 int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state,
                          float* pos_err_hist, float* vel_hist, float* model_ins,
-                         const float* weights, const float* norm, float* dvel_out, void* stream);
+                         const float* weights, const float* norm, float* dvel_out, void* workspace, void* stream);
 
 /* Allocation-free variant of lgk_actuator_advance.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses

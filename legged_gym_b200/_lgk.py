@@ -178,7 +178,8 @@ def load():
         "lgk_compute_poses": (C.c_int, [cp, fp, fp, fp]),
         "lgk_clip_actions_poses": (C.c_int, [cp, fp, fp, fp, fp]),
         "lgk_compute_torques": (C.c_int, [cp, fp, fp, fp, fp, fp]),
-        "lgk_actuator_advance": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp, fp]),
+        "lgk_actuator_workspace_bytes": (C.c_int64, []),
+        "lgk_actuator_advance": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp, fp, fp]),
         "lgk_actuator_advance_static": (C.c_int, [C.c_int32, fp, fp, fp, fp, fp, fp, fp, fp]),
         "lgk_lstm_actuator_advance": (C.c_int, [cp, C.POINTER(LgkLstmWeights), fp, fp, fp, fp, fp, fp, fp]),
         "lgk_lstm_reset_hidden": (C.c_int, [C.c_int32, C.c_int32, fp, fp, C.c_int32, fp, fp, fp]),
@@ -205,7 +206,7 @@ def load():
 
 EXPORTED_SYMBOLS = [
     "lgk_abi_version", "lgk_sizeof_consts", "lgk_sizeof_buffers", "lgk_launch_count", "lgk_workspace_bytes",
-    "lgk_build_height_min3", "lgk_generate_terrain", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance",
+    "lgk_build_height_min3", "lgk_generate_terrain", "lgk_clip_actions", "lgk_compute_poses", "lgk_clip_actions_poses", "lgk_compute_torques", "lgk_actuator_advance", "lgk_actuator_workspace_bytes",
     "lgk_actuator_advance_static",
     "lgk_lstm_actuator_advance", "lgk_lstm_reset_hidden", "lgk_post_physics_step", "lgk_pre_reward_state", "lgk_reset_idx", "lgk_reset_all", "lgk_set_step_counter", "lgk_debug_yaw_quat",
 ]

@@ -14,7 +14,8 @@ int lgk_clip_actions_poses_impl(const LgkConsts*, const float*, float*, float*, 
 int lgk_compute_torques_impl(const LgkConsts*, const float*, const float*, const float*, float*, cudaStream_t);
 int lgk_debug_yaw_quat_impl(const float*, int, int, float*, cudaStream_t);
 int lgk_actuator_advance_impl(int, const float*, const float*, float*, float*, float*, const float*, const float*,
-                              float*, cudaStream_t);
+                              float*, void*, cudaStream_t);
+long long lgk_actuator_workspace_bytes_impl();
 int lgk_actuator_advance_static_impl(int, const float*, const float*, float*, float*, const float*, const float*, float*,
                                      cudaStream_t);
 int lgk_lstm_actuator_advance_impl(const LgkConsts*, const LgkLstmWeights*, const float*, const float*, float*, float*,
@@ -163,16 +164,19 @@ int lgk_compute_torques(const LgkConsts* c, const float* actions, const float* d
   return lgk_compute_torques_impl(c, actions, dof_state, last_dof_vel, torques_out, (cudaStream_t)stream);
 }
 
+int64_t lgk_actuator_workspace_bytes(void) { return (int64_t)lgk_actuator_workspace_bytes_impl(); }
+
 int lgk_actuator_advance(int32_t num_envs, const float* actions, const float* dof_state, float* pos_err_hist,
                          float* vel_hist, float* model_ins, const float* weights, const float* norm, float* dvel_out,
-                         void* stream) {
+                         void* workspace, void* stream) {
   if (num_envs < 0) return LGK_ERR_DIM;
   if (!actions || !dof_state || !pos_err_hist || !vel_hist || !model_ins || !weights || !norm || !dvel_out)
     return LGK_ERR_NULL;
   if ((reinterpret_cast<uintptr_t>(dof_state) & 7u) != 0) return LGK_ERR_ALIGN;
+  if (workspace && (reinterpret_cast<uintptr_t>(workspace) & 127u) != 0) return LGK_ERR_ALIGN;   // TMA source
   if (num_envs > 0) g_launches += 2;   /* zero envs: set-up only, nothing is launched */
   return lgk_actuator_advance_impl(num_envs, actions, dof_state, pos_err_hist, vel_hist, model_ins, weights, norm,
-                                   dvel_out, (cudaStream_t)stream);
+                                   dvel_out, workspace, (cudaStream_t)stream);
 }
 
 int lgk_actuator_advance_static(int32_t num_envs, const float* actions, const float* dof_state, float* pos_err_hist,

@@ -193,11 +193,11 @@ __global__ void __launch_bounds__(HIST_THREADS)
 lgk_act_hist_kernel(int N, const float* __restrict__ actions, const float* __restrict__ dof_state,
                     float* __restrict__ pe_hist, float* __restrict__ v_hist, float* __restrict__ model_ins,
                     const float* __restrict__ norm, int hist_ctas, const float* __restrict__ weights,
-                    float* __restrict__ img, float* __restrict__ cblock) {
+                    float* __restrict__ img) {
   pdl_launch_dependents();   // the MLP kernel behind this one may set itself up on free SMs (it waits before reading)
   if ((int)blockIdx.x >= hist_ctas) {
     // CTAs past the history work build the tcgen05 MLP's weight images (lgk_umma_prep.cuh) under it
-    lgk_umma_prep_element(((int)blockIdx.x - hist_ctas) * HIST_THREADS + (int)threadIdx.x, weights, img, cblock);
+    lgk_umma_prep_element(((int)blockIdx.x - hist_ctas) * HIST_THREADS + (int)threadIdx.x, weights, img);
     return;
   }
   __shared__ __align__(16) float s_pe[HIST_THREADS * ACT_HIST];
@@ -359,12 +359,15 @@ lgk_act_mlp_kernel(int rows_total, const float* __restrict__ model_ins, const fl
 extern "C" int lgk_act_mlp_tc_impl(int rows, const float* model_ins, const float* weights, const float* norm,
                                    float* dvel, cudaStream_t st);
 
-extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* norm, float* dvel, cudaStream_t st);
-extern "C" int lgk_umma_workspace(cudaStream_t st, float** img, float** cblock);
+extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const unsigned char* images,
+                                     const float* norm, float* dvel, cudaStream_t st);
+extern "C" int lgk_umma_setup(const float* weights, cudaStream_t st, bool refresh);
+
+extern "C" long long lgk_actuator_workspace_bytes_impl() { return (long long)um::G_TOTAL; }
 
 extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const float* dof_state, float* pe_hist,
                                          float* v_hist, float* model_ins, const float* weights, const float* norm,
-                                         float* dvel, cudaStream_t st) {
+                                         float* dvel, void* workspace, cudaStream_t st) {
   // LGK_MLP_KERNEL picks the MLP kernel (read per call, cheap, so that one process can time / test them all):
   //   "umma" tcgen05 3xTF32, activations + accumulator in tensor memory (lgk_mlp_umma.cu; the default)
   //   "mma"  warp-level 3xTF32 mma.sync (lgk_mlp_tc.cu)      "ffma" the fp32 FFMA kernel below
@@ -374,22 +377,24 @@ extern "C" int lgk_actuator_advance_impl(int N, const float* actions, const floa
   const bool ffma = (e && e[0] == '1') || (k && k[0] == 'f');
   const bool mma = !ffma && k && k[0] == 'm';
   const bool umma = !ffma && !mma;
-  float *img = nullptr, *cblock = nullptr;
+  float* img = static_cast<float*>(workspace);
   if (umma) {
-    const int rc = lgk_umma_workspace(st, &img, &cblock);
+    if (img == nullptr) return LGK_ERR_NULL;   // the tcgen05 kernel's weight images live in the caller's workspace
+    // zero envs = the set-up call: the host copy of the biases / output layer this launch carries in its parameters
+    // is (re)read from the device blob (a synchronous copy: not inside a stream capture)
+    const int rc = lgk_umma_setup(weights, st, /*refresh=*/N <= 0);
     if (rc) return rc;
   }
-  // zero envs: set-up only (the tcgen05 kernel's per-device workspace must exist before a stream capture)
   if (N <= 0) return 0;
   const int n = N * ACT_DOF;
   const int hist_ctas = (n + HIST_THREADS - 1) / HIST_THREADS;
   const int prep_ctas = umma ? um::PREP_ELEMENTS / HIST_THREADS : 0;
   lgk_act_hist_kernel<<<hist_ctas + prep_ctas, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm,
-                                                                     hist_ctas, weights, img, cblock);
+                                                                     hist_ctas, weights, img);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int rows = N * ACT_LEGS;
   if (mma) return lgk_act_mlp_tc_impl(rows, model_ins, weights, norm, dvel, st);
-  if (umma) return lgk_act_mlp_umma_impl(rows, model_ins, norm, dvel, st);
+  if (umma) return lgk_act_mlp_umma_impl(rows, model_ins, weights, static_cast<const unsigned char*>(workspace), norm, dvel, st);
   const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -438,7 +443,7 @@ extern "C" int lgk_actuator_advance_static_impl(int N, const float* actions, con
   const int n = N * ACT_DOF;
   const int hist_ctas = (n + HIST_THREADS - 1) / HIST_THREADS;
   lgk_act_hist_kernel<<<hist_ctas, HIST_THREADS, 0, st>>>(N, actions, dof_state, pe_hist, v_hist, model_ins, norm,
-                                                          hist_ctas, weights, nullptr, nullptr);
+                                                          hist_ctas, weights, nullptr);
   LGK_CUDA_RETURN_IF(cudaGetLastError());
   const int rows = N * ACT_LEGS;
   const int tiles = (rows + MLP_ROWS - 1) / MLP_ROWS;

@@ -47,11 +47,14 @@ constexpr uint32_t UM_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((ACT_HID >> 
 }  // namespace
 
 // biases of the three hidden layers times 2*log2(e) (the epilogue's tanh takes its argument in that scale),
-// W3 [3][128], b3 [3] (+1 pad) -- written by the prep kernel
-__constant__ float c_um[um::CBLOCK_FLOATS];
-#define C_BS(l, col) c_um[(l) * ACT_HID + (col)]
-#define C_W3(o, col) c_um[3 * ACT_HID + (o) * ACT_HID + (col)]
-#define C_B3(o) c_um[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + (o)]
+// W3 [3][128], b3 [3] (+1 pad).  They travel BY VALUE in the kernel's parameter block (3 KB of the 32 KB sm_100
+// allows): parameters live in the constant bank, so the epilogue's FFMAs still take them as immediate constant-bank
+// operands, but every launch has its own copy -- no __constant__ symbol shared by the launches of a device, no
+// device-side write into constant memory.  `P` is the kernel's parameter in every user below.
+struct UmConsts { float v[um::CBLOCK_FLOATS]; };
+#define C_BS(l, col) P.v[(l) * ACT_HID + (col)]
+#define C_W3(o, col) P.v[3 * ACT_HID + (o) * ACT_HID + (col)]
+#define C_B3(o) P.v[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + (o)]
 
 // ---- tcgen05 / tensor-memory helpers ---------------------------------------------------------------------
 __device__ __forceinline__ void um_tmem_alloc(uint32_t* slot_smem, uint32_t cols) {
@@ -191,7 +194,7 @@ __device__ __forceinline__ void um_issue_lo(uint32_t d, uint32_t tmem, uint32_t 
 // hidden-layer epilogue for this thread's row, 16 columns at col0 = 32G + 16*HALF: D -> tanh(D + b) -> hi / lo
 // into the A columns.  L, HALF and G are compile-time so that the biases are immediate constant-bank operands.
 template <int L, int HALF, int G>
-__device__ __forceinline__ void um_epilogue_group(uint32_t trow, uint32_t d_col) {
+__device__ __forceinline__ void um_epilogue_group(const UmConsts& P, uint32_t trow, uint32_t d_col) {
   constexpr int col0 = G * 32 + HALF * 16;
   uint32_t v[16], hi[16], lo[16];
   um_ld16(trow + d_col + col0, v);
@@ -205,7 +208,7 @@ __device__ __forceinline__ void um_epilogue_group(uint32_t trow, uint32_t d_col)
 }
 // last hidden layer: tanh, then this thread's share of the 128 -> 3 output layer (FMA pipe, W3 from the constant bank)
 template <int HALF, int G>
-__device__ __forceinline__ void um_final_group(uint32_t trow, uint32_t d_col, float (&p)[ACT_LEG_DOF]) {
+__device__ __forceinline__ void um_final_group(const UmConsts& P, uint32_t trow, uint32_t d_col, float (&p)[ACT_LEG_DOF]) {
   constexpr int col0 = G * 32 + HALF * 16;
   uint32_t v[16];
   um_ld16(trow + d_col + col0, v);
@@ -239,7 +242,7 @@ __device__ __forceinline__ void um_stage_inputs(uint32_t trow, const float2 (&x)
 
 __global__ void __launch_bounds__(UM_THREADS, 1)
 lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, const unsigned char* __restrict__ wimg,
-                        const float* __restrict__ norm, float* __restrict__ dvel) {
+                        const float* __restrict__ norm, float* __restrict__ dvel, const __grid_constant__ UmConsts P) {
   extern __shared__ __align__(1024) unsigned char um_smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(um_smem + S_BARS);
   uint64_t* bar_res = bars + 0;    // resident weight images landed (TMA)
@@ -371,10 +374,10 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
   } while (0)
 #define UM_HIDDEN_LAYER(L, H)                                           \
   do {                                                                  \
-    um_epilogue_group<L, H, 0>(trow, dsel * ACT_HID); UM_GROUP_DONE(0); \
-    um_epilogue_group<L, H, 1>(trow, dsel * ACT_HID); UM_GROUP_DONE(1); \
-    um_epilogue_group<L, H, 2>(trow, dsel * ACT_HID); UM_GROUP_DONE(2); \
-    um_epilogue_group<L, H, 3>(trow, dsel * ACT_HID); UM_GROUP_DONE(3); \
+    um_epilogue_group<L, H, 0>(P, trow, dsel * ACT_HID); UM_GROUP_DONE(0); \
+    um_epilogue_group<L, H, 1>(P, trow, dsel * ACT_HID); UM_GROUP_DONE(1); \
+    um_epilogue_group<L, H, 2>(P, trow, dsel * ACT_HID); UM_GROUP_DONE(2); \
+    um_epilogue_group<L, H, 3>(P, trow, dsel * ACT_HID); UM_GROUP_DONE(3); \
   } while (0)
     for (int tile = blockIdx.x, it = 0; tile < num_tiles; tile += gridDim.x, ++it) {
       const int row = tile * UM_ROWS + q * 32 + lane;
@@ -411,11 +414,11 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
       UM_STAMP(pr, pb + 11);
       float p[ACT_LEG_DOF] = {0.f, 0.f, 0.f};
       if (half == 0) {
-        um_final_group<0, 0>(trow, dsel * ACT_HID, p); um_final_group<0, 1>(trow, dsel * ACT_HID, p);
-        um_final_group<0, 2>(trow, dsel * ACT_HID, p); um_final_group<0, 3>(trow, dsel * ACT_HID, p);
+        um_final_group<0, 0>(P, trow, dsel * ACT_HID, p); um_final_group<0, 1>(P, trow, dsel * ACT_HID, p);
+        um_final_group<0, 2>(P, trow, dsel * ACT_HID, p); um_final_group<0, 3>(P, trow, dsel * ACT_HID, p);
       } else {
-        um_final_group<1, 0>(trow, dsel * ACT_HID, p); um_final_group<1, 1>(trow, dsel * ACT_HID, p);
-        um_final_group<1, 2>(trow, dsel * ACT_HID, p); um_final_group<1, 3>(trow, dsel * ACT_HID, p);
+        um_final_group<1, 0>(P, trow, dsel * ACT_HID, p); um_final_group<1, 1>(P, trow, dsel * ACT_HID, p);
+        um_final_group<1, 2>(P, trow, dsel * ACT_HID, p); um_final_group<1, 3>(P, trow, dsel * ACT_HID, p);
       }
       UM_STAMP(pr, pb + 12);
       um_fence_before();
@@ -444,40 +447,72 @@ lgk_act_mlp_umma_kernel(int rows_total, const float* __restrict__ model_ins, con
   if (warp == UM_EPI_WARPS) um_tmem_free(tmem, T_COLS);
 }
 
-// The per-device workspace: the weight images (global memory, TMA source) and the address of the constant block.
-// First call on a device allocates; that is not allowed inside a stream capture (lgk_actuator_advance with zero
-// envs does just this, the Go1 env calls it when it is built).
-static unsigned char* g_images[64] = {nullptr};
-static float* g_cblock[64] = {nullptr};
+// Host side.  The weight images (hi / lo UMMA images of W0, W1, W2: um::G_TOTAL bytes) live in memory the CALLER owns
+// (lgk_actuator_workspace_bytes); the history kernel's extra CTAs rebuild them from the fp32 blob on every call.  The
+// 772 floats that travel in the parameter block (scaled biases, W3, b3) must be on the HOST at launch time: the
+// set-up call (lgk_actuator_advance with zero envs; not inside a stream capture) copies them from the device blob once
+// per (device, weights pointer) into a small table here.  That table is the library's only state on this path: it is
+// read-only between set-up calls and keyed by the caller's pointer, so two envs with different nets, on one stream or
+// two, never share anything.  Changing the weights in place requires another set-up call.
+#include <mutex>
+#include <vector>
+namespace {
+struct UmHostEntry { int dev; const float* weights; UmConsts c; };
+std::mutex g_um_mutex;
+std::vector<UmHostEntry> g_um_table;
+int g_um_configured[64] = {0};
+}  // namespace
 
-extern "C" int lgk_umma_workspace(cudaStream_t st, float** img, float** cblock) {
+extern "C" int lgk_umma_setup(const float* weights, cudaStream_t st, bool refresh) {
   int dev = 0;
   LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
-  if (!g_images[dev]) {
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    LGK_CUDA_RETURN_IF(cudaStreamIsCapturing(st, &cap));
-    if (cap != cudaStreamCaptureStatusNone) return (int)cudaErrorStreamCaptureUnsupported;
-    LGK_CUDA_RETURN_IF(cudaMalloc(&g_images[dev], G_TOTAL));
-    LGK_CUDA_RETURN_IF(cudaGetSymbolAddress(reinterpret_cast<void**>(&g_cblock[dev]), c_um));
+  std::lock_guard<std::mutex> lock(g_um_mutex);
+  UmHostEntry* e = nullptr;
+  for (auto& x : g_um_table) if (x.dev == dev && x.weights == weights) e = &x;
+  if (e && !refresh) return 0;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  LGK_CUDA_RETURN_IF(cudaStreamIsCapturing(st, &cap));
+  if (cap != cudaStreamCaptureStatusNone) return (int)cudaErrorStreamCaptureUnsupported;   // make the set-up call first
+  if (!g_um_configured[dev]) {
     LGK_CUDA_RETURN_IF(cudaFuncSetAttribute(lgk_act_mlp_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S_TOTAL));
+    g_um_configured[dev] = 1;
   }
-  *img = reinterpret_cast<float*>(g_images[dev]);
-  *cblock = g_cblock[dev];
+  // blob: W0[128,30] b0 W1[128,128] b1 W2[128,128] b2 W3[3,128] b3
+  const size_t o_b0 = (size_t)ACT_HID * ACT_IN, o_b1 = o_b0 + ACT_HID + (size_t)ACT_HID * ACT_HID,
+               o_b2 = o_b1 + ACT_HID + (size_t)ACT_HID * ACT_HID, o_w3 = o_b2 + ACT_HID;
+  UmConsts c = {};
+  LGK_CUDA_RETURN_IF(cudaStreamSynchronize(st));   // the blob may have been written on this stream just now
+  LGK_CUDA_RETURN_IF(cudaMemcpy(c.v, weights + o_b0, sizeof(float) * ACT_HID, cudaMemcpyDeviceToHost));
+  LGK_CUDA_RETURN_IF(cudaMemcpy(c.v + ACT_HID, weights + o_b1, sizeof(float) * ACT_HID, cudaMemcpyDeviceToHost));
+  LGK_CUDA_RETURN_IF(cudaMemcpy(c.v + 2 * ACT_HID, weights + o_b2, sizeof(float) * ACT_HID, cudaMemcpyDeviceToHost));
+  LGK_CUDA_RETURN_IF(cudaMemcpy(c.v + 3 * ACT_HID, weights + o_w3, sizeof(float) * (ACT_LEG_DOF * ACT_HID + ACT_LEG_DOF),
+                                cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 3 * ACT_HID; ++i) c.v[i] *= 2.885390081777927f;   // (fp32 product, as the device prep did)
+  if (e) e->c = c; else g_um_table.push_back(UmHostEntry{dev, weights, c});
   return 0;
 }
 
 // the MLP on images that are already built for these weights (the history kernel's extra CTAs build them)
-extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* norm, float* dvel, cudaStream_t st) {
+extern "C" int lgk_act_mlp_umma_impl(int rows, const float* model_ins, const float* weights, const unsigned char* images,
+                                     const float* norm, float* dvel, cudaStream_t st) {
   int dev = 0, sms = 148;
   LGK_CUDA_RETURN_IF(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64 || !g_images[dev]) return (int)cudaErrorInvalidValue;
   if (rows <= 0) return 0;
+  { const int rc = lgk_umma_setup(weights, st, false); if (rc) return rc; }   // (a table look-up after the set-up call)
+  UmConsts c;
+  {
+    std::lock_guard<std::mutex> lock(g_um_mutex);
+    const UmHostEntry* e = nullptr;
+    for (const auto& x : g_um_table) if (x.dev == dev && x.weights == weights) e = &x;
+    if (!e) return (int)cudaErrorInvalidValue;
+    c = e->c;
+  }
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int tiles = (rows + UM_ROWS - 1) / UM_ROWS;
   const int grid = tiles < sms ? tiles : sms;
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(lgk_act_mlp_umma_kernel, dim3(grid), dim3(UM_THREADS), (size_t)S_TOTAL, st, rows, model_ins,
-                                    (const unsigned char*)g_images[dev], norm, dvel));
+                                    images, norm, dvel, c));
 #ifdef UM_PROFILE
   if (getenv("LGK_UMMA_PROFILE")) {
     long long h[64];

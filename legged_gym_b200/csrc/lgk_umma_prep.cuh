@@ -39,18 +39,12 @@ __device__ __forceinline__ uint32_t um_img_index(int n, int k, int K) {
   return (uint32_t)(((n >> 3) * (K >> 2) + (k >> 2)) * 32 + (n & 7) * 4 + (k & 3));
 }
 
-// thread i of um::PREP_ELEMENTS: its elements of the six images and of the constant block
-__device__ __forceinline__ void lgk_umma_prep_element(int i, const float* __restrict__ weights, float* __restrict__ img,
-                                                      float* __restrict__ cblock) {
+// thread i of um::PREP_ELEMENTS: its elements of the six images
+__device__ __forceinline__ void lgk_umma_prep_element(int i, const float* __restrict__ weights, float* __restrict__ img) {
   using namespace um;
   const float* W0 = weights;
-  const float* B0 = W0 + ACT_HID * ACT_IN;
-  const float* W1 = B0 + ACT_HID;
-  const float* B1 = W1 + ACT_HID * ACT_HID;
-  const float* W2 = B1 + ACT_HID;
-  const float* B2 = W2 + ACT_HID * ACT_HID;
-  const float* W3 = B2 + ACT_HID;
-  const float* B3 = W3 + ACT_LEG_DOF * ACT_HID;
+  const float* W1 = W0 + ACT_HID * ACT_IN + ACT_HID;
+  const float* W2 = W1 + ACT_HID * ACT_HID + ACT_HID;
   uint32_t* out = reinterpret_cast<uint32_t*>(img);
   if (i < ACT_HID * K0) {
     const int n = i / K0, k = i % K0;
@@ -71,12 +65,5 @@ __device__ __forceinline__ void lgk_umma_prep_element(int i, const float* __rest
     out[G_W2HI / 4 + at] = hi;
     out[G_W2LO / 4 + at] = lo;
   }
-  if (i < ACT_HID) {
-    cblock[i] = B0[i] * 2.885390081777927f;
-    cblock[ACT_HID + i] = B1[i] * 2.885390081777927f;
-    cblock[2 * ACT_HID + i] = B2[i] * 2.885390081777927f;
-  }
-  if (i < ACT_LEG_DOF * ACT_HID) cblock[3 * ACT_HID + i] = W3[i];
-  if (i < ACT_LEG_DOF) cblock[3 * ACT_HID + ACT_LEG_DOF * ACT_HID + i] = B3[i];
 }
 

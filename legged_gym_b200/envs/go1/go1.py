@@ -56,12 +56,16 @@ class Go1(LeggedRobot):
         if getattr(self.cfg.control, "use_actuator_network", False):
             self.actuator_weights = self._load_actuator_weights().to(self.device)
             if self.device.startswith("cuda") if isinstance(self.device, str) else self.device.type == "cuda":
-                # zero envs = set-up only: the tcgen05 MLP kernel allocates its per-device weight-image workspace
+                # the tcgen05 MLP kernel's weight images live in memory this env owns (one workspace per weight set)
+                nbytes = int(self._kernels().lgk_actuator_workspace_bytes())
+                self._actuator_workspace = torch.zeros((nbytes + 7) // 8, dtype=torch.int64, device=self.device)
+                # zero envs = set-up only: the kernel's host-side copy of the biases / output layer is read back
                 # here, so that the first real call may already sit inside a CUDA-graph capture
                 P = _lgk.ptr
                 _lgk.check("lgk_actuator_advance", self._kernels().lgk_actuator_advance(
                     0, P(self.dVel), P(self.dof_state), P(self.pos_err_buffs), P(self.vel_buffs), P(self.model_ins),
-                    P(self.actuator_weights), P(self._act_norm), P(self.dVel), _lgk.current_stream(self.device)))
+                    P(self.actuator_weights), P(self._act_norm), P(self.dVel), P(self._actuator_workspace),
+                    _lgk.current_stream(self.device)))
 
     def _load_actuator_weights(self) -> torch.Tensor:
         sd = getattr(self.cfg.control, "actuator_net_state_dict", None)
@@ -106,5 +110,5 @@ class Go1(LeggedRobot):
         _lgk.check("lgk_actuator_advance", lib.lgk_actuator_advance(
             self.num_envs, P(actions), P(self.dof_state), P(self.pos_err_buffs), P(self.vel_buffs),
             P(self.model_ins), P(self.actuator_weights), P(self._act_norm), P(self.dVel),
-            _lgk.current_stream(self.device)))
+            P(getattr(self, "_actuator_workspace", None)), _lgk.current_stream(self.device)))
         return self.dVel

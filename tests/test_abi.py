@@ -73,7 +73,9 @@ def test_argument_errors_are_status_codes_not_crashes():
     assert lib.lgk_post_physics_step(C.byref(_consts()), None, null) == -1
     b = _lgk.LgkBuffers()
     assert lib.lgk_post_physics_step(C.byref(_consts(num_bodies=17, num_commands=4, num_obs=48)), C.byref(b), null) == -2
-    assert lib.lgk_actuator_advance(-1, one, one, one, one, one, one, one, one, null) == -2   # 0 envs = set-up call
+    assert lib.lgk_actuator_advance(-1, one, one, one, one, one, one, one, one, null, null) == -2   # 0 envs = set-up call
+    assert lib.lgk_actuator_advance(4, one, one, one, one, one, one, one, one, C.c_void_p(64), null) == -5   # workspace alignment
+    assert lib.lgk_actuator_workspace_bytes() >= 2 * 128 * 32 * 4 + 4 * 128 * 128 * 4
     w = _lgk.LgkLstmWeights()
     assert lib.lgk_lstm_actuator_advance(C.byref(_consts()), None, one, one, null, one, one, one, null) == -1
     assert lib.lgk_lstm_actuator_advance(C.byref(_consts()), C.byref(w), one, one, null, C.c_void_p(20), one, one, null) == -5

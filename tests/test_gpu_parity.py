@@ -815,10 +815,42 @@ def test_actuator_net_is_graph_capturable():
         assert torch.equal(graphed.pos_err_buffs, eager.pos_err_buffs)
 
 
+def test_actuator_two_weight_sets_on_two_streams():
+    """Two envs with different actuator-net weights on TWO streams of one device, many substeps in flight at once:
+    each env owns its weight-image workspace and every launch carries its biases / output layer in its own
+    parameter block, so nothing is shared (round 1 kept one image buffer and one __constant__ block per device)."""
+    from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
+    from oracle import legged_oracle as lo
+    n = 8192
+
+    def with_seed(seed):
+        def edit(cfg):
+            cfg.control.actuator_net_random_seed = seed
+        return edit
+    envs = [helpers.make_env("go1_rough_actuator", n, device=DEV, extra=with_seed(s)) for s in (0, 7)]
+    oracles = [lo.ActuatorOracle(n, random_mlp_state_dict(s)) for s in (0, 7)]
+    atols = [helpers.actuator_dvel_atol(random_mlp_state_dict(s)) for s in (0, 7)]
+    assert envs[0]._actuator_workspace.data_ptr() != envs[1]._actuator_workspace.data_ptr()
+    fr = synthetic.make_frames(envs[0], 1, seed=12)[0]
+    for env in envs:
+        synthetic.load_frame(env, fr)
+    streams = [torch.cuda.Stream(DEV), torch.cuda.Stream(DEV)]
+    torch.cuda.synchronize()
+    reps = 6
+    for k in range(reps):                      # interleaved issue: the two streams' kernels overlap on the GPU
+        for env, st in zip(envs, streams):
+            with torch.cuda.stream(st):
+                env.actuator_advance(fr["actions"])
+    torch.cuda.synchronize()
+    for env, act, atol in zip(envs, oracles, atols):
+        for k in range(reps):
+            want = act.advance(fr["actions"].cpu(), env.dof_pos.cpu(), env.dof_vel.cpu())
+        helpers.assert_close_abs("dVel after 6 overlapped substeps", env.dVel, want, atol)
+
+
 def test_actuator_two_weight_sets_alternate():
-    """Two envs with different actuator-net weights take turns on one stream: the weight images and the constant
-    block (biases, output layer) of the tcgen05 kernel are rebuilt on every call, behind a programmatic launch
-    dependency, and must never be stale."""
+    """Two envs with different actuator-net weights take turns on one stream: the weight images of the tcgen05 kernel
+    are rebuilt on every call, behind a programmatic launch dependency, and must never be stale."""
     from legged_gym_b200.envs.go1.go1 import random_mlp_state_dict
     from oracle import legged_oracle as lo
     n = 640

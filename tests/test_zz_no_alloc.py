@@ -41,6 +41,7 @@ def _run(entry, n, blob, norm, calls, kernel_env, monkeypatch):
     pe = torch.zeros(n, 12, 5, device=DEV)
     vh = torch.zeros(n, 12, 5, device=DEV)
     mi = torch.full((n, 120), float("nan"), device=DEV)
+    ws = torch.zeros((int(lib.lgk_actuator_workspace_bytes()) + 7) // 8, dtype=torch.int64, device=DEV)
     st = _lgk.current_stream(DEV)
     outs = []
     for actions, dof_state in calls:
@@ -49,7 +50,7 @@ def _run(entry, n, blob, norm, calls, kernel_env, monkeypatch):
         if entry == "static":
             rc = lib.lgk_actuator_advance_static(n, P(a), P(ds), P(pe), P(vh), P(w), P(nm), P(dvel), st)
         else:
-            rc = lib.lgk_actuator_advance(n, P(a), P(ds), P(pe), P(vh), P(mi), P(w), P(nm), P(dvel), st)
+            rc = lib.lgk_actuator_advance(n, P(a), P(ds), P(pe), P(vh), P(mi), P(w), P(nm), P(dvel), P(ws), st)
         _lgk.check(entry, rc)
         torch.cuda.synchronize()
         outs.append(dvel.cpu())
