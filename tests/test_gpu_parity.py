@@ -128,6 +128,48 @@ def test_generic_scan_width_256_points():
     assert helpers.run_parity("go1_flat", 200, 3, extra=wide) > 0
 
 
+def test_scan_of_357_points_runs_in_two_chunks():
+    """21 x 17 = 357 scan points (more than the 256 the generic scan instantiation takes per chunk; round 1
+    rejected such a grid with LGK_ERR_DIM): two chunks per env, two Philox blocks per lane."""
+    def wide(cfg):
+        scenarios.go1_rough_full(cfg)
+        cfg.terrain.measured_points_x = [round(-1.0 + 0.1 * i, 2) for i in range(21)]
+        cfg.terrain.measured_points_y = [round(-0.8 + 0.1 * i, 2) for i in range(17)]
+        cfg.env.num_observations = 48 + 357
+    assert helpers.run_parity("go1_flat", 200, 3, extra=wide) > 0
+    assert helpers.run_parity("go1_flat", 130, 2, extra=wide, oracle_device="cuda:0") > 0
+
+
+def _ten_dof_biped(cfg):
+    """A robot no shipped task has: 10 joints (not a multiple of 4: the step kernel's scalar joint path, no bulk
+    copies of the joint rows), 11 bodies, two feet."""
+    from legged_gym_b200.sim import assets
+    names = [f"{side}_{j}_joint" for side in ("left", "right") for j in ("hip_roll", "hip_pitch", "knee", "ankle", "toe")]
+    bodies = ["pelvis"] + [f"{side}_{b}" for side in ("left", "right") for b in ("hip", "thigh", "shin", "tarsus", "toe")]
+    assets.BUILTIN_ASSETS["biped10"] = assets.RobotAsset(
+        "biped10", names, bodies, lower=[-0.5 - 0.05 * i for i in range(10)], upper=[0.6 + 0.05 * i for i in range(10)],
+        velocity=[8.0 + i for i in range(10)], effort=[40.0 + 3 * i for i in range(10)], body_mass=[1.0] * 11)
+    scenarios.go1_rough_full(cfg)
+    cfg.asset.file = "{LEGGED_GYM_ROOT_DIR}/resources/robots/biped10/urdf/biped10.urdf"
+    cfg.asset.name = "biped10"
+    cfg.asset.foot_name = "toe"
+    cfg.asset.penalize_contacts_on = ["shin", "tarsus"]
+    cfg.asset.terminate_after_contacts_on = ["pelvis"]
+    cfg.init_state.default_joint_angles = {n: 0.05 * (i - 4) for i, n in enumerate(names)}
+    cfg.control.stiffness = {"hip_roll": 100., "hip_pitch": 120., "knee": 200., "ankle": 60., "toe": 25.}
+    cfg.control.damping = {"hip_roll": 3., "hip_pitch": 3.5, "knee": 6., "ankle": 2., "toe": 1.}
+    cfg.env.num_actions = 10
+    cfg.env.num_observations = 12 + 3 * 10 + 187
+
+
+def test_ten_dof_robot_takes_the_generic_instantiation():
+    """D = 10: the <DT = 0> step kernel (scalar joint loop, Philox block per joint pair rotated into place), the
+    finish kernel and the scan kernel for a body / joint layout none of the shipped robots has, against the oracle
+    (rough terrain, all reward terms, both oracle devices), plus the substep kernels' scalar paths."""
+    assert helpers.run_parity("a1_variant", 517, 4, extra=_ten_dof_biped) > 0
+    assert helpers.run_parity("a1_variant", 96, 3, extra=_ten_dof_biped, oracle_device="cuda:0") >= 0
+
+
 @pytest.mark.parametrize("num_envs", [1, 3, 33, 127, 1800])
 def test_ragged_env_counts(num_envs):
     """env counts that are not multiples of the warp / CTA tile (config 1 uses 1800)."""
