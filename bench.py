@@ -173,7 +173,7 @@ def run_ours(args):
     N = env.num_envs
     frames = synthetic.make_frames(env, NUM_FRAMES, seed=1234 + 1000 * 2 + rank, device=device)
     # the statistics all-reduce (the path's only collective) must fire inside any timed region, however short
-    stats_interval = min(24, max(1, args.steps // 4))
+    stats_interval = min(24, max(1, args.steps // 2))
     stats = ShardedStats(env, interval=stats_interval) if world > 1 else None
     n_collectives = [0]
     stream = torch.cuda.Stream(device)
@@ -209,7 +209,10 @@ def run_ours(args):
             n_collectives[0] += 1
 
     with torch.cuda.stream(stream):
-        for i in range(max(args.warmup, 3)):
+        # (with several ranks the warm-up runs at least two statistics all-reduces: the first one sets NCCL's
+        # connections up, which is not a timed event)
+        n_warm = max(args.warmup, 3) if stats is None else max(args.warmup, 2 * stats_interval)
+        for i in range(n_warm):
             replay(i)
         t_end = time.time() + 0.3          # settle clocks under load before timing
         i = 0
