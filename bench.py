@@ -216,8 +216,8 @@ def run_ours(args):
             replay(i)
         t_end = time.time() + 0.3          # settle clocks under load before timing
         i = 0
-        while time.time() < t_end:
-            replay(i)
+        while time.time() < t_end:         # time-bounded: NO collective in here (the ranks run different counts)
+            graphs[i % NUM_FRAMES].replay()
             i += 1
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -304,6 +304,8 @@ def run_ours(args):
             "collectives_in_timed_region": collectives_timed, "stats_allreduce_interval": stats_interval if world > 1 else None,
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "launches_per_step": int(launches_per_step),
             "roofline": roofline, "cpu_baseline": cpu, "torch_cuda": torch_cuda, "clocks": clocks.summary(),
+            # workspace header word 4: finish-kernel warps that gave up waiting for a scan hand-over (must be 0)
+            "scan_timeouts": int(env._workspace.view(torch.int32)[4].item()),
         }
         print(json.dumps(line))
     if world > 1:
@@ -612,6 +614,9 @@ def main():
                          "(BASELINE.json configs[2], with --envs 16384)")
     args = ap.parse_args()
     SCENARIO = args.scenario
+    if os.environ.get("LGK_BENCH_WATCHDOG"):     # development: dump every thread's Python stack if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["LGK_BENCH_WATCHDOG"]), exit=True)
     if args.impl == "reference":
         run_reference(args)
     else:
