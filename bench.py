@@ -283,7 +283,17 @@ def run_ours(args):
         roofline = {"post_physics_step": roofline, **_actuator_roofline(env, frames, stream)}
 
     # ---- end to end through the public API with host buffers --------------------------------------
-    e2e = None if args.no_e2e else run_e2e(env, frames, args, world, device, stream)
+    e2e = None
+    if not args.no_e2e:
+        chunks = args.e2e_chunks if (N % (args.e2e_chunks * 128) == 0 and N // args.e2e_chunks >= 8192) else 1
+        if chunks > 1:
+            try:
+                e2e = run_e2e_chunked(frames, args, world, rank, device, chunks)
+            except Exception as exc:   # noqa: BLE001  (fall back to the one-env path; say why)
+                print(f"[bench] chunked e2e leg failed ({type(exc).__name__}: {exc}); falling back", file=sys.stderr)
+                e2e = None
+        if e2e is None:
+            e2e = run_e2e(env, frames, args, world, device, stream)
 
     # ---- CPU baseline (rank 0, single-GPU runs only) ------------------------------------------------
     cpu = None
@@ -312,6 +322,102 @@ def run_ours(args):
         import torch.distributed as dist
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_e2e_chunked(frames, args, world, rank, device, chunks):
+    """The host-buffer path with the GPU's envs held by `chunks` LeggedRobot instances (env-sharded exactly like ranks:
+    global env ids, own Philox offsets), each stepping on a stream of its own: PCIe is the limiter of this path (the
+    940 B observation row of every env crosses it every step), so the read-back of chunk k's results runs while chunk
+    k + 1 computes and only the first chunk's kernels and the actions' upload stay exposed.  Every step still ends
+    with a host sync on all chunks (the caller consumes the step's result before the next one)."""
+    names = ("root_states", "dof_state", "contact_forces", "torques", "actions")
+    sim_names = names[:4]
+    N = frames[0]["actions"].shape[0]
+    n = N // chunks
+    envs = [_build_env(n, device, rank * chunks + c, world * chunks) for c in range(chunks)]
+    host = [{k: fr[k].cpu().pin_memory() for k in names} for fr in frames]
+    rows = lambda t, c: t.view(N, -1)[c * n:(c + 1) * n]          # chunk c's rows of a per-env tensor
+    dev = [[{k: torch.empty_like(rows(frames[0][k], c)).contiguous() for k in names} for _ in range(2)] for c in range(chunks)]
+    streams = [torch.cuda.Stream(device) for _ in range(chunks)]
+    copy_stream = torch.cuda.Stream(device)
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    O = envs[0].obs_buf.shape[1]
+    out_h = {"obs": torch.empty(N, O, dtype=torch.float).pin_memory(), "rew": torch.empty(N, dtype=torch.float).pin_memory(),
+             "reset": torch.empty(N, dtype=torch.bool).pin_memory()}
+    h2d = sum(host[0][k].numel() * host[0][k].element_size() for k in names)
+    d2h = sum(v.numel() * v.element_size() for v in out_h.values())
+    shape = {k: dev[0][0][k].shape for k in names}
+    # one captured step() per chunk and input set (public API, graph-capturable)
+    graphs = [[None, None] for _ in range(chunks)]
+    for c, env in enumerate(envs):
+        with torch.cuda.stream(streams[c]):
+            for k in range(2):
+                for nm in names:
+                    dev[c][k][nm].copy_(rows(frames[0][nm], c).view(shape[nm]))
+                env.bind_sim_tensors(**{nm: dev[c][k][nm] for nm in sim_names})
+                env.step(dev[c][k]["actions"])
+                streams[c].synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=streams[c]):
+                    env.step(dev[c][k]["actions"])
+                graphs[c][k] = g
+    torch.cuda.synchronize()
+
+    def prefetch(i):
+        h = host[i % len(host)]
+        with torch.cuda.stream(copy_stream):
+            for c in range(chunks):
+                for nm in sim_names:
+                    dev[c][i % 2][nm].copy_(rows(h[nm], c).view(shape[nm]), non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
+    def one(i):
+        h = host[i % len(host)]
+        for c, env in enumerate(envs):
+            st = streams[c]
+            with torch.cuda.stream(st):
+                dev[c][i % 2]["actions"].copy_(rows(h["actions"], c).view(shape["actions"]), non_blocking=True)
+                st.wait_event(ready[i % 2])
+                graphs[c][i % 2].replay()
+                out_h["obs"][c * n:(c + 1) * n].copy_(env.obs_buf, non_blocking=True)
+                out_h["rew"][c * n:(c + 1) * n].copy_(env.rew_buf, non_blocking=True)
+                out_h["reset"][c * n:(c + 1) * n].copy_(env.reset_buf, non_blocking=True)
+        prefetch(i + 1)                 # the other input set: step i-1 finished with it before the last sync
+        for st in streams:
+            st.synchronize()            # the caller consumes the step's result before the next one
+
+    prefetch(0)
+    steps = max(10, min(args.steps, 200))
+    for i in range(3):
+        one(i)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    main = torch.cuda.current_stream(device)
+    e0.record(main)
+    for st in streams:
+        st.wait_event(e0)
+    for i in range(steps):
+        one(i)
+    for st in streams:
+        main.wait_stream(st)
+    e1.record(main)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    assert bool(torch.isfinite(out_h["obs"]).all()) and float(out_h["obs"].abs().sum()) > 0.0
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return {"value": round(N * world * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": round(ms / steps, 5), "chunks": chunks,
+            "path": f"pinned host buffers -> LeggedRobot.step() -> pinned host buffers, host-synchronised every step; the "
+                    f"GPU's envs are held by {chunks} env instances of {n} envs stepping on streams of their own (each "
+                    f"step() captured once through the public API and replayed), so that chunk k's read-back runs under "
+                    f"chunk k+1's kernels; next step's simulator state is copied in on a further stream meanwhile"}
 
 
 def _actuator_roofline(env, frames, stream):
@@ -373,15 +479,39 @@ def run_e2e(env, frames, args, world, device, stream):
                 d[k].copy_(h[k], non_blocking=True)
             ready[i % 2].record(copy_stream)
 
+    # env.step() on each of the two input sets, captured once through the public API (LeggedRobot.step() is
+    # graph-capturable and sync-free, tests/test_gpu_parity.py): a replay costs one launch instead of the ~10 ctypes
+    # calls of an eager step, whose host time sits on the critical path when every step ends in a host sync
+    step_graphs = []
+    zero_copy = bool(getattr(args, "e2e_zero_copy", False))
+    if zero_copy:
+        env.bind_output_tensors(obs_buf=out_h["obs"], rew_buf=out_h["rew"])
+    if not args.e2e_eager:
+        with torch.cuda.stream(stream):
+            for k in range(2):
+                env.bind_sim_tensors(**{n: dev[k][n] for n in sim_names})
+                env.step(dev[k]["actions"])            # eager once: seeds the device step counter
+                stream.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    env.step(dev[k]["actions"])
+                step_graphs.append(g)
+        torch.cuda.synchronize()
+
     def one(i):
         h, d = host[i % len(host)], dev[i % 2]
         d["actions"].copy_(h["actions"], non_blocking=True)
         stream.wait_event(ready[i % 2])
-        env.bind_sim_tensors(**{k: d[k] for k in sim_names})
-        obs, _, rew, reset, _ = env.step(d["actions"])
+        if step_graphs:
+            step_graphs[i % 2].replay()
+            obs, rew, reset = env.obs_buf, env.rew_buf, env.reset_buf
+        else:
+            env.bind_sim_tensors(**{k: d[k] for k in sim_names})
+            obs, _, rew, reset, _ = env.step(d["actions"])
         prefetch(i + 1)                 # the other input set: step i-1 finished with it before the last sync
-        out_h["obs"].copy_(obs, non_blocking=True)
-        out_h["rew"].copy_(rew, non_blocking=True)
+        if not zero_copy:
+            out_h["obs"].copy_(obs, non_blocking=True)
+            out_h["rew"].copy_(rew, non_blocking=True)
         out_h["reset"].copy_(reset, non_blocking=True)
         stream.synchronize()            # the caller consumes the step's result before the next one
 
@@ -423,8 +553,12 @@ def run_e2e(env, frames, args, world, device, stream):
         out_h["reset"].copy_(env.reset_buf, non_blocking=True)
 
     def leg_step():
-        env.step(dev[0]["actions"])
+        if step_graphs:
+            step_graphs[0].replay()
+        else:
+            env.step(dev[0]["actions"])
     t_h2d, t_d2h, t_step = leg(leg_h2d), leg(leg_d2h), leg(leg_step)
+    env._dev_step_counter = -1      # graph replays advanced the device step counter behind the host's copy
     breakdown = {"h2d_ms": round(t_h2d, 4), "h2d_gbs": round(h2d / t_h2d / 1e6, 1), "step_kernels_ms": round(t_step, 4),
                  "d2h_ms": round(t_d2h, 4), "d2h_gbs": round(d2h / t_d2h / 1e6, 1),
                  "sync_and_launch_ms": round(max(ms / steps - t_step - t_d2h, 0.0), 4),
@@ -438,8 +572,11 @@ def run_e2e(env, frames, args, world, device, stream):
         ms = float(t.item())
     return {"value": round(N * world * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": round(ms / steps, 5), "breakdown": breakdown,
-            "path": "pinned host buffers -> LeggedRobot.step() -> pinned host buffers, stream-synchronised every step; "
-                    "next step's simulator state is copied in (second stream) while this step's results are copied out"}
+            "path": "pinned host buffers -> LeggedRobot.step() ("
+                    + ("captured once per input set through the public API and replayed as a CUDA graph" if step_graphs
+                       else "eager")
+                    + ") -> pinned host buffers, stream-synchronised every step; next step's simulator state is copied in "
+                      "(second stream) while this step's results are copied out"}
 
 
 def torch_cuda_competitor(envs, device):
@@ -608,6 +745,13 @@ def main():
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="development: skip the host-buffer leg (e2e: null)")
+    ap.add_argument("--e2e-eager", action="store_true", help="e2e leg with an eager step() instead of a captured one")
+    ap.add_argument("--e2e-zero-copy", action="store_true",
+                    help="e2e leg (one env): the kernels write observations and rewards straight into the pinned host buffers "
+                         "(bind_output_tensors on mapped host memory) instead of a device->host copy after the step")
+    ap.add_argument("--e2e-chunks", type=int, default=1,
+                    help="e2e leg: the envs of a GPU as this many env instances stepping on streams of their own, so that "
+                         "the read-back of one chunk's observations runs under the next chunk's kernels (1 = one env)")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--scenario", default=SCENARIO,
                     help="parity-test scenario to time instead of the headline one, e.g. go1_rough_actuator "
