@@ -110,10 +110,15 @@ class ClockSampler:
             time.sleep(0.002)
 
     def __enter__(self):
-        if self.nv is not None:
+        if self.nv is not None and self._thr is None:
             self._thr = threading.Thread(target=self._run, daemon=True)
             self._thr.start()
         return self
+
+    def mark(self):
+        """The timed region starts here: summary() reports the samples from this point on when there are at least
+        three of them (a 20-step region is shorter than one sampling period), else the settle loop's as well."""
+        self._mark = len(self.samples)
 
     def __exit__(self, *a):
         self._stop.set()
@@ -123,9 +128,10 @@ class ClockSampler:
     def summary(self):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
-        s = sorted(self.samples)
+        timed = self.samples[getattr(self, "_mark", 0):]
+        s = sorted(timed if len(timed) >= 3 else self.samples)
         return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "samples_in_timed_region": len(timed)}
 
 
 def _dist_setup(n_gpus):
@@ -173,7 +179,10 @@ def run_ours(args):
     N = env.num_envs
     frames = synthetic.make_frames(env, NUM_FRAMES, seed=1234 + 1000 * 2 + rank, device=device)
     # the statistics all-reduce (the path's only collective) must fire inside any timed region, however short
-    stats_interval = min(24, max(1, args.steps // 2))
+    # production cadence is every 24 steps; a shorter timed region gets exactly one all-reduce, half-way through it
+    # (see `phase` below).  Measured at 2 GPUs, 20 steps: each all-reduce in the window costs ~45 us -- its own CTA
+    # and the three small kernels around it take SM slots from the scan kernel's all-resident grid for one step
+    stats_interval = min(24, max(1, args.steps))
     stats = ShardedStats(env, interval=stats_interval) if world > 1 else None
     n_collectives = [0]
     stream = torch.cuda.Stream(device)
@@ -203,9 +212,13 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # phase of the periodic all-reduce against the timed window: half an interval in, so that no all-reduce is the
+    # window's very last event (its whole latency would then be exposed, which no steady-state step sees)
+    phase = stats_interval // 2
+
     def replay(i):
         graphs[i % NUM_FRAMES].replay()
-        if stats is not None and stats.after_step(i) is not None:
+        if stats is not None and stats.after_step(i + phase) is not None:
             n_collectives[0] += 1
 
     with torch.cuda.stream(stream):
@@ -214,6 +227,12 @@ def run_ours(args):
         n_warm = max(args.warmup, 3) if stats is None else max(args.warmup, 2 * stats_interval)
         for i in range(n_warm):
             replay(i)
+        # the clock sampler (NVML set-up, thread start) comes up BEFORE the ranks line up: started behind the barrier it
+        # skewed the ranks' windows against each other by its own start-up time, and with an all-reduce inside the window
+        # the early rank then waits for the late one.  It samples from the settle loop on (the same graph replays as
+        # the timed region), marked below.
+        sampler = ClockSampler(local)
+        sampler.__enter__()
         t_end = time.time() + 0.3          # settle clocks under load before timing
         i = 0
         while time.time() < t_end:         # time-bounded: NO collective in here (the ranks run different counts)
@@ -221,7 +240,8 @@ def run_ours(args):
             i += 1
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with ClockSampler(local) as clocks:
+        with sampler as clocks:
+            clocks.mark()
             n_collectives[0] = 0
             e0.record(stream)
             for i in range(args.steps):
