@@ -30,6 +30,28 @@
 
 #define LGK_SCAN_MIN_CTAS LGK_SCAN_REG_CTAS
 
+#ifdef LGK_SCAN_STAGED
+// A/B variant (north star: "shared-memory or TMA-staged terrain tiles"), built with -DLGK_SCAN_STAGED: the cells an
+// env's scan can touch -- a window of ST_ROWS x ST_COLS int16 of the min-of-three table around the root -- are staged
+// into the warp's shared memory by ST_ROWS 64-byte bulk async copies (double-buffered: env k + 1 travels while env k
+// is scanned), and the per-point gathers read shared memory instead of L2.  Envs whose window leaves the table fall
+// back to the gathers.  Measured against the default: DESIGN.md section 3.
+constexpr int ST_ROWS = 24, ST_COLS = 32;
+template <bool MUL_RCP, int NP>
+__device__ __forceinline__ void scan_gather_tile(const StepArgs& a, const ScanEnv& e, const ScanLane (&ln)[NP],
+                                                 int (&raw)[NP], const short* tile, int base32) {
+  const LgkConsts& c = a.c;
+  const float inv_hs = 1.0f / c.horizontal_scale;
+  const int max_px = c.terrain_rows - 2, max_py = c.terrain_cols - 2;
+#pragma unroll
+  for (int it = 0; it < NP; ++it) {
+    const int cell = scan_cell<MUL_RCP>(e, ln[it].p, a.one, c.border_size, inv_hs, c.horizontal_scale, max_px, max_py,
+                                        ST_COLS);
+    raw[it] = tile[cell - base32];
+  }
+}
+#endif
+
 template <bool TAPS, bool MUL_RCP, int NP>   // NP = 0: any H, passes in chunks of 8, constants re-read per env
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_SCAN_MIN_CTAS)
 lgk_scan_kernel(const __grid_constant__ StepArgs a) {
@@ -46,6 +68,15 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
   __shared__ int s_hp_all[LGK_WARPS_PER_CTA][SCAN_GROUP * RS];
   float* s_es = s_es_all[wic];
   int* s_hp = s_hp_all[wic];
+#ifdef LGK_SCAN_STAGED
+  __shared__ __align__(128) short s_tile_all[LGK_WARPS_PER_CTA][2][ST_ROWS * ST_COLS];
+  __shared__ __align__(8) uint64_t s_bar_all[LGK_WARPS_PER_CTA][2];
+  short (*s_tile)[ST_ROWS * ST_COLS] = s_tile_all[wic];
+  uint64_t* s_bar = s_bar_all[wic];
+  if (lane == 0) { mbar_init(s_bar, 1); mbar_init(s_bar + 1, 1); }
+  __syncwarp();
+  unsigned st_phase = 0;   // bit b: parity of buffer b's barrier
+#endif
 
   const int epg = a.scan_epc;   // envs per group (= per flag): 8, fewer for small N
 
@@ -65,6 +96,34 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
     clip_h = __any_sync(LGK_FULL_MASK, clip_h);
   }
 
+#ifdef LGK_SCAN_STAGED
+  float st_rc = 1.0e9f;   // window half-width in cells (+1.5 cells of margin); staging is off when it does not fit
+  if (!GENERIC && !(c.flags & LGK_F_TERRAIN_PLANE)) {
+    float r2m = 0.f;
+#pragma unroll
+    for (int it = 0; it < CH; ++it) r2m = fmaxf(r2m, fmaf(ln[it].p.x, ln[it].p.x, ln[it].p.y * ln[it].p.y));
+#pragma unroll
+    for (int o = 16; o; o >>= 1) r2m = fmaxf(r2m, __shfl_xor_sync(LGK_FULL_MASK, r2m, o));
+    st_rc = sqrtf(r2m) / c.horizontal_scale + 1.5f;
+  }
+  const bool st_on = !clip_h && a.b.measured_heights == nullptr && 2.f * st_rc + 1.f <= (float)ST_ROWS &&
+                     2.f * st_rc + 8.f <= (float)ST_COLS && (c.terrain_pitch & 7) == 0;
+  const float st_inv_hs = 1.0f / c.horizontal_scale;
+  // window of env `el` of the group (operands in s_es) -> buffer `buf`; returns ix0 * ST_COLS + iy0, or -1 (not staged)
+  auto stage = [&](int el, int buf) -> int {
+    if (!st_on) return -1;
+    const float cx = (s_es[el * 8 + 4] + c.border_size) * st_inv_hs, cy = (s_es[el * 8 + 5] + c.border_size) * st_inv_hs;
+    if (!(fabsf(cx) < 1.0e6f && fabsf(cy) < 1.0e6f)) return -1;
+    const int ix0 = (int)floorf(cx - st_rc), iy0 = ((int)floorf(cy - st_rc)) & ~7;
+    if (ix0 < 0 || iy0 < 0 || ix0 + ST_ROWS > c.terrain_rows - 1 || iy0 + ST_COLS > c.terrain_pitch) return -1;
+    if (lane == 0) mbar_expect_tx(s_bar + buf, ST_ROWS * ST_COLS * 2);
+    __syncwarp();
+    if (lane < ST_ROWS)
+      bulk_g2s(s_tile[buf] + lane * ST_COLS, a.b.height_min3 + (size_t)(ix0 + lane) * c.terrain_pitch + iy0, ST_COLS * 2,
+               s_bar + buf);
+    return ix0 * ST_COLS + iy0;
+  };
+#endif
   pdl_wait();   // root_states belong to the simulator: written by whatever ran before this launch
   // The whole grid is resident: the step kernel behind this launch may take SM slots as soon as warps here retire.
   pdl_launch_dependents();
@@ -87,10 +146,16 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
       d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
     }
     __syncwarp();
+#ifdef LGK_SCAN_STAGED
+    int st_base = stage(0, 0), st_base_next = -1;
+#endif
 
 #pragma unroll 1
     for (int el = 0; el < ne; ++el) {
       const int env = env0 + el;
+#ifdef LGK_SCAN_STAGED
+      if (el + 1 < ne) st_base_next = stage(el + 1, (el + 1) & 1);
+#endif
       const float4 ea = reinterpret_cast<const float4*>(s_es + el * 8)[0];
       const float4 eb = reinterpret_cast<const float4*>(s_es + el * 8)[1];
       ScanEnv e;
@@ -115,9 +180,23 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
         } else if (clip_h || mrow != nullptr) {   // (warp-uniform)
           hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
         } else {          // the common case: no final clip needed, heights not materialised
+#ifdef LGK_SCAN_STAGED
+          if (st_base >= 0) {   // (warp-uniform)
+            const int buf = el & 1;
+            mbar_wait(s_bar + buf, (st_phase >> buf) & 1u);
+            st_phase ^= 1u << buf;
+            int raw[CH];
+            scan_gather_tile<MUL_RCP, CH>(a, e, ln, raw, s_tile[buf], st_base);
+            hsum += scan_emit<TAPS, CH, false, false, false>(a, e.zo, ln, raw, 0, lane, rnd, orow, trow, nullptr, false);
+          } else
+#endif
           hsum += scan_passes<TAPS, MUL_RCP, CH, false, false>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
         }
       }
+#ifdef LGK_SCAN_STAGED
+      st_base = st_base_next;
+      __syncwarp();   // every lane has read the tile before the copy after next overwrites it
+#endif
       s_hp[el * RS + lane] = hsum;
     }
     __syncwarp();
