@@ -55,7 +55,7 @@ def config_dict(envs_per_gpu, world, decimation=4, num_obs=235, reward_terms=21)
     """`config` of the JSON line: the same dict from both arms (the driver compares them key by key)."""
     return {"workload": workload_name(envs_per_gpu, decimation), "envs_per_gpu": envs_per_gpu,
             "envs_total": envs_per_gpu * world, "num_obs": num_obs, "reward_terms": reward_terms,
-            "rng": "ours: in-kernel Philox4x32-10; reference: torch CPU generator",
+            "rng": "ours: in-kernel Philox4x32-7; reference: torch CPU generator",
             "l2": f"inputs cycle through {NUM_FRAMES} state frames resident in HBM "
                   f"({NUM_FRAMES * envs_per_gpu * 448 / 1e6:.0f} MB) -- larger than L2 at the default size",
             "parallelism": f"env-sharded x{world}, terrain replica per GPU, NCCL all-reduce of episode statistics "
@@ -292,8 +292,11 @@ def run_ours(args):
             traffic = json.load(open(tpath)).get(str(N))
         except Exception:   # noqa: BLE001
             traffic = None
-    roofline = {"kernel": "post_physics_step = lgk_scan_kernel + lgk_step_kernel + lgk_finish_kernel "
-                          "(chained with programmatic dependent launch, overlapping; timed as one unit)",
+    chain3 = os.environ.get("LGK_CHAIN", "")[:1] == "3"
+    roofline = {"kernel": ("post_physics_step = lgk_scan_kernel + lgk_step_kernel + lgk_finish_kernel (LGK_CHAIN=3)" if chain3
+                           else "post_physics_step = lgk_step_kernel + lgk_scan_kernel<FUSED> (height scan, reward "
+                                "sums, reset tail, statistics)") +
+                          " (chained with programmatic dependent launch; timed as one unit)",
                 "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
                 "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": traffic,
                 "algorithmic_bytes_per_env_step": bpe, "kernel_ms": round(k_ms, 5), "peak_source": peak_src,
@@ -334,8 +337,9 @@ def run_ours(args):
             "collectives_in_timed_region": collectives_timed, "stats_allreduce_interval": stats_interval if world > 1 else None,
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "launches_per_step": int(launches_per_step),
             "roofline": roofline, "cpu_baseline": cpu, "torch_cuda": torch_cuda, "clocks": clocks.summary(),
-            # workspace header word 4: finish-kernel warps that gave up waiting for a scan hand-over (must be 0)
-            "scan_timeouts": int(env._workspace.view(torch.int32)[4].item()),
+            # workspace header word 5 (LgkWorkspace.scan_timeouts): warps that gave up waiting for a hand-over flag
+            # (three-launch chain only; must be 0)
+            "scan_timeouts": int(env._workspace.view(torch.int32)[5].item()),
         }
         print(json.dumps(line))
     if world > 1:

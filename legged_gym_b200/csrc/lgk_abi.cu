@@ -5,6 +5,7 @@
 
 extern "C" {
 int lgk_post_physics_step_impl(const LgkConsts*, const LgkBuffers*, cudaStream_t);
+int lgk_chain_mode(int);
 int lgk_reset_idx_impl(const LgkConsts*, const LgkBuffers*, const long long*, int, cudaStream_t);
 int lgk_pre_reward_state_impl(const LgkConsts*, const LgkBuffers*, cudaStream_t);
 int lgk_build_height_min3_impl(const int16_t*, int, int, int16_t*, int, cudaStream_t);
@@ -220,7 +221,8 @@ int lgk_lstm_reset_hidden(int32_t num_envs, int32_t num_dof, const int32_t* env_
 int lgk_post_physics_step(const LgkConsts* c, const LgkBuffers* b, void* stream) {
   int rc = check_step(c, b);
   if (rc) return rc;
-  g_launches += 2 + (c->num_height_points > 0 ? 1 : 0);   // (scan kernel,) step kernel, finish kernel
+  // default: step kernel, tail kernel (scan, rewards, statistics); LGK_CHAIN=3: (scan kernel,) step kernel, finish kernel
+  g_launches += lgk_chain_mode(c->num_envs) ? 2 : 2 + (c->num_height_points > 0 ? 1 : 0);
   return lgk_post_physics_step_impl(c, b, (cudaStream_t)stream);
 }
 

@@ -71,7 +71,13 @@ static_assert(sizeof(LgkWorkspace) <= LGK_WS_HEADER_BYTES, "workspace header too
 
 __host__ __device__ inline int lgk_max_warps(int num_envs) { return (num_envs + 3) / 4 + LGK_WARPS_PER_CTA; }
 
-// ---- Philox4x32-10 (counter-based; same generator family torch/curand use) ----------
+// ---- Philox4x32-R (counter-based; same generator family torch/curand use) ----------
+// R = LGK_PHILOX_ROUNDS = 7: the fewest rounds with which Philox4x32 passes BigCrush (Salmon et al., SC'11, table 2;
+// Random123 ships it as philox4x32_R(7)); the noise fields of an observation row do not need the safety margin of the
+// 10-round default of curand / torch, and every round is 4 instructions per block (-DLGK_PHILOX_ROUNDS=10 builds that)
+#ifndef LGK_PHILOX_ROUNDS
+#define LGK_PHILOX_ROUNDS 7
+#endif
 struct Philox {
   static __device__ __forceinline__ uint4 round(uint4 ctr, uint2 key) {
     const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
@@ -106,7 +112,7 @@ enum : unsigned int {
 };
 __device__ __forceinline__ uint4 lgk_philox(const uint64_t seed, unsigned long long step, unsigned int env_global,
                                             unsigned int block) {
-  return Philox::gen<10>(make_uint4(env_global, block, (unsigned int)step, (unsigned int)(step >> 32)),
+  return Philox::gen<LGK_PHILOX_ROUNDS>(make_uint4(env_global, block, (unsigned int)step, (unsigned int)(step >> 32)),
                          make_uint2((unsigned int)seed, (unsigned int)(seed >> 32)));
 }
 
@@ -115,7 +121,7 @@ __device__ __forceinline__ uint4 philox_keyed(const unsigned int (&pk)[20], unsi
                                               unsigned int env_global, unsigned int block) {
   uint4 ctr = make_uint4(env_global, block, (unsigned int)step, (unsigned int)(step >> 32));
 #pragma unroll
-  for (int r = 0; r < 10; ++r) ctr = Philox::round(ctr, make_uint2(pk[2 * r], pk[2 * r + 1]));
+  for (int r = 0; r < LGK_PHILOX_ROUNDS; ++r) ctr = Philox::round(ctr, make_uint2(pk[2 * r], pk[2 * r + 1]));
   return ctr;
 }
 
@@ -173,6 +179,7 @@ __device__ __forceinline__ float wrap_to_pi(float a) {
   return m;
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
 // tanh to ~2 ulp with two MUFU ops instead of the ~25-instruction library routine: 1 - 2 / (exp(2x) + 1) away
@@ -234,6 +241,7 @@ __device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, u
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 // generic-proxy shared-memory writes -> visible to the async proxy (before a bulk store reads them)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

@@ -217,8 +217,268 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tail kernel: the second (and last) launch of the two-launch chain, behind the step kernel -- the height scan of
+// lgk_scan_kernel plus everything that is left of post_physics_step once the scan is known, by the CTAs that did the
+// scan:
+//   scan      as above, warp w of a CTA takes group w of the CTA's unit of 4 groups (<= 64 consecutive envs).  Envs the
+//             step kernel reset take their operands from the side row (old pose, root z after the reset, :227), so
+//             their columns are computed once and there is no fix-up pass
+//   rewards   compute_reward's sums (:195-212) over the step kernel's term values, after a CTA barrier: lanes = envs,
+//             rows warp-uniform (warp w: envs 32 (w & 1) .. + 31 of the unit, rows w >> 1, + 2, ...), so scale and source
+//             row come from the parameter block through uniform registers and every access to the [R,N] episode-sum
+//             rows / the [term][N] value table is a coalesced row segment; r = value * scale, sum += r in place (zeroed
+//             for reset envs after the statistics took it, :184-185); base_height from the scan's height sums, which
+//             never leave the CTA.  The scaled values meet in shared memory ([row][64]) and one thread per env adds
+//             them up in the reference's order, clips (only_positive_rewards) and adds the termination term
+//   resets    the root rows the step kernel held back while poses were still being read (:414-434) are stored
+//   lists     CTA 0 compacts the step kernel's per-tile bitmasks into the ascending id lists (:150, :342)
+//   counters  the CTA that finishes last publishes extras["episode"] (:182-190) and advances the step counter (:119)
+// The row loads of a unit wait under the arithmetic of the other CTAs of the SM: what was a 16 us launch of
+// dependent round trips at the end of the three-launch chain costs a few per cent of the scan's issue slots here.
+// a.fused == 2: no grid-wide wait for the step kernel -- a warp waits for the flags of the step CTAs that own its
+// group's envs, so the scan starts under the step kernel's last wave.
+#define TAIL_UNIT (4 * SCAN_GROUP_FUSED)
+// compute_reward (:195-212) for one env per thread: every row in the reference's order -- r = value * scale, sum += r
+// in place (zeroed for reset envs after the statistics took it, :184-185), reward += r; only_positive clip; the
+// termination row after the clip.  The loads of up to TAIL_BATCH rows (sum and value each) are in flight together:
+// one or two L2 round trips per env in all.  Out of line on purpose: inlined into the scan loop -- two dozen per-lane
+// constants live across it under a tight register cap -- the compiler rematerialised every address in every row;
+// as a function of its own it has the registers to keep a batch of rows.  Everything comes by value or through
+// shared memory (rows: per-row {source row, scale, kind}, filled from the parameter block once per CTA).
+struct TailRow { float scale; int kind; };   // kind 1: base_height, 2: termination
+#define TAIL_BATCH 8
+static __device__ __noinline__ void tail_rewards_env(float* gp, unsigned n_envs, int nrows, int env, bool reset, float bh,
+                                                     float target, float term_v, bool only_positive,
+                                                     float* __restrict__ stat, const float* const* __restrict__ srcs,
+                                                     const TailRow* __restrict__ rows, float* __restrict__ rew_out) {
+  float rew = 0.f;
+  bool clip_due = only_positive;
+  const int last = nrows - 1;
+#pragma unroll 1
+  for (int r0 = 0; r0 < nrows; r0 += TAIL_BATCH) {
+    // (slots past the last row shadow it: every load is unconditional, only the stores look at the row index)
+    float s[TAIL_BATCH], v[TAIL_BATCH];
+#pragma unroll
+    for (int j = 0; j < TAIL_BATCH; ++j) {
+      const int r = min(r0 + j, last);
+      s[j] = gp[(unsigned)r * n_envs];   // (element offsets fit 32 bits: rows x envs < 2^32)
+      v[j] = srcs[r][env];
+    }
+#pragma unroll
+    for (int j = 0; j < TAIL_BATCH; ++j) {
+      const int r = min(r0 + j, last);
+      const bool live = r0 + j <= last;
+      const TailRow t = rows[r];
+      float val = v[j];
+      if (t.kind != 0) {
+        if (t.kind == 1) { const float d = (val - bh) - target; val = d * d; }
+        else if (live) {   // the termination row: added after the positive clip (:206-212)
+          val = term_v;
+          if (clip_due) { rew = fmaxf(rew, 0.f); clip_due = false; }
+        }
+      }
+      const float rr = mul_rn(val, t.scale);
+      const float total = add_rn(s[j], rr);
+      rew = add_rn(rew, live ? rr : 0.f);
+      if (live) {
+        gp[(unsigned)r * n_envs] = reset ? 0.f : total;
+        if (reset) atomicAdd(stat + r, total);
+      }
+    }
+  }
+  if (clip_due) rew = fmaxf(rew, 0.f);
+  *rew_out = rew;
+}
+template <bool TAPS, bool MUL_RCP, int NP>   // NP = 0: any H (0 included), passes in chunks of 8, constants re-read per env
+__global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_TAIL_CTAS_PER_SM)
+lgk_tail_kernel(const __grid_constant__ StepArgs a) {
+  const LgkConsts& c = a.c;
+  const LgkBuffers& b = a.b;
+  constexpr bool GENERIC = NP == 0;
+  constexpr int CH = GENERIC ? 8 : NP;   // passes per chunk
+  constexpr int GS = SCAN_GROUP_FUSED;
+  const int N = c.num_envs, H = c.num_height_points, O = c.num_obs;
+  const int OH = 12 + 3 * c.num_dof;
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const bool add_noise = c.flags & LGK_F_ADD_NOISE;
+
+  __shared__ __align__(16) float s_es_all[LGK_WARPS_PER_CTA][GS * 8];
+  __shared__ int s_hp_all[LGK_WARPS_PER_CTA][GS * RS];   // per-lane partial height sums of the group's envs
+  __shared__ int s_hs[TAIL_UNIT];             // height sum of each env of the unit
+  __shared__ unsigned char s_fl[TAIL_UNIT];   // bit 0: reset, bit 1: time-out (the step kernel's decision)
+  __shared__ unsigned s_last;
+  __shared__ __align__(8) TailRow s_rows[LGK_MAX_REWARDS];
+  __shared__ const float* s_srcs[LGK_MAX_REWARDS];
+  if (threadIdx.x < LGK_MAX_REWARDS) {   // (read after the unit's first CTA barrier)
+    const int r = threadIdx.x;
+    TailRow t;
+    s_srcs[r] = a.row_src[r];
+    t.scale = a.row_scale[r];
+    t.kind = r == a.bh_row ? 1 : (r == c.num_rewards ? 2 : 0);
+    s_rows[r] = t;
+  }
+  float* s_es = s_es_all[wic];
+  int* s_hp = s_hp_all[wic];
+
+  const int epg = a.scan_epc;   // envs per group: 16, fewer for small N
+
+  // (The step kernel lets this grid go only after its own wait, so the header read below is never ahead of the
+  // previous step's last kernel.)
+  const bool by_flags = a.fused == 2;
+  if (!by_flags) pdl_wait();
+  pdl_launch_dependents();
+
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  const unsigned long long csc = ws->step_counter + 1ull;   // common_step_counter after += 1 (:119)
+  const unsigned stamp = ws->launch_seq + 1u;
+  const int nchunks = GENERIC ? (H + 255) / 256 : 1;
+  // CTA 0 compacts the id lists instead of walking units (the first CTA, so that it is resident from the start)
+  const int scan_ctas = (int)gridDim.x - 1;
+  const bool list_cta = blockIdx.x == 0;
+  if (list_cta) {
+    if (by_flags) pdl_wait();   // needs every step CTA's masks
+    compact_id_lists<LGK_CTA_THREADS>(a, a.step_grid);
+  }
+  const int nb_envs = a.n_big * a.per;   // envs of the step kernel's full-size CTAs (the rest: per_small each)
+  const int unit_envs = LGK_WARPS_PER_CTA * epg;
+  const int n_units = (N + unit_envs - 1) / unit_envs;
+  const int nrows = a.num_rows;
+
+#pragma unroll 1
+  for (int unit = list_cta ? n_units : (int)blockIdx.x - 1; unit < n_units; unit += scan_ctas) {   // (CTA-uniform)
+    const int uenv0 = unit * unit_envs;
+    const int une = min(unit_envs, N - uenv0);
+    // this lane's scan offsets and noise factors (same for every env).  Read per unit, not once per CTA: they must not
+    // be live across the out-of-line reward pass below (the compiler kept them in local memory for the whole kernel
+    // and re-read them for every env); most CTAs take one unit anyway
+    ScanLane ln[CH];
+    bool clip_h = false;
+    if (!GENERIC) {
+#pragma unroll
+      for (int it = 0; it < CH; ++it) {
+        ln[it] = scan_lane_consts<TAPS>(a, it * 32 + lane, OH);
+        // the scan columns are bounded by obs_scale_height * 1 + noise: when that is inside clip_observations for
+        // every column (warp-uniform), the final clip is the identity and is skipped
+        const float ns = TAPS ? ln[it].ka : ln[it].ka * 32768.0f;
+        clip_h |= !(fabsf(c.obs_scale_height) + fabsf(ns) <= c.clip_obs);
+      }
+      clip_h = __any_sync(LGK_FULL_MASK, clip_h);
+    }
+    // ---- this warp's group: scan ------------------------------------------------------------------------------
+    const int env0 = uenv0 + wic * epg;
+    const int ne = max(0, min(epg, N - env0));
+    if (by_flags && ne > 0) {   // the step CTAs that own envs env0 .. env0 + ne - 1 are through (one lane per flag)
+      const int el = env0 + ne - 1;
+      const int f0 = env0 < nb_envs ? env0 / a.per : a.n_big + (env0 - nb_envs) / a.per_small;
+      const int f1 = el < nb_envs ? el / a.per : a.n_big + (el - nb_envs) / a.per_small;
+      if (f0 + lane <= f1) wait_scan_flag(a, ws, a.scan_flags + f0 + lane, stamp);
+      __syncwarp();
+    }
+    if (ne > 0 && lane < nrows) {   // the reward pass's rows of this group's envs: on their way into L2 under the scan
+      prefetch_l2(b.episode_sums + (size_t)lane * N + env0);
+      prefetch_l2(a.row_src[lane] + env0);
+    }
+    if (lane < ne) {
+      const bool rst = b.reset_buf[env0 + lane] != 0, tmo = b.time_out_buf[env0 + lane] != 0;
+      s_fl[wic * epg + lane] = (unsigned char)((rst ? 1 : 0) | (tmo ? 2 : 0));
+      if (a.scan_first) {
+        float4* d = reinterpret_cast<float4*>(s_es + lane * 8);
+        if (rst) {   // reset this step: the old pose with the new root z, as the step kernel left it
+          const float4* sd = reinterpret_cast<const float4*>(a.side + (size_t)(env0 + lane) * LGK_SIDE_FLOATS);
+          d[0] = sd[0];
+          d[1] = sd[1];
+        } else {
+          const float* r = b.root_states + (size_t)(env0 + lane) * 13;
+          const ScanEnv e = scan_env_operands(r[0], r[1], r[2], r[5], r[6]);
+          d[0] = make_float4(e.k_t.x, e.k_t.y, e.k_c.x, e.k_c.y);
+          d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
+        }
+      }
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int el = 0; el < ne; ++el) {
+      const int env = env0 + el;
+      const float4 ea = reinterpret_cast<const float4*>(s_es + el * 8)[0];
+      const float4 eb = reinterpret_cast<const float4*>(s_es + el * 8)[1];
+      ScanEnv e;
+      e.k_t = make_float2(ea.x, ea.y);
+      e.k_c = make_float2(ea.z, ea.w);
+      e.r2 = make_float2(eb.x, eb.y);
+      e.yw = eb.z;
+      e.zo = eb.w;
+      float* orow = b.obs_buf + (size_t)env * O + OH;
+      const float* trow = (TAPS && add_noise) ? b.tap_noise + (size_t)env * O + OH : nullptr;
+      float* mrow = b.measured_heights != nullptr ? b.measured_heights + (size_t)env * H : nullptr;
+      const unsigned eg = (unsigned)(c.env_id_offset + env);
+      int hsum = 0;
+#pragma unroll 1
+      for (int ch = 0; ch < nchunks; ++ch) {
+        uint4 rnd = make_uint4(0, 0, 0, 0);
+        if (!TAPS && add_noise) rnd = philox_keyed(a.pk, csc, eg, LGK_SITE_NOISE_SCAN + 32u * (unsigned)ch + lane);
+        if (GENERIC) {
+#pragma unroll
+          for (int it = 0; it < CH; ++it) ln[it] = scan_lane_consts<TAPS>(a, (ch * CH + it) * 32 + lane, OH);
+          hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, ch * CH, lane, rnd, orow, trow, mrow, true);
+        } else if (clip_h || mrow != nullptr) {   // (warp-uniform)
+          hsum += scan_passes<TAPS, MUL_RCP, CH, true>(a, e, ln, 0, lane, rnd, orow, trow, mrow, false);
+        } else {          // the common case: no final clip needed, heights not materialised
+          hsum += scan_passes<TAPS, MUL_RCP, CH, false, false>(a, e, ln, 0, lane, rnd, orow, trow, nullptr, false);
+        }
+      }
+      s_hp[el * RS + lane] = hsum;
+    }
+    __syncwarp();
+    {   // sum over the points of each env's heights: lane (q, k) adds half of the 32 partial sums of env k
+      const int k = lane & (GS - 1), q = lane / GS;
+      const int* hp = s_hp + k * RS + q * GS;
+      int hs = 0;
+#pragma unroll
+      for (int i = 0; i < GS; ++i) hs += hp[i];
+#pragma unroll
+      for (int o = GS; o < 32; o <<= 1) hs += __shfl_xor_sync(LGK_FULL_MASK, hs, o);
+      if (q == 0 && k < ne) s_hs[wic * epg + k] = hs;
+    }
+    __syncthreads();   // every group of the unit is scanned: height sums and flags are in shared memory
+    // ---- rewards of the unit: one env per thread (warps 0, 1), rows in the reference's order ----------------------
+    if ((int)threadIdx.x < une) {
+      const int u = threadIdx.x, env = uenv0 + u;
+      const unsigned fl = s_fl[u];
+      const bool reset = fl & 1u, time_out = fl & 2u;
+      float bh = 0.f;   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height)
+      if (a.scan_first && a.bh_active) bh = ((float)s_hs[u] * c.vertical_scale) / (float)H;
+      tail_rewards_env(b.episode_sums + env, (unsigned)N, nrows, env, reset, bh, c.base_height_target,
+                       (reset && !time_out) ? 1.f : 0.f, (c.flags & LGK_F_ONLY_POSITIVE) != 0,
+                       a.stat_copies + (size_t)((env >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS, s_srcs, s_rows, b.rew_buf + env);
+    }
+    if (wic >= 2) {   // the root rows the step kernel held back while poses were still being read (:414-434)
+      const int u = (wic & 1) * 32 + lane;
+      unsigned m = __ballot_sync(LGK_FULL_MASK, u < une && (s_fl[u < une ? u : 0] & 1u));
+      for (; m; m &= m - 1u) {   // (warp-uniform)
+        const int e = uenv0 + (wic & 1) * 32 + __ffs(m) - 1;
+        if (lane < 13) b.root_states[(size_t)e * 13 + lane] = a.side[(size_t)e * LGK_SIDE_FLOATS + 8 + lane];
+      }
+    }
+    __syncthreads();   // shared memory is free for the next unit
+  }
+  // ---- the last CTA to get here publishes the step's statistics and advances the counters ------------------------
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    s_last = (atomicAdd(&ws->fin_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (!s_last) return;   // (CTA-uniform)
+  __threadfence();
+  if (by_flags) pdl_wait();   // (every step CTA has handed over: returns at once; the dependency is now formal)
+  publish_step_statistics(a, csc);
+}
+
 template <bool TAPS, bool MUL_RCP, int NP>
 static int launch_scan(const StepArgs& args, int grid, cudaStream_t stream) {
+  if (args.fused)   // (the id-list CTA is part of scan_grid)
+    return (int)lgk_launch_pdl(lgk_tail_kernel<TAPS, MUL_RCP, NP>, dim3(grid), dim3(LGK_CTA_THREADS), 0, stream, args);
   return (int)lgk_launch_pdl(lgk_scan_kernel<TAPS, MUL_RCP, NP>, dim3(grid), dim3(LGK_CTA_THREADS), 0, stream, args);
 }
 

@@ -286,149 +286,20 @@ static __device__ __noinline__ void tile_store_fallback(const StepArgs& a, const
 #pragma unroll 1
   for (int i = t; i < ne * D; i += nt) { la[i] = sm[a.L.act + i]; lv[i] = sm[a.L.ldv + i]; }
 }
-// ---------------------------------------------------------------------------------------------
-// The two once-per-step serial jobs of post_physics_step.  Both run inside the finish kernel (below), each on one CTA:
-//   1. ordered compaction of the per-tile reset / resample bitmasks into ascending id lists (:150, :342) -- needs
-//      the step kernel's masks only, so a dedicated CTA of the finish grid does it next to the reward CTAs
-//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119) -- needs every reward CTA's
-//      sums, so the CTA that finishes last does it (ticket counter in the workspace header)
-// (earlier versions: a finisher CTA inside the fused tile kernel, 16-20 us on one busy SM; then an epilogue launch of
-// its own, 7-11 us at the end of the chain with the GPU otherwise idle)
-#define FIN_THREADS 128
-#define STAT_COPIES 64   // replicated accumulator rows of the reset statistics (see lgk_finish_kernel)
-template <int THREADS>
-__device__ __forceinline__ void compact_id_lists(const StepArgs& a, int n_ctas) {
-  constexpr int NW = THREADS / 32;
-  __shared__ int s_scan[2][NW + 1];
-  const LgkBuffers& b = a.b;
-  const int N = a.c.num_envs;
-  const int tid = threadIdx.x, lane = tid & 31, wic = tid >> 5;
-  const LgkWorkspace* ws = reinterpret_cast<const LgkWorkspace*>(b.workspace);
-  const int nt = n_ctas * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
-  const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
-  const unsigned* rm = mask_base;
-  const unsigned* sv = mask_base + lgk_max_warps(N);
-  // slots of sub-tiles past a CTA's range were never written this launch: skip them
-  const bool one_sub = a.max_sub == 1;
-  auto slot_env0 = [&](int t) {
-    if (one_sub) return t < a.n_big ? t * a.per : a.n_big * a.per + (t - a.n_big) * a.per_small;
-    const int cta = t / a.max_sub, k = t - cta * a.max_sub;
-    return cta * a.per + k * TILE;
-  };
-  auto slot_ok = [&](int t) {
-    if (one_sub) return true;
-    const int cta = t / a.max_sub, k = t - cta * a.max_sub;
-    return k * TILE < min(a.per, N - cta * a.per);
-  };
-  const int per = (nt + THREADS - 1) / THREADS;   // 16 at 65536 envs
-  const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
-  int c0 = 0, c1 = 0;
-#pragma unroll 8
-  for (int t = t0; t < t1; ++t)
-    if (slot_ok(t)) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
-  // block-wide exclusive scan of (c0, c1): shuffles inside a warp, warp totals through shared memory
-  int i0 = c0, i1 = c1;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int y0 = __shfl_up_sync(LGK_FULL_MASK, i0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, i1, o);
-    if (lane >= o) { i0 += y0; i1 += y1; }
-  }
-  if (lane == 31) { s_scan[0][wic] = i0; s_scan[1][wic] = i1; }
-  __syncthreads();
-  if (wic == 0) {   // exclusive scan of the warp totals
-    int w0 = lane < NW ? s_scan[0][lane] : 0, w1 = lane < NW ? s_scan[1][lane] : 0;
-    const int t0w = w0, t1w = w1;
-#pragma unroll
-    for (int o = 1; o < NW; o <<= 1) {
-      const int y0 = __shfl_up_sync(LGK_FULL_MASK, w0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, w1, o);
-      if (lane >= o) { w0 += y0; w1 += y1; }
-    }
-    if (lane < NW) { s_scan[0][lane] = w0 - t0w; s_scan[1][lane] = w1 - t1w; }
-    if (lane == NW - 1) { s_scan[0][NW] = w0; s_scan[1][NW] = w1; }
-  }
-  __syncthreads();
-  int o0 = s_scan[0][wic] + i0 - c0, o1 = s_scan[1][wic] + i1 - c1;
-  if (c0 + c1 != 0) {
-#pragma unroll 1
-    for (int t = t0; t < t1; ++t) {
-      if (!slot_ok(t)) continue;
-      unsigned m = rm[t], m2 = sv[t];
-      const int e0 = slot_env0(t);
-      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
-      while (m2) { const int bit = __ffs(m2) - 1; m2 &= m2 - 1; b.resample_ids[o1++] = e0 + bit; }
-    }
-  }
-  if (tid == 0) {
-    b.counts[0] = s_scan[0][NW];
-    b.counts[1] = s_scan[1][NW];
-  }
-}
-
-// episode statistics of the step (the last CTA of the finish kernel to get done, all of its threads) and the
-// counters of the next step
-__device__ __forceinline__ void publish_step_statistics(const StepArgs& a, unsigned long long csc) {
-  const LgkConsts& c = a.c;
-  const LgkBuffers& b = a.b;
-  const int N = c.num_envs;
-  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
-  constexpr int NW = FIN_THREADS / 32;
-  __shared__ float s_part[NW][33];
-  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
-  const int parity = (int)(csc & 1ull);
-  const int num_rows = a.num_rows;
-  // the reset envs' episode sums were added into STAT_COPIES replicated rows (spread by env, see the finish kernel):
-  // thread (row = lane, quarter = warp) adds a quarter of the copies -- independent L2 loads, all in flight -- and
-  // zeroes them for the next step
-  {
-    float* cp = a.stat_copies + (size_t)wic * (STAT_COPIES / NW) * LGK_MAX_REWARDS + lane;
-    float v[STAT_COPIES / NW];
-#pragma unroll
-    for (int k = 0; k < STAT_COPIES / NW; ++k) v[k] = __ldcg(cp + k * LGK_MAX_REWARDS);
-    float acc = 0.f;
-#pragma unroll
-    for (int k = 0; k < STAT_COPIES / NW; ++k) { acc += v[k]; cp[k * LGK_MAX_REWARDS] = 0.f; }
-    s_part[wic][lane] = acc;
-  }
-  __syncthreads();
-  if (wic != 0) return;
-  const int n_reset = ws->reset_count[parity];
-  const int level_sum = ws->level_sum[parity];
-  if (lane < num_rows) {
-    float s = ws->stats[parity][lane];   // (+ what lgk_reset_idx calls may have left: nothing today)
-#pragma unroll
-    for (int k = 0; k < NW; ++k) s += s_part[k][lane];
-    b.episode_stats[lane] = s;
-    b.episode_stats[num_rows + 4 + lane] += s;   // running sums since the host last cleared them
-    if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
-      b.extras[lane] = (s / (float)n_reset) / c.max_episode_length_s;
-    ws->stats[parity][lane] = 0.f;
-    ws->stats[parity ^ 1][lane] = 0.f;
-  }
-  if (lane == 0) {
-    b.episode_stats[num_rows] = (float)n_reset;
-    b.episode_stats[num_rows + 1] = (float)level_sum;
-    b.episode_stats[num_rows + 2] = (float)N;
-    b.episode_stats[2 * num_rows + 4] += (float)n_reset;
-    b.episode_stats[2 * num_rows + 5] = (float)level_sum;
-    b.episode_stats[2 * num_rows + 6] = (float)N;
-    if (n_reset > 0 && (c.flags & LGK_F_TERRAIN_CURRICULUM))
-      b.extras[num_rows] = (float)level_sum / (float)N;   // mean(terrain_levels.float()) (:188)
-    ws->level_sum[parity ^ 1] = 0;
-    ws->reset_count[parity ^ 1] = 0;
-    ws->fin_ticket = 0u;
-    ws->step_counter = csc;
-    ws->launch_seq += 1u;
-  }
-}
 
 template <int DT, bool TAPS, bool MUL_RCP>
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_MIN_CTAS)
 lgk_step_kernel(const __grid_constant__ StepArgs a) {
-  pdl_launch_dependents();   // the finish kernel may be scheduled as soon as the last tile CTA has started
+  // Fused chain: this is the first launch.  It waits for whatever ran before, and only then lets the scan kernel be
+  // scheduled -- that kernel's CTAs take SM slots as the last wave here retires, and with hand-over flags they start
+  // on the envs whose step CTAs are through; releasing them before the wait would let them run next to the PREVIOUS
+  // step's last kernel when this grid fits the GPU at once.
+  if (a.fused) pdl_wait();
+  pdl_launch_dependents();   // the next kernel of the chain may be scheduled as soon as the last tile CTA has started
   // Behind the scan kernel this launch needs no wait on entry: that kernel waits for ITS predecessor before it lets
   // its dependents go, so every input here (simulator tensors, clipped actions, the previous step's state) is
   // complete when the first CTA starts, and nothing here depends on the scan itself.  Without a scan kernel: wait now.
-  if (!a.scan_first) pdl_wait();
+  if (!a.scan_first && !a.fused) pdl_wait();
   const LgkConsts& c = a.c;
   const LgkBuffers& b = a.b;
   const TileLayout& L = a.L;
@@ -887,6 +758,13 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
       LGK_STAMP(6);
     }
   }   // sub-tiles
+  if (a.fused == 2) {
+    // hand this CTA's envs over to the scan kernel: everything the four warps wrote (and the bulk stores, complete --
+    // not only read -- for the thread that committed them) is ordered before the flag
+    if (tid == 32) bulk_wait_all();
+    __syncthreads();
+    if (tid == 32) flag_release(a.scan_flags + blockIdx.x, ws->launch_seq + 1u);
+  }
   if (wic == 0 && lane == 0) LGK_CTA_STAMP(1);
 #ifdef LGK_PROFILE
   if (wic == 3 && lane == 0 && blockIdx.x < 4096) lgk_prof_cta[blockIdx.x * 4 + 3] = lgk_gtime();   // W3 leaves
@@ -911,15 +789,6 @@ lgk_step_kernel(const __grid_constant__ StepArgs a) {
 //                  15 us: ~12 000 red.add on a single cache line at 65 536 envs)
 // and the CTA that finishes last adds the replicated rows up into extras["episode"] and advances the step counter.
 #define LGK_FIX_CTAS_MAX 296   // at most 2 x 148 CTAs of the finish kernel work on the reset envs
-__device__ __forceinline__ void wait_scan_flag(const StepArgs& a, LgkWorkspace* ws, const unsigned* f, unsigned stamp) {
-  // Bounded (~0.3 s): a hand-over that never comes -- it cannot, the scan grid was resident before the step kernel
-  // even started -- must fail the step's results, not hang the GPU; the header counts such give-ups
-  unsigned polls = 0;
-  while (flag_acquire(f) != stamp) {
-    if (++polls > (1u << 22)) { atomicAdd(&ws->scan_timeouts, 1u); break; }
-    __nanosleep(40);
-  }
-}
 template <bool TAPS, bool MUL_RCP, int NP>
 __device__ __forceinline__ void finish_fix_cta(const StepArgs& a, int fix_ctas) {
   const LgkBuffers& b = a.b;
@@ -1208,6 +1077,24 @@ static int device_info(int dev, DeviceInfo* out) {
   return 0;
 }
 
+// The chain.  Default: two launches -- step kernel, then the tail kernel (scan + rewards + reset tail + statistics,
+// lgk_scan.cu); from 12 288 envs on the tail kernel takes the step CTAs' results over through hand-over flags (it starts
+// under the step kernel's last wave), below that it waits for the whole step grid (measured: 4 096 envs 25.3 us against
+// 26.7 us with flags, 16 384 envs 31.8 / 30.9, 65 536 envs 68.9 / 67.5).  LGK_CHAIN in the environment overrides:
+// "3": the three-launch chain of earlier rounds (scan, step, finish kernel), kept for A/B measurements; "2w": tail kernel
+// with the grid-wide wait; "2f": tail kernel with hand-over flags.  Returns 0 (three launches), 1 (wait) or 2 (flags).
+extern "C" int lgk_chain_mode(int num_envs) {
+  static const int forced = [] {
+    const char* e = getenv("LGK_CHAIN");
+    if (e && e[0] == '3') return 0;
+    if (e && e[0] == '2' && e[1] == 'w') return 1;
+    if (e && e[0] == '2' && e[1] == 'f') return 2;
+    return -1;
+  }();
+  if (forced >= 0) return forced;
+  return num_envs >= 12288 ? 2 : 1;
+}
+
 template <int DT, bool TAPS, bool MUL_RCP>
 static int launch_step(const StepArgs& args, int dev, int grid, size_t smem, cudaStream_t stream) {
   auto kern = lgk_step_kernel<DT, TAPS, MUL_RCP>;
@@ -1223,6 +1110,14 @@ static int launch_step(const StepArgs& args, int dev, int grid, size_t smem, cud
     fprintf(stderr, "[lgk] %s: %s\n", what, cudaGetErrorString(e));
   };
   dbg_sync("before post_physics_step");
+  if (args.fused) {   // two launches: step kernel, then scan + rewards + statistics
+    LGK_CUDA_RETURN_IF(lgk_launch_pdl(kern, dim3(grid), dim3(LGK_CTA_THREADS), smem, stream, args));
+    dbg_sync("step kernel");
+    const int rc = lgk_scan_launch(args, stream);
+    if (rc) return rc;
+    dbg_sync("scan kernel (fused)");
+    return (int)cudaGetLastError();
+  }
   if (args.scan_first) { const int rc = lgk_scan_launch(args, stream); if (rc) return rc; }
   dbg_sync("scan kernel");
   LGK_CUDA_RETURN_IF(lgk_launch_pdl(kern, dim3(grid), dim3(LGK_CTA_THREADS), smem, stream, args));
@@ -1336,6 +1231,23 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     grid = args.n_big + (rest > 0 ? (rest + args.per_small - 1) / args.per_small : 0);
   }
   args.max_sub = (args.per + TILE - 1) / TILE;
+  args.step_grid = grid;
+  args.fused = lgk_chain_mode(c->num_envs);
+  {
+    int xi = 0;
+    args.bh_row = -2;
+    for (int r = 0; r < LGK_MAX_REWARDS; ++r) {
+      args.row_src[r] = args.rv;   // (rows past the terms: never used as a value, but always a valid address)
+      args.row_scale[r] = r == c->num_rewards ? c->termination_scale : 0.f;
+      if (r < c->num_rewards) {
+        const int term = c->rewards[r].term;
+        args.row_src[r] = term == LGK_REW_EXTERNAL ? b->ext_rewards + (size_t)(xi++) * c->num_envs
+                                                   : args.rv + (size_t)term * args.rv_pitch;
+        args.row_scale[r] = c->rewards[r].scale;
+        if (term == LGK_REW_BASE_HEIGHT) args.bh_row = r;
+      }
+    }
+  }
   // scan kernel: a persistent grid, resident at once; its warps walk groups of 8 envs (fewer when that would not
   // give every warp a group)
   {
@@ -1344,12 +1256,15 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
       const int v = e ? atoi(e) : 0;
       return (v >= 1 && v <= LGK_SCAN_REG_CTAS) ? v : LGK_SCAN_CTAS_PER_SM;
     }();
-    const int cap = num_sms * scan_per_sm;
-    int epg = SCAN_GROUP;
-    while (epg > 1 && (c->num_envs + epg - 1) / epg < cap * LGK_WARPS_PER_CTA) epg >>= 1;
+    const int cap = num_sms * (args.fused ? LGK_TAIL_CTAS_PER_SM : scan_per_sm);
+    // fused chain: groups of 16 as long as they keep 4/5 of the warps busy (65 536 envs: 4 096 groups, one each)
+    int epg = args.fused ? SCAN_GROUP_FUSED : SCAN_GROUP;
+    const int want = args.fused ? cap * LGK_WARPS_PER_CTA * 4 / 5 : cap * LGK_WARPS_PER_CTA;
+    while (epg > 1 && (c->num_envs + epg - 1) / epg < want) epg >>= 1;
     args.scan_epc = epg;
     args.scan_tiles = (c->num_envs + epg - 1) / epg;
-    const int ctas = (args.scan_tiles + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA;
+    // (fused: a CTA takes the four groups of a unit, + the id-list CTA)
+    const int ctas = (args.scan_tiles + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA + (args.fused ? 1 : 0);
     args.scan_grid = ctas < cap ? ctas : cap;
   }
   const bool taps = c->rng_mode == LGK_RNG_TAPS;

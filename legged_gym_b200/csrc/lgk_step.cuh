@@ -15,6 +15,12 @@
                                  // leave room for step CTAs from the start -- measured slower)
 #define RS (TILE + 1)   // row stride of [row][env] tables: conflict-free by row and by env
 #define SCAN_GROUP 8    // envs a scan warp takes per group (one hand-over flag per group)
+#ifndef LGK_TAIL_CTAS_PER_SM
+#define LGK_TAIL_CTAS_PER_SM 7   // tail kernel: register cap 72; 65 536 envs are 1 024 units + the id-list CTA <= 7 x 148
+#endif
+#ifndef SCAN_GROUP_FUSED
+#define SCAN_GROUP_FUSED 16   // ... in the fused chain (one trip of the persistent loop for most warps at 65 536 envs)
+#endif
 
 struct TileLayout {   // offsets (in floats, multiples of 4) into dynamic shared memory
   int root, dof, act, ldv, cmd, fat, ep, lvl, cf, tq, lact, head, scr, total;
@@ -42,6 +48,13 @@ struct StepArgs {
   unsigned* scan_flags;   // [ceil(N / scan_epc)] (workspace): launch_seq + 1 once the scan group's columns and sums are out
   int scan_tiles;    // scan groups of this launch = ceil(N / scan_epc); the scan grid's warps walk them persistently
   int scan_grid;     // CTAs of the scan kernel: all resident at once
+  int fused;         // two-launch chain: step kernel, then the scan kernel in its FUSED form (rewards, statistics)
+  int step_grid;     // CTAs of the step kernel (the id-list compaction walks their mask slots)
+  // fused chain, per episode-sum row (reward terms in order, then termination): where the term's values are ([N]
+  // floats: a row of the step kernel's value table, or of ext_rewards), the scale, and which row is base_height (-2: none)
+  const float* row_src[LGK_MAX_REWARDS];
+  float row_scale[LGK_MAX_REWARDS];
+  int bh_row;
   float* rv;         // [LGK_REW_COUNT][rv_pitch] (workspace): value of every reward term by env, step -> finish kernel
   int rv_pitch;      // floats per row of rv (N rounded up to 32)
   float* stat_copies;   // [64][LGK_MAX_REWARDS] (workspace): replicated accumulators of the reset envs' episode sums
@@ -251,6 +264,152 @@ __device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, 
   int raw[NP];
   scan_gather<MUL_RCP, NP, SLN>(a, e, ln, lane, raw, sln);
   return scan_emit<TAPS, NP, CLIP, MAT, SLN>(a, e.zo, ln, raw, it0, lane, rnd, orow, trow, mrow, check_all, sln);
+}
+
+// ---------------------------------------------------------------------------------------------
+// The two once-per-step serial jobs of post_physics_step.  Both run inside the finish kernel (below), each on one CTA:
+//   1. ordered compaction of the per-tile reset / resample bitmasks into ascending id lists (:150, :342) -- needs
+//      the step kernel's masks only, so a dedicated CTA of the finish grid does it next to the reward CTAs
+//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119) -- needs every reward CTA's
+//      sums, so the CTA that finishes last does it (ticket counter in the workspace header)
+// (earlier versions: a finisher CTA inside the fused tile kernel, 16-20 us on one busy SM; then an epilogue launch of
+// its own, 7-11 us at the end of the chain with the GPU otherwise idle)
+#define FIN_THREADS 128
+#define STAT_COPIES 64   // replicated accumulator rows of the reset statistics (see lgk_finish_kernel)
+template <int THREADS>
+__device__ __forceinline__ void compact_id_lists(const StepArgs& a, int n_ctas) {
+  constexpr int NW = THREADS / 32;
+  __shared__ int s_scan[2][NW + 1];
+  const LgkBuffers& b = a.b;
+  const int N = a.c.num_envs;
+  const int tid = threadIdx.x, lane = tid & 31, wic = tid >> 5;
+  const LgkWorkspace* ws = reinterpret_cast<const LgkWorkspace*>(b.workspace);
+  const int nt = n_ctas * a.max_sub;      // mask slots, (cta, sub) order = ascending env order
+  const unsigned* mask_base = reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(ws) + LGK_WS_HEADER_BYTES);
+  const unsigned* rm = mask_base;
+  const unsigned* sv = mask_base + lgk_max_warps(N);
+  // slots of sub-tiles past a CTA's range were never written this launch: skip them
+  const bool one_sub = a.max_sub == 1;
+  auto slot_env0 = [&](int t) {
+    if (one_sub) return t < a.n_big ? t * a.per : a.n_big * a.per + (t - a.n_big) * a.per_small;
+    const int cta = t / a.max_sub, k = t - cta * a.max_sub;
+    return cta * a.per + k * TILE;
+  };
+  auto slot_ok = [&](int t) {
+    if (one_sub) return true;
+    const int cta = t / a.max_sub, k = t - cta * a.max_sub;
+    return k * TILE < min(a.per, N - cta * a.per);
+  };
+  const int per = (nt + THREADS - 1) / THREADS;   // 16 at 65536 envs
+  const int t0 = min(nt, tid * per), t1 = min(nt, t0 + per);
+  int c0 = 0, c1 = 0;
+#pragma unroll 8
+  for (int t = t0; t < t1; ++t)
+    if (slot_ok(t)) { c0 += __popc(rm[t]); c1 += __popc(sv[t]); }
+  // block-wide exclusive scan of (c0, c1): shuffles inside a warp, warp totals through shared memory
+  int i0 = c0, i1 = c1;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y0 = __shfl_up_sync(LGK_FULL_MASK, i0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, i1, o);
+    if (lane >= o) { i0 += y0; i1 += y1; }
+  }
+  if (lane == 31) { s_scan[0][wic] = i0; s_scan[1][wic] = i1; }
+  __syncthreads();
+  if (wic == 0) {   // exclusive scan of the warp totals
+    int w0 = lane < NW ? s_scan[0][lane] : 0, w1 = lane < NW ? s_scan[1][lane] : 0;
+    const int t0w = w0, t1w = w1;
+#pragma unroll
+    for (int o = 1; o < NW; o <<= 1) {
+      const int y0 = __shfl_up_sync(LGK_FULL_MASK, w0, o), y1 = __shfl_up_sync(LGK_FULL_MASK, w1, o);
+      if (lane >= o) { w0 += y0; w1 += y1; }
+    }
+    if (lane < NW) { s_scan[0][lane] = w0 - t0w; s_scan[1][lane] = w1 - t1w; }
+    if (lane == NW - 1) { s_scan[0][NW] = w0; s_scan[1][NW] = w1; }
+  }
+  __syncthreads();
+  int o0 = s_scan[0][wic] + i0 - c0, o1 = s_scan[1][wic] + i1 - c1;
+  if (c0 + c1 != 0) {
+#pragma unroll 1
+    for (int t = t0; t < t1; ++t) {
+      if (!slot_ok(t)) continue;
+      unsigned m = rm[t], m2 = sv[t];
+      const int e0 = slot_env0(t);
+      while (m) { const int bit = __ffs(m) - 1; m &= m - 1; b.reset_ids[o0++] = e0 + bit; }
+      while (m2) { const int bit = __ffs(m2) - 1; m2 &= m2 - 1; b.resample_ids[o1++] = e0 + bit; }
+    }
+  }
+  if (tid == 0) {
+    b.counts[0] = s_scan[0][NW];
+    b.counts[1] = s_scan[1][NW];
+  }
+}
+
+// episode statistics of the step (the last CTA of the finish kernel to get done, all of its threads) and the
+// counters of the next step
+__device__ __forceinline__ void publish_step_statistics(const StepArgs& a, unsigned long long csc) {
+  const LgkConsts& c = a.c;
+  const LgkBuffers& b = a.b;
+  const int N = c.num_envs;
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  constexpr int NW = FIN_THREADS / 32;
+  __shared__ float s_part[NW][33];
+  LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
+  const int parity = (int)(csc & 1ull);
+  const int num_rows = a.num_rows;
+  // the reset envs' episode sums were added into STAT_COPIES replicated rows (spread by env, see the finish kernel):
+  // thread (row = lane, quarter = warp) adds a quarter of the copies -- independent L2 loads, all in flight -- and
+  // zeroes them for the next step
+  {
+    float* cp = a.stat_copies + (size_t)wic * (STAT_COPIES / NW) * LGK_MAX_REWARDS + lane;
+    float v[STAT_COPIES / NW];
+#pragma unroll
+    for (int k = 0; k < STAT_COPIES / NW; ++k) v[k] = __ldcg(cp + k * LGK_MAX_REWARDS);
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < STAT_COPIES / NW; ++k) { acc += v[k]; cp[k * LGK_MAX_REWARDS] = 0.f; }
+    s_part[wic][lane] = acc;
+  }
+  __syncthreads();
+  if (wic != 0) return;
+  const int n_reset = ws->reset_count[parity];
+  const int level_sum = ws->level_sum[parity];
+  if (lane < num_rows) {
+    float s = ws->stats[parity][lane];   // (+ what lgk_reset_idx calls may have left: nothing today)
+#pragma unroll
+    for (int k = 0; k < NW; ++k) s += s_part[k][lane];
+    b.episode_stats[lane] = s;
+    b.episode_stats[num_rows + 4 + lane] += s;   // running sums since the host last cleared them
+    if (n_reset > 0)   // extras["episode"]["rew_<k>"] = mean(sum[ids]) / max_episode_length_s (:184)
+      b.extras[lane] = (s / (float)n_reset) / c.max_episode_length_s;
+    ws->stats[parity][lane] = 0.f;
+    ws->stats[parity ^ 1][lane] = 0.f;
+  }
+  if (lane == 0) {
+    b.episode_stats[num_rows] = (float)n_reset;
+    b.episode_stats[num_rows + 1] = (float)level_sum;
+    b.episode_stats[num_rows + 2] = (float)N;
+    b.episode_stats[2 * num_rows + 4] += (float)n_reset;
+    b.episode_stats[2 * num_rows + 5] = (float)level_sum;
+    b.episode_stats[2 * num_rows + 6] = (float)N;
+    if (n_reset > 0 && (c.flags & LGK_F_TERRAIN_CURRICULUM))
+      b.extras[num_rows] = (float)level_sum / (float)N;   // mean(terrain_levels.float()) (:188)
+    ws->level_sum[parity ^ 1] = 0;
+    ws->reset_count[parity ^ 1] = 0;
+    ws->fin_ticket = 0u;
+    ws->step_counter = csc;
+    ws->launch_seq += 1u;
+  }
+}
+
+// hand-over flags between kernels that run side by side: wait until *f carries this launch's stamp
+__device__ __forceinline__ void wait_scan_flag(const StepArgs& a, LgkWorkspace* ws, const unsigned* f, unsigned stamp) {
+  // Bounded (~0.3 s): a hand-over that never comes -- it cannot, the scan grid was resident before the step kernel
+  // even started -- must fail the step's results, not hang the GPU; the header counts such give-ups
+  unsigned polls = 0;
+  while (flag_acquire(f) != stamp) {
+    if (++polls > (1u << 22)) { atomicAdd(&ws->scan_timeouts, 1u); break; }
+    __nanosleep(40);
+  }
 }
 
 // launches lgk_scan_kernel for args.c.num_envs envs (lgk_scan.cu)
