@@ -290,6 +290,42 @@ static __device__ __noinline__ void tail_rewards_env(float* gp, unsigned n_envs,
   if (clip_due) rew = fmaxf(rew, 0.f);
   *rew_out = rew;
 }
+// The same from staged rows: the unit's episode-sum rows and term-value rows were copied into shared memory
+// ([2][nrows][TAIL_UNIT] floats) by cp.async before the scan began, so nothing here waits for global memory -- the
+// latency of the rows passed under the CTA's own scan.  st: this env's column of the stage.
+static __device__ __noinline__ void tail_rewards_env_staged(const float* __restrict__ st, float* gp, unsigned n_envs,
+                                                            int nrows, bool reset, float bh, float target, float term_v,
+                                                            bool only_positive, float* __restrict__ stat,
+                                                            const TailRow* __restrict__ rows, float* __restrict__ rew_out) {
+  float rew = 0.f;
+  bool clip_due = only_positive;
+  const float* sv = st + nrows * TAIL_UNIT;
+#pragma unroll 4
+  for (int r = 0; r < nrows; ++r) {
+    const TailRow t = rows[r];
+    float val = sv[r * TAIL_UNIT];
+    if (t.kind != 0) {
+      if (t.kind == 1) { const float d = (val - bh) - target; val = d * d; }
+      else {   // the termination row: added after the positive clip (:206-212)
+        val = term_v;
+        if (clip_due) { rew = fmaxf(rew, 0.f); clip_due = false; }
+      }
+    }
+    const float rr = mul_rn(val, t.scale);
+    const float total = add_rn(st[r * TAIL_UNIT], rr);
+    rew = add_rn(rew, rr);
+    gp[(unsigned)r * n_envs] = reset ? 0.f : total;   // zeroed for reset envs after the statistics took it (:184-185)
+    if (reset) atomicAdd(stat + r, total);
+  }
+  if (clip_due) rew = fmaxf(rew, 0.f);
+  *rew_out = rew;
+}
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src_gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
 template <bool TAPS, bool MUL_RCP, int NP>   // NP = 0: any H (0 included), passes in chunks of 8, constants re-read per env
 __global__ void __launch_bounds__(LGK_CTA_THREADS, LGK_TAIL_CTAS_PER_SM)
 lgk_tail_kernel(const __grid_constant__ StepArgs a) {
@@ -308,6 +344,7 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
   __shared__ int s_hs[TAIL_UNIT];             // height sum of each env of the unit
   __shared__ unsigned char s_fl[TAIL_UNIT];   // bit 0: reset, bit 1: time-out (the step kernel's decision)
   __shared__ unsigned s_last;
+  extern __shared__ __align__(16) float s_stage[];   // a.tail_staged: [2][nrows][TAIL_UNIT] rows of the unit (sums, values)
   __shared__ __align__(8) TailRow s_rows[LGK_MAX_REWARDS];
   __shared__ const float* s_srcs[LGK_MAX_REWARDS];
   if (threadIdx.x < LGK_MAX_REWARDS) {   // (read after the unit's first CTA barrier)
@@ -375,11 +412,23 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       if (f0 + lane <= f1) wait_scan_flag(a, ws, a.scan_flags + f0 + lane, stamp);
       __syncwarp();
     }
-    if (ne > 0 && lane < nrows) {   // the reward pass's rows of this group's envs: on their way into L2 under the scan
+    if (a.tail_staged) {
+      // the reward pass's rows of this group's 16 envs -> shared memory, 16 bytes per copy, asynchronously: they
+      // arrive under the scan below (chunk i: row i >> 2 of the sums, then of the values; quarter i & 3 of the 64 bytes)
+      for (int i = lane; i < nrows * 8; i += 32) {
+        const int row2 = i >> 2, qd = i & 3;
+        const float* src = (row2 < nrows ? b.episode_sums + (size_t)row2 * N : a.row_src[row2 - nrows]) + env0 + 4 * qd;
+        cp_async16(s_stage + row2 * TAIL_UNIT + wic * GS + 4 * qd, src);
+      }
+    } else if (ne > 0 && lane < nrows) {   // ... or at least on their way into L2
       prefetch_l2(b.episode_sums + (size_t)lane * N + env0);
       prefetch_l2(a.row_src[lane] + env0);
     }
     if (lane < ne) {
+      // (the pose is read next to the flags, not behind them: one round trip at the start of the unit instead of two)
+      const float* r = b.root_states + (size_t)(env0 + lane) * 13;
+      float rx = 0.f, ry = 0.f, rz = 0.f, qz = 0.f, qw = 1.f;
+      if (a.scan_first) { rx = r[0]; ry = r[1]; rz = r[2]; qz = r[5]; qw = r[6]; }
       const bool rst = b.reset_buf[env0 + lane] != 0, tmo = b.time_out_buf[env0 + lane] != 0;
       s_fl[wic * epg + lane] = (unsigned char)((rst ? 1 : 0) | (tmo ? 2 : 0));
       if (a.scan_first) {
@@ -389,8 +438,7 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
           d[0] = sd[0];
           d[1] = sd[1];
         } else {
-          const float* r = b.root_states + (size_t)(env0 + lane) * 13;
-          const ScanEnv e = scan_env_operands(r[0], r[1], r[2], r[5], r[6]);
+          const ScanEnv e = scan_env_operands(rx, ry, rz, qz, qw);
           d[0] = make_float4(e.k_t.x, e.k_t.y, e.k_c.x, e.k_c.y);
           d[1] = make_float4(e.r2.x, e.r2.y, e.yw, e.zo);
         }
@@ -440,6 +488,7 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       for (int o = GS; o < 32; o <<= 1) hs += __shfl_xor_sync(LGK_FULL_MASK, hs, o);
       if (q == 0 && k < ne) s_hs[wic * epg + k] = hs;
     }
+    if (a.tail_staged) cp_async_wait_all();   // (this thread's copies; the barrier makes everybody's visible)
     __syncthreads();   // every group of the unit is scanned: height sums and flags are in shared memory
     // ---- rewards of the unit: one env per thread (warps 0, 1), rows in the reference's order ----------------------
     if ((int)threadIdx.x < une) {
@@ -448,9 +497,15 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       const bool reset = fl & 1u, time_out = fl & 2u;
       float bh = 0.f;   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height)
       if (a.scan_first && a.bh_active) bh = ((float)s_hs[u] * c.vertical_scale) / (float)H;
-      tail_rewards_env(b.episode_sums + env, (unsigned)N, nrows, env, reset, bh, c.base_height_target,
-                       (reset && !time_out) ? 1.f : 0.f, (c.flags & LGK_F_ONLY_POSITIVE) != 0,
-                       a.stat_copies + (size_t)((env >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS, s_srcs, s_rows, b.rew_buf + env);
+      float* stat = a.stat_copies + (size_t)((env >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS;
+      const float term_v = (reset && !time_out) ? 1.f : 0.f;   // the termination row's value (:209-212)
+      const bool only_pos = (c.flags & LGK_F_ONLY_POSITIVE) != 0;
+      if (a.tail_staged)
+        tail_rewards_env_staged(s_stage + u, b.episode_sums + env, (unsigned)N, nrows, reset, bh, c.base_height_target,
+                                term_v, only_pos, stat, s_rows, b.rew_buf + env);
+      else
+        tail_rewards_env(b.episode_sums + env, (unsigned)N, nrows, env, reset, bh, c.base_height_target, term_v, only_pos,
+                         stat, s_srcs, s_rows, b.rew_buf + env);
     }
     if (wic >= 2) {   // the root rows the step kernel held back while poses were still being read (:414-434)
       const int u = (wic & 1) * 32 + lane;
@@ -478,7 +533,8 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
 template <bool TAPS, bool MUL_RCP, int NP>
 static int launch_scan(const StepArgs& args, int grid, cudaStream_t stream) {
   if (args.fused)   // (the id-list CTA is part of scan_grid)
-    return (int)lgk_launch_pdl(lgk_tail_kernel<TAPS, MUL_RCP, NP>, dim3(grid), dim3(LGK_CTA_THREADS), 0, stream, args);
+    return (int)lgk_launch_pdl(lgk_tail_kernel<TAPS, MUL_RCP, NP>, dim3(grid), dim3(LGK_CTA_THREADS),
+                               args.tail_staged ? (size_t)2 * args.num_rows * TAIL_UNIT * sizeof(float) : 0, stream, args);
   return (int)lgk_launch_pdl(lgk_scan_kernel<TAPS, MUL_RCP, NP>, dim3(grid), dim3(LGK_CTA_THREADS), 0, stream, args);
 }
 

@@ -1267,6 +1267,14 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     const int ctas = (args.scan_tiles + LGK_WARPS_PER_CTA - 1) / LGK_WARPS_PER_CTA + (args.fused ? 1 : 0);
     args.scan_grid = ctas < cap ? ctas : cap;
   }
+  {
+    // staged reward rows: every group full (16 envs) and every row segment 16-byte aligned.  LGK_TAIL_STAGE=0: off
+    static const bool stage_on = [] { const char* e = getenv("LGK_TAIL_STAGE"); return !(e && e[0] == '0'); }();
+    bool ok = stage_on && args.fused && args.scan_epc == SCAN_GROUP_FUSED && c->num_envs % SCAN_GROUP_FUSED == 0 &&
+              args.num_rows > 0 && al16(b->episode_sums) && al16(args.rv);
+    for (int r = 0; r < args.num_rows && ok; ++r) ok = al16(args.row_src[r]);
+    args.tail_staged = ok ? 1 : 0;
+  }
   const bool taps = c->rng_mode == LGK_RNG_TAPS;
   const bool mul = c->index_math == LGK_INDEX_MUL_RCP;
 #define LGK_DISPATCH(DT)                                                             \

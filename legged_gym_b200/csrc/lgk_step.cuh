@@ -55,6 +55,8 @@ struct StepArgs {
   const float* row_src[LGK_MAX_REWARDS];
   float row_scale[LGK_MAX_REWARDS];
   int bh_row;
+  int tail_staged;   // the tail kernel copies a unit's reward rows into shared memory (cp.async) before its scan:
+                     // full groups of 16 envs, every row 16-byte aligned
   float* rv;         // [LGK_REW_COUNT][rv_pitch] (workspace): value of every reward term by env, step -> finish kernel
   int rv_pitch;      // floats per row of rv (N rounded up to 32)
   float* stat_copies;   // [64][LGK_MAX_REWARDS] (workspace): replicated accumulators of the reset envs' episode sums
