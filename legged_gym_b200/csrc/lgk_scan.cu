@@ -1,11 +1,12 @@
-// Height-scan kernel (sm_100a): _get_heights (legged_robot.py:818-854) and the scan columns of the observation
-// row (:225-231) for every env, lanes = scan points.
-//
-// The scan reads nothing but the simulator's root states (position, yaw) and the terrain table, so it is the first
-// launch of post_physics_step; the step kernel (lgk_step.cu) follows under programmatic dependent launch and
-// needs the one number this kernel hands over per env -- the sum of the measured heights, for _reward_base_height
-// (:871) -- only in its last phase.  Envs the step kernel resets get their scan columns rewritten there (the
-// observation uses the root z after the reset, :227); for everyone else what this kernel writes is final.
+// Height scan (sm_100a): _get_heights (legged_robot.py:818-854) and the scan columns of the observation row
+// (:225-231) for every env, lanes = scan points -- in two kernels that share the per-env code (lgk_step.cuh):
+//   lgk_tail_kernel  (second half of this file) the default: the last launch of the two-launch chain, behind the step
+//                    kernel; scan, then reward sums, reset tail, id lists and statistics by the same CTAs
+//   lgk_scan_kernel  (below) the scan alone, first launch of the three-launch chain of earlier rounds (LGK_CHAIN=3):
+//                    it hands the sum of the measured heights (for _reward_base_height, :871) and the finished columns
+//                    over to lgk_finish_kernel group by group through flags in the workspace; envs the step kernel
+//                    resets get their scan columns rewritten there (the observation uses the root z after the reset,
+//                    :227).  The rest of this comment describes that kernel.
 //
 // The scan and the step kernel do not depend on each other (the step kernel neither reads heights nor writes the
 // root state: the new root row of a reset env waits in a side buffer until the finish kernel stores it).  This grid
@@ -220,22 +221,22 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
 // ---------------------------------------------------------------------------------------------
 // Tail kernel: the second (and last) launch of the two-launch chain, behind the step kernel -- the height scan of
 // lgk_scan_kernel plus everything that is left of post_physics_step once the scan is known, by the CTAs that did the
-// scan:
-//   scan      as above, warp w of a CTA takes group w of the CTA's unit of 4 groups (<= 64 consecutive envs).  Envs the
-//             step kernel reset take their operands from the side row (old pose, root z after the reset, :227), so
-//             their columns are computed once and there is no fix-up pass
-//   rewards   compute_reward's sums (:195-212) over the step kernel's term values, after a CTA barrier: lanes = envs,
-//             rows warp-uniform (warp w: envs 32 (w & 1) .. + 31 of the unit, rows w >> 1, + 2, ...), so scale and source
-//             row come from the parameter block through uniform registers and every access to the [R,N] episode-sum
-//             rows / the [term][N] value table is a coalesced row segment; r = value * scale, sum += r in place (zeroed
-//             for reset envs after the statistics took it, :184-185); base_height from the scan's height sums, which
-//             never leave the CTA.  The scaled values meet in shared memory ([row][64]) and one thread per env adds
-//             them up in the reference's order, clips (only_positive_rewards) and adds the termination term
-//   resets    the root rows the step kernel held back while poses were still being read (:414-434) are stored
-//   lists     CTA 0 compacts the step kernel's per-tile bitmasks into the ascending id lists (:150, :342)
-//   counters  the CTA that finishes last publishes extras["episode"] (:182-190) and advances the step counter (:119)
-// The row loads of a unit wait under the arithmetic of the other CTAs of the SM: what was a 16 us launch of
-// dependent round trips at the end of the three-launch chain costs a few per cent of the scan's issue slots here.
+// scan.  A CTA takes units of 4 groups (<= 64 consecutive envs), warp w the unit's group w:
+//   stage     the unit's rows of the [R,N] episode sums and of the step kernel's [term][N] value table -> shared
+//             memory by 16-byte cp.async, issued before the scan: their latency passes under the CTA's own arithmetic
+//             (every CTA of the grid does the same amount of work at the same time, so nobody else's would hide it)
+//   scan      as in lgk_scan_kernel.  Envs the step kernel reset take their operands from the side row (old pose,
+//             root z after the reset, :227): their columns are computed once, there is no fix-up pass.  The sums of the
+//             heights never leave the CTA
+//   rewards   compute_reward (:195-212) after a CTA barrier, one env per thread (warps 0, 1), rows in the reference's
+//             order from the staged copies: r = value * scale, sum += r in place (zeroed for reset envs after the
+//             statistics took it, :184-185), reward += r, only_positive clip, termination term; base_height from the
+//             scan's height sum.  Row stores are coalesced 128-byte segments.  Out-of-line functions with the row
+//             constants in shared memory (see tail_rewards_env)
+//   resets    warps 2, 3 store the root rows the step kernel held back while poses were still being read (:414-434)
+//   lists     CTA 0 compacts the step kernel's per-tile bitmasks into the ascending id lists (:150, :342) ...
+//   counters  ... and, once every other CTA has left its release-ordered increment, publishes extras["episode"]
+//             (:182-190) and advances the step counter (:119)
 // a.fused == 2: no grid-wide wait for the step kernel -- a warp waits for the flags of the step CTAs that own its
 // group's envs, so the scan starts under the step kernel's last wave.
 #define TAIL_UNIT (4 * SCAN_GROUP_FUSED)
@@ -343,11 +344,10 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
   __shared__ int s_hp_all[LGK_WARPS_PER_CTA][GS * RS];   // per-lane partial height sums of the group's envs
   __shared__ int s_hs[TAIL_UNIT];             // height sum of each env of the unit
   __shared__ unsigned char s_fl[TAIL_UNIT];   // bit 0: reset, bit 1: time-out (the step kernel's decision)
-  __shared__ unsigned s_last;
   extern __shared__ __align__(16) float s_stage[];   // a.tail_staged: [2][nrows][TAIL_UNIT] rows of the unit (sums, values)
   __shared__ __align__(8) TailRow s_rows[LGK_MAX_REWARDS];
   __shared__ const float* s_srcs[LGK_MAX_REWARDS];
-  if (threadIdx.x < LGK_MAX_REWARDS) {   // (read after the unit's first CTA barrier)
+  if (threadIdx.x < LGK_MAX_REWARDS) {   // (kernel parameters: nothing an earlier kernel wrote)
     const int r = threadIdx.x;
     TailRow t;
     s_srcs[r] = a.row_src[r];
@@ -355,6 +355,7 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
     t.kind = r == a.bh_row ? 1 : (r == c.num_rewards ? 2 : 0);
     s_rows[r] = t;
   }
+  __syncthreads();   // the row tables are read by every warp's staging loop
   float* s_es = s_es_all[wic];
   int* s_hp = s_hp_all[wic];
 
@@ -517,15 +518,24 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
     }
     __syncthreads();   // shared memory is free for the next unit
   }
-  // ---- the last CTA to get here publishes the step's statistics and advances the counters ------------------------
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    s_last = (atomicAdd(&ws->fin_ticket, 1u) == gridDim.x - 1) ? 1u : 0u;
+  // ---- statistics and counters: CTA 0, once every other CTA has checked in ---------------------------------------
+  // The other CTAs leave a release-ordered increment behind and go (no fence + atomic round trip + second barrier at
+  // the end of every CTA: with all of them finishing together those 1 024 same-address atomics were ~4 us of every
+  // CTA's life); CTA 0, idle since it compacted the id lists, polls the count and publishes.
+  if (!list_cta) {
+    __syncthreads();   // every warp of this CTA is through: its statistics atomics are ordered before the increment
+    if (threadIdx.x == 0) ticket_release(&ws->fin_ticket);
+    return;
+  }
+  if (threadIdx.x == 0) {   // bounded like every hand-over wait here: a count that never comes is reported, not hung on
+    unsigned polls = 0;
+    while (flag_acquire(&ws->fin_ticket) != gridDim.x - 1) {
+      if (++polls > (1u << 22)) { atomicAdd(&ws->scan_timeouts, 1u); break; }
+      __nanosleep(64);
+    }
   }
   __syncthreads();
-  if (!s_last) return;   // (CTA-uniform)
-  __threadfence();
+  __threadfence();   // (also drops this SM's L1 copy of the header line, read at the start of the kernel)
   if (by_flags) pdl_wait();   // (every step CTA has handed over: returns at once; the dependency is now formal)
   publish_step_statistics(a, csc);
 }

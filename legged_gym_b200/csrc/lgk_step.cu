@@ -1,20 +1,23 @@
 // Step kernel of post_physics_step (sm_100a): one CTA of four warps per tile of 32 envs, lanes = envs.
 //
-// post_physics_step() (reference legged_robot.py:109-141) is three launches chained with programmatic dependent launch:
-//   lgk_scan_kernel    (lgk_scan.cu)  _get_heights + the scan columns of the observation row, lanes = points
+// post_physics_step() (reference legged_robot.py:109-141) is two launches chained with programmatic dependent launch:
 //   lgk_step_kernel    (this file)    everything per env that needs no height: episode counters, body-frame
 //                                     velocities / projected gravity, command resampling + heading command, pushes,
 //                                     terminations, the VALUE of every _reward_* term, resets (terrain curriculum, dof
 //                                     state, commands), the noisy scaled head of the observation row, last_* copies,
 //                                     the per-tile reset / resample bitmasks behind the ascending id lists
-//   lgk_finish_kernel  (this file)    lanes = envs over the [R,N] episode-sum rows: scale, in-place sums, ordered
-//                                     reward sum, statistics of the reset envs; base_height from the scan's height
-//                                     sums; the root state and the scan columns of the envs reset this step; one CTA
-//                                     compacts the bitmasks into the id lists, the last CTA to finish publishes
-//                                     extras and advances the step counter
-// The scan and the step kernel do not depend on each other: the step kernel neither reads heights nor writes the
-// root state (the new root row of a reset env goes to a side buffer in the workspace; the finish kernel stores it),
-// so the step CTAs start as soon as the scan's persistent CTAs begin to retire, without waiting for anything.
+//   lgk_tail_kernel    (lgk_scan.cu)  _get_heights + the scan columns of the observation row (lanes = points), then
+//                                     -- by the CTAs that did the scan -- compute_reward's scaled in-place sums over
+//                                     this kernel's term values (base_height from the scan's height sums), the held-back
+//                                     root rows of the envs reset this step, the id lists (one CTA), extras and the
+//                                     step counter (the same CTA, once everybody else has checked in)
+// This kernel neither reads heights nor writes the root state: the new root row of a reset env goes to a side buffer
+// in the workspace together with the scan operands of the old pose and the new root z (:227), so the tail kernel
+// computes that env's scan columns once and stores the row when the pose is no longer needed.  From 12 288 envs on
+// every CTA here raises a hand-over flag when its envs are through and the tail kernel's warps start on those envs
+// under this kernel's last wave; below that the tail kernel waits for the whole grid (lgk_chain_mode).
+// LGK_CHAIN=3 in the environment runs the three-launch chain of earlier rounds instead (lgk_scan_kernel, this kernel,
+// lgk_finish_kernel below), kept for A/B measurements.
 //
 // Work decomposition of this kernel
 //   grid    CTA c owns the contiguous env range [c*per, (c+1)*per) and walks it in sub-tiles of <= 32 envs.
@@ -32,7 +35,7 @@
 //   -- the only CTA barrier of a sub-tile --
 //   store   W0..W2 write the staged heads to the observation rows, 128 B per warp store; last_actions and
 //           last_dof_vel leave through bulk async stores;  W3 writes the term values of its 32 envs into the
-//           [term][N] table of the workspace (one coalesced 128 B store per term) for the finish kernel.
+//           [term][N] table of the workspace (one coalesced 128 B store per term) for the tail kernel.
 //
 // Code size matters (four roles live in different regions of the code at once): paths that run for ~1 % of the
 // envs, once per launch, or only for ragged / unaligned tiles are __noinline__.

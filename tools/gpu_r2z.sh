@@ -17,6 +17,9 @@ for rep in 1 2; do
   LGK_CHAIN=2w one wait 65536
   LGK_CHAIN=3 one chain3 65536
 done
+for v in ${VARIANTS:-}; do
+  for rep in 1 2; do LGK_LIB_PATH=$PWD/build/liblgk_$v.so one $v 65536; done
+done
 for e in 4096 16384; do
   one default $e
   LGK_TAIL_STAGE=0 one nostage $e
