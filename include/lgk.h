@@ -93,7 +93,7 @@ typedef enum LgkIndexMath {
 
 /* random-number source */
 typedef enum LgkRngMode {
-  LGK_RNG_PHILOX = 0,  /* in-kernel Philox4x32-10 keyed by (seed, step, env, site)         */
+  LGK_RNG_PHILOX = 0,  /* in-kernel Philox4x32-7 keyed by (seed, step, env, site)          */
   LGK_RNG_TAPS = 1     /* caller-provided uniforms, one row per env (parity mode)          */
 } LgkRngMode;
 

@@ -16,6 +16,8 @@ struct LgkWorkspace {
                                      // scan flags of the NEXT launch is launch_seq + 1.  lgk_set_step_counter keeps it
   unsigned int fin_ticket;           // CTAs of the finish kernel that are done (the last one publishes the statistics)
   unsigned int scan_timeouts;        // step CTAs that gave up waiting for a scan tile (never, unless the launch order broke)
+  unsigned int unit_next;            // tail kernel: next unit of envs to hand out (its CTAs draw units from this counter;
+                                     // zero between launches)
   int level_sum[2];                  // sum(terrain_levels) accumulators, indexed by step parity
   int reset_count[2];                // number of reset envs, indexed by step parity
   float stats[2][LGK_MAX_REWARDS + 4];   // per-parity: sum over reset ids of episode_sums[k]

@@ -372,7 +372,6 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
   const unsigned stamp = ws->launch_seq + 1u;
   const int nchunks = GENERIC ? (H + 255) / 256 : 1;
   // CTA 0 compacts the id lists instead of walking units (the first CTA, so that it is resident from the start)
-  const int scan_ctas = (int)gridDim.x - 1;
   const bool list_cta = blockIdx.x == 0;
   if (list_cta) {
     if (by_flags) pdl_wait();   // needs every step CTA's masks
@@ -383,8 +382,20 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
   const int n_units = (N + unit_envs - 1) / unit_envs;
   const int nrows = a.num_rows;
 
+  // Units are drawn from a counter in the workspace header, not dealt by CTA index: the CTAs of this grid become
+  // resident one by one as the step kernel's last wave retires, and the ones that start early must take more of the
+  // work -- with one fixed unit per CTA the kernel ended one full unit after the LAST CTA had started, whatever the
+  // early ones had done by then.  It also takes the CTAs of an SM out of step with each other: the reward pass of
+  // one (latency) meets the scan of another (arithmetic).
+  __shared__ int s_unit;
+  int unit = n_units;
+  if (!list_cta) {
+    if (threadIdx.x == 0) s_unit = (int)atomicAdd(&ws->unit_next, 1u);
+    __syncthreads();
+    unit = s_unit;
+  }
 #pragma unroll 1
-  for (int unit = list_cta ? n_units : (int)blockIdx.x - 1; unit < n_units; unit += scan_ctas) {   // (CTA-uniform)
+  while (unit < n_units) {   // (CTA-uniform)
     const int uenv0 = unit * unit_envs;
     const int une = min(unit_envs, N - uenv0);
     // this lane's scan offsets and noise factors (same for every env).  Read per unit, not once per CTA: they must not
@@ -414,12 +425,13 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       __syncwarp();
     }
     if (a.tail_staged) {
-      // the reward pass's rows of this group's 16 envs -> shared memory, 16 bytes per copy, asynchronously: they
-      // arrive under the scan below (chunk i: row i >> 2 of the sums, then of the values; quarter i & 3 of the 64 bytes)
-      for (int i = lane; i < nrows * 8; i += 32) {
-        const int row2 = i >> 2, qd = i & 3;
+      // the reward pass's rows of this group's 16 (8) envs -> shared memory, 16 bytes per copy, asynchronously: they
+      // arrive under the scan below (chunk i: row i >> 2 (1) of the sums, then of the values; 16-byte piece i & 3 (1))
+      const int qsh = epg == 16 ? 2 : epg == 8 ? 1 : 0;   // 4, 2 or 1 copies per row and group
+      for (int i = lane; i < (nrows * 2) << qsh; i += 32) {
+        const int row2 = i >> qsh, qd = i & ((1 << qsh) - 1);
         const float* src = (row2 < nrows ? b.episode_sums + (size_t)row2 * N : a.row_src[row2 - nrows]) + env0 + 4 * qd;
-        cp_async16(s_stage + row2 * TAIL_UNIT + wic * GS + 4 * qd, src);
+        cp_async16(s_stage + row2 * TAIL_UNIT + wic * epg + 4 * qd, src);
       }
     } else if (ne > 0 && lane < nrows) {   // ... or at least on their way into L2
       prefetch_l2(b.episode_sums + (size_t)lane * N + env0);
@@ -516,7 +528,10 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
         if (lane < 13) b.root_states[(size_t)e * 13 + lane] = a.side[(size_t)e * LGK_SIDE_FLOATS + 8 + lane];
       }
     }
-    __syncthreads();   // shared memory is free for the next unit
+    // (s_unit was read by everybody behind an earlier barrier of this trip)
+    if (threadIdx.x == 0) s_unit = (int)atomicAdd(&ws->unit_next, 1u);
+    __syncthreads();   // shared memory is free for the next unit, and the next unit is known
+    unit = s_unit;
   }
   // ---- statistics and counters: CTA 0, once every other CTA has checked in ---------------------------------------
   // The other CTAs leave a release-ordered increment behind and go (no fence + atomic round trip + second barrier at

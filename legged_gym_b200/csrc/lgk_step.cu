@@ -46,7 +46,9 @@
 #include "lgk_step.cuh"
 
 #ifndef LGK_MIN_CTAS
-#define LGK_MIN_CTAS 6
+#define LGK_MIN_CTAS 7   // register cap 72: 2 048 tiles are two waves of 7 x 148 slots.  (Six CTAs at 80 registers were as fast
+                         // while a scan kernel ran ahead of this one; as the first launch of the two-launch chain, with the
+                         // tail kernel moving in behind its last wave, seven are 1 us per step faster: 65.4 against 66.5 us)
 #endif
 
 #ifdef LGK_PROFILE
@@ -1261,7 +1263,9 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
     }();
     const int cap = num_sms * (args.fused ? LGK_TAIL_CTAS_PER_SM : scan_per_sm);
     // fused chain: groups of 16 as long as they keep 4/5 of the warps busy (65 536 envs: 4 096 groups, one each)
+    static const int tail_epg = [] { const char* e = getenv("LGK_TAIL_EPG"); const int v = e ? atoi(e) : 0; return v; }();
     int epg = args.fused ? SCAN_GROUP_FUSED : SCAN_GROUP;
+    if (args.fused && (tail_epg == 8 || tail_epg == 4)) epg = tail_epg;   // (A/B: smaller units for the tail kernel's counter)
     const int want = args.fused ? cap * LGK_WARPS_PER_CTA * 4 / 5 : cap * LGK_WARPS_PER_CTA;
     while (epg > 1 && (c->num_envs + epg - 1) / epg < want) epg >>= 1;
     args.scan_epc = epg;
@@ -1273,7 +1277,7 @@ extern "C" int lgk_post_physics_step_impl(const LgkConsts* c, const LgkBuffers* 
   {
     // staged reward rows: every group full (16 envs) and every row segment 16-byte aligned.  LGK_TAIL_STAGE=0: off
     static const bool stage_on = [] { const char* e = getenv("LGK_TAIL_STAGE"); return !(e && e[0] == '0'); }();
-    bool ok = stage_on && args.fused && args.scan_epc == SCAN_GROUP_FUSED && c->num_envs % SCAN_GROUP_FUSED == 0 &&
+    bool ok = stage_on && args.fused && (args.scan_epc == 16 || args.scan_epc == 8 || args.scan_epc == 4) && c->num_envs % args.scan_epc == 0 &&
               args.num_rows > 0 && al16(b->episode_sums) && al16(args.rv);
     for (int r = 0; r < args.num_rows && ok; ++r) ok = al16(args.row_src[r]);
     args.tail_staged = ok ? 1 : 0;

@@ -398,6 +398,7 @@ __device__ __forceinline__ void publish_step_statistics(const StepArgs& a, unsig
     ws->level_sum[parity ^ 1] = 0;
     ws->reset_count[parity ^ 1] = 0;
     ws->fin_ticket = 0u;
+    ws->unit_next = 0u;
     ws->step_counter = csc;
     ws->launch_seq += 1u;
   }
