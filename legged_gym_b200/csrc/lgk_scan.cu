@@ -291,35 +291,44 @@ static __device__ __noinline__ void tail_rewards_env(float* gp, unsigned n_envs,
   if (clip_due) rew = fmaxf(rew, 0.f);
   *rew_out = rew;
 }
-// The same from staged rows: the unit's episode-sum rows and term-value rows were copied into shared memory
-// ([2][nrows][TAIL_UNIT] floats) by cp.async before the scan began, so nothing here waits for global memory -- the
-// latency of the rows passed under the CTA's own scan.  st: this env's column of the stage.
-static __device__ __noinline__ void tail_rewards_env_staged(const float* __restrict__ st, float* gp, unsigned n_envs,
-                                                            int nrows, bool reset, float bh, float target, float term_v,
-                                                            bool only_positive, float* __restrict__ stat,
-                                                            const TailRow* __restrict__ rows, float* __restrict__ rew_out) {
-  float rew = 0.f;
-  bool clip_due = only_positive;
-  const float* sv = st + nrows * TAIL_UNIT;
+// The same from staged rows, by two threads per env: the unit's episode-sum rows and term-value rows were copied into
+// shared memory ([2][nrows][TAIL_UNIT] floats) by cp.async before the scan began, so nothing here waits for global
+// memory -- the latency of the rows passed under the CTA's own scan.  Thread (half, env) scales and sums the first /
+// second half of the rows and leaves the scaled values in the value slots; after a CTA barrier (every thread of the
+// CTA calls this, active or not) thread (0, env) adds them up in the reference's order.  st: this env's column.
+static __device__ __noinline__ void tail_rewards_env_staged(float* __restrict__ st, float* gp, unsigned n_envs, int nrows,
+                                                            int nrew, int half, bool act, bool reset, float bh,
+                                                            float target, float term_v, bool only_positive,
+                                                            float* __restrict__ stat, const TailRow* __restrict__ rows,
+                                                            float* __restrict__ rew_out) {
+  float* sv = st + nrows * TAIL_UNIT;
+  const int nh = (nrows + 1) >> 1;
+  if (act) {
+    const int r_end = half ? nrows : nh;
 #pragma unroll 4
-  for (int r = 0; r < nrows; ++r) {
-    const TailRow t = rows[r];
-    float val = sv[r * TAIL_UNIT];
-    if (t.kind != 0) {
-      if (t.kind == 1) { const float d = (val - bh) - target; val = d * d; }
-      else {   // the termination row: added after the positive clip (:206-212)
-        val = term_v;
-        if (clip_due) { rew = fmaxf(rew, 0.f); clip_due = false; }
+    for (int r = half ? nh : 0; r < r_end; ++r) {
+      const TailRow t = rows[r];
+      float val = sv[r * TAIL_UNIT];
+      if (t.kind != 0) {
+        if (t.kind == 1) { const float d = (val - bh) - target; val = d * d; }
+        else val = term_v;   // the termination row (:209-212)
       }
+      const float rr = mul_rn(val, t.scale);
+      const float total = add_rn(st[r * TAIL_UNIT], rr);
+      sv[r * TAIL_UNIT] = rr;
+      gp[(unsigned)r * n_envs] = reset ? 0.f : total;   // zeroed for reset envs after the statistics took it (:184-185)
+      if (reset) atomicAdd(stat + r, total);
     }
-    const float rr = mul_rn(val, t.scale);
-    const float total = add_rn(st[r * TAIL_UNIT], rr);
-    rew = add_rn(rew, rr);
-    gp[(unsigned)r * n_envs] = reset ? 0.f : total;   // zeroed for reset envs after the statistics took it (:184-185)
-    if (reset) atomicAdd(stat + r, total);
   }
-  if (clip_due) rew = fmaxf(rew, 0.f);
-  *rew_out = rew;
+  __syncthreads();
+  if (act && half == 0) {
+    float rew = 0.f;
+#pragma unroll 4
+    for (int r = 0; r < nrew; ++r) rew = add_rn(rew, sv[r * TAIL_UNIT]);
+    if (only_positive) rew = fmaxf(rew, 0.f);
+    if (nrows > nrew) rew = add_rn(rew, sv[nrew * TAIL_UNIT]);   // added after the positive clip (:206-212)
+    *rew_out = rew;
+  }
 }
 __device__ __forceinline__ void cp_async16(void* dst_smem, const void* src_gmem) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
@@ -503,22 +512,29 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
     }
     if (a.tail_staged) cp_async_wait_all();   // (this thread's copies; the barrier makes everybody's visible)
     __syncthreads();   // every group of the unit is scanned: height sums and flags are in shared memory
-    // ---- rewards of the unit: one env per thread (warps 0, 1), rows in the reference's order ----------------------
-    if ((int)threadIdx.x < une) {
+    // ---- rewards of the unit: rows in the reference's order; staged rows: two threads per env ------------------------
+    if (a.tail_staged) {   // (CTA-uniform: there is a barrier inside)
+      const int u = threadIdx.x & (TAIL_UNIT - 1), half = threadIdx.x / TAIL_UNIT;
+      const bool act = u < une;
+      const int uc = act ? u : 0, env = uenv0 + uc;
+      const unsigned fl = s_fl[uc];
+      const bool reset = fl & 1u, time_out = fl & 2u;
+      float bh = 0.f;   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height)
+      if (a.scan_first && a.bh_active) bh = ((float)s_hs[uc] * c.vertical_scale) / (float)H;
+      tail_rewards_env_staged(s_stage + uc, b.episode_sums + env, (unsigned)N, nrows, c.num_rewards, half, act, reset, bh,
+                              c.base_height_target, (reset && !time_out) ? 1.f : 0.f, (c.flags & LGK_F_ONLY_POSITIVE) != 0,
+                              a.stat_copies + (size_t)((env >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS, s_rows,
+                              b.rew_buf + env);
+    } else if ((int)threadIdx.x < une) {   // one env per thread (warps 0, 1), rows read in place
       const int u = threadIdx.x, env = uenv0 + u;
       const unsigned fl = s_fl[u];
       const bool reset = fl & 1u, time_out = fl & 2u;
-      float bh = 0.f;   // _reward_base_height (:871): mean_h(root_z - measured_height) = root_z - mean_h(height)
+      float bh = 0.f;
       if (a.scan_first && a.bh_active) bh = ((float)s_hs[u] * c.vertical_scale) / (float)H;
-      float* stat = a.stat_copies + (size_t)((env >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS;
-      const float term_v = (reset && !time_out) ? 1.f : 0.f;   // the termination row's value (:209-212)
-      const bool only_pos = (c.flags & LGK_F_ONLY_POSITIVE) != 0;
-      if (a.tail_staged)
-        tail_rewards_env_staged(s_stage + u, b.episode_sums + env, (unsigned)N, nrows, reset, bh, c.base_height_target,
-                                term_v, only_pos, stat, s_rows, b.rew_buf + env);
-      else
-        tail_rewards_env(b.episode_sums + env, (unsigned)N, nrows, env, reset, bh, c.base_height_target, term_v, only_pos,
-                         stat, s_srcs, s_rows, b.rew_buf + env);
+      tail_rewards_env(b.episode_sums + env, (unsigned)N, nrows, env, reset, bh, c.base_height_target,
+                       (reset && !time_out) ? 1.f : 0.f, (c.flags & LGK_F_ONLY_POSITIVE) != 0,
+                       a.stat_copies + (size_t)((env >> 5) & (STAT_COPIES - 1)) * LGK_MAX_REWARDS, s_srcs, s_rows,
+                       b.rew_buf + env);
     }
     if (wic >= 2) {   // the root rows the step kernel held back while poses were still being read (:414-434)
       const int u = (wic & 1) * 32 + lane;
