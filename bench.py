@@ -12,7 +12,7 @@ simulator state (legged_gym_b200/utils/synthetic.py).  Prints ONE JSON line (ran
             that live in HBM (8 x 29 MB of inputs at 65536 envs, larger than L2).
   e2e       the same step through the public API with HOST buffers: every step copies that step's
             simulator state + actions from pinned host memory and reads obs / rewards / resets back.
-  roofline  the three kernels of post_physics_step timed as one unit: algorithmic bytes per call / CUDA-event time
+  roofline  the kernels of post_physics_step (two launches; three with LGK_CHAIN=3) timed as one unit: algorithmic bytes per call / CUDA-event time
             (for --scenario go1_rough_actuator: the tensor-bound actuator MLP kernel).
   cpu_baseline  the reference's own, unmodified LeggedRobot.step() (staged into oracle/_ref by oracle/make_ref.sh,
             imported over the tensor-only simulator stand-in) timed on this box's host cores on a bounded sample of
@@ -181,7 +181,7 @@ def run_ours(args):
     # the statistics all-reduce (the path's only collective) must fire inside any timed region, however short
     # production cadence is every 24 steps; a shorter timed region gets exactly one all-reduce, half-way through it
     # (see `phase` below).  Measured at 2 GPUs, 20 steps: each all-reduce in the window costs ~45 us -- its own CTA
-    # and the three small kernels around it take SM slots from the scan kernel's all-resident grid for one step
+    # and the three small kernels around it take SM slots from the chain's grids for one step
     stats_interval = min(24, max(1, args.steps))
     stats = ShardedStats(env, interval=stats_interval) if world > 1 else None
     n_collectives = [0]
