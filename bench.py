@@ -294,7 +294,7 @@ def run_ours(args):
             traffic = None
     chain3 = os.environ.get("LGK_CHAIN", "")[:1] == "3"
     roofline = {"kernel": ("post_physics_step = lgk_scan_kernel + lgk_step_kernel + lgk_finish_kernel (LGK_CHAIN=3)" if chain3
-                           else "post_physics_step = lgk_step_kernel + lgk_scan_kernel<FUSED> (height scan, reward "
+                           else "post_physics_step = lgk_step_kernel + lgk_tail_kernel (height scan, reward "
                                 "sums, reset tail, statistics)") +
                           " (chained with programmatic dependent launch; timed as one unit)",
                 "bound": "hbm", "achieved": round(achieved, 1), "peak": peak,
