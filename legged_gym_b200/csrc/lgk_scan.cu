@@ -221,18 +221,20 @@ lgk_scan_kernel(const __grid_constant__ StepArgs a) {
 // ---------------------------------------------------------------------------------------------
 // Tail kernel: the second (and last) launch of the two-launch chain, behind the step kernel -- the height scan of
 // lgk_scan_kernel plus everything that is left of post_physics_step once the scan is known, by the CTAs that did the
-// scan.  A CTA takes units of 4 groups (<= 64 consecutive envs), warp w the unit's group w:
+// scan.  A CTA takes units of 4 groups (<= 64 consecutive envs) from a counter in the workspace header, warp w the
+// unit's group w:
 //   stage     the unit's rows of the [R,N] episode sums and of the step kernel's [term][N] value table -> shared
 //             memory by 16-byte cp.async, issued before the scan: their latency passes under the CTA's own arithmetic
 //             (every CTA of the grid does the same amount of work at the same time, so nobody else's would hide it)
 //   scan      as in lgk_scan_kernel.  Envs the step kernel reset take their operands from the side row (old pose,
 //             root z after the reset, :227): their columns are computed once, there is no fix-up pass.  The sums of the
 //             heights never leave the CTA
-//   rewards   compute_reward (:195-212) after a CTA barrier, one env per thread (warps 0, 1), rows in the reference's
-//             order from the staged copies: r = value * scale, sum += r in place (zeroed for reset envs after the
-//             statistics took it, :184-185), reward += r, only_positive clip, termination term; base_height from the
-//             scan's height sum.  Row stores are coalesced 128-byte segments.  Out-of-line functions with the row
-//             constants in shared memory (see tail_rewards_env)
+//   rewards   compute_reward (:195-212) after a CTA barrier, from the staged copies, two threads per env (first / second
+//             half of the rows): r = value * scale, sum += r in place (zeroed for reset envs after the statistics took
+//             it, :184-185); base_height from the scan's height sum; then one thread per env adds the scaled values
+//             up in the reference's order, clips (only_positive) and adds the termination term.  Row stores are
+//             coalesced 128-byte segments.  Out-of-line functions with the row constants in shared memory (see
+//             tail_rewards_env; that one -- one env per thread, rows read in place -- serves ragged env counts)
 //   resets    warps 2, 3 store the root rows the step kernel held back while poses were still being read (:414-434)
 //   lists     CTA 0 compacts the step kernel's per-tile bitmasks into the ascending id lists (:150, :342) ...
 //   counters  ... and, once every other CTA has left its release-ordered increment, publishes extras["episode"]
