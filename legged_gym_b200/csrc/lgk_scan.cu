@@ -435,9 +435,19 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       if (f0 + lane <= f1) wait_scan_flag(a, ws, a.scan_flags + f0 + lane, stamp);
       __syncwarp();
     }
+    // the pose and the step kernel's decision for env0 + lane: read next to each other (one round trip, not two), and
+    // before the staging copies are issued, so that their latency passes under that loop
+    float rx = 0.f, ry = 0.f, rz = 0.f, qz = 0.f, qw = 1.f;
+    bool rst = false, tmo = false;
+    if (lane < ne) {
+      const float* r = b.root_states + (size_t)(env0 + lane) * 13;
+      if (a.scan_first) { rx = r[0]; ry = r[1]; rz = r[2]; qz = r[5]; qw = r[6]; }
+      rst = b.reset_buf[env0 + lane] != 0;
+      tmo = b.time_out_buf[env0 + lane] != 0;
+    }
     if (a.tail_staged) {
-      // the reward pass's rows of this group's 16 (8) envs -> shared memory, 16 bytes per copy, asynchronously: they
-      // arrive under the scan below (chunk i: row i >> 2 (1) of the sums, then of the values; 16-byte piece i & 3 (1))
+      // the reward pass's rows of this group's 16 envs -> shared memory, 16 bytes per copy, asynchronously: they arrive
+      // under the scan below (chunk i: row i >> 2 of the sums, then of the values; quarter i & 3 of the 64 bytes)
       const int qsh = epg == 16 ? 2 : epg == 8 ? 1 : 0;   // 4, 2 or 1 copies per row and group
       for (int i = lane; i < (nrows * 2) << qsh; i += 32) {
         const int row2 = i >> qsh, qd = i & ((1 << qsh) - 1);
@@ -449,11 +459,6 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       prefetch_l2(a.row_src[lane] + env0);
     }
     if (lane < ne) {
-      // (the pose is read next to the flags, not behind them: one round trip at the start of the unit instead of two)
-      const float* r = b.root_states + (size_t)(env0 + lane) * 13;
-      float rx = 0.f, ry = 0.f, rz = 0.f, qz = 0.f, qw = 1.f;
-      if (a.scan_first) { rx = r[0]; ry = r[1]; rz = r[2]; qz = r[5]; qw = r[6]; }
-      const bool rst = b.reset_buf[env0 + lane] != 0, tmo = b.time_out_buf[env0 + lane] != 0;
       s_fl[wic * epg + lane] = (unsigned char)((rst ? 1 : 0) | (tmo ? 2 : 0));
       if (a.scan_first) {
         float4* d = reinterpret_cast<float4*>(s_es + lane * 8);
