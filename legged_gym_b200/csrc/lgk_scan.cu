@@ -445,7 +445,7 @@ lgk_tail_kernel(const __grid_constant__ StepArgs a) {
       rst = b.reset_buf[env0 + lane] != 0;
       tmo = b.time_out_buf[env0 + lane] != 0;
     }
-    if (a.tail_staged) {
+    if (a.tail_staged && ne > 0) {   // (a unit's last groups may lie past the last env: N % 64 != 0)
       // the reward pass's rows of this group's 16 envs -> shared memory, 16 bytes per copy, asynchronously: they arrive
       // under the scan below (chunk i: row i >> 2 of the sums, then of the values; quarter i & 3 of the 64 bytes)
       const int qsh = epg == 16 ? 2 : epg == 8 ? 1 : 0;   // 4, 2 or 1 copies per row and group
