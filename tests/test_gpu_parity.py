@@ -737,10 +737,10 @@ def _full_env(seed, n=65536):
     return env
 
 
-def test_full_size_properties_with_in_kernel_rng():
+@pytest.mark.parametrize("N", [65536, 65552])   # 65 552: a multiple of 16 but not of 64 (the tail kernel's last unit is ragged)
+def test_full_size_properties_with_in_kernel_rng(N):
     from oracle import legged_oracle as lo
-    N = 65536
-    env = _full_env(1)
+    env = _full_env(1, N)
     frames = synthetic.make_frames(env, 2, seed=21)
     p = lo.OracleParams.from_env(env, device=DEV)
     n_resets = 0
@@ -786,6 +786,9 @@ def test_full_size_properties_with_in_kernel_rng():
         assert torch.equal(env.obs_buf[:, 36:48], env.actions)                        # zero noise scale columns
         assert torch.equal(env.last_actions, env.actions) and torch.equal(env.last_dof_vel, env.dof_vel)
         assert (env.rew_buf[keep] >= 0).all()                                         # only_positive_rewards
+        # every env's sums were visited, the ragged last unit included: exp(-err / sigma) * scale * dt > 0 each step
+        assert torch.isfinite(env.rew_buf).all()
+        assert (env.episode_sums["tracking_lin_vel"][keep] > 0).all() and (env.episode_sums["torques"][keep] < 0).all()
         n_resets += nr
     assert n_resets > 1000
 
