@@ -14,7 +14,7 @@ struct LgkWorkspace {
   unsigned int done_ticket;          // CTAs finished in the current launch
   unsigned int launch_seq;           // post_physics_step launches so far (the epilogue adds 1); value of the per-tile
                                      // scan flags of the NEXT launch is launch_seq + 1.  lgk_set_step_counter keeps it
-  unsigned int fin_ticket;           // CTAs of the finish kernel that are done (the last one publishes the statistics)
+  unsigned int fin_ticket;           // CTAs of the chain's last kernel that are done (statistics are published when all are)
   unsigned int scan_timeouts;        // step CTAs that gave up waiting for a scan tile (never, unless the launch order broke)
   unsigned int unit_next;            // tail kernel: next unit of envs to hand out (its CTAs draw units from this counter;
                                      // zero between launches)

@@ -44,7 +44,7 @@ struct StepArgs {
   int scan_epc;      // envs per group of the scan kernel (1, 2, 4 or 8)
   float one;         // 1.0f the compiler cannot see: blocks ptxas' contraction of mul.rn.f32x2 + add.rn.f32x2
   unsigned expo23;   // 0x4b000000 (the float 2^23) the compiler cannot see: PRMT's register operand (field_as_float_bits)
-  int* hsum;         // [N] sum over the scan points of the raw int16 heights (workspace), scan -> finish kernel
+  int* hsum;         // [N] sum over the scan points of the raw int16 heights (workspace), scan -> finish kernel (three-launch chain only)
   unsigned* scan_flags;   // [ceil(N / scan_epc)] (workspace): launch_seq + 1 once the scan group's columns and sums are out
   int scan_tiles;    // scan groups of this launch = ceil(N / scan_epc); the scan grid's warps walk them persistently
   int scan_grid;     // CTAs of the scan kernel: all resident at once
@@ -57,12 +57,12 @@ struct StepArgs {
   int bh_row;
   int tail_staged;   // the tail kernel copies a unit's reward rows into shared memory (cp.async) before its scan:
                      // full groups of 16 envs, every row 16-byte aligned
-  float* rv;         // [LGK_REW_COUNT][rv_pitch] (workspace): value of every reward term by env, step -> finish kernel
+  float* rv;         // [LGK_REW_COUNT][rv_pitch] (workspace): value of every reward term by env, step kernel -> tail kernel
   int rv_pitch;      // floats per row of rv (N rounded up to 32)
   float* stat_copies;   // [64][LGK_MAX_REWARDS] (workspace): replicated accumulators of the reset envs' episode sums
   int* fix_list;     // [N] (workspace): the envs reset this step, in any order (reset_count of the step parity entries)
   float* side;       // [N][LGK_SIDE_FLOATS] (workspace): rows of the envs reset this step -- 8 scan operands with the new
-                     // root z, the 13 floats of the new root state -- step -> finish kernel
+                     // root z, the 13 floats of the new root state -- step kernel -> tail kernel
   unsigned pk[20];   // Philox4x32-10 round keys of c.seed
   // bulk-load table: lane i of W0 copies input array i of a sub-tile (source base, offset into shared
   // memory in floats, bytes per env); src == nullptr: nothing to copy
@@ -83,7 +83,7 @@ __host__ __device__ inline size_t lgk_ws_hsum_offset(int num_envs) {
 __host__ __device__ inline size_t lgk_ws_flags_offset(int num_envs) {
   return (lgk_ws_hsum_offset(num_envs) + 4u * (size_t)num_envs + 15u) & ~(size_t)15u;
 }
-// ... the [term][N] table of reward-term values and the side rows of reset envs (step kernel -> finish kernel)
+// ... the [term][N] table of reward-term values and the side rows of reset envs (step kernel -> tail kernel)
 #define LGK_SIDE_FLOATS 24
 __host__ __device__ inline int lgk_ws_rv_pitch(int num_envs) { return (num_envs + 31) & ~31; }
 __host__ __device__ inline size_t lgk_ws_rv_offset(int num_envs) {
@@ -92,7 +92,7 @@ __host__ __device__ inline size_t lgk_ws_rv_offset(int num_envs) {
 __host__ __device__ inline size_t lgk_ws_side_offset(int num_envs) {
   return lgk_ws_rv_offset(num_envs) + 4u * (size_t)LGK_REW_COUNT * (size_t)lgk_ws_rv_pitch(num_envs);
 }
-// ... and the list of the envs reset this step (any order), filled by the step kernel for the finish kernel
+// ... and the list of the envs reset this step (any order), filled by the step kernel for the finish kernel (three-launch chain only)
 __host__ __device__ inline size_t lgk_ws_fix_offset(int num_envs) {
   return lgk_ws_side_offset(num_envs) + 4u * (size_t)LGK_SIDE_FLOATS * (size_t)num_envs;
 }
@@ -269,15 +269,16 @@ __device__ __forceinline__ int scan_passes(const StepArgs& a, const ScanEnv& e, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// The two once-per-step serial jobs of post_physics_step.  Both run inside the finish kernel (below), each on one CTA:
+// The two once-per-step serial jobs of post_physics_step.  Both run on one CTA of the chain's last kernel (CTA 0 of the
+// tail kernel does both; in the three-launch chain CTA 0 of the finish kernel does the first, its last CTA to finish the second):
 //   1. ordered compaction of the per-tile reset / resample bitmasks into ascending id lists (:150, :342) -- needs
-//      the step kernel's masks only, so a dedicated CTA of the finish grid does it next to the reward CTAs
-//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119) -- needs every reward CTA's
-//      sums, so the CTA that finishes last does it (ticket counter in the workspace header)
+//      the step kernel's masks only, so a dedicated CTA does it next to the CTAs that scan / sum
+//   2. episode statistics behind extras["episode"] (:182-190), step counter += 1 (:119) -- needs every CTA's sums
+//      of the reset envs, so it waits for all of them (check-in counter in the workspace header)
 // (earlier versions: a finisher CTA inside the fused tile kernel, 16-20 us on one busy SM; then an epilogue launch of
 // its own, 7-11 us at the end of the chain with the GPU otherwise idle)
 #define FIN_THREADS 128
-#define STAT_COPIES 64   // replicated accumulator rows of the reset statistics (see lgk_finish_kernel)
+#define STAT_COPIES 64   // replicated accumulator rows of the reset statistics (see lgk_tail_kernel / lgk_finish_kernel)
 template <int THREADS>
 __device__ __forceinline__ void compact_id_lists(const StepArgs& a, int n_ctas) {
   constexpr int NW = THREADS / 32;
@@ -346,7 +347,7 @@ __device__ __forceinline__ void compact_id_lists(const StepArgs& a, int n_ctas) 
   }
 }
 
-// episode statistics of the step (the last CTA of the finish kernel to get done, all of its threads) and the
+// episode statistics of the step (one CTA of the chain's last kernel, all of its threads, once every other CTA is done) and the
 // counters of the next step
 __device__ __forceinline__ void publish_step_statistics(const StepArgs& a, unsigned long long csc) {
   const LgkConsts& c = a.c;
@@ -358,7 +359,7 @@ __device__ __forceinline__ void publish_step_statistics(const StepArgs& a, unsig
   LgkWorkspace* ws = reinterpret_cast<LgkWorkspace*>(b.workspace);
   const int parity = (int)(csc & 1ull);
   const int num_rows = a.num_rows;
-  // the reset envs' episode sums were added into STAT_COPIES replicated rows (spread by env, see the finish kernel):
+  // the reset envs' episode sums were added into STAT_COPIES replicated rows (spread by env, see the tail / finish kernel):
   // thread (row = lane, quarter = warp) adds a quarter of the copies -- independent L2 loads, all in flight -- and
   // zeroes them for the next step
   {
@@ -418,7 +419,7 @@ __device__ __forceinline__ void wait_scan_flag(const StepArgs& a, LgkWorkspace* 
 // launches lgk_scan_kernel for args.c.num_envs envs (lgk_scan.cu)
 int lgk_scan_launch(const StepArgs& args, cudaStream_t stream);
 
-// The scan columns of one env by one warp: the finish kernel's fix-up for the envs reset this step (their
+// The scan columns of one env by one warp (three-launch chain only): the finish kernel's fix-up for the envs reset this step (their
 // observation uses the new root z, :227; everything else -- indices, heights, noise -- is what the scan kernel
 // computed).  sc: the env's 8 operands (k_t, k_c, r2, yw, zo).  NP = ceil(H / 32) for the specialised widths (every
 // gather of the env in flight together, like the scan kernel), 0 = any H, pass by pass.
